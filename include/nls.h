@@ -1,0 +1,190 @@
+/*
+ * nls.h -- C ABI of the B200-native time-stepping engine (libnls_b200.so).
+ *
+ * This is the drop-in boundary "B3" of SURVEY.md section 8(b): the only layer
+ * that touches CUDA.  Everything above it (the C++ solver classes with the
+ * reference's names in include/nls/, the *_driver CLIs, bench.py, the tests)
+ * talks to the GPU exclusively through these entry points.  Plain C, opaque
+ * handle, int status (0 = ok, <0 = error; text via nls_last_error()), caller
+ * owned host buffers, no exceptions across the boundary, no CPU fallback:
+ * every entry point fails with NLS_ERR_CUDA when no sm_100 device is present.
+ *
+ * Reference interfaces replaced (paths relative to the reference checkout):
+ *   nls_create/nls_destroy   device/nlse_solver_dev.hpp:53-92 (ctor/dtor of
+ *                            NLSESolverDevice), device/sg_solver_dev.hpp:92-150,
+ *                            nlsolvers/device/include/nlse_dev.hpp:78-176
+ *   nls_set_field            H2D copies in those ctors (nlse_solver_dev.hpp:64)
+ *   nls_step                 NLSESolverDevice::step nlse_solver_dev.hpp:94-111,
+ *                            SGESolverDevice::step sg_single_dev.hpp:81-90,
+ *                            host steps nlsolvers/host/include/nlse_cubic_solver.hpp:55-74,
+ *                            sg_single_solver.hpp:43-59, sg_single_sv_solver.hpp:9-19
+ *                            + neumann_bc_no_velocity boundaries.hpp:40-57
+ *   nls_get_field            transfer_snapshots nlse_solver_dev.hpp:113-118
+ *   nls_matfunc              MatrixFunctionApplicator{Real,Complex}::apply
+ *                            device/matfunc_complex.hpp:155-177, matfunc_real.hpp:171-234;
+ *                            host expm_multiply eigen_krylov_complex.hpp:54-83 etc.
+ *   nls_lanczos              lanczos_iteration(_complex) device/lanczos.hpp:126-194,
+ *                            device/lanczos_complex.hpp:318-551
+ *   nls_stencil_apply        DeviceSpMV<T>::multiply device/spmv.hpp:65-72
+ *   nls_reduce               calculate_energy_kernel_2d device/sg_solver_dev.hpp:51-80,
+ *                            mass: finalized_scripts/compare_utils_complex_2d.py:142-143
+ */
+#ifndef NLS_H
+#define NLS_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct nls_engine *nls_handle;
+
+/* status codes */
+enum {
+  NLS_OK = 0,
+  NLS_ERR_ARG = -1,      /* bad descriptor / argument */
+  NLS_ERR_CUDA = -2,     /* CUDA runtime error (incl. "no device") */
+  NLS_ERR_STATE = -3,    /* call not valid for this handle's equation/integrator */
+  NLS_ERR_NONFINITE = -4 /* reserved */
+};
+
+/* equation = pointwise nonlinearity */
+enum {
+  NLS_EQ_NLSE_CUBIC = 0, /* g = m |u|^2                      nlse_cubic_solver.hpp:55-74 */
+  NLS_EQ_NLSE_CQ = 1,    /* g = m (s1|u|^2 + s2|u|^4)        nlse_cubic_quintic_solver.hpp:10-29 */
+  NLS_EQ_NLSE_SAT = 2,   /* g = m |u|^2/(1+kappa u) (sic)    nlse_saturating_solver.hpp:11-33 */
+  NLS_EQ_SGE = 3,        /* f = sin u, filter mod-cosine     sg_single_solver.hpp:43-59 */
+  NLS_EQ_KGE = 4,        /* f = u^3, filter id_sqrt          kg_solver.hpp:13-22 */
+  NLS_EQ_PHI4 = 5,       /* f = u - u^3                      phi4_solver.hpp:13-23 */
+  NLS_EQ_SGE_DOUBLE = 6, /* f = sin u + 0.6 sin 2u           sg_double_solver.hpp:13-23 */
+  NLS_EQ_SGE_SINH = 7    /* f = sinh u                       sg_hyperbolic_solver.hpp:13-23 */
+};
+
+/* integrator */
+enum {
+  NLS_INT_SS2 = 0,      /* Strang splitting, NLSE only */
+  NLS_INT_GAUTSCHI = 1, /* Gautschi-type, real equations only */
+  NLS_INT_SV = 2        /* Stoermer-Verlet, real equations only */
+};
+
+/* Laplacian flavour */
+enum {
+  NLS_LAP_UNIFORM = 0, /* build_laplacian_noflux[_3d]              laplacians.hpp:9-52, :105-156 */
+  NLS_LAP_ANISO = 1    /* build_anisotropic_laplacian_noflux[_3d]  laplacians.hpp:54-103, :158-218 */
+};
+
+/* re-orthogonalisation mode of the Lanczos process */
+enum {
+  NLS_REORTH_FULL = 0, /* alpha step + one block-dot + one block-update pass (reference: MGS sweep) */
+  NLS_REORTH_NONE = 1  /* plain 3-term recurrence (not the reference algorithm; opt-in) */
+};
+
+/* matrix functions f(T) applied through the Krylov basis */
+enum {
+  NLS_FN_EXP = 0,         /* exp(t*lambda), t complex          eigen_krylov_complex.hpp:54-83 */
+  NLS_FN_SINC = 1,        /* sinc(t*lambda)                    eigen_krylov_complex.hpp:85-103 */
+  NLS_FN_COS_SQRT = 2,    /* cos(t sqrt|lambda|)               eigen_krylov_real.hpp:57-87 */
+  NLS_FN_SINC2_SQRT = 3,  /* sinc^2(t sqrt|lambda|)            eigen_krylov_real.hpp:89-123 */
+  NLS_FN_ID_SQRT = 4,     /* t sqrt|lambda|                    eigen_krylov_real.hpp:125-152 */
+  NLS_FN_SINC2_HALF = 5,  /* sinc^2(t/2 sqrt|lambda|)          eigen_krylov_real.hpp:154-183 */
+  NLS_FN_MOD_COSINE = 6   /* [cos^2(th/2) sin(th)/th]^2        eigen_krylov_real.hpp:185-209 */
+};
+
+/* fields addressable through nls_set_field / nls_get_field */
+enum {
+  NLS_FIELD_U = 0,      /* state u (complex128 for NLSE, float64 otherwise) */
+  NLS_FIELD_U_PAST = 1, /* previous state (real equations) */
+  NLS_FIELD_V = 2,      /* get: (u-u_past)/dt  sg_single_driver.cpp:113; set: u_past = u - dt*v (:70) */
+  NLS_FIELD_M = 3,      /* m(x): float64, n values, shared by the whole batch */
+  NLS_FIELD_C = 4       /* c(x): float64, n values (NLS_LAP_ANISO only) */
+};
+
+/* reductions */
+enum {
+  NLS_RED_MASS = 0,     /* sum |u|^2 * dx*dy[*dz] (per trajectory) */
+  NLS_RED_NONFINITE = 1 /* number of non-finite entries of u */
+};
+
+typedef struct nls_desc {
+  uint32_t struct_size; /* = sizeof(nls_desc) */
+  uint32_t nx, ny, nz;  /* nz == 1 => 2D. Layout: idx = (k*ny + j)*nx + i */
+  double dx, dy, dz;    /* scale: 1/(dx*dy) in 2D, 1/(dx*dx) in 3D (laplacians.hpp:49,:153) */
+  int32_t equation;
+  int32_t integrator;
+  int32_t laplacian;
+  int32_t reorth;
+  uint32_t krylov_m;    /* 2..64 */
+  uint32_t batch;       /* number of independent trajectories in this handle (>=1) */
+  double s1, s2, kappa; /* cubic-quintic / saturable parameters */
+  double op_sign;       /* +1: operator is L, -1: operator is -L (kg_driver.cpp:93). 0 => +1 */
+  double dt;            /* time step of the real integrators (used by V get/set) */
+  int32_t device;       /* CUDA device ordinal */
+  /* z-slab decomposition (3D only): this handle owns planes [z0, z0+nz) of a
+   * global grid with nz_global planes; 0 => not decomposed (nz_global = nz). */
+  uint32_t nz_global;
+  uint32_t z0;
+  uint32_t flags;       /* NLS_FLAG_* */
+} nls_desc;
+
+enum {
+  NLS_FLAG_NO_GRAPH = 1u /* launch kernels directly instead of replaying a CUDA graph */
+};
+
+const char *nls_last_error(void);
+int nls_version(void);
+/* number of CUDA devices visible, or a negative status */
+int nls_device_count(void);
+
+int nls_create(const nls_desc *desc, nls_handle *out);
+int nls_destroy(nls_handle h);
+
+/* host -> device. bytes must equal the field's size (batch*n*scalar for U/U_PAST/V, n*8 for M/C). */
+int nls_set_field(nls_handle h, int field, const void *host_src, size_t bytes);
+/* device -> host (synchronous on the handle's stream). */
+int nls_get_field(nls_handle h, int field, void *host_dst, size_t bytes);
+/* same, but source/destination are device pointers on the handle's device */
+int nls_set_field_dev(nls_handle h, int field, const void *dev_src, size_t bytes);
+int nls_get_field_dev(nls_handle h, int field, void *dev_dst, size_t bytes);
+
+/* advance nsteps time steps (each followed by the no-flux boundary copy).
+ * Asynchronous on the handle's stream; nls_sync waits. */
+int nls_step(nls_handle h, double dt, uint32_t nsteps);
+int nls_sync(nls_handle h);
+
+/* y = op_sign * L x for the handle's stencil; x,y host arrays of batch*n scalars */
+int nls_stencil_apply(nls_handle h, const void *host_x, void *host_y);
+/* out = f(t L) in  (Krylov approximation with the handle's m); host arrays */
+int nls_matfunc(nls_handle h, int fn, double t_re, double t_im, const void *host_in,
+                void *host_out);
+/* run the Lanczos process on host_in; returns V (m columns of n scalars, column
+ * after column), alpha[m] (diag of T; scalar type), beta[m] (beta[0]=||in||,
+ * beta[j+1]=T(j+1,j)); trajectory 0 of the batch only. Any output may be NULL. */
+int nls_lanczos(nls_handle h, const void *host_in, void *host_V, void *host_alpha,
+                double *host_beta);
+/* out[batch] */
+int nls_reduce(nls_handle h, int what, double *out);
+
+/* number of kernel launches issued (directly or through graph replays) since creation */
+uint64_t nls_launch_count(nls_handle h);
+/* the CUDA stream (cudaStream_t) the handle launches on */
+void *nls_stream(nls_handle h);
+/* time a run of nsteps steps with CUDA events on the handle's stream; ms returned */
+int nls_step_timed(nls_handle h, double dt, uint32_t nsteps, float *ms);
+
+/* ---- z-slab decomposition across GPUs (one handle per GPU) ---- */
+/* opaque IPC descriptor of this handle's halo mailbox (64-byte cudaIpcMemHandle_t + sizes) */
+int nls_slab_export(nls_handle h, void *buf128);
+/* connect to the lower (z0-1) and upper (z0+nz) neighbours; either may be NULL */
+int nls_slab_connect(nls_handle h, const void *lower128, const void *upper128);
+/* install the scalar all-reduce callback used at every Lanczos reduction point:
+ * it must sum `count` doubles in place across all slabs (called from the host
+ * thread that calls nls_step, with the stream synchronised). */
+typedef void (*nls_allreduce_fn)(double *vals, int count, void *user);
+int nls_slab_set_allreduce(nls_handle h, nls_allreduce_fn fn, void *user);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NLS_H */

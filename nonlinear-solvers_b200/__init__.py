@@ -1,0 +1,9 @@
+"""nls_b200 -- B200-native time-stepping engine for NLSE / sine-Gordon / Klein-Gordon.
+
+Python is only the thin host-side mirror used by tests and bench.py; the product is the
+C-ABI library ``libnls_b200.so`` (include/nls.h) and the C++ classes/drivers above it.
+"""
+from .binding import (  # noqa: F401
+    Desc, Engine, NlsError, load_library, library_path, build_library,
+    EQ, INT, LAP, FN, FIELD, RED, REORTH, FLAG_NO_GRAPH,
+)

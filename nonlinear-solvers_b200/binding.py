@@ -1,0 +1,231 @@
+"""ctypes mirror of include/nls.h (the C ABI of libnls_b200.so).
+
+No torch types cross this boundary: host numpy arrays or raw device pointers only.
+There is NO CPU fallback: if the CUDA library is missing, or no GPU is visible,
+every compute call raises NlsError.
+"""
+import ctypes as C
+import os
+import subprocess
+import sys
+from types import SimpleNamespace
+
+import numpy as np
+
+_PKG = os.path.dirname(os.path.abspath(__file__))
+_ROOT = os.path.dirname(_PKG)
+_CSRC = os.path.join(_PKG, "csrc")
+_LIB = os.path.join(_PKG, "libnls_b200.so")
+
+EQ = SimpleNamespace(NLSE_CUBIC=0, NLSE_CQ=1, NLSE_SAT=2, SGE=3, KGE=4, PHI4=5, SGE_DOUBLE=6, SGE_SINH=7)
+INT = SimpleNamespace(SS2=0, GAUTSCHI=1, SV=2)
+LAP = SimpleNamespace(UNIFORM=0, ANISO=1)
+REORTH = SimpleNamespace(FULL=0, NONE=1)
+FN = SimpleNamespace(EXP=0, SINC=1, COS_SQRT=2, SINC2_SQRT=3, ID_SQRT=4, SINC2_HALF=5, MOD_COSINE=6)
+FIELD = SimpleNamespace(U=0, U_PAST=1, V=2, M=3, C=4)
+RED = SimpleNamespace(MASS=0, NONFINITE=1)
+FLAG_NO_GRAPH = 1
+
+
+class NlsError(RuntimeError):
+    pass
+
+
+class Desc(C.Structure):
+    """struct nls_desc (include/nls.h)."""
+    _fields_ = [
+        ("struct_size", C.c_uint32), ("nx", C.c_uint32), ("ny", C.c_uint32), ("nz", C.c_uint32),
+        ("dx", C.c_double), ("dy", C.c_double), ("dz", C.c_double),
+        ("equation", C.c_int32), ("integrator", C.c_int32), ("laplacian", C.c_int32),
+        ("reorth", C.c_int32), ("krylov_m", C.c_uint32), ("batch", C.c_uint32),
+        ("s1", C.c_double), ("s2", C.c_double), ("kappa", C.c_double),
+        ("op_sign", C.c_double), ("dt", C.c_double), ("device", C.c_int32),
+        ("nz_global", C.c_uint32), ("z0", C.c_uint32), ("flags", C.c_uint32),
+    ]
+
+    @classmethod
+    def make(cls, nx, ny, nz=1, L=None, dx=None, equation=0, integrator=0, laplacian=0, reorth=0,
+             krylov_m=10, batch=1, s1=0.0, s2=0.0, kappa=0.0, op_sign=1.0, dt=0.0, device=0,
+             nz_global=0, z0=0, flags=0):
+        """dx follows the drivers: dx = 2*Lx/(nx-1) (nlse_cubic_driver.cpp:46)."""
+        d = cls()
+        d.struct_size = C.sizeof(cls)
+        d.nx, d.ny, d.nz = nx, ny, nz
+        if dx is None:
+            dx = 2.0 * L / (nx - 1)
+        d.dx = d.dy = d.dz = dx
+        d.equation, d.integrator, d.laplacian, d.reorth = equation, integrator, laplacian, reorth
+        d.krylov_m, d.batch = krylov_m, batch
+        d.s1, d.s2, d.kappa, d.op_sign, d.dt, d.device = s1, s2, kappa, op_sign, dt, device
+        d.nz_global, d.z0, d.flags = nz_global, z0, flags
+        return d
+
+    @property
+    def n(self):
+        return self.nx * self.ny * self.nz
+
+    @property
+    def is_complex(self):
+        return self.equation <= EQ.NLSE_SAT
+
+    @property
+    def dtype(self):
+        return np.complex128 if self.is_complex else np.float64
+
+
+NVCC_FLAGS = ["-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
+              "-Xcompiler", "-fPIC", "-shared", "--expt-relaxed-constexpr"]
+
+
+def library_path():
+    return _LIB
+
+
+def build_library(force=False, verbose=False):
+    """Compile csrc/*.cu for sm_100a in-tree (nvcc cross-compiles without a GPU)."""
+    srcs = sorted(os.path.join(_CSRC, f) for f in os.listdir(_CSRC) if f.endswith(".cu"))
+    deps = srcs + [os.path.join(_CSRC, f) for f in os.listdir(_CSRC) if f.endswith((".cuh", ".h"))]
+    deps.append(os.path.join(_ROOT, "include", "nls.h"))
+    if not force and os.path.exists(_LIB) and all(os.path.getmtime(_LIB) >= os.path.getmtime(s) for s in deps):
+        return _LIB
+    nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+    cmd = [nvcc] + NVCC_FLAGS + ["-I", os.path.join(_ROOT, "include"), "-o", _LIB] + srcs + ["-lcudart"]
+    if verbose:
+        cmd.insert(1, "-Xptxas=-v")
+        print(" ".join(cmd), file=sys.stderr)
+    subprocess.run(cmd, check=True)
+    return _LIB
+
+
+_lib = None
+_vp, _sz, _dp = C.c_void_p, C.c_size_t, C.POINTER(C.c_double)
+_SIGS = {
+    "nls_last_error": (C.c_char_p, []),
+    "nls_version": (C.c_int, []),
+    "nls_device_count": (C.c_int, []),
+    "nls_create": (C.c_int, [C.POINTER(Desc), C.POINTER(_vp)]),
+    "nls_destroy": (C.c_int, [_vp]),
+    "nls_set_field": (C.c_int, [_vp, C.c_int, _vp, _sz]),
+    "nls_get_field": (C.c_int, [_vp, C.c_int, _vp, _sz]),
+    "nls_set_field_dev": (C.c_int, [_vp, C.c_int, _vp, _sz]),
+    "nls_get_field_dev": (C.c_int, [_vp, C.c_int, _vp, _sz]),
+    "nls_step": (C.c_int, [_vp, C.c_double, C.c_uint32]),
+    "nls_sync": (C.c_int, [_vp]),
+    "nls_stencil_apply": (C.c_int, [_vp, _vp, _vp]),
+    "nls_matfunc": (C.c_int, [_vp, C.c_int, C.c_double, C.c_double, _vp, _vp]),
+    "nls_lanczos": (C.c_int, [_vp, _vp, _vp, _vp, _dp]),
+    "nls_reduce": (C.c_int, [_vp, C.c_int, _dp]),
+    "nls_launch_count": (C.c_uint64, [_vp]),
+    "nls_stream": (_vp, [_vp]),
+    "nls_step_timed": (C.c_int, [_vp, C.c_double, C.c_uint32, C.POINTER(C.c_float)]),
+    "nls_slab_export": (C.c_int, [_vp, _vp]),
+    "nls_slab_connect": (C.c_int, [_vp, _vp, _vp]),
+    "nls_slab_set_allreduce": (C.c_int, [_vp, _vp, _vp]),
+}
+EXPORTS = tuple(_SIGS)
+
+
+def load_library(path=None):
+    """dlopen libnls_b200.so and declare every entry point of include/nls.h."""
+    global _lib
+    if _lib is not None and path is None:
+        return _lib
+    p = path or _LIB
+    if not os.path.exists(p):
+        raise NlsError(f"{p} not built: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                       "(there is no CPU fallback)")
+    lib = C.CDLL(p)
+    for name, (res, args) in _SIGS.items():
+        fn = getattr(lib, name)  # AttributeError if the symbol is missing
+        fn.restype, fn.argtypes = res, args
+    if path is None:
+        _lib = lib
+    return lib
+
+
+def _ptr(a):
+    return a.ctypes.data_as(_vp)
+
+
+class Engine:
+    """Host-side handle: mirrors the reference solver classes' life cycle
+    (ctor uploads state, step(), transfer back; device/nlse_solver_dev.hpp:53-118)."""
+
+    def __init__(self, desc, lib=None):
+        self.lib = lib or load_library()
+        self.desc = desc
+        self.h = _vp()
+        self._check(self.lib.nls_create(C.byref(desc), C.byref(self.h)))
+
+    def _check(self, rc):
+        if rc != 0:
+            raise NlsError(f"nls error {rc}: {self.lib.nls_last_error().decode()}")
+
+    def close(self):
+        if self.h:
+            self.lib.nls_destroy(self.h)
+            self.h = _vp()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _state_shape(self):
+        d = self.desc
+        return (d.batch, d.nz, d.ny, d.nx) if d.nz > 1 else (d.batch, d.ny, d.nx)
+
+    def set(self, field, arr):
+        dt = self.desc.dtype if field in (FIELD.U, FIELD.U_PAST, FIELD.V) else np.float64
+        a = np.ascontiguousarray(arr, dtype=dt)
+        self._check(self.lib.nls_set_field(self.h, field, _ptr(a), a.nbytes))
+
+    def get(self, field=FIELD.U):
+        out = np.empty(self._state_shape(), dtype=self.desc.dtype)
+        self._check(self.lib.nls_get_field(self.h, field, _ptr(out), out.nbytes))
+        return out
+
+    def step(self, dt, nsteps=1, sync=True):
+        self._check(self.lib.nls_step(self.h, dt, nsteps))
+        if sync:
+            self._check(self.lib.nls_sync(self.h))
+
+    def step_timed(self, dt, nsteps):
+        ms = C.c_float()
+        self._check(self.lib.nls_step_timed(self.h, dt, nsteps, C.byref(ms)))
+        return ms.value
+
+    def sync(self):
+        self._check(self.lib.nls_sync(self.h))
+
+    def stencil_apply(self, x):
+        x = np.ascontiguousarray(x, dtype=self.desc.dtype)
+        y = np.empty_like(x)
+        self._check(self.lib.nls_stencil_apply(self.h, _ptr(x), _ptr(y)))
+        return y
+
+    def matfunc(self, fn, t, x):
+        x = np.ascontiguousarray(x, dtype=self.desc.dtype)
+        y = np.empty_like(x)
+        t = complex(t)
+        self._check(self.lib.nls_matfunc(self.h, fn, t.real, t.imag, _ptr(x), _ptr(y)))
+        return y
+
+    def lanczos(self, x):
+        d = self.desc
+        x = np.ascontiguousarray(x, dtype=d.dtype)
+        V = np.empty((d.krylov_m, d.n), dtype=d.dtype)
+        alpha = np.empty(d.krylov_m, dtype=d.dtype)
+        beta = np.empty(d.krylov_m, dtype=np.float64)
+        self._check(self.lib.nls_lanczos(self.h, _ptr(x), _ptr(V), _ptr(alpha),
+                                         beta.ctypes.data_as(_dp)))
+        return V, alpha, beta
+
+    def reduce(self, what):
+        out = np.empty(self.desc.batch, dtype=np.float64)
+        self._check(self.lib.nls_reduce(self.h, what, out.ctypes.data_as(_dp)))
+        return out
+
+    def launch_count(self):
+        return int(self.lib.nls_launch_count(self.h))
