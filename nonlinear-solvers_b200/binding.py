@@ -186,6 +186,12 @@ class Engine:
         self._check(self.lib.nls_get_field(self.h, field, _ptr(out), out.nbytes))
         return out
 
+    def get_into(self, field, out):
+        """device -> caller-provided host array (e.g. pinned memory)."""
+        assert out.flags.c_contiguous and out.dtype == self.desc.dtype
+        self._check(self.lib.nls_get_field(self.h, field, _ptr(out), out.nbytes))
+        return out
+
     def step(self, dt, nsteps=1, sync=True):
         self._check(self.lib.nls_step(self.h, dt, nsteps))
         if sync:

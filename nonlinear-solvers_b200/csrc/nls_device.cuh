@@ -1,0 +1,204 @@
+// nls_device.cuh -- device-side building blocks: scalar traits, grid geometry, the
+// matrix-free no-flux stencil (K1) and the deterministic grid-wide reduction.
+//
+// The stencil reproduces, row for row, the sparse matrices the reference assembles in
+// nlsolvers/common/include/laplacians.hpp:9-218 (uniform and anisotropic, 2D and 3D),
+// including its quirks: it is written on the FLAT index,
+// exactly like the reference's triplet loops, so the corner rows (-3 diagonal with two
+// neighbours) and the 3D "y-neighbour without plane check" coupling fall out of the same
+// conditions (idx+nx < N, (idx+1) % nx != 0, ...) instead of being special-cased.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace nls {
+
+constexpr int kThreads = 256;
+constexpr int kMaxM = 64;
+constexpr int kMaxBlocksPerTraj = 148 * 4; // persistent-style grid: 4 CTAs of 256 thr per SM
+
+// ---------------------------------------------------------------- scalar traits
+template <class S> struct Sc;
+template <> struct Sc<double> {
+  static constexpr int W = 1; // doubles per scalar
+  __device__ static double zero() { return 0.0; }
+  __device__ static double mulr(double a, double r) { return a * r; }
+  __device__ static double add(double a, double b) { return a + b; }
+  __device__ static double sub(double a, double b) { return a - b; }
+  __device__ static double mul(double a, double b) { return a * b; }
+  __device__ static double fma_r(double r, double a, double acc) { return fma(r, a, acc); } // acc + r*a
+  __device__ static double abs2(double a) { return a * a; }
+  // acc[0..W) += conj(a) * b
+  __device__ static void dot_acc(double *acc, double a, double b) { acc[0] = fma(a, b, acc[0]); }
+  __device__ static double from(const double *p) { return p[0]; }
+};
+template <> struct Sc<double2> {
+  static constexpr int W = 2;
+  __device__ static double2 zero() { return make_double2(0.0, 0.0); }
+  __device__ static double2 mulr(double2 a, double r) { return make_double2(a.x * r, a.y * r); }
+  __device__ static double2 add(double2 a, double2 b) { return make_double2(a.x + b.x, a.y + b.y); }
+  __device__ static double2 sub(double2 a, double2 b) { return make_double2(a.x - b.x, a.y - b.y); }
+  __device__ static double2 mul(double2 a, double2 b) {
+    return make_double2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x);
+  }
+  __device__ static double2 fma_r(double r, double2 a, double2 acc) {
+    return make_double2(fma(r, a.x, acc.x), fma(r, a.y, acc.y));
+  }
+  __device__ static double abs2(double2 a) { return a.x * a.x + a.y * a.y; }
+  __device__ static void dot_acc(double *acc, double2 a, double2 b) {
+    acc[0] = fma(a.x, b.x, fma(a.y, b.y, acc[0]));
+    acc[1] = fma(a.x, b.y, fma(-a.y, b.x, acc[1]));
+  }
+  __device__ static double2 from(const double *p) { return make_double2(p[0], p[1]); }
+};
+
+// ---------------------------------------------------------------- geometry
+struct Geom {
+  long long n;     // sites owned by this handle (per trajectory)
+  long long nglob; // sites of the global grid (== n unless z-slab decomposed)
+  long long goff;  // global flat index of local site 0 (z0 * nx * ny)
+  long long plane; // nx*ny (0 in 2D)
+  int nx, ny, nz_loc, nz_glob;
+  int z0;
+  int dim3;      // 0: 2D, 1: 3D
+  long long halo; // ghost elements in front of (and behind) every trajectory's array
+  long long stride; // elements between consecutive trajectories (= n + 2*halo)
+  double sc;     // op_sign / (dx*dy)   [2D]   or   op_sign / (dx*dx)   [3D]
+};
+
+// y = (L x)(idx) for one site.  x points at local site 0 (ghost planes, if any, sit at
+// negative indices / beyond n).  cf (ANISO only) is laid out like x.
+template <class S, bool ANISO>
+__device__ __forceinline__ S stencil_site(const Geom &g, const S *__restrict__ x,
+                                          const double *__restrict__ cf, long long idx, double pre) {
+  using T = Sc<S>;
+  const long long gi = idx + g.goff;
+  const unsigned ugi = (unsigned)gi;
+  const unsigned i = ugi % (unsigned)g.nx;
+  const bool has_xm = i != 0;                      // (gi) % nx != 0       laplacians.hpp:33
+  const bool has_xp = i != (unsigned)(g.nx - 1);   // (gi+1) % nx != 0
+  const bool has_ym = gi >= g.nx;                  // loop i < N-nx, no plane check (:39, :140)
+  const bool has_yp = gi + g.nx < g.nglob;
+  const bool has_zm = g.dim3 && gi >= g.plane;     // :145
+  const bool has_zp = g.dim3 && gi + g.plane < g.nglob;
+  const S xc = T::mulr(x[idx], pre);
+  S acc = T::zero();
+  if (!ANISO) {
+    double dg;
+    if (!g.dim3) {
+      const unsigned j = ugi / (unsigned)g.nx;
+      const bool ring = i == 0 || i == (unsigned)(g.nx - 1) || j == 0 || j == (unsigned)(g.ny - 1);
+      dg = ring ? -3.0 : -4.0; // :23-30
+    } else {
+      const unsigned jj = ugi / (unsigned)g.nx;
+      const unsigned j = jj % (unsigned)g.ny, k = jj / (unsigned)g.ny;
+      const bool face = i == 0 || i == (unsigned)(g.nx - 1) || j == 0 || j == (unsigned)(g.ny - 1) ||
+                        k == 0 || k == (unsigned)(g.nz_glob - 1);
+      dg = face ? -5.0 : -6.0; // :124-127
+    }
+    // accumulate in increasing column order, like the CSC product of the reference
+    if (has_zm) acc = T::fma_r(g.sc, T::mulr(x[idx - g.plane], pre), acc);
+    if (has_ym) acc = T::fma_r(g.sc, T::mulr(x[idx - g.nx], pre), acc);
+    if (has_xm) acc = T::fma_r(g.sc, T::mulr(x[idx - 1], pre), acc);
+    acc = T::fma_r(dg * g.sc, xc, acc);
+    if (has_xp) acc = T::fma_r(g.sc, T::mulr(x[idx + 1], pre), acc);
+    if (has_yp) acc = T::fma_r(g.sc, T::mulr(x[idx + g.nx], pre), acc);
+    if (has_zp) acc = T::fma_r(g.sc, T::mulr(x[idx + g.plane], pre), acc);
+  } else {
+    const double cc = cf[idx];
+    // weights (c_a + c_b)/2 and the diagonal sum in the reference's accumulation order:
+    // x-links (i-1,i),(i,i+1); y-links; z-links   (:75-95, :181-210)
+    const double wxm = has_xm ? (cf[idx - 1] + cc) / 2.0 : 0.0;
+    const double wxp = has_xp ? (cc + cf[idx + 1]) / 2.0 : 0.0;
+    const double wym = has_ym ? (cf[idx - g.nx] + cc) / 2.0 : 0.0;
+    const double wyp = has_yp ? (cc + cf[idx + g.nx]) / 2.0 : 0.0;
+    const double wzm = has_zm ? (cf[idx - g.plane] + cc) / 2.0 : 0.0;
+    const double wzp = has_zp ? (cc + cf[idx + g.plane]) / 2.0 : 0.0;
+    double ds = 0.0;
+    if (has_xm) ds += wxm;
+    if (has_xp) ds += wxp;
+    if (has_ym) ds += wym;
+    if (has_yp) ds += wyp;
+    if (has_zm) ds += wzm;
+    if (has_zp) ds += wzp;
+    if (has_zm) acc = T::fma_r(wzm * g.sc, T::mulr(x[idx - g.plane], pre), acc);
+    if (has_ym) acc = T::fma_r(wym * g.sc, T::mulr(x[idx - g.nx], pre), acc);
+    if (has_xm) acc = T::fma_r(wxm * g.sc, T::mulr(x[idx - 1], pre), acc);
+    acc = T::fma_r(-ds * g.sc, xc, acc);
+    if (has_xp) acc = T::fma_r(wxp * g.sc, T::mulr(x[idx + 1], pre), acc);
+    if (has_yp) acc = T::fma_r(wyp * g.sc, T::mulr(x[idx + g.nx], pre), acc);
+    if (has_zp) acc = T::fma_r(wzp * g.sc, T::mulr(x[idx + g.plane], pre), acc);
+  }
+  return acc;
+}
+
+// clamp a local flat index onto the interior: the fused form of neumann_bc_no_velocity
+// (nlsolvers/host/include/boundaries.hpp:40-57, boundaries_3d.hpp:8-32).  The reference
+// copies x-faces, then y-faces (all x), then z-faces (all x,y); the composition is
+// u(i,j,k) <- u_new(clamp(i), clamp(j), clamp(k)) with clamp(a) = min(max(a,1), n_a-2).
+__device__ __forceinline__ long long clamp_site(const Geom &g, long long idx) {
+  const unsigned ugi = (unsigned)(idx + g.goff);
+  unsigned i = ugi % (unsigned)g.nx;
+  unsigned jj = ugi / (unsigned)g.nx;
+  unsigned j = g.dim3 ? jj % (unsigned)g.ny : jj;
+  unsigned k = g.dim3 ? jj / (unsigned)g.ny : 0u;
+  i = min(max(i, 1u), (unsigned)(g.nx - 2));
+  j = min(max(j, 1u), (unsigned)(g.ny - 2));
+  if (g.dim3) k = min(max(k, 1u), (unsigned)(g.nz_glob - 2));
+  const long long gi = ((long long)k * g.ny + j) * g.nx + i;
+  return gi - g.goff; // may point into a ghost plane only if nz_loc == 1 (rejected at create)
+}
+
+// ---------------------------------------------------------------- reductions
+// Deterministic two-stage grid reduction of K doubles per trajectory:
+//   stage 1: warp shuffles -> shared memory -> one partial per CTA in `partials`
+//   stage 2: the last CTA of the trajectory to arrive (atomic ticket) sums the partials in
+//            a fixed order and stores the K totals to `dst`; no host round trip, no
+//            floating-point atomics, bit-reproducible for a given launch shape.
+struct RedCtx {
+  double *partials;  // [batch][gridDim.x][K]
+  unsigned *tickets; // [batch]
+};
+
+template <int K>
+__device__ __forceinline__ void grid_reduce(double (&acc)[K], const RedCtx &rc, double *dst) {
+  __shared__ double s_part[kThreads / 32][K];
+  __shared__ bool s_last;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int k = 0; k < K; ++k) {
+    double v = acc[k];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+    if (lane == 0) s_part[warp][k] = v;
+  }
+  __syncthreads();
+  const int b = blockIdx.y, nblk = gridDim.x;
+  double *mine = rc.partials + ((size_t)b * nblk + blockIdx.x) * K;
+  if (threadIdx.x < K) {
+    double v = 0.0;
+#pragma unroll
+    for (int w = 0; w < kThreads / 32; ++w) v += s_part[w][threadIdx.x];
+    mine[threadIdx.x] = v;
+  }
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned t = atomicAdd(&rc.tickets[b], 1u);
+    s_last = (t == (unsigned)nblk - 1u);
+    if (s_last) rc.tickets[b] = 0u; // re-arm for the next kernel on this stream
+  }
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  const double *all = rc.partials + (size_t)b * nblk * K;
+  for (int k = warp; k < K; k += kThreads / 32) {
+    double v = 0.0;
+    for (int blk = lane; blk < nblk; blk += 32) v += __ldcg(&all[(size_t)blk * K + k]);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+    if (lane == 0) dst[k] = v;
+  }
+}
+
+} // namespace nls

@@ -1,0 +1,655 @@
+// nls_engine.cu -- host side of libnls_b200.so: the C ABI of include/nls.h.
+// Owns device memory, one stream per handle, CUDA-graph capture of a whole time step.
+// No CPU fallback anywhere: without a CUDA device every entry point returns NLS_ERR_CUDA.
+#include "nls_kernels.cuh"
+
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+using namespace nls;
+
+namespace {
+thread_local std::string g_err;
+
+int fail(int code, const std::string &msg) {
+  g_err = msg;
+  return code;
+}
+
+#define CU(call)                                                                          \
+  do {                                                                                    \
+    cudaError_t e_ = (call);                                                              \
+    if (e_ != cudaSuccess)                                                                \
+      return fail(NLS_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_));      \
+  } while (0)
+
+template <class S> struct Ptrs {};
+} // namespace
+
+struct nls_engine {
+  nls_desc d{};
+  Geom g{};
+  bool cplx = false;
+  int W = 1;
+  size_t esz = 8;
+  int m = 10;
+  int batch = 1;
+  int nblk = 1;
+  cudaStream_t stream = nullptr;
+  // device memory (all n-vectors: [batch][stride] scalars)
+  void *V = nullptr;     // m-1 columns
+  void *wbuf[2] = {nullptr, nullptr};
+  void *w0 = nullptr;    // start vector (rho / g / matfunc input)
+  void *u[3] = {nullptr, nullptr, nullptr};
+  void *acc = nullptr;   // Gautschi accumulator
+  double *mf = nullptr, *cf = nullptr;
+  double *scalA = nullptr, *scalB = nullptr, *coef = nullptr, *redout = nullptr;
+  RedCtx rc{nullptr, nullptr};
+  int *status = nullptr;
+  size_t colstride = 0;  // scalars between basis columns
+  // stepping state
+  int nphase = 1, phase = 0;
+  bool start_valid = false;
+  double start_dt = 0.0;
+  cudaGraphExec_t gexec[3] = {nullptr, nullptr, nullptr};
+  double gdt[3] = {0, 0, 0};
+  uint64_t glaunch[3] = {0, 0, 0};
+  uint64_t launches = 0;
+  bool capturing = false;
+  uint64_t cap_count = 0;
+  // slabs
+  nls_allreduce_fn allreduce = nullptr;
+  void *allreduce_user = nullptr;
+
+  size_t vec_elems() const { return (size_t)batch * g.stride; }
+  size_t vec_bytes() const { return vec_elems() * esz; }
+  dim3 grid() const { return dim3((unsigned)nblk, (unsigned)batch); }
+  void count() {
+    if (capturing) cap_count++;
+    else launches++;
+  }
+  int ui() const { return cplx ? phase : 0; } // index of the current u buffer (SV: see sv_idx)
+};
+
+namespace {
+
+#define LAUNCH(e, kern, gr, ...)                       \
+  do {                                                 \
+    kern<<<gr, kThreads, 0, (e)->stream>>>(__VA_ARGS__); \
+    (e)->count();                                      \
+  } while (0)
+
+template <class S>
+S *col(nls_engine *e, int j) {
+  return (S *)e->V + (size_t)j * e->colstride;
+}
+
+// ---------------------------------------------------------------- Lanczos (K2)
+template <class S, bool ANISO>
+void lanczos_t(nls_engine *e, const S *start, double *scal) {
+  const int m = e->m;
+  const dim3 gr = e->grid();
+  for (int j = 0; j < m - 1; ++j) {
+    const S *wprev = j == 0 ? start : (const S *)e->wbuf[(j - 1) & 1];
+    S *wout = (S *)e->wbuf[j & 1];
+    const S *vprev = j > 0 ? col<S>(e, j - 1) : nullptr;
+    LAUNCH(e, (k_lanczos_pa<S, ANISO>), gr, e->g, wprev, vprev, col<S>(e, j), wout, e->cf, scal, j,
+           e->rc);
+    if (e->d.reorth == NLS_REORTH_NONE) {
+      LAUNCH(e, (k_lanczos_pc<S, 4, true>), gr, e->g, wout, (const S *)e->V, e->colstride, j, j, 1,
+             scal, kOffAlpha + j * e->W, scal, e->rc);
+      continue;
+    }
+    const int nv = j + 1;
+    for (int i0 = 0; i0 < nv; i0 += 16) {
+      const int cnt = nv - i0 < 16 ? nv - i0 : 16;
+      if (cnt <= 4) LAUNCH(e, (k_lanczos_pb<S, 4>), gr, e->g, wout, (const S *)e->V, e->colstride, j, i0, cnt, scal, e->rc);
+      else if (cnt <= 8) LAUNCH(e, (k_lanczos_pb<S, 8>), gr, e->g, wout, (const S *)e->V, e->colstride, j, i0, cnt, scal, e->rc);
+      else if (cnt <= 12) LAUNCH(e, (k_lanczos_pb<S, 12>), gr, e->g, wout, (const S *)e->V, e->colstride, j, i0, cnt, scal, e->rc);
+      else LAUNCH(e, (k_lanczos_pb<S, 16>), gr, e->g, wout, (const S *)e->V, e->colstride, j, i0, cnt, scal, e->rc);
+    }
+    for (int i0 = 0; i0 < nv; i0 += 16) {
+      const int cnt = nv - i0 < 16 ? nv - i0 : 16;
+      const bool last = i0 + 16 >= nv;
+      const int hoff = kOffH + i0 * e->W;
+#define PC(NV)                                                                                      \
+  do {                                                                                              \
+    if (last) LAUNCH(e, (k_lanczos_pc<S, NV, true>), gr, e->g, wout, (const S *)e->V, e->colstride, j, i0, cnt, scal, hoff, scal, e->rc); \
+    else LAUNCH(e, (k_lanczos_pc<S, NV, false>), gr, e->g, wout, (const S *)e->V, e->colstride, j, i0, cnt, scal, hoff, scal, e->rc);     \
+  } while (0)
+      if (cnt <= 4) PC(4);
+      else if (cnt <= 8) PC(8);
+      else if (cnt <= 12) PC(12);
+      else PC(16);
+#undef PC
+    }
+  }
+}
+
+template <class S>
+void lanczos(nls_engine *e, const S *start, double *scal) {
+  if (e->d.laplacian == NLS_LAP_ANISO) lanczos_t<S, true>(e, start, scal);
+  else lanczos_t<S, false>(e, start, scal);
+}
+
+template <class S>
+const S *wlast(nls_engine *e) {
+  return (const S *)e->wbuf[(e->m - 2) & 1];
+}
+
+void tridiag(nls_engine *e, const double *scal, int nfn, int f0, double t0r, double t0i, int f1,
+             double t1r, double t1i) {
+  TridiagArgs a;
+  a.m = e->m;
+  a.W = e->W;
+  a.nfn = nfn;
+  a.fn[0] = f0; a.tr[0] = t0r; a.ti[0] = t0i;
+  a.fn[1] = f1; a.tr[1] = t1r; a.ti[1] = t1i;
+  k_tridiag<<<e->batch, 32, 0, e->stream>>>(scal, e->coef, a, e->status);
+  e->count();
+}
+
+// ---------------------------------------------------------------- one time step
+template <int EQ>
+void nlse_step_t(nls_engine *e, double dt) {
+  const double2 *uin = (const double2 *)e->u[e->phase];
+  double2 *uout = (double2 *)e->u[1 - e->phase];
+  lanczos<double2>(e, (const double2 *)e->w0, e->scalA);
+  tridiag(e, e->scalA, 1, NLS_FN_EXP, 0.0, dt, 0, 0, 0); // expm_multiply(L, rho, tau = i dt)
+  NlseParams p{0.5 * dt, e->d.s1, e->d.s2, e->d.kappa};
+  LAUNCH(e, (k_nlse_finish<EQ>), e->grid(), e->g, (const double2 *)e->V, e->colstride,
+         wlast<double2>(e), e->coef, e->m, uin, e->mf, uout, (double2 *)e->w0, p, e->scalA, e->rc);
+}
+
+template <int EQ>
+void gautschi_step_t(nls_engine *e, double dt) {
+  double *u = (double *)e->u[0], *up = (double *)e->u[1];
+  lanczos<double>(e, u, e->scalA);
+  const int filt = EQ == NLS_EQ_SGE ? NLS_FN_MOD_COSINE : NLS_FN_ID_SQRT;
+  tridiag(e, e->scalA, 2, filt, dt, 0.0, NLS_FN_COS_SQRT, dt, 0.0);
+  LAUNCH(e, (k_gautschi_a<EQ>), e->grid(), e->g, (const double *)e->V, e->colstride,
+         wlast<double>(e), e->coef, e->m, u, up, e->mf, (double *)e->w0, (double *)e->acc, e->scalB,
+         e->rc);
+  lanczos<double>(e, (const double *)e->w0, e->scalB);
+  tridiag(e, e->scalB, 1, NLS_FN_SINC2_HALF, dt, 0.0, 0, 0, 0);
+  LAUNCH(e, (k_gautschi_b<0>), e->grid(), e->g, (const double *)e->V, e->colstride,
+         wlast<double>(e), e->coef, e->m, (const double *)e->acc, u, dt * dt, e->scalA, e->rc);
+}
+
+template <int EQ>
+void sv_step_t(nls_engine *e, double dt) {
+  // rotating buffers: u = buf[phase], u_past = buf[(phase+2)%3], new = buf[(phase+1)%3]
+  const double *u = (const double *)e->u[e->phase];
+  const double *up = (const double *)e->u[(e->phase + 2) % 3];
+  double *un = (double *)e->u[(e->phase + 1) % 3];
+  if (e->d.laplacian == NLS_LAP_ANISO)
+    LAUNCH(e, (k_sv<EQ, true>), e->grid(), e->g, u, up, e->mf, e->cf, un, dt * dt);
+  else
+    LAUNCH(e, (k_sv<EQ, false>), e->grid(), e->g, u, up, e->mf, e->cf, un, dt * dt);
+}
+
+void issue_step(nls_engine *e, double dt) {
+  const int eq = e->d.equation;
+  if (e->cplx) {
+    if (eq == NLS_EQ_NLSE_CUBIC) nlse_step_t<NLS_EQ_NLSE_CUBIC>(e, dt);
+    else if (eq == NLS_EQ_NLSE_CQ) nlse_step_t<NLS_EQ_NLSE_CQ>(e, dt);
+    else nlse_step_t<NLS_EQ_NLSE_SAT>(e, dt);
+    return;
+  }
+#define REAL_DISPATCH(fn)                                                        \
+  switch (eq) {                                                                  \
+  case NLS_EQ_SGE: fn<NLS_EQ_SGE>(e, dt); break;                                 \
+  case NLS_EQ_KGE: fn<NLS_EQ_KGE>(e, dt); break;                                 \
+  case NLS_EQ_PHI4: fn<NLS_EQ_PHI4>(e, dt); break;                               \
+  case NLS_EQ_SGE_DOUBLE: fn<NLS_EQ_SGE_DOUBLE>(e, dt); break;                   \
+  default: fn<NLS_EQ_SGE_SINH>(e, dt); break;                                    \
+  }
+  if (e->d.integrator == NLS_INT_SV) { REAL_DISPATCH(sv_step_t) }
+  else { REAL_DISPATCH(gautschi_step_t) }
+#undef REAL_DISPATCH
+}
+
+// current-state buffers (real equations)
+double *cur_u(nls_engine *e) {
+  return (double *)(e->d.integrator == NLS_INT_SV ? e->u[e->phase] : e->u[0]);
+}
+double *cur_upast(nls_engine *e) {
+  return (double *)(e->d.integrator == NLS_INT_SV ? e->u[(e->phase + 2) % 3] : e->u[1]);
+}
+
+// make the start vector of the next step valid (first step, or after a state/dt change)
+int ensure_start(nls_engine *e, double dt) {
+  if (e->d.integrator == NLS_INT_SV) return NLS_OK;
+  if (e->start_valid && (!e->cplx || e->start_dt == dt)) return NLS_OK;
+  if (e->cplx) {
+    NlseParams p{0.5 * dt, e->d.s1, e->d.s2, e->d.kappa};
+    const double2 *u = (const double2 *)e->u[e->phase];
+    switch (e->d.equation) {
+    case NLS_EQ_NLSE_CUBIC:
+      LAUNCH(e, (k_nlse_prephase<NLS_EQ_NLSE_CUBIC>), e->grid(), e->g, u, e->mf, (double2 *)e->w0, p, e->scalA, e->rc);
+      break;
+    case NLS_EQ_NLSE_CQ:
+      LAUNCH(e, (k_nlse_prephase<NLS_EQ_NLSE_CQ>), e->grid(), e->g, u, e->mf, (double2 *)e->w0, p, e->scalA, e->rc);
+      break;
+    default:
+      LAUNCH(e, (k_nlse_prephase<NLS_EQ_NLSE_SAT>), e->grid(), e->g, u, e->mf, (double2 *)e->w0, p, e->scalA, e->rc);
+    }
+  } else {
+    LAUNCH(e, (k_norm2<double>), e->grid(), e->g, (const double *)e->u[0], e->scalA + kOffNrm2,
+           kScalStride, e->rc);
+  }
+  CU(cudaGetLastError());
+  e->start_valid = true;
+  e->start_dt = dt;
+  return NLS_OK;
+}
+
+int run_steps(nls_engine *e, double dt, uint32_t nsteps) {
+  int rc = ensure_start(e, dt);
+  if (rc) return rc;
+  const bool use_graph = !(e->d.flags & NLS_FLAG_NO_GRAPH);
+  for (uint32_t s = 0; s < nsteps; ++s) {
+    const int p = e->phase;
+    if (use_graph) {
+      if (e->gexec[p] && e->gdt[p] != dt) {
+        cudaGraphExecDestroy(e->gexec[p]);
+        e->gexec[p] = nullptr;
+      }
+      if (!e->gexec[p]) {
+        cudaGraph_t graph;
+        CU(cudaStreamBeginCapture(e->stream, cudaStreamCaptureModeThreadLocal));
+        e->capturing = true;
+        e->cap_count = 0;
+        issue_step(e, dt);
+        e->capturing = false;
+        CU(cudaStreamEndCapture(e->stream, &graph));
+        CU(cudaGraphInstantiate(&e->gexec[p], graph, 0));
+        cudaGraphDestroy(graph);
+        e->gdt[p] = dt;
+        e->glaunch[p] = e->cap_count;
+      }
+      CU(cudaGraphLaunch(e->gexec[p], e->stream));
+      e->launches += e->glaunch[p];
+    } else {
+      issue_step(e, dt);
+      CU(cudaGetLastError());
+    }
+    e->phase = (p + 1) % e->nphase;
+  }
+  return NLS_OK;
+}
+
+// host <-> device copies of [batch][n] host arrays into [batch][stride] (+halo) device arrays
+int copy_in(nls_engine *e, void *dev, const void *host, size_t esz, int nb, bool from_dev) {
+  const cudaMemcpyKind k = from_dev ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+  if (e->g.stride == e->g.n) {
+    CU(cudaMemcpyAsync(dev, host, (size_t)nb * e->g.n * esz, k, e->stream));
+    return NLS_OK;
+  }
+  for (int b = 0; b < nb; ++b)
+    CU(cudaMemcpyAsync((char *)dev + ((size_t)b * e->g.stride + e->g.halo) * esz,
+                       (const char *)host + (size_t)b * e->g.n * esz, e->g.n * esz, k, e->stream));
+  return NLS_OK;
+}
+int copy_out(nls_engine *e, void *host, const void *dev, size_t esz, int nb, bool to_dev) {
+  const cudaMemcpyKind k = to_dev ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost;
+  if (e->g.stride == e->g.n) {
+    CU(cudaMemcpyAsync(host, dev, (size_t)nb * e->g.n * esz, k, e->stream));
+  } else {
+    for (int b = 0; b < nb; ++b)
+      CU(cudaMemcpyAsync((char *)host + (size_t)b * e->g.n * esz,
+                         (const char *)dev + ((size_t)b * e->g.stride + e->g.halo) * esz,
+                         e->g.n * esz, k, e->stream));
+  }
+  CU(cudaStreamSynchronize(e->stream));
+  return NLS_OK;
+}
+
+int check_status(nls_engine *e) {
+  int st = 0;
+  CU(cudaMemcpyAsync(&st, e->status, sizeof(int), cudaMemcpyDeviceToHost, e->stream));
+  CU(cudaStreamSynchronize(e->stream));
+  if (st) return fail(NLS_ERR_STATE, "tridiagonal eigensolver did not converge (non-finite state?)");
+  return NLS_OK;
+}
+
+} // namespace
+
+// =========================================================================== C ABI
+extern "C" {
+
+const char *nls_last_error(void) { return g_err.c_str(); }
+int nls_version(void) { return 100; }
+
+int nls_device_count(void) {
+  int n = 0;
+  CU(cudaGetDeviceCount(&n));
+  return n;
+}
+
+int nls_destroy(nls_handle e) {
+  if (!e) return NLS_OK;
+  cudaSetDevice(e->d.device);
+  if (e->stream) cudaStreamSynchronize(e->stream);
+  for (auto &ge : e->gexec)
+    if (ge) cudaGraphExecDestroy(ge);
+  void *ptrs[] = {e->V, e->wbuf[0], e->wbuf[1], e->w0, e->u[0], e->u[1], e->u[2], e->acc, e->mf, e->cf,
+                  e->scalA, e->scalB, e->coef, e->redout, e->rc.partials, e->rc.tickets, e->status};
+  for (void *p : ptrs)
+    if (p) cudaFree(p);
+  if (e->stream) cudaStreamDestroy(e->stream);
+  delete e;
+  return NLS_OK;
+}
+
+int nls_create(const nls_desc *desc, nls_handle *out) {
+  if (!desc || !out || desc->struct_size != sizeof(nls_desc)) return fail(NLS_ERR_ARG, "bad descriptor");
+  const nls_desc &d = *desc;
+  if (d.nx < 3 || d.ny < 3 || d.nz == 0 || d.nz == 2 || d.krylov_m < 2 || d.krylov_m > (uint32_t)kMaxM ||
+      d.batch < 1)
+    return fail(NLS_ERR_ARG, "bad sizes: need nx,ny>=3, nz==1 or >=3, 2<=m<=64, batch>=1");
+  if (d.equation < NLS_EQ_NLSE_CUBIC || d.equation > NLS_EQ_SGE_SINH) return fail(NLS_ERR_ARG, "bad equation");
+  const bool cplx = d.equation <= NLS_EQ_NLSE_SAT;
+  if (cplx && d.integrator != NLS_INT_SS2) return fail(NLS_ERR_ARG, "NLSE needs NLS_INT_SS2");
+  if (!cplx && d.integrator != NLS_INT_GAUTSCHI && d.integrator != NLS_INT_SV)
+    return fail(NLS_ERR_ARG, "real equations need NLS_INT_GAUTSCHI or NLS_INT_SV");
+  if (!(d.dx > 0) || !(d.dy > 0)) return fail(NLS_ERR_ARG, "dx, dy must be positive");
+  const uint32_t nzg = d.nz_global ? d.nz_global : d.nz;
+  if (d.nz_global && (d.nz == 1 || d.z0 + d.nz > nzg)) return fail(NLS_ERR_ARG, "bad slab");
+  if ((unsigned long long)d.nx * d.ny * nzg >= (1ull << 32)) return fail(NLS_ERR_ARG, "grid too large (2^32 sites)");
+  int ndev = 0;
+  CU(cudaGetDeviceCount(&ndev));
+  if (d.device < 0 || d.device >= ndev) return fail(NLS_ERR_CUDA, "no such CUDA device (there is no CPU fallback)");
+  CU(cudaSetDevice(d.device));
+
+  nls_engine *e = new nls_engine;
+  e->d = d;
+  e->cplx = cplx;
+  e->W = cplx ? 2 : 1;
+  e->esz = cplx ? 16 : 8;
+  e->m = (int)d.krylov_m;
+  e->batch = (int)d.batch;
+  Geom &g = e->g;
+  g.nx = d.nx; g.ny = d.ny; g.nz_loc = d.nz; g.nz_glob = nzg; g.z0 = d.z0;
+  g.dim3 = d.nz > 1;
+  g.plane = g.dim3 ? (long long)d.nx * d.ny : 0;
+  g.n = (long long)d.nx * d.ny * d.nz;
+  g.nglob = (long long)d.nx * d.ny * nzg;
+  g.goff = (long long)d.z0 * d.nx * d.ny;
+  g.halo = (d.nz_global && nzg != d.nz) ? g.plane : 0;
+  g.stride = g.n + 2 * g.halo;
+  const double sgn = d.op_sign == 0.0 ? 1.0 : d.op_sign;
+  // L *= 1/(dx*dy) (laplacians.hpp:49); 3D: 1/(dx*dx) (:153)
+  g.sc = sgn * (1.0 / (g.dim3 ? d.dx * d.dx : d.dx * d.dy));
+  long long want = (g.n + kThreads - 1) / kThreads;
+  long long cap = (148LL * 16 + e->batch - 1) / e->batch;
+  if (cap < 16) cap = 16;
+  if (cap > kMaxBlocksPerTraj) cap = kMaxBlocksPerTraj;
+  e->nblk = (int)(want < cap ? want : cap);
+  e->colstride = e->vec_elems();
+  e->nphase = cplx ? 2 : (d.integrator == NLS_INT_SV ? 3 : 1);
+
+  auto alloc = [&](void **p, size_t bytes) -> bool {
+    if (cudaMalloc(p, bytes) != cudaSuccess) return false;
+    return cudaMemsetAsync(*p, 0, bytes, 0) == cudaSuccess;
+  };
+  bool ok = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking) == cudaSuccess;
+  const size_t vb = e->vec_bytes();
+  const bool krylov = d.integrator != NLS_INT_SV;
+  // the Krylov buffers are also used by nls_matfunc / nls_lanczos / nls_stencil_apply
+  ok = ok && alloc(&e->V, vb * (e->m - 1));
+  ok = ok && alloc(&e->wbuf[0], vb) && alloc(&e->wbuf[1], vb) && alloc(&e->w0, vb);
+  ok = ok && alloc(&e->u[0], vb) && alloc(&e->u[1], vb);
+  if (d.integrator == NLS_INT_SV) ok = ok && alloc(&e->u[2], vb);
+  if (d.integrator == NLS_INT_GAUTSCHI) ok = ok && alloc(&e->acc, vb);
+  ok = ok && alloc((void **)&e->mf, g.stride * 8) && alloc((void **)&e->cf, g.stride * 8);
+  ok = ok && alloc((void **)&e->scalA, (size_t)e->batch * kScalStride * 8);
+  ok = ok && alloc((void **)&e->scalB, (size_t)e->batch * kScalStride * 8);
+  ok = ok && alloc((void **)&e->coef, (size_t)e->batch * 2 * kCoefStride * 8);
+  ok = ok && alloc((void **)&e->redout, (size_t)e->batch * 8);
+  ok = ok && alloc((void **)&e->rc.partials, (size_t)e->batch * e->nblk * 32 * 8);
+  ok = ok && alloc((void **)&e->rc.tickets, (size_t)e->batch * 4);
+  ok = ok && alloc((void **)&e->status, 4);
+  (void)krylov;
+  if (ok && d.laplacian == NLS_LAP_ANISO) { // default c == 1
+    std::vector<double> ones(g.stride, 1.0);
+    ok = cudaMemcpy(e->cf, ones.data(), g.stride * 8, cudaMemcpyHostToDevice) == cudaSuccess;
+  }
+  ok = ok && cudaDeviceSynchronize() == cudaSuccess;
+  if (!ok) {
+    std::string msg = std::string("allocation failed: ") + cudaGetErrorString(cudaGetLastError());
+    nls_destroy(e);
+    return fail(NLS_ERR_CUDA, msg);
+  }
+  *out = e;
+  return NLS_OK;
+}
+
+static int set_field_impl(nls_handle e, int field, const void *src, size_t bytes, bool dev) {
+  if (!e || !src) return fail(NLS_ERR_ARG, "null argument");
+  CU(cudaSetDevice(e->d.device));
+  const size_t sb = (size_t)e->batch * e->g.n * e->esz, fb = (size_t)e->g.n * 8;
+  int rc;
+  switch (field) {
+  case NLS_FIELD_U:
+    if (bytes != sb) return fail(NLS_ERR_ARG, "set U: size mismatch");
+    rc = copy_in(e, e->cplx ? e->u[e->phase] : (void *)cur_u(e), src, e->esz, e->batch, dev);
+    break;
+  case NLS_FIELD_U_PAST:
+    if (e->cplx) return fail(NLS_ERR_STATE, "U_PAST: real equations only");
+    if (bytes != sb) return fail(NLS_ERR_ARG, "set U_PAST: size mismatch");
+    rc = copy_in(e, cur_upast(e), src, 8, e->batch, dev);
+    break;
+  case NLS_FIELD_V: { // u_past = u0 - dt*v0  (sg_single_driver.cpp:70)
+    if (e->cplx) return fail(NLS_ERR_STATE, "V: real equations only");
+    if (bytes != sb) return fail(NLS_ERR_ARG, "set V: size mismatch");
+    rc = copy_in(e, e->wbuf[0], src, 8, e->batch, dev);
+    if (rc) return rc;
+    LAUNCH(e, k_upast_from_v, e->grid(), e->g, cur_u(e), (const double *)e->wbuf[0], cur_upast(e), e->d.dt);
+    CU(cudaGetLastError());
+    break;
+  }
+  case NLS_FIELD_M:
+    if (bytes != fb) return fail(NLS_ERR_ARG, "set M: size mismatch");
+    rc = copy_in(e, e->mf, src, 8, 1, dev);
+    break;
+  case NLS_FIELD_C:
+    if (bytes != fb) return fail(NLS_ERR_ARG, "set C: size mismatch");
+    rc = copy_in(e, e->cf, src, 8, 1, dev);
+    break;
+  default: return fail(NLS_ERR_ARG, "bad field");
+  }
+  if (rc) return rc;
+  e->start_valid = false;
+  CU(cudaStreamSynchronize(e->stream)); // host buffer may be reused by the caller
+  return NLS_OK;
+}
+
+static int get_field_impl(nls_handle e, int field, void *dst, size_t bytes, bool dev) {
+  if (!e || !dst) return fail(NLS_ERR_ARG, "null argument");
+  CU(cudaSetDevice(e->d.device));
+  const size_t sb = (size_t)e->batch * e->g.n * e->esz;
+  if (bytes != sb) return fail(NLS_ERR_ARG, "get: size mismatch");
+  int rc;
+  switch (field) {
+  case NLS_FIELD_U:
+    rc = copy_out(e, dst, e->cplx ? e->u[e->phase] : (void *)cur_u(e), e->esz, e->batch, dev);
+    break;
+  case NLS_FIELD_U_PAST:
+    if (e->cplx) return fail(NLS_ERR_STATE, "U_PAST: real equations only");
+    rc = copy_out(e, dst, cur_upast(e), 8, e->batch, dev);
+    break;
+  case NLS_FIELD_V: // v = (u - u_past)/dt  (sg_single_driver.cpp:113)
+    if (e->cplx) return fail(NLS_ERR_STATE, "V: real equations only");
+    LAUNCH(e, k_velocity, e->grid(), e->g, cur_u(e), cur_upast(e), (double *)e->wbuf[0], e->d.dt);
+    CU(cudaGetLastError());
+    rc = copy_out(e, dst, e->wbuf[0], 8, e->batch, dev);
+    break;
+  default: return fail(NLS_ERR_ARG, "bad field");
+  }
+  if (rc) return rc;
+  return check_status(e);
+}
+
+int nls_set_field(nls_handle h, int f, const void *s, size_t b) { return set_field_impl(h, f, s, b, false); }
+int nls_set_field_dev(nls_handle h, int f, const void *s, size_t b) { return set_field_impl(h, f, s, b, true); }
+int nls_get_field(nls_handle h, int f, void *d, size_t b) { return get_field_impl(h, f, d, b, false); }
+int nls_get_field_dev(nls_handle h, int f, void *d, size_t b) { return get_field_impl(h, f, d, b, true); }
+
+int nls_step(nls_handle e, double dt, uint32_t nsteps) {
+  if (!e) return fail(NLS_ERR_ARG, "null handle");
+  CU(cudaSetDevice(e->d.device));
+  return run_steps(e, dt, nsteps);
+}
+
+int nls_sync(nls_handle e) {
+  if (!e) return fail(NLS_ERR_ARG, "null handle");
+  CU(cudaSetDevice(e->d.device));
+  CU(cudaStreamSynchronize(e->stream));
+  return check_status(e);
+}
+
+int nls_step_timed(nls_handle e, double dt, uint32_t nsteps, float *ms) {
+  if (!e || !ms) return fail(NLS_ERR_ARG, "null argument");
+  CU(cudaSetDevice(e->d.device));
+  int rc = ensure_start(e, dt);
+  if (rc) return rc;
+  cudaEvent_t a, b;
+  CU(cudaEventCreate(&a));
+  CU(cudaEventCreate(&b));
+  CU(cudaEventRecord(a, e->stream));
+  rc = run_steps(e, dt, nsteps);
+  CU(cudaEventRecord(b, e->stream));
+  CU(cudaEventSynchronize(b));
+  CU(cudaEventElapsedTime(ms, a, b));
+  cudaEventDestroy(a);
+  cudaEventDestroy(b);
+  return rc ? rc : check_status(e);
+}
+
+uint64_t nls_launch_count(nls_handle e) { return e ? e->launches : 0; }
+void *nls_stream(nls_handle e) { return e ? (void *)e->stream : nullptr; }
+
+int nls_stencil_apply(nls_handle e, const void *x, void *y) {
+  if (!e || !x || !y) return fail(NLS_ERR_ARG, "null argument");
+  CU(cudaSetDevice(e->d.device));
+  int rc = copy_in(e, e->w0, x, e->esz, e->batch, false);
+  if (rc) return rc;
+  const bool an = e->d.laplacian == NLS_LAP_ANISO;
+  if (e->cplx) {
+    if (an) LAUNCH(e, (k_stencil<double2, true>), e->grid(), e->g, (const double2 *)e->w0, (double2 *)e->wbuf[0], e->cf);
+    else LAUNCH(e, (k_stencil<double2, false>), e->grid(), e->g, (const double2 *)e->w0, (double2 *)e->wbuf[0], e->cf);
+  } else {
+    if (an) LAUNCH(e, (k_stencil<double, true>), e->grid(), e->g, (const double *)e->w0, (double *)e->wbuf[0], e->cf);
+    else LAUNCH(e, (k_stencil<double, false>), e->grid(), e->g, (const double *)e->w0, (double *)e->wbuf[0], e->cf);
+  }
+  CU(cudaGetLastError());
+  e->start_valid = false; // w0 was overwritten
+  return copy_out(e, y, e->wbuf[0], e->esz, e->batch, false);
+}
+
+// upload `in` into w0, ||in||^2 -> scalA.nrm2[0], run the Lanczos process
+static int lanczos_from_host(nls_handle e, const void *in) {
+  int rc = copy_in(e, e->w0, in, e->esz, e->batch, false);
+  if (rc) return rc;
+  e->start_valid = false;
+  if (e->cplx) {
+    LAUNCH(e, (k_norm2<double2>), e->grid(), e->g, (const double2 *)e->w0, e->scalA + kOffNrm2, kScalStride, e->rc);
+    lanczos<double2>(e, (const double2 *)e->w0, e->scalA);
+  } else {
+    LAUNCH(e, (k_norm2<double>), e->grid(), e->g, (const double *)e->w0, e->scalA + kOffNrm2, kScalStride, e->rc);
+    lanczos<double>(e, (const double *)e->w0, e->scalA);
+  }
+  CU(cudaGetLastError());
+  return NLS_OK;
+}
+
+int nls_matfunc(nls_handle e, int fn, double t_re, double t_im, const void *in, void *out) {
+  if (!e || !in || !out) return fail(NLS_ERR_ARG, "null argument");
+  if (fn < NLS_FN_EXP || fn > NLS_FN_MOD_COSINE) return fail(NLS_ERR_ARG, "bad function id");
+  if (!e->cplx && fn <= NLS_FN_SINC && fn == NLS_FN_EXP && t_im != 0.0)
+    return fail(NLS_ERR_STATE, "complex exp needs a complex-state handle");
+  CU(cudaSetDevice(e->d.device));
+  int rc = lanczos_from_host(e, in);
+  if (rc) return rc;
+  tridiag(e, e->scalA, 1, fn, t_re, t_im, 0, 0, 0);
+  void *dst = e->u[2] ? e->u[2] : e->acc ? e->acc : e->u[1 - e->phase]; // scratch not holding state
+  if (e->cplx)
+    LAUNCH(e, (k_combine<double2>), e->grid(), e->g, (const double2 *)e->V, e->colstride, wlast<double2>(e), e->coef, 0, e->m, (double2 *)dst);
+  else {
+    // real scratch: SV has no spare buffer that is not state -> use wbuf not holding wlast
+    dst = e->wbuf[1 - ((e->m - 2) & 1)];
+    LAUNCH(e, (k_combine<double>), e->grid(), e->g, (const double *)e->V, e->colstride, wlast<double>(e), e->coef, 0, e->m, (double *)dst);
+  }
+  CU(cudaGetLastError());
+  rc = copy_out(e, out, dst, e->esz, e->batch, false);
+  return rc ? rc : check_status(e);
+}
+
+int nls_lanczos(nls_handle e, const void *in, void *hV, void *halpha, double *hbeta) {
+  if (!e || !in) return fail(NLS_ERR_ARG, "null argument");
+  CU(cudaSetDevice(e->d.device));
+  int rc = lanczos_from_host(e, in);
+  if (rc) return rc;
+  CU(cudaStreamSynchronize(e->stream));
+  const int m = e->m;
+  std::vector<double> sc(kScalStride);
+  CU(cudaMemcpy(sc.data(), e->scalA, kScalStride * 8, cudaMemcpyDeviceToHost));
+  if (hbeta)
+    for (int j = 0; j < m; ++j) hbeta[j] = std::sqrt(sc[kOffNrm2 + j]);
+  if (halpha) {
+    std::memset(halpha, 0, (size_t)m * e->esz); // T(m-1,m-1) stays 0
+    std::memcpy(halpha, &sc[kOffAlpha], (size_t)(m - 1) * e->esz);
+  }
+  if (hV) {
+    const size_t nb = (size_t)e->g.n * e->esz;
+    for (int j = 0; j < m - 1; ++j)
+      CU(cudaMemcpy((char *)hV + j * nb, (char *)e->V + ((size_t)j * e->colstride + e->g.halo) * e->esz, nb,
+                    cudaMemcpyDeviceToHost));
+    char *lastc = (char *)hV + (size_t)(m - 1) * nb;
+    CU(cudaMemcpy(lastc, (const char *)e->wbuf[(m - 2) & 1] + e->g.halo * e->esz, nb, cudaMemcpyDeviceToHost));
+    // V.col(m-1) = w / T(m-1,m-2)   (eigen_krylov_complex.hpp:46; presentation only)
+    const double off = std::sqrt(sc[kOffNrm2 + m - 1]);
+    double *p = (double *)lastc;
+    for (size_t i = 0; i < (size_t)e->g.n * e->W; ++i) p[i] /= off;
+  }
+  return NLS_OK;
+}
+
+int nls_reduce(nls_handle e, int what, double *out) {
+  if (!e || !out) return fail(NLS_ERR_ARG, "null argument");
+  CU(cudaSetDevice(e->d.device));
+  if (e->cplx) {
+    const double2 *u = (const double2 *)e->u[e->phase];
+    if (what == NLS_RED_MASS) LAUNCH(e, (k_reduce_state<double2, NLS_RED_MASS>), e->grid(), e->g, u, e->redout, e->rc);
+    else LAUNCH(e, (k_reduce_state<double2, NLS_RED_NONFINITE>), e->grid(), e->g, u, e->redout, e->rc);
+  } else {
+    const double *u = cur_u(e);
+    if (what == NLS_RED_MASS) LAUNCH(e, (k_reduce_state<double, NLS_RED_MASS>), e->grid(), e->g, u, e->redout, e->rc);
+    else LAUNCH(e, (k_reduce_state<double, NLS_RED_NONFINITE>), e->grid(), e->g, u, e->redout, e->rc);
+  }
+  CU(cudaGetLastError());
+  CU(cudaMemcpyAsync(out, e->redout, (size_t)e->batch * 8, cudaMemcpyDeviceToHost, e->stream));
+  CU(cudaStreamSynchronize(e->stream));
+  if (what == NLS_RED_MASS) {
+    const double cell = e->g.dim3 ? e->d.dx * e->d.dy * e->d.dz : e->d.dx * e->d.dy;
+    for (int b = 0; b < e->batch; ++b) out[b] *= cell;
+  }
+  return NLS_OK;
+}
+
+int nls_slab_export(nls_handle, void *) { return fail(NLS_ERR_STATE, "z-slab exchange not built in this round"); }
+int nls_slab_connect(nls_handle, const void *, const void *) {
+  return fail(NLS_ERR_STATE, "z-slab exchange not built in this round");
+}
+int nls_slab_set_allreduce(nls_handle e, nls_allreduce_fn fn, void *user) {
+  if (!e) return fail(NLS_ERR_ARG, "null handle");
+  e->allreduce = fn;
+  e->allreduce_user = user;
+  return NLS_OK;
+}
+
+} // extern "C"

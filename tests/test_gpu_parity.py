@@ -1,0 +1,284 @@
+"""GPU parity tests (run with -m gpu on a B200): the CUDA path, called through the C ABI,
+against the CPU oracle on the same seeded inputs.  Shapes/seeds follow the reference's own
+test programs.  Tolerances: fp64 path, north-star bar is rel-L2 <= 1e-10
+after the stated step count; per-op checks are much tighter."""
+import numpy as np
+import pytest
+
+from conftest import rel_l2
+import ics
+import nls_b200
+from nls_b200 import Desc, Engine, EQ, INT, LAP, FN, FIELD, RED, REORTH
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def orc(oracle_lib):
+    return oracle_lib
+
+
+def randn(d, seed=42, batch=1):
+    rng = np.random.default_rng(seed)
+    x = rng.standard_normal((batch, d.n))
+    if d.is_complex:
+        x = x + 1j * rng.standard_normal((batch, d.n))
+    return x
+
+
+# ---- K1: stencil vs assembled CSR (device/test_spmv.cpp:12-108 shapes) -------------------
+@pytest.mark.parametrize("nx", [128, 256, 541])
+@pytest.mark.parametrize("eq", [EQ.NLSE_CUBIC, EQ.SGE])
+def test_stencil_2d_uniform(orc, nx, eq):
+    integ = INT.SS2 if eq == EQ.NLSE_CUBIC else INT.GAUTSCHI
+    d = Desc.make(nx, nx, L=5.0, equation=eq, integrator=integ)
+    x = randn(d)
+    got = Engine(d).stencil_apply(x)
+    ref = orc.Oracle(d).stencil_apply(x)
+    assert rel_l2(got, ref) < 1e-15
+    # corner rows (quirk Q1) checked explicitly
+    g2, r2 = got.reshape(nx, nx), ref.reshape(nx, nx)
+    for c in [(0, 0), (0, -1), (-1, 0), (-1, -1)]:
+        assert abs(g2[c] - r2[c]) <= 1e-12 * abs(r2[c])
+
+
+@pytest.mark.parametrize("lap", [LAP.UNIFORM, LAP.ANISO])
+@pytest.mark.parametrize("eq", [EQ.NLSE_CUBIC, EQ.KGE])
+def test_stencil_3d_with_wrap_quirk(orc, lap, eq):
+    integ = INT.SS2 if eq == EQ.NLSE_CUBIC else INT.GAUTSCHI
+    n = 24
+    d = Desc.make(n, n, n, L=2.0, equation=eq, integrator=integ, laplacian=lap, op_sign=-1.0 if eq == EQ.KGE else 1.0)
+    c = np.random.default_rng(5).uniform(0.5, 1.5, d.n)
+    x = randn(d, 7)
+    e, o = Engine(d), orc.Oracle(d)
+    if lap == LAP.ANISO:
+        e.set(FIELD.C, c)
+        o.set(FIELD.C, c)
+    assert rel_l2(e.stencil_apply(x), o.stencil_apply(x)) < 1e-15
+
+
+def test_stencil_2d_aniso_batch(orc):
+    d = Desc.make(100, 100, L=3.0, equation=EQ.NLSE_CUBIC, laplacian=LAP.ANISO, batch=3)
+    c = np.random.default_rng(5).uniform(0.5, 1.5, d.n)
+    x = randn(d, 9, batch=3)
+    e, o = Engine(d), orc.Oracle(d)
+    e.set(FIELD.C, c)
+    o.set(FIELD.C, c)
+    assert rel_l2(e.stencil_apply(x), o.stencil_apply(x)) < 1e-15
+
+
+# ---- K2: Lanczos V, T, beta (device/test_lanczos.cpp:14-141 shapes) -----------------------
+@pytest.mark.parametrize("nx,m", [(44, 10), (50, 20), (100, 30), (200, 10), (541, 10)])
+@pytest.mark.parametrize("eq", [EQ.SGE, EQ.NLSE_CUBIC])
+def test_lanczos_basis(orc, nx, m, eq):
+    integ = INT.SS2 if eq == EQ.NLSE_CUBIC else INT.GAUTSCHI
+    d = Desc.make(nx, nx, L=5.0, equation=eq, integrator=integ, krylov_m=m)
+    x = randn(d)
+    V, a, b = Engine(d).lanczos(x)
+    Vo, ao, bo = orc.Oracle(d).lanczos(x)
+    assert np.allclose(b, bo, rtol=1e-12)
+    assert np.allclose(a, ao, rtol=1e-11, atol=1e-11 * np.abs(ao).max())
+    assert a[-1] == 0
+    # first columns agree tightly; later ones to the conditioning of the recurrence
+    assert rel_l2(V[:5], Vo[:5]) < 1e-12
+    assert rel_l2(V, Vo) < 1e-8
+    G = V.conj() @ V.T
+    assert np.abs(G - np.eye(m)).max() < 1e-12
+
+
+# ---- K2+K3+K4: matrix functions (device/test_matfunc_real.cpp, test_matfunc_complex.cpp) --
+@pytest.mark.parametrize("nx,m", [(50, 5), (50, 10), (50, 20), (300, 10)])
+@pytest.mark.parametrize("fn", [FN.COS_SQRT, FN.SINC2_SQRT, FN.ID_SQRT, FN.SINC2_HALF, FN.MOD_COSINE])
+def test_matfunc_real(orc, nx, m, fn):
+    d = Desc.make(nx, nx, L=5.0, equation=EQ.SGE, integrator=INT.GAUTSCHI, krylov_m=m, op_sign=-1.0)
+    x = randn(d)
+    x /= np.linalg.norm(x)
+    got = Engine(d).matfunc(fn, 1e-2, x)
+    ref = orc.Oracle(d).matfunc(fn, 1e-2, x)
+    assert rel_l2(got, ref) < 1e-12
+
+
+@pytest.mark.parametrize("nx,m", [(100, 5), (100, 10), (100, 20), (400, 10)])
+@pytest.mark.parametrize("fn,t", [(FN.EXP, 1e-2j), (FN.EXP, 1e-2), (FN.SINC, 1e-2)])
+def test_matfunc_complex(orc, nx, m, fn, t):
+    d = Desc.make(nx, nx, L=5.0, equation=EQ.NLSE_CUBIC, krylov_m=m)
+    x = randn(d)
+    got = Engine(d).matfunc(fn, t, x)
+    ref = orc.Oracle(d).matfunc(fn, t, x)
+    assert rel_l2(got, ref) < 1e-12
+
+
+def test_expm_vs_scipy_on_gpu(orc):
+    """The reference's own external anchor (check_krylov_compute.py:41-49), GPU side."""
+    from scipy.sparse.linalg import expm_multiply
+    n = 20
+    d = Desc.make(n, n, n, L=2.0, equation=EQ.NLSE_CUBIC, laplacian=LAP.ANISO, krylov_m=30)
+    A = orc.Oracle(d).csr()
+    u0 = ics.gaussian_bumps_3d(n, 2.0, K=1).ravel()
+    got = Engine(d).matfunc(FN.EXP, 1e-2j, u0)
+    ref = expm_multiply(1e-2j * A.astype(complex), u0)
+    assert rel_l2(got, ref) < 1e-8
+
+
+# ---- full steps -----------------------------------------------------------------------------
+def run_pair(orc, d, u0, steps, dt, mfield=None, v0=None, cfield=None):
+    e, o = Engine(d), orc.Oracle(d)
+    for s in (e, o):
+        s.set(FIELD.U, u0)
+        if v0 is not None:
+            s.set(FIELD.V, v0)
+        s.set(FIELD.M, np.ones(d.n) if mfield is None else mfield)
+        if cfield is not None:
+            s.set(FIELD.C, cfield)
+        s.step(dt, steps)
+    return e, o
+
+
+@pytest.mark.parametrize("eq", [EQ.NLSE_CUBIC, EQ.NLSE_CQ, EQ.NLSE_SAT])
+def test_nlse_2d_steps(orc, eq):
+    n, L, dt = 96, 10.0, 1e-3
+    d = Desc.make(n, n, L=L, equation=eq, krylov_m=10, s1=1.0, s2=-0.1, kappa=0.3)
+    mf = 1.0 + 0.2 * np.random.default_rng(1).standard_normal(d.n)
+    e, o = run_pair(orc, d, ics.gaussian_bumps_2d(n, L), 50, dt, mf)
+    assert rel_l2(e.get(), o.get()) < 1e-11
+    assert np.allclose(e.reduce(RED.MASS), o.reduce(RED.MASS), rtol=1e-12)
+    assert e.reduce(RED.NONFINITE)[0] == 0
+
+
+def test_nlse_2d_odd_grid_and_step_splitting(orc):
+    """nsteps issued in pieces (graph replay, phase flip) equals one call; odd nx."""
+    n, L, dt = 67, 8.0, 1e-3
+    d = Desc.make(n, n, L=L, equation=EQ.NLSE_CUBIC, krylov_m=8)
+    u0 = ics.gaussian_bumps_2d(n, L)
+    e1 = Engine(d); e1.set(FIELD.U, u0); e1.set(FIELD.M, np.ones(d.n)); e1.step(dt, 7)
+    e2 = Engine(d); e2.set(FIELD.U, u0); e2.set(FIELD.M, np.ones(d.n))
+    for k in (1, 2, 3, 1):
+        e2.step(dt, k)
+    assert np.array_equal(e1.get(), e2.get())
+    o = orc.Oracle(d); o.set(FIELD.U, u0); o.set(FIELD.M, np.ones(d.n)); o.step(dt, 7)
+    assert rel_l2(e1.get(), o.get()) < 1e-12
+    dn = Desc.make(n, n, L=L, equation=EQ.NLSE_CUBIC, krylov_m=8, flags=nls_b200.FLAG_NO_GRAPH)
+    e3 = Engine(dn); e3.set(FIELD.U, u0); e3.set(FIELD.M, np.ones(dn.n)); e3.step(dt, 7)
+    assert np.array_equal(e1.get(), e3.get())
+
+
+def test_nlse_default_m_is_zero_like_reference(orc):
+    """nlse_cubic_driver.cpp:63: without an m file the CPU driver runs m == 0."""
+    n, L = 48, 10.0
+    d = Desc.make(n, n, L=L, equation=EQ.NLSE_CUBIC)
+    u0 = ics.gaussian_bumps_2d(n, L)
+    e, o = Engine(d), orc.Oracle(d)
+    for s in (e, o):
+        s.set(FIELD.U, u0)
+        s.step(1e-3, 5)
+    assert rel_l2(e.get(), o.get()) < 1e-12
+
+
+def test_nlse_3d_cubic_quintic_aniso(orc):
+    """C3 at reduced size: 3D cubic-quintic, anisotropic builder semantics (c == 1 + noise), m=12."""
+    n, L, dt = 32, 6.0, 5e-4
+    d = Desc.make(n, n, n, L=L, equation=EQ.NLSE_CQ, laplacian=LAP.ANISO, krylov_m=12, s1=1.0, s2=-0.1)
+    c = 1.0 + 0.1 * np.random.default_rng(2).standard_normal(d.n)
+    e, o = run_pair(orc, d, ics.gaussian_bumps_3d(n, L), 10, dt, cfield=c)
+    assert rel_l2(e.get(), o.get()) < 1e-11
+
+
+@pytest.mark.parametrize("eq", [EQ.SGE, EQ.KGE, EQ.PHI4, EQ.SGE_DOUBLE, EQ.SGE_SINH])
+@pytest.mark.parametrize("integ", [INT.GAUTSCHI, INT.SV])
+def test_real_2d_steps(orc, eq, integ):
+    n, L, dt = 96, 10.0, 1e-3
+    d = Desc.make(n, n, L=L, equation=eq, integrator=integ, krylov_m=10, dt=dt,
+                  op_sign=-1.0 if (eq == EQ.KGE and integ == INT.GAUTSCHI) else 1.0)
+    u0 = ics.kink_2d(n, L)
+    if eq in (EQ.KGE, EQ.PHI4, EQ.SGE_SINH):
+        u0 = 0.2 * u0  # keep the polynomial / sinh nonlinearities bounded
+    v0 = 0.05 * np.cos(u0)
+    steps = 40 if integ == INT.GAUTSCHI else 200
+    e, o = run_pair(orc, d, u0, steps, dt, v0=v0)
+    assert rel_l2(e.get(), o.get()) < 1e-11
+    assert rel_l2(e.get(FIELD.V), o.get(FIELD.V)) < 1e-7
+    assert rel_l2(e.get(FIELD.U_PAST), o.get(FIELD.U_PAST)) < 1e-11
+
+
+def test_kge_3d_sv_and_gautschi(orc):
+    n, L, dt = 24, 4.0, 1e-3
+    for integ in (INT.SV, INT.GAUTSCHI):
+        d = Desc.make(n, n, n, L=L, equation=EQ.KGE, integrator=integ, laplacian=LAP.ANISO, krylov_m=10,
+                      dt=dt, op_sign=-1.0 if integ == INT.GAUTSCHI else 1.0)
+        u0 = 0.3 * np.abs(ics.gaussian_bumps_3d(n, L))
+        e, o = run_pair(orc, d, u0, 10, dt, v0=np.zeros_like(u0))
+        assert rel_l2(e.get(), o.get()) < 1e-11
+
+
+def test_batched_ensemble_matches_single(orc):
+    """C4 semantics at small size: a batch handle equals independent single-trajectory handles."""
+    n, L, dt, B = 64, 10.0, 1e-3, 5
+    u0 = np.stack([ics.gaussian_bumps_2d(n, L, seed=10000 + t) for t in range(B)])
+    db = Desc.make(n, n, L=L, equation=EQ.NLSE_CUBIC, batch=B)
+    eb = Engine(db); eb.set(FIELD.U, u0); eb.set(FIELD.M, np.ones(db.n)); eb.step(dt, 20)
+    got = eb.get()
+    ob = orc.Oracle(db); ob.set(FIELD.U, u0); ob.set(FIELD.M, np.ones(db.n)); ob.step(dt, 20)
+    assert rel_l2(got, ob.get()) < 1e-11
+    d1 = Desc.make(n, n, L=L, equation=EQ.NLSE_CUBIC)
+    e1 = Engine(d1); e1.set(FIELD.U, u0[3:4]); e1.set(FIELD.M, np.ones(d1.n)); e1.step(dt, 20)
+    assert rel_l2(got[3], e1.get()[0]) < 1e-13
+
+
+def test_three_term_mode(orc):
+    n, L, dt = 64, 10.0, 1e-3
+    d = Desc.make(n, n, L=L, equation=EQ.NLSE_CUBIC, reorth=REORTH.NONE)
+    e, o = run_pair(orc, d, ics.gaussian_bumps_2d(n, L), 20, dt)
+    assert rel_l2(e.get(), o.get()) < 1e-11
+
+
+def test_config1_full_trajectory_parity(orc):
+    """BASELINE config 1: NLSE 2D cubic focusing 256x256, dt=1e-3, nt=1000 (999 steps), m=10,
+    100 snapshots; rel-L2 of every snapshot <= 1e-10 and mass series to 1e-8."""
+    n, L, T, nt, ns = 256, 10.0, 1.0, 1000, 100
+    dt, freq = T / nt, nt // ns
+    d = Desc.make(n, n, L=L, equation=EQ.NLSE_CUBIC, krylov_m=10)
+    u0 = ics.gaussian_bumps_2d(n, L, seed=1234)
+    e, o = Engine(d), orc.Oracle(d)
+    for s in (e, o):
+        s.set(FIELD.U, u0)
+        s.set(FIELD.M, np.ones(d.n))
+    worst, worst_mass = 0.0, 0.0
+    done = 0  # driver loop i=1..nt-1; snapshot when i % freq == 0 (nlse_cubic_driver.cpp:96-105)
+    while done < nt - 1:
+        k = min(freq - done % freq, nt - 1 - done)
+        e.step(dt, k)
+        o.step(dt, k)
+        done += k
+        if done % freq == 0 and done // freq < ns:
+            worst = max(worst, rel_l2(e.get(), o.get()))
+            me, mo = e.reduce(RED.MASS)[0], o.reduce(RED.MASS)[0]
+            worst_mass = max(worst_mass, abs(me - mo) / mo)
+    print(f"C1 worst snapshot rel-L2 {worst:.3e}, worst mass mismatch {worst_mass:.3e}")
+    assert worst <= 1e-10
+    assert worst_mass <= 1e-8
+
+
+def test_config2_sge_256_parity(orc):
+    """BASELINE config 2 at the oracle-affordable size: sine-Gordon 256^2 Gautschi, 300 steps,
+    and Stoermer-Verlet 2000 steps."""
+    n, L, dt = 256, 10.0, 1e-3
+    u0 = ics.kink_2d(n, L)
+    for integ, steps in ((INT.GAUTSCHI, 300), (INT.SV, 2000)):
+        d = Desc.make(n, n, L=L, equation=EQ.SGE, integrator=integ, krylov_m=10, dt=dt)
+        e, o = run_pair(orc, d, u0, steps, dt, v0=np.zeros_like(u0))
+        err = rel_l2(e.get(), o.get())
+        print(f"C2 256^2 integ={integ} steps={steps} rel-L2 {err:.3e}")
+        assert err <= 1e-10
+
+
+def test_linearity_and_norm_preservation_full_size():
+    """Size-independent properties at BASELINE size (1024^2): exp(i t L) is linear and, L being
+    symmetric, norm preserving; the Krylov approximation inherits both to rounding."""
+    n = 1024
+    d = Desc.make(n, n, L=10.0, equation=EQ.NLSE_CUBIC, krylov_m=10)
+    e = Engine(d)
+    a, b = ics.gaussian_bumps_2d(n, 10.0, seed=1), ics.gaussian_bumps_2d(n, 10.0, seed=2)
+    fa = e.matfunc(FN.EXP, 1e-3j, a)
+    assert abs(np.linalg.norm(fa) / np.linalg.norm(a) - 1) < 1e-12
+    f2a = e.matfunc(FN.EXP, 1e-3j, (2.0 - 1.0j) * a)
+    assert rel_l2(f2a, (2.0 - 1.0j) * fa) < 1e-13
