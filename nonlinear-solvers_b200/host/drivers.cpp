@@ -1,0 +1,229 @@
+// drivers.cpp -- the reference's *_driver command lines (SURVEY.md 8b "B1") on top of the
+// B200 engine.  One table-driven program; the executable's basename (or `nls_driver <name>`)
+// selects the driver, so the Python launchers' `--exe` keeps working unchanged.
+//
+// Kept from the reference, per driver (file:line in the table below):
+//   positional argv and usage-on-wrong-argc (exit 1), dx = 2*Lx/(nx-1), dt = T/nt,
+//   freq = nt/num_snapshots, loop i = 1..nt-1, boundary copy after every step, snapshot rule
+//   i % freq == 0 && i/freq < num_snapshots, snapshot 0 = initial data, .npy shapes
+//   (ny,nx) / (nz,ny,nx) in and (ns,[nz,]ny,nx) out, default m when no file is given,
+//   the sign of the operator (+L or -L) and the hard-coded Krylov dimension.
+// Optional trailing flags (not in the reference; ignored by its launchers):
+//   --m K   Krylov dimension      --device D   CUDA device ordinal
+#include "../../include/nls/solvers.hpp"
+#include "npy.hpp"
+
+#include <chrono>
+#include <cstdlib>
+#include <iostream>
+#include <libgen.h>
+
+using nls_host::read_npy;
+using nls_host::write_npy;
+using cplx = std::complex<double>;
+
+namespace {
+
+struct Spec {
+  const char *name;
+  int dim;          // 2 or 3
+  int equation;     // NLS_EQ_*
+  int integrator;   // NLS_INT_*
+  int nscal;        // extra scalars after the box lengths: cq -> s1 s2, saturating -> kappa
+  bool fields_req;  // true: "... m.npy c.npy" both required (gen-2 device drivers, all 3D drivers)
+  double m_default; // value of m(x) when the optional m file is absent
+  double op_sign;   // +1: L, -1: -L
+  uint32_t krylov;  // Krylov dimension hard-coded by that driver
+  const char *ref;  // reference source
+};
+
+const Spec kSpecs[] = {
+    // host (CPU) drivers, nlsolvers/host/drivers/
+    {"nlse_cubic", 2, NLS_EQ_NLSE_CUBIC, NLS_INT_SS2, 0, false, 0.0, 1, 10, "nlse_cubic_driver.cpp:18-117"},
+    {"nlse_cubic_quintic", 2, NLS_EQ_NLSE_CQ, NLS_INT_SS2, 2, false, 0.0, 1, 10, "nlse_cubic_quintic_driver.cpp:18-118"},
+    {"nlse_saturating", 2, NLS_EQ_NLSE_SAT, NLS_INT_SS2, 1, false, 0.0, 1, 10, "nlse_saturating_driver.cpp:18-117"},
+    {"nlse_cubic_host_3d", 3, NLS_EQ_NLSE_CUBIC, NLS_INT_SS2, 0, true, 0.0, 1, 10, "nlse_cubic_driver_3d.cpp:21-140"},
+    {"sg_single", 2, NLS_EQ_SGE, NLS_INT_GAUTSCHI, 0, false, 1.0, 1, 10, "sg_single_driver.cpp:20-126"},
+    {"sg_single_sv", 2, NLS_EQ_SGE, NLS_INT_SV, 0, false, 1.0, 1, 10, "sg_single_driver_sv.cpp:20-126"},
+    {"sg_double", 2, NLS_EQ_SGE_DOUBLE, NLS_INT_GAUTSCHI, 0, false, 1.0, -1, 10, "sg_double_driver.cpp:20-125"},
+    {"sg_hyperbolic", 2, NLS_EQ_SGE_SINH, NLS_INT_GAUTSCHI, 0, false, 1.0, -1, 10, "sg_hyperbolic_driver.cpp:20-125"},
+    {"kg", 2, NLS_EQ_KGE, NLS_INT_GAUTSCHI, 0, false, 1.0, -1, 10, "kg_driver.cpp:20-126"},
+    {"kg_sv", 2, NLS_EQ_KGE, NLS_INT_SV, 0, false, 1.0, 1, 10, "kg_sv_driver.cpp:20-126"},
+    {"phi4", 2, NLS_EQ_PHI4, NLS_INT_GAUTSCHI, 0, false, 1.0, -1, 10, "phi4_driver.cpp:20-123"},
+    {"kg_driver_3d", 3, NLS_EQ_KGE, NLS_INT_GAUTSCHI, 0, true, 1.0, -1, 10, "kg_driver_3d.cpp:20-146"},
+    {"kg_sv_driver_3d", 3, NLS_EQ_KGE, NLS_INT_SV, 0, true, 1.0, 1, 10, "kg_sv_driver_3d.cpp:20-146"},
+    // gen-2 device drivers, nlsolvers/device/drivers/ (names from its CMakeLists.txt:55-73)
+    {"nlse_2d_dev", 2, NLS_EQ_NLSE_CUBIC, NLS_INT_SS2, 0, true, 0.0, 1, 20, "nlse_cubic_driver_2d.cpp:19-125"},
+    {"nlse_3d_dev", 3, NLS_EQ_NLSE_CUBIC, NLS_INT_SS2, 0, true, 0.0, 1, 25, "nlse_cubic_driver_3d.cpp:19-133"},
+    {"nlse_cubic_quintic_dev", 2, NLS_EQ_NLSE_CQ, NLS_INT_SS2, 2, false, 1.0, 1, 15, "nlse_cubic_quintic_driver_dev.cpp:16-118"},
+    {"kg_gautschi_2d_dev", 2, NLS_EQ_KGE, NLS_INT_GAUTSCHI, 0, true, 1.0, -1, 10, "kg_driver_dev_2d.cpp:20-165"},
+    {"kg_sv_2d_dev", 2, NLS_EQ_KGE, NLS_INT_SV, 0, true, 1.0, 1, 10, "kg_sv_driver_dev_2d.cpp:20-162"},
+    {"kg_gautschi_3d_dev", 3, NLS_EQ_KGE, NLS_INT_GAUTSCHI, 0, true, 1.0, -1, 10, "kg_driver_dev_3d.cpp:19-170"},
+    {"kg_sv_3d_dev", 3, NLS_EQ_KGE, NLS_INT_SV, 0, true, 1.0, 1, 10, "kg_sv_driver_dev_3d.cpp"},
+    {"sge_sv_2d_dev", 2, NLS_EQ_SGE, NLS_INT_SV, 0, true, 1.0, 1, 10, "sg_sv_driver_dev_2d.cpp:20-162"},
+    {"sge_sv_3d_dev", 3, NLS_EQ_SGE, NLS_INT_SV, 0, true, 1.0, 1, 10, "sg_sv_driver_dev_3d.cpp"},
+};
+
+bool is_nlse(const Spec &s) { return s.equation <= NLS_EQ_NLSE_SAT; }
+
+int usage(const Spec &s, const char *argv0) {
+  std::cerr << "Usage: " << argv0 << (s.dim == 3 ? " nx ny nz Lx Ly Lz" : " nx ny Lx Ly");
+  if (s.nscal == 2) std::cerr << " sigma1 sigma2";
+  if (s.nscal == 1) std::cerr << " kappa";
+  if (is_nlse(s)) std::cerr << " input_u0.npy output_traj.npy";
+  else std::cerr << " input_u0.npy input_v0.npy output_traj.npy output_vel.npy";
+  std::cerr << " T nt num_snapshots" << (s.fields_req ? " input_m.npy input_c.npy" : " [input_m.npy]")
+            << " [--m K] [--device D]\n";
+  return 1;
+}
+
+template <class T>
+bool load_checked(const std::string &file, const std::vector<uint64_t> &want, std::vector<T> &out, const char *what) {
+  std::vector<uint64_t> shape;
+  out = read_npy<T>(file, shape);
+  if (shape == want) return true;
+  std::cerr << "Error: " << what << " array dimensions mismatch\nExpected:";
+  for (auto v : want) std::cerr << " " << v;
+  std::cerr << "\nGot:";
+  for (auto v : shape) std::cerr << " " << v;
+  std::cerr << "\n";
+  return false;
+}
+
+int run(const Spec &s, int argc, char **argv) {
+  // strip the optional trailing flags
+  uint32_t krylov = s.krylov;
+  int device = 0;
+  if (const char *e = std::getenv("NLS_KRYLOV_M")) krylov = (uint32_t)std::stoul(e);
+  std::vector<char *> av(argv, argv + argc);
+  for (size_t i = 1; i + 1 < av.size();) {
+    const std::string a = av[i];
+    if (a == "--m") { krylov = (uint32_t)std::stoul(av[i + 1]); av.erase(av.begin() + i, av.begin() + i + 2); }
+    else if (a == "--device") { device = std::stoi(av[i + 1]); av.erase(av.begin() + i, av.begin() + i + 2); }
+    else ++i;
+  }
+  const int ac = (int)av.size();
+  const int nbox = s.dim == 3 ? 6 : 4, nfiles = is_nlse(s) ? 2 : 4;
+  const int base = 1 + nbox + s.nscal + nfiles + 3;
+  if (s.fields_req ? ac != base + 2 : (ac != base && ac != base + 1)) return usage(s, av[0]);
+
+  int p = 1;
+  const uint32_t nx = std::stoul(av[p++]), ny = std::stoul(av[p++]);
+  const uint32_t nz = s.dim == 3 ? std::stoul(av[p++]) : 1;
+  const double Lx = std::stod(av[p++]), Ly = std::stod(av[p++]);
+  if (s.dim == 3) (void)std::stod(av[p++]); // Lz is parsed but dz is computed from Ly (nlse_cubic_driver_3d.cpp:51)
+  double sc[2] = {0, 0};
+  for (int k = 0; k < s.nscal; ++k) sc[k] = std::stod(av[p++]);
+  const std::string in_u = av[p++];
+  const std::string in_v = is_nlse(s) ? "" : av[p++];
+  const std::string out_u = av[p++];
+  const std::string out_v = is_nlse(s) ? "" : av[p++];
+  const double T = std::stod(av[p++]);
+  const uint32_t nt = std::stoul(av[p++]), ns = std::stoul(av[p++]);
+  const std::string m_file = p < ac ? av[p++] : "";
+  const std::string c_file = p < ac ? av[p++] : "";
+  if (ns == 0 || ns > nt) {
+    std::cerr << "Error: need 0 < num_snapshots <= nt (the reference divides by nt/num_snapshots)\n";
+    return 1;
+  }
+  nls::Grid g;
+  g.nx = nx; g.ny = ny; g.nz = nz;
+  g.dx = 2 * Lx / (nx - 1);
+  g.dy = 2 * Ly / (ny - 1);
+  g.dz = s.dim == 3 ? 2 * Ly / (nz - 1) : 0.0;
+  g.op_sign = s.op_sign;
+  const double dt = T / nt;
+  const uint32_t freq = nt / ns;
+  const size_t n = g.n();
+  std::vector<uint64_t> want = s.dim == 3 ? std::vector<uint64_t>{nz, ny, nx} : std::vector<uint64_t>{ny, nx};
+  std::vector<uint64_t> oshape = want;
+  oshape.insert(oshape.begin(), ns);
+
+  std::vector<double> m(n, s.m_default), c;
+  if (!m_file.empty()) {
+    std::vector<double> mm;
+    bool ok;
+    try { ok = load_checked(m_file, want, mm, "m(x)"); }
+    catch (const std::exception &e) { std::cerr << "Error loading m: " << e.what() << "\n"; throw std::runtime_error("Aborting"); }
+    if (ok) m.swap(mm);
+    else if (s.fields_req) throw std::runtime_error("Faulty m");
+    else { std::cerr << "Using default m=1.0 everywhere\n"; m.assign(n, 1.0); } // nlse_cubic_driver.cpp:69-74
+  }
+  if (!c_file.empty()) {
+    bool ok;
+    try { ok = load_checked(c_file, want, c, "c(x)"); }
+    catch (const std::exception &e) { std::cerr << "Error loading c: " << e.what() << "\n"; throw std::runtime_error("Faulty c"); }
+    if (!ok) throw std::runtime_error("Faulty c");
+    g.c = c.data();
+  }
+
+  const auto t0 = std::chrono::steady_clock::now();
+  if (is_nlse(s)) {
+    std::vector<cplx> u0;
+    if (!load_checked(in_u, want, u0, "Input")) return 1;
+    nls::Handle h(g, s.equation, NLS_INT_SS2, krylov, dt, sc[0], sc[1], sc[0], 1, device);
+    h.set(NLS_FIELD_M, m.data(), n * 8);
+    h.set(NLS_FIELD_U, u0.data(), n * 16);
+    std::vector<cplx> traj((size_t)ns * n);
+    std::copy(u0.begin(), u0.end(), traj.begin());
+    // run up to the next snapshot step in one asynchronous call; same steps, same snapshots
+    for (uint32_t i = 1; i < nt;) {
+      uint32_t next = (i / freq + (i % freq ? 1 : 0)) * freq; // first multiple of freq >= i
+      if (next >= nt) next = nt - 1;
+      h.step(dt, next - i + 1);
+      i = next + 1;
+      if (next % freq == 0 && next / freq < ns) h.get(NLS_FIELD_U, traj.data() + (size_t)(next / freq) * n, n * 16);
+    }
+    h.sync();
+    write_npy(out_u, traj.data(), oshape);
+  } else {
+    std::vector<double> u0, v0;
+    if (!load_checked(in_u, want, u0, "Input") || !load_checked(in_v, want, v0, "Input velocity")) return 1;
+    nls::Handle h(g, s.equation, s.integrator, krylov, dt, 0, 0, 0, 1, device);
+    h.set(NLS_FIELD_M, m.data(), n * 8);
+    h.set(NLS_FIELD_U, u0.data(), n * 8);
+    h.set(NLS_FIELD_V, v0.data(), n * 8);
+    std::vector<double> tu((size_t)ns * n), tv((size_t)ns * n);
+    std::copy(u0.begin(), u0.end(), tu.begin());
+    std::copy(v0.begin(), v0.end(), tv.begin());
+    for (uint32_t i = 1; i < nt;) {
+      uint32_t next = (i / freq + (i % freq ? 1 : 0)) * freq;
+      if (next >= nt) next = nt - 1;
+      h.step(dt, next - i + 1);
+      i = next + 1;
+      if (next % freq == 0 && next / freq < ns) {
+        h.get(NLS_FIELD_U, tu.data() + (size_t)(next / freq) * n, n * 8);
+        h.get(NLS_FIELD_V, tv.data() + (size_t)(next / freq) * n, n * 8);
+      }
+    }
+    h.sync();
+    write_npy(out_u, tu.data(), oshape);
+    write_npy(out_v, tv.data(), oshape);
+  }
+  if (std::getenv("NLS_VERBOSE")) {
+    const double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    std::cerr << s.name << " [" << s.ref << "]: " << (nt - 1) << " steps of " << n << " sites in " << sec
+              << " s (" << (double)n * (nt - 1) / sec << " site-steps/s incl. I/O staging), krylov m=" << krylov << "\n";
+  }
+  return 0;
+}
+
+} // namespace
+
+int main(int argc, char **argv) {
+  std::string self = basename(argv[0]);
+  const Spec *spec = nullptr;
+  for (const Spec &s : kSpecs)
+    if (self == s.name) spec = &s;
+  if (!spec && argc >= 2) { // nls_driver <name> args...
+    for (const Spec &s : kSpecs)
+      if (std::string(argv[1]) == s.name) spec = &s;
+    if (spec) { ++argv; --argc; }
+  }
+  if (!spec) {
+    std::cerr << "nls_driver: unknown driver '" << self << "'. Known drivers:\n";
+    for (const Spec &s : kSpecs) std::cerr << "  " << s.name << "   (" << s.ref << ")\n";
+    return 1;
+  }
+  return run(*spec, argc, argv); // exceptions (unreadable files, CUDA errors) abort like the reference
+}

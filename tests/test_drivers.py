@@ -1,0 +1,153 @@
+"""The reference's driver command lines on the B200 engine.
+
+CPU part: argv contract, usage/exit codes, shape checks, loud failure without a GPU.
+GPU part (-m gpu): whole trajectories written by the CLIs vs the oracle driven through the same
+loop semantics as the reference drivers (nlse_cubic_driver.cpp:96-115, sg_single_driver.cpp:110-124).
+"""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from conftest import rel_l2
+import ics
+import nls_b200
+from nls_b200 import Desc, EQ, INT, LAP, FIELD
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+HOST = os.path.join(ROOT, "nonlinear-solvers_b200", "host")
+BIN = os.path.join(HOST, "bin")
+
+
+@pytest.fixture(scope="module")
+def drivers():
+    nls_b200.build_library()
+    subprocess.run(["make", "-C", HOST, "-s"], check=True)
+    return BIN
+
+
+def run(drivers, name, *args, check=False):
+    return subprocess.run([os.path.join(drivers, name)] + [str(a) for a in args], capture_output=True, text=True,
+                          check=check)
+
+
+def test_usage_on_wrong_argc(drivers):
+    for name in ["nlse_cubic", "nlse_cubic_quintic", "nlse_saturating", "sg_single", "kg_sv", "nlse_3d_dev",
+                 "kg_gautschi_3d_dev", "nlse_2d_dev"]:
+        r = run(drivers, name, 16, 16)
+        assert r.returncode == 1 and "Usage:" in r.stderr, name
+    r = run(drivers, "nls_driver", "no_such_driver")
+    assert r.returncode == 1 and "Known drivers" in r.stderr
+
+
+def test_shape_mismatch_returns_1(drivers, tmp_path):
+    np.save(tmp_path / "u0.npy", np.zeros((8, 9), dtype=np.complex128))
+    r = run(drivers, "nlse_cubic", 16, 16, 5.0, 5.0, tmp_path / "u0.npy", tmp_path / "o.npy", 0.01, 10, 5)
+    assert r.returncode == 1 and "dimensions mismatch" in r.stderr
+
+
+def test_wrong_dtype_aborts(drivers, tmp_path):
+    np.save(tmp_path / "u0.npy", np.zeros((16, 16), dtype=np.float32))
+    r = run(drivers, "nlse_cubic", 16, 16, 5.0, 5.0, tmp_path / "u0.npy", tmp_path / "o.npy", 0.01, 10, 5)
+    assert r.returncode != 0 and "dtype" in r.stderr
+
+
+def test_no_gpu_fails_loudly(drivers, tmp_path):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    np.save(tmp_path / "u0.npy", ics.gaussian_bumps_2d(16, 5.0))
+    r = run(drivers, "nlse_cubic", 16, 16, 5.0, 5.0, tmp_path / "u0.npy", tmp_path / "o.npy", 0.01, 10, 5)
+    assert r.returncode != 0 and not (tmp_path / "o.npy").exists()
+    assert "nls_create" in r.stderr
+
+
+# ------------------------------------------------------------------------------------- GPU
+def oracle_trajectory(oracle_lib, d, u0, v0, m, c, T, nt, ns):
+    """The reference driver loop on the oracle."""
+    dt, freq = T / nt, nt // ns
+    o = oracle_lib.Oracle(d)
+    if c is not None:
+        o.set(FIELD.C, c)
+    o.set(FIELD.M, m)
+    o.set(FIELD.U, u0)
+    if v0 is not None:
+        o.set(FIELD.V, v0)
+    tu = np.zeros((ns,) + u0.shape, dtype=u0.dtype)
+    tv = np.zeros_like(tu)
+    tu[0] = u0
+    if v0 is not None:
+        tv[0] = v0
+    for i in range(1, nt):
+        o.step(dt, 1)
+        if i % freq == 0 and i // freq < ns:
+            tu[i // freq] = o.get()[0]
+            if v0 is not None:
+                tv[i // freq] = o.get(FIELD.V)[0]
+    return tu, tv
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,eq,extra,mdef", [
+    ("nlse_cubic", EQ.NLSE_CUBIC, [], None), ("nlse_cubic", EQ.NLSE_CUBIC, [], 1.0),
+    ("nlse_cubic_quintic", EQ.NLSE_CQ, [1.0, -0.1], 1.0), ("nlse_saturating", EQ.NLSE_SAT, [0.3], 1.0)])
+def test_nlse_cli_trajectory(drivers, oracle_lib, tmp_path, name, eq, extra, mdef):
+    n, L, T, nt, ns = 48, 6.0, 0.05, 50, 10
+    u0 = ics.gaussian_bumps_2d(n, L)
+    np.save(tmp_path / "u0.npy", u0)
+    args = [n, n, L, L] + extra + [tmp_path / "u0.npy", tmp_path / "traj.npy", T, nt, ns]
+    m = np.zeros(n * n)  # driver default m == 0 (nlse_cubic_driver.cpp:63)
+    if mdef is not None:
+        m = np.full(n * n, mdef) * (1 + 0.1 * np.cos(np.arange(n * n)))
+        np.save(tmp_path / "m.npy", m.reshape(n, n))
+        args.append(tmp_path / "m.npy")
+    run(drivers, name, *args, check=True)
+    got = np.load(tmp_path / "traj.npy")
+    assert got.shape == (ns, n, n) and got.dtype == np.complex128
+    s1, s2 = (extra + [0, 0])[:2]
+    d = Desc.make(n, n, L=L, equation=eq, krylov_m=10, s1=s1, s2=s2, kappa=s1)
+    ref, _ = oracle_trajectory(oracle_lib, d, u0, None, m, None, T, nt, ns)
+    assert np.array_equal(got[0], u0)
+    assert rel_l2(got, ref) < 1e-11
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,eq,integ,sign", [
+    ("sg_single", EQ.SGE, INT.GAUTSCHI, 1.0), ("sg_single_sv", EQ.SGE, INT.SV, 1.0), ("kg", EQ.KGE, INT.GAUTSCHI, -1.0),
+    ("kg_sv", EQ.KGE, INT.SV, 1.0), ("phi4", EQ.PHI4, INT.GAUTSCHI, -1.0), ("sg_double", EQ.SGE_DOUBLE, INT.GAUTSCHI, -1.0),
+    ("sg_hyperbolic", EQ.SGE_SINH, INT.GAUTSCHI, -1.0)])
+def test_real_cli_trajectory(drivers, oracle_lib, tmp_path, name, eq, integ, sign):
+    n, L, T, nt, ns = 48, 6.0, 0.2, 40, 8
+    u0 = 0.3 * ics.kink_2d(n, L)
+    v0 = 0.05 * np.cos(u0)
+    np.save(tmp_path / "u0.npy", u0)
+    np.save(tmp_path / "v0.npy", v0)
+    m = 1.0 + 0.2 * np.sin(np.arange(n * n) / 7.0)
+    np.save(tmp_path / "m.npy", m.reshape(n, n))
+    run(drivers, name, n, n, L, L, tmp_path / "u0.npy", tmp_path / "v0.npy", tmp_path / "tu.npy", tmp_path / "tv.npy",
+        T, nt, ns, tmp_path / "m.npy", check=True)
+    d = Desc.make(n, n, L=L, equation=eq, integrator=integ, krylov_m=10, dt=T / nt, op_sign=sign)
+    ru, rv = oracle_trajectory(oracle_lib, d, u0, v0, m, None, T, nt, ns)
+    gu, gv = np.load(tmp_path / "tu.npy"), np.load(tmp_path / "tv.npy")
+    assert gu.shape == (ns, n, n)
+    assert rel_l2(gu, ru) < 1e-11
+    assert rel_l2(gv, rv) < 1e-8  # (u - u_past)/dt amplifies rounding by 1/dt
+
+
+@pytest.mark.gpu
+def test_3d_device_driver_cli(drivers, oracle_lib, tmp_path):
+    n, L, T, nt, ns = 20, 3.0, 0.02, 20, 5
+    u0 = ics.gaussian_bumps_3d(n, L)
+    rng = np.random.default_rng(11)
+    m = np.ones(n ** 3)
+    c = rng.uniform(0.8, 1.2, n ** 3)
+    for nm, a in [("u0", u0), ("m", m.reshape(n, n, n)), ("c", c.reshape(n, n, n))]:
+        np.save(tmp_path / f"{nm}.npy", a)
+    run(drivers, "nlse_3d_dev", n, n, n, L, L, L, tmp_path / "u0.npy", tmp_path / "traj.npy", T, nt, ns,
+        tmp_path / "m.npy", tmp_path / "c.npy", check=True)
+    d = Desc.make(n, n, n, L=L, equation=EQ.NLSE_CUBIC, laplacian=LAP.ANISO, krylov_m=25)
+    ref, _ = oracle_trajectory(oracle_lib, d, u0, None, m, c, T, nt, ns)
+    got = np.load(tmp_path / "traj.npy")
+    assert got.shape == (ns, n, n, n)
+    assert rel_l2(got, ref) < 1e-11
