@@ -129,7 +129,8 @@ typedef struct nls_desc {
 } nls_desc;
 
 enum {
-  NLS_FLAG_NO_GRAPH = 1u /* launch kernels directly instead of replaying a CUDA graph */
+  NLS_FLAG_NO_GRAPH = 1u, /* launch kernels directly instead of replaying a CUDA graph */
+  NLS_FLAG_NO_PERSISTENT = 2u /* never use the persistent cooperative step kernel */
 };
 
 const char *nls_last_error(void);

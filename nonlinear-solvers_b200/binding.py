@@ -25,6 +25,7 @@ FN = SimpleNamespace(EXP=0, SINC=1, COS_SQRT=2, SINC2_SQRT=3, ID_SQRT=4, SINC2_H
 FIELD = SimpleNamespace(U=0, U_PAST=1, V=2, M=3, C=4)
 RED = SimpleNamespace(MASS=0, NONFINITE=1)
 FLAG_NO_GRAPH = 1
+FLAG_NO_PERSISTENT = 2
 
 
 class NlsError(RuntimeError):

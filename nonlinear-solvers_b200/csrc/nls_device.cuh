@@ -68,9 +68,11 @@ struct Geom {
 
 // y = (L x)(idx) for one site.  x points at local site 0 (ghost planes, if any, sit at
 // negative indices / beyond n).  cf (ANISO only) is laid out like x.
-template <class S, bool ANISO>
-__device__ __forceinline__ S stencil_site(const Geom &g, const S *__restrict__ x,
-                                          const double *__restrict__ cf, long long idx, double pre) {
+// x is any callable long long -> S (global pointer, or the shared-memory tile of the persistent
+// kernel); it is only evaluated at neighbours that exist.
+template <class S, bool ANISO, class X>
+__device__ __forceinline__ S stencil_site_f(const Geom &g, X x, const double *__restrict__ cf,
+                                            long long idx, double pre) {
   using T = Sc<S>;
   const long long gi = idx + g.goff;
   const unsigned ugi = (unsigned)gi;
@@ -81,7 +83,7 @@ __device__ __forceinline__ S stencil_site(const Geom &g, const S *__restrict__ x
   const bool has_yp = gi + g.nx < g.nglob;
   const bool has_zm = g.dim3 && gi >= g.plane;     // :145
   const bool has_zp = g.dim3 && gi + g.plane < g.nglob;
-  const S xc = T::mulr(x[idx], pre);
+  const S xc = T::mulr(x(idx), pre);
   S acc = T::zero();
   if (!ANISO) {
     double dg;
@@ -97,13 +99,13 @@ __device__ __forceinline__ S stencil_site(const Geom &g, const S *__restrict__ x
       dg = face ? -5.0 : -6.0; // :124-127
     }
     // accumulate in increasing column order, like the CSC product of the reference
-    if (has_zm) acc = T::fma_r(g.sc, T::mulr(x[idx - g.plane], pre), acc);
-    if (has_ym) acc = T::fma_r(g.sc, T::mulr(x[idx - g.nx], pre), acc);
-    if (has_xm) acc = T::fma_r(g.sc, T::mulr(x[idx - 1], pre), acc);
+    if (has_zm) acc = T::fma_r(g.sc, T::mulr(x(idx - g.plane), pre), acc);
+    if (has_ym) acc = T::fma_r(g.sc, T::mulr(x(idx - g.nx), pre), acc);
+    if (has_xm) acc = T::fma_r(g.sc, T::mulr(x(idx - 1), pre), acc);
     acc = T::fma_r(dg * g.sc, xc, acc);
-    if (has_xp) acc = T::fma_r(g.sc, T::mulr(x[idx + 1], pre), acc);
-    if (has_yp) acc = T::fma_r(g.sc, T::mulr(x[idx + g.nx], pre), acc);
-    if (has_zp) acc = T::fma_r(g.sc, T::mulr(x[idx + g.plane], pre), acc);
+    if (has_xp) acc = T::fma_r(g.sc, T::mulr(x(idx + 1), pre), acc);
+    if (has_yp) acc = T::fma_r(g.sc, T::mulr(x(idx + g.nx), pre), acc);
+    if (has_zp) acc = T::fma_r(g.sc, T::mulr(x(idx + g.plane), pre), acc);
   } else {
     const double cc = cf[idx];
     // weights (c_a + c_b)/2 and the diagonal sum in the reference's accumulation order:
@@ -121,15 +123,25 @@ __device__ __forceinline__ S stencil_site(const Geom &g, const S *__restrict__ x
     if (has_yp) ds += wyp;
     if (has_zm) ds += wzm;
     if (has_zp) ds += wzp;
-    if (has_zm) acc = T::fma_r(wzm * g.sc, T::mulr(x[idx - g.plane], pre), acc);
-    if (has_ym) acc = T::fma_r(wym * g.sc, T::mulr(x[idx - g.nx], pre), acc);
-    if (has_xm) acc = T::fma_r(wxm * g.sc, T::mulr(x[idx - 1], pre), acc);
+    if (has_zm) acc = T::fma_r(wzm * g.sc, T::mulr(x(idx - g.plane), pre), acc);
+    if (has_ym) acc = T::fma_r(wym * g.sc, T::mulr(x(idx - g.nx), pre), acc);
+    if (has_xm) acc = T::fma_r(wxm * g.sc, T::mulr(x(idx - 1), pre), acc);
     acc = T::fma_r(-ds * g.sc, xc, acc);
-    if (has_xp) acc = T::fma_r(wxp * g.sc, T::mulr(x[idx + 1], pre), acc);
-    if (has_yp) acc = T::fma_r(wyp * g.sc, T::mulr(x[idx + g.nx], pre), acc);
-    if (has_zp) acc = T::fma_r(wzp * g.sc, T::mulr(x[idx + g.plane], pre), acc);
+    if (has_xp) acc = T::fma_r(wxp * g.sc, T::mulr(x(idx + 1), pre), acc);
+    if (has_yp) acc = T::fma_r(wyp * g.sc, T::mulr(x(idx + g.nx), pre), acc);
+    if (has_zp) acc = T::fma_r(wzp * g.sc, T::mulr(x(idx + g.plane), pre), acc);
   }
   return acc;
+}
+
+template <class S> struct GlobalFetch {
+  const S *__restrict__ p;
+  __device__ __forceinline__ S operator()(long long i) const { return p[i]; }
+};
+template <class S, bool ANISO>
+__device__ __forceinline__ S stencil_site(const Geom &g, const S *__restrict__ x,
+                                          const double *__restrict__ cf, long long idx, double pre) {
+  return stencil_site_f<S, ANISO>(g, GlobalFetch<S>{x}, cf, idx, pre);
 }
 
 // clamp a local flat index onto the interior: the fused form of neumann_bc_no_velocity

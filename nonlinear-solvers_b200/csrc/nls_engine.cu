@@ -1,7 +1,7 @@
 // nls_engine.cu -- host side of libnls_b200.so: the C ABI of include/nls.h.
 // Owns device memory, one stream per handle, CUDA-graph capture of a whole time step.
 // No CPU fallback anywhere: without a CUDA device every entry point returns NLS_ERR_CUDA.
-#include "nls_kernels.cuh"
+#include "nls_persist.cuh"
 
 #include <cmath>
 #include <cstdio>
@@ -60,6 +60,14 @@ struct nls_engine {
   uint64_t launches = 0;
   bool capturing = false;
   uint64_t cap_count = 0;
+  // persistent cooperative kernel (nls_persist.cuh)
+  bool pk_ok = false;
+  int pk_ncta = 0;
+  long long pk_csz = 0;
+  size_t pk_smem = 0;
+  double *pk_part = nullptr;
+  unsigned *pk_bar = nullptr;
+  uint64_t pk_launches = 0;
   // slabs
   nls_allreduce_fn allreduce = nullptr;
   void *allreduce_user = nullptr;
@@ -247,7 +255,11 @@ int ensure_start(nls_engine *e, double dt) {
   return NLS_OK;
 }
 
+int run_steps_pk(nls_engine *e, double dt, uint32_t nsteps);
+
 int run_steps(nls_engine *e, double dt, uint32_t nsteps) {
+  if (nsteps == 0) return NLS_OK;
+  if (e->pk_ok) return run_steps_pk(e, dt, nsteps);
   int rc = ensure_start(e, dt);
   if (rc) return rc;
   const bool use_graph = !(e->d.flags & NLS_FLAG_NO_GRAPH);
@@ -279,6 +291,75 @@ int run_steps(nls_engine *e, double dt, uint32_t nsteps) {
     }
     e->phase = (p + 1) % e->nphase;
   }
+  return NLS_OK;
+}
+
+// ---- persistent path: one cooperative launch advances nsteps steps
+void pk_setup(nls_engine *e) {
+  const nls_desc &d = e->d;
+  e->pk_ok = false;
+  if (d.flags & NLS_FLAG_NO_PERSISTENT) return;
+  if (e->batch != 1 || e->g.halo != 0 || d.reorth != NLS_REORTH_FULL) return;
+  if (d.integrator != NLS_INT_SS2 && d.integrator != NLS_INT_GAUTSCHI) return;
+  int dev = d.device, nsm = 0, smem_max = 0, coop = 0;
+  cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev);
+  cudaDeviceGetAttribute(&smem_max, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+  cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
+  if (!coop || nsm <= 0 || nsm > kPkPartStride) return;
+  long long csz = (e->g.n + nsm - 1) / nsm;
+  if (csz < 64) csz = 64;
+  const int ncta = (int)((e->g.n + csz - 1) / csz);
+  const size_t smem = pk_smem_bytes(e->esz, csz, e->g.nx, e->m);
+  if (smem > (size_t)smem_max) return;
+  const bool an = d.laplacian == NLS_LAP_ANISO;
+  const void *fn = e->cplx ? (an ? (const void *)k_pk_nlse<true> : (const void *)k_pk_nlse<false>)
+                           : (an ? (const void *)k_pk_gautschi<true> : (const void *)k_pk_gautschi<false>);
+  if (cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) {
+    cudaGetLastError();
+    return;
+  }
+  int occ = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn, kPkThreads, smem) != cudaSuccess || occ < 1) {
+    cudaGetLastError();
+    return;
+  }
+  if (cudaMalloc((void **)&e->pk_part, (size_t)2 * kPkMaxK * kPkPartStride * 8) != cudaSuccess) return;
+  if (cudaMalloc((void **)&e->pk_bar, 16) != cudaSuccess) return;
+  cudaMemset(e->pk_part, 0, (size_t)2 * kPkMaxK * kPkPartStride * 8);
+  e->pk_ncta = ncta;
+  e->pk_csz = csz;
+  e->pk_smem = smem;
+  e->pk_ok = true;
+}
+
+int run_steps_pk(nls_engine *e, double dt, uint32_t nsteps) {
+  PkArgs a;
+  a.g = e->g;
+  a.m = e->m; a.eq = e->d.equation; a.integ = e->d.integrator;
+  a.aniso = e->d.laplacian == NLS_LAP_ANISO;
+  a.nsteps = (int)nsteps; a.ncta = e->pk_ncta; a.csz = e->pk_csz;
+  a.dt = dt; a.s1 = e->d.s1; a.s2 = e->d.s2; a.kappa = e->d.kappa;
+  a.V = e->V; a.colstride = e->colstride;
+  a.acc = e->acc; a.mf = e->mf; a.cf = e->cf;
+  a.part = e->pk_part; a.bar = e->pk_bar; a.status = e->status;
+  CU(cudaMemsetAsync(e->pk_bar, 0, 16, e->stream));
+  const bool an = a.aniso;
+  if (e->cplx) {
+    a.u0 = e->u[e->phase]; a.u1 = e->u[1 - e->phase];
+    double2 *sv0 = (double2 *)e->w0, *sv1 = (double2 *)e->wbuf[0];
+    void *args[] = {&a, &sv0, &sv1};
+    const void *fn = an ? (const void *)k_pk_nlse<true> : (const void *)k_pk_nlse<false>;
+    CU(cudaLaunchCooperativeKernel(fn, dim3(a.ncta), dim3(kPkThreads), args, e->pk_smem, e->stream));
+    e->phase = (e->phase + (int)(nsteps & 1u)) & 1;
+  } else {
+    a.u0 = e->u[0]; a.u1 = e->u[1];
+    double *gb = (double *)e->w0;
+    void *args[] = {&a, &gb};
+    const void *fn = an ? (const void *)k_pk_gautschi<true> : (const void *)k_pk_gautschi<false>;
+    CU(cudaLaunchCooperativeKernel(fn, dim3(a.ncta), dim3(kPkThreads), args, e->pk_smem, e->stream));
+  }
+  e->launches += 1;
+  e->start_valid = false; // the multi-kernel path's start vector / norms are stale now
   return NLS_OK;
 }
 
@@ -337,7 +418,8 @@ int nls_destroy(nls_handle e) {
   for (auto &ge : e->gexec)
     if (ge) cudaGraphExecDestroy(ge);
   void *ptrs[] = {e->V, e->wbuf[0], e->wbuf[1], e->w0, e->u[0], e->u[1], e->u[2], e->acc, e->mf, e->cf,
-                  e->scalA, e->scalB, e->coef, e->redout, e->rc.partials, e->rc.tickets, e->status};
+                  e->scalA, e->scalB, e->coef, e->redout, e->rc.partials, e->rc.tickets, e->status,
+                  e->pk_part, e->pk_bar};
   for (void *p : ptrs)
     if (p) cudaFree(p);
   if (e->stream) cudaStreamDestroy(e->stream);
@@ -419,6 +501,7 @@ int nls_create(const nls_desc *desc, nls_handle *out) {
     ok = cudaMemcpy(e->cf, ones.data(), g.stride * 8, cudaMemcpyHostToDevice) == cudaSuccess;
   }
   ok = ok && cudaDeviceSynchronize() == cudaSuccess;
+  if (ok) pk_setup(e);
   if (!ok) {
     std::string msg = std::string("allocation failed: ") + cudaGetErrorString(cudaGetLastError());
     nls_destroy(e);

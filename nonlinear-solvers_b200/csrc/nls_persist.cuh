@@ -1,0 +1,613 @@
+// nls_persist.cuh -- the persistent cooperative time-stepping kernel ("pk").
+//
+// One launch advances a trajectory by `nsteps` whole time steps.  One CTA per SM, each CTA owns
+// one contiguous chunk of the flat site index for the entire launch:
+//   * the working vector of the Lanczos process (w) and the stencil input tile with its +-nx
+//     halo rows live in shared memory across phases (never re-read from HBM),
+//   * basis columns are kept UN-normalised in global memory (column i = w_i, v_i = w_i/beta_i;
+//     the 1/beta_i factors are folded into the scalar coefficients), so a column is written
+//     exactly once and a chunk's columns are only ever re-read by the CTA that wrote them,
+//   * the two global reductions of a Lanczos iteration (h = V^H w, ||w||^2) are grid barriers
+//     through one L2 counter; every CTA sums the per-CTA partials in the same fixed order, so
+//     all CTAs hold bit-identical scalars and T never leaves the chip,
+//   * the m x m tridiagonal eigensolve runs redundantly in warp 0 of every CTA (no broadcast),
+//   * the basis recombination, the pointwise nonlinear step, the no-flux boundary copy and the
+//     next step's start vector + norm are the tail phase of the same kernel.
+// Reference semantics: nlsolvers/host/include/eigen_krylov_{complex,real}.hpp (Lanczos and the
+// function tables), nlse_*_solver.hpp / sg_single_solver.hpp / kg_solver.hpp (steps),
+// boundaries.hpp:40-57 (boundary copy).  Same results as the multi-kernel path of
+// nls_kernels.cuh up to re-orthogonalisation rounding (one block Gram-Schmidt pass including
+// the alpha term, instead of alpha step + block pass).
+#pragma once
+#include "nls_kernels.cuh"
+
+namespace nls {
+
+constexpr int kPkThreads = 512;
+constexpr int kPkWarps = kPkThreads / 32;
+constexpr int kPkMaxK = 2 * kMaxM + 2;   // doubles per reduction (complex h for up to kMaxM columns)
+constexpr int kPkNV = 8;                 // columns per unrolled group
+constexpr int kPkPartStride = 160;       // >= max CTAs, padded
+
+struct PkArgs {
+  Geom g;
+  int m, eq, integ, aniso, nsteps, ncta;
+  long long csz;       // sites per chunk (chunk c = sites [c*csz, min((c+1)*csz, n)))
+  double dt, s1, s2, kappa;
+  void *V;             // m columns; column i at V + i*colstride (scalars)
+  size_t colstride;
+  void *u0, *u1;       // NLSE: u ping-pong (u0 current at entry); real: u0 = u, u1 = u_past
+  void *acc;           // Gautschi accumulator 2 cos(.)u - u_past
+  const double *mf, *cf;
+  double *part;        // [2][kPkMaxK][kPkPartStride] per-CTA partial sums
+  unsigned *bar;       // [0] arrival counter, [1] abort flag   (zeroed before every launch)
+  int *status;
+};
+
+// ---------------------------------------------------------------- grid barrier
+struct GridSync {
+  unsigned *ctr;
+  unsigned target; // arrivals expected at the next barrier
+  unsigned ncta;
+  int slot;        // parity of the barrier count: which partial-sum slot is live
+};
+
+__device__ __forceinline__ unsigned ld_acquire_u32(const unsigned *p) {
+  unsigned v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void red_release_add_u32(unsigned *p, unsigned v) {
+  asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+// All CTAs are co-resident (cooperative launch).  Returns false if the barrier timed out or
+// another CTA raised the abort flag (the kernel then unwinds instead of hanging the GPU).
+__device__ __forceinline__ bool grid_barrier(GridSync &gs) {
+  __shared__ int s_ok;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    gs.target += gs.ncta;
+    red_release_add_u32(gs.ctr, 1u);
+    int ok = 1;
+    const long long t0 = clock64();
+    while (ld_acquire_u32(gs.ctr) < gs.target) {
+      if (clock64() - t0 > 4000000000LL || ld_acquire_u32(gs.ctr + 1) != 0u) { // ~2 s
+        atomicExch(gs.ctr + 1, 1u);
+        ok = 0;
+        break;
+      }
+    }
+    s_ok = ok;
+  } else {
+    gs.target += gs.ncta;
+  }
+  gs.slot ^= 1;
+  __syncthreads();
+  return s_ok != 0;
+}
+
+// CTA-level partial sums: acc[K] per thread -> one value per CTA in part[slot][k][cta].
+// Must be followed by grid_barrier and then pk_gather.
+template <int K>
+__device__ __forceinline__ void pk_publish(double (&acc)[K], double *part, int slot, double (*s_red)[kPkWarps], int koff = 0) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int k = 0; k < K; ++k) {
+    double v = acc[k];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+    if (lane == 0) s_red[k][warp] = v;
+  }
+  __syncthreads();
+  if (threadIdx.x < K) {
+    double v = 0.0;
+#pragma unroll
+    for (int w = 0; w < kPkWarps; ++w) v += s_red[threadIdx.x][w];
+    part[((size_t)slot * kPkMaxK + koff + threadIdx.x) * kPkPartStride + blockIdx.x] = v;
+  }
+  __syncthreads(); // s_red may be reused by the next publish
+}
+
+// after the barrier: every CTA sums the partials of all CTAs in the same order -> s_out[k]
+__device__ __forceinline__ void pk_gather(int K, const double *part, int slot, int ncta, double *s_out) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int k = warp; k < K; k += kPkWarps) {
+    const double *p = part + ((size_t)slot * kPkMaxK + k) * kPkPartStride;
+    double v = 0.0;
+    for (int c = lane; c < ncta; c += 32) v += __ldcg(p + c);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if (lane == 0) s_out[k] = v;
+  }
+  __syncthreads();
+}
+
+// ---------------------------------------------------------------- in-kernel tridiagonal solve
+// One warp.  Implicit-shift QL on (d, e); the rotation scalars are computed redundantly by all
+// lanes from a lane-private copy of d/e (shared memory, [index][lane] layout -> conflict-free,
+// no warp synchronisation), eigenvector rows are distributed over the lanes.
+// Output: co[2*i], co[2*i+1] = (beta0 * Q f(t Lambda) Q^T e1)_i * colscale_i for nfn functions.
+struct PkTri {
+  double *d;  // [m][32]   lane-private copies
+  double *e;  // [m][32]
+  double *Z;  // [m][ldz]  eigenvector rows
+  int ldz;
+};
+
+__device__ __forceinline__ bool pk_tridiag_warp(PkTri &T, int m) {
+  const int lane = threadIdx.x & 31;
+#define D(i) T.d[(i) * 32 + lane]
+#define E(i) T.e[(i) * 32 + lane]
+  bool ok = true;
+  for (int l = 0; l < m && ok; ++l) {
+    int iter = 0, mm;
+    do {
+      for (mm = l; mm < m - 1; ++mm) {
+        const double dd = fabs(D(mm)) + fabs(D(mm + 1));
+        if (fabs(E(mm)) <= 2.220446049250313e-16 * dd) break;
+      }
+      if (mm != l) {
+        if (iter++ == 60) { ok = false; break; }
+        double g = (D(l + 1) - D(l)) / (2.0 * E(l));
+        double r = sqrt(fma(g, g, 1.0));
+        g = D(mm) - D(l) + E(l) / (g + copysign(r, g));
+        double s = 1.0, c = 1.0, p = 0.0;
+        int i;
+        bool early = false;
+        for (i = mm - 1; i >= l; --i) {
+          double f = s * E(i);
+          const double b = c * E(i);
+          r = sqrt(fma(f, f, g * g));
+          E(i + 1) = r;
+          if (r == 0.0) {
+            D(i + 1) -= p;
+            E(mm) = 0.0;
+            early = true;
+            break;
+          }
+          const double ir = 1.0 / r;
+          s = f * ir;
+          c = g * ir;
+          g = D(i + 1) - p;
+          r = (D(i) - g) * s + 2.0 * c * b;
+          p = s * r;
+          D(i + 1) = g + p;
+          g = c * r - b;
+          for (int k = lane; k < m; k += 32) { // rotate columns i, i+1 of Z (rows over lanes)
+            double *zr = T.Z + k * T.ldz + i;
+            const double z1 = zr[1], z0 = zr[0];
+            zr[1] = s * z0 + c * z1;
+            zr[0] = c * z0 - s * z1;
+          }
+        }
+        if (early) continue;
+        D(l) -= p;
+        E(l) = g;
+        E(mm) = 0.0;
+      }
+    } while (mm != l);
+  }
+#undef D
+#undef E
+  return ok;
+}
+
+
+// ---------------------------------------------------------------- shared-memory context
+template <class S> struct PkCtx {
+  S *X;               // stencil tile: sites [s0 - nx, s0 + csz + nx)
+  S *Wt;              // w tile: sites [s0, s0 + csz)
+  PkTri tri;
+  double (*red)[kPkWarps]; // [2*kPkNV + 2][kPkWarps]
+  double *vals;       // [kPkMaxK] gathered sums
+  double *alpha;      // [kMaxM]   T(j,j)
+  double *nrm2;       // [kMaxM+1] nrm2[0] = ||start||^2, nrm2[j+1] = ||w_j||^2
+  double *coef;       // [2][2*kMaxM] complex coefficients (two function sets)
+  S *gco;             // [kMaxM] re-orthogonalisation coefficients of the current iteration
+  long long s0, cnt;  // first owned site, number of owned sites (may be 0)
+};
+
+// tile fetch: shared memory inside [lo, hi), otherwise the global column (z-neighbours)
+template <class S> struct TileFetch {
+  const S *X;
+  const S *col;
+  long long lo, hi;
+  __device__ __forceinline__ S operator()(long long i) const {
+    if (i >= lo && i < hi) return X[i - lo];
+    return __ldcg(col + i);
+  }
+};
+
+template <class S> __device__ __forceinline__ S pk_ldcg(const S *p) { return __ldcg(p); }
+
+// column i of the Krylov basis: i == 0 is the start-vector buffer, i >= 1 lives in V
+template <class S>
+__device__ __forceinline__ S *pk_col(const PkArgs &a, S *start, int i) {
+  return i == 0 ? start : (S *)a.V + (size_t)(i - 1) * a.colstride;
+}
+
+// load the +-nx halo rows of column `col` into the X tile (after a grid barrier)
+template <class S>
+__device__ __forceinline__ void pk_load_halo(const PkArgs &a, PkCtx<S> &c, const S *col) {
+  const int nx = a.g.nx;
+  if (c.cnt > 0) {
+    for (int t = threadIdx.x; t < 2 * nx; t += kPkThreads) {
+      const bool up = t >= nx;
+      const long long idx = up ? c.s0 + c.cnt + (t - nx) : c.s0 - nx + t;
+      const long long xi = up ? nx + c.cnt + (t - nx) : t;
+      if (idx >= 0 && idx < a.g.n) c.X[xi] = __ldcg(col + idx);
+    }
+  }
+  __syncthreads();
+}
+
+// ---------------------------------------------------------------- one Lanczos run
+// On entry: X centre holds the start vector's owned sites, nrm2[0] = ||start||^2 (gathered),
+// the start vector is complete in global memory (a barrier has passed since it was written).
+// On exit: columns 0..m-1 complete in global memory, alpha[0..m-2], nrm2[0..m-1] in shared.
+template <class S, bool ANISO>
+__device__ bool pk_lanczos(const PkArgs &a, PkCtx<S> &c, GridSync &gs, S *start) {
+  using T = Sc<S>;
+  constexpr int W = T::W;
+  const Geom &g = a.g;
+  const int nx = g.nx;
+  const double *cb = ANISO ? a.cf : nullptr;
+  for (int j = 0; j < a.m - 1; ++j) {
+    S *colj = pk_col<S>(a, start, j);
+    const S *colm = j > 0 ? pk_col<S>(a, start, j - 1) : nullptr;
+    S *coln = pk_col<S>(a, start, j + 1);
+    pk_load_halo<S>(a, c, colj);
+    const double bj = sqrt(c.nrm2[j]);
+    const double inv_bj = 1.0 / bj;
+    const double cm = j > 0 ? -bj / sqrt(c.nrm2[j - 1]) : 0.0; // -beta_j * (1/beta_{j-1})
+    TileFetch<S> xf{c.X, colj, c.s0 - nx, c.s0 + c.cnt + nx};
+    // ---- phase A: w = L v_j - beta_j v_{j-1};  sums_i = w_i^H w for i <= j
+    const int nprev = j; // columns 0..j-1 come from global memory, column j from the X tile
+    for (int i0 = 0; i0 == 0 || i0 < nprev; i0 += kPkNV) {
+      double acc[kPkNV * W];
+      double accA[W];
+#pragma unroll
+      for (int k = 0; k < kPkNV * W; ++k) acc[k] = 0.0;
+#pragma unroll
+      for (int k = 0; k < W; ++k) accA[k] = 0.0;
+      const int cntc = min(kPkNV, nprev - i0);
+#pragma unroll 2
+      for (long long li = threadIdx.x; li < c.cnt; li += kPkThreads) {
+        const long long idx = c.s0 + li;
+        S w;
+        if (i0 == 0) {
+          w = T::mulr(stencil_site_f<S, ANISO>(g, xf, cb, idx, 1.0), inv_bj);
+          if (j > 0) w = T::fma_r(cm, __ldcg(colm + idx), w);
+          c.Wt[li] = w;
+          T::dot_acc(accA, c.X[li + nx], w);
+        } else {
+          w = c.Wt[li];
+        }
+#pragma unroll
+        for (int i = 0; i < kPkNV; ++i)
+          if (i < cntc) T::dot_acc(acc + i * W, __ldcg(pk_col<S>(a, start, i0 + i) + idx), w);
+      }
+      pk_publish<kPkNV * W>(acc, a.part, gs.slot, c.red, i0 * W);
+      if (i0 == 0) pk_publish<W>(accA, a.part, gs.slot, c.red, j * W);
+    }
+    if (!grid_barrier(gs)) return false;
+    pk_gather((j + 1) * W, a.part, gs.slot ^ 1, a.ncta, c.vals);
+    // h_i = sums_i / beta_i ; w -= h_i v_i = (sums_i / beta_i^2) w_i ; alpha = h_j
+    if (threadIdx.x <= j) {
+      const int i = threadIdx.x;
+      const double ib2 = 1.0 / c.nrm2[i];
+      c.gco[i] = T::mulr(T::from(c.vals + i * W), ib2);
+      if (i == j) c.alpha[j] = c.vals[j * W] * inv_bj; // T(j,j) = Re(v_j^H w) = Re(sums_j)/beta_j
+    }
+    __syncthreads();
+    // ---- phase B: w -= sum_i g_i w_i ; ||w||^2 ; w -> column j+1 (global) and X centre
+    {
+      double nrm[1] = {0.0};
+      const S gj = c.gco[j];
+#pragma unroll 2
+      for (long long li = threadIdx.x; li < c.cnt; li += kPkThreads) {
+        const long long idx = c.s0 + li;
+        S w = c.Wt[li];
+        for (int i0 = 0; i0 < nprev; i0 += kPkNV) {
+          S v[kPkNV];
+#pragma unroll
+          for (int i = 0; i < kPkNV; ++i)
+            if (i0 + i < nprev) v[i] = __ldcg(pk_col<S>(a, start, i0 + i) + idx);
+#pragma unroll
+          for (int i = 0; i < kPkNV; ++i)
+            if (i0 + i < nprev) w = T::sub(w, T::mul(c.gco[i0 + i], v[i]));
+        }
+        w = T::sub(w, T::mul(gj, c.X[li + nx]));
+        nrm[0] += T::abs2(w);
+        coln[idx] = w;
+        c.X[li + nx] = w;
+      }
+      pk_publish<1>(nrm, a.part, gs.slot, c.red, 0);
+    }
+    if (!grid_barrier(gs)) return false;
+    pk_gather(1, a.part, gs.slot ^ 1, a.ncta, c.vals);
+    if (threadIdx.x == 0) c.nrm2[j + 1] = c.vals[0];
+    __syncthreads();
+  }
+  return true;
+}
+
+// warp 0: eigen-decomposition of T and the coefficient vectors
+//   co_f[i] = beta_0 * (Q f(t Lambda) Q^T e_1)_i / beta_i      (columns are un-normalised)
+template <class S>
+__device__ __forceinline__ void pk_coefficients(const PkArgs &a, PkCtx<S> &c, int nfn, int f0, double t0r,
+                                                double t0i, int f1, double t1r, double t1i) {
+  const int m = a.m;
+  if (threadIdx.x < 32) {
+    const int lane = threadIdx.x;
+    PkTri &T = c.tri;
+    for (int i = 0; i < m; ++i) {
+      T.d[i * 32 + lane] = i < m - 1 ? c.alpha[i] : 0.0; // T(m-1,m-1) = 0
+      T.e[i * 32 + lane] = i < m - 1 ? sqrt(c.nrm2[i + 1]) : 0.0;
+    }
+    for (int i = lane; i < m; i += 32)
+      for (int k = 0; k < m; ++k) T.Z[i * T.ldz + k] = i == k ? 1.0 : 0.0;
+    __syncwarp();
+    const bool ok = pk_tridiag_warp(T, m);
+    __syncwarp();
+    if (!ok && lane == 0) atomicExch(a.status, 1);
+    const double beta0 = sqrt(c.nrm2[0]);
+    for (int f = 0; f < nfn; ++f) {
+      const int fn = f ? f1 : f0;
+      const double tr = f ? t1r : t0r, ti = f ? t1i : t0i;
+      double *co = c.coef + f * 2 * kMaxM;
+      __syncwarp();
+      for (int k = lane; k < m; k += 32) { // f(t lambda_k) -> e[k][0..1] (e is free after QL)
+        const double2 fv = fn_eval(fn, tr, ti, T.d[k * 32 + lane]);
+        T.e[k * 32] = fv.x;
+        T.e[k * 32 + 1] = fv.y;
+      }
+      __syncwarp();
+      for (int i = lane; i < m; i += 32) {
+        double sr = 0.0, si = 0.0;
+        for (int k = 0; k < m; ++k) {
+          const double2 fv = make_double2(T.e[k * 32], T.e[k * 32 + 1]);
+          const double zz = T.Z[i * T.ldz + k] * T.Z[k];
+          sr = fma(zz, fv.x, sr);
+          si = fma(zz, fv.y, si);
+        }
+        const double scale = beta0 / sqrt(c.nrm2[i]);
+        co[2 * i] = sr * scale;
+        co[2 * i + 1] = si * scale;
+      }
+    }
+  }
+  __syncthreads();
+}
+
+// y(site) = sum_i co_i * column_i[site]   (any site: columns are complete in global memory)
+template <class S> struct PkCombine;
+template <> struct PkCombine<double> {
+  __device__ static __forceinline__ double eval(const PkArgs &a, const double *start, const double *co, long long site) {
+    double s = 0.0;
+    for (int i0 = 0; i0 < a.m; i0 += kPkNV) {
+      double v[kPkNV];
+#pragma unroll
+      for (int i = 0; i < kPkNV; ++i)
+        if (i0 + i < a.m) v[i] = __ldcg(pk_col<double>(a, (double *)start, i0 + i) + site);
+#pragma unroll
+      for (int i = 0; i < kPkNV; ++i)
+        if (i0 + i < a.m) s = fma(v[i], co[2 * (i0 + i)], s);
+    }
+    return s;
+  }
+  // two coefficient sets in one pass
+  __device__ static __forceinline__ void eval2(const PkArgs &a, const double *start, const double *co0,
+                                               const double *co1, long long site, double &y0, double &y1) {
+    y0 = 0.0;
+    y1 = 0.0;
+    for (int i0 = 0; i0 < a.m; i0 += kPkNV) {
+      double v[kPkNV];
+#pragma unroll
+      for (int i = 0; i < kPkNV; ++i)
+        if (i0 + i < a.m) v[i] = __ldcg(pk_col<double>(a, (double *)start, i0 + i) + site);
+#pragma unroll
+      for (int i = 0; i < kPkNV; ++i)
+        if (i0 + i < a.m) {
+          y0 = fma(v[i], co0[2 * (i0 + i)], y0);
+          y1 = fma(v[i], co1[2 * (i0 + i)], y1);
+        }
+    }
+  }
+};
+template <> struct PkCombine<double2> {
+  __device__ static __forceinline__ double2 eval(const PkArgs &a, const double2 *start, const double *co, long long site) {
+    double2 s = make_double2(0.0, 0.0);
+    for (int i0 = 0; i0 < a.m; i0 += kPkNV) {
+      double2 v[kPkNV];
+#pragma unroll
+      for (int i = 0; i < kPkNV; ++i)
+        if (i0 + i < a.m) v[i] = __ldcg(pk_col<double2>(a, (double2 *)start, i0 + i) + site);
+#pragma unroll
+      for (int i = 0; i < kPkNV; ++i)
+        if (i0 + i < a.m) {
+          const double cr = co[2 * (i0 + i)], ci = co[2 * (i0 + i) + 1];
+          s.x = fma(v[i].x, cr, fma(-v[i].y, ci, s.x));
+          s.y = fma(v[i].x, ci, fma(v[i].y, cr, s.y));
+        }
+    }
+    return s;
+  }
+};
+
+// shared-memory bytes the kernel needs for (n-chunk, nx, m)
+inline size_t pk_smem_bytes(size_t esz, long long csz, int nx, int m) {
+  size_t b = (size_t)(2 * csz + 2 * nx) * esz;          // X + Wt
+  b += (size_t)m * 32 * 8 * 2 + (size_t)m * (m + 1) * 8; // tridiagonal work space
+  b += (size_t)(2 * kPkNV + 2) * kPkWarps * 8;           // red
+  b += (size_t)kPkMaxK * 8 + kMaxM * 8 + (kMaxM + 1) * 8 + 4 * kMaxM * 8 + kMaxM * 16;
+  return b + 64;
+}
+
+template <class S>
+__device__ __forceinline__ void pk_carve(const PkArgs &a, PkCtx<S> &c, unsigned char *smem) {
+  const long long tile = a.csz + 2 * a.g.nx;
+  c.X = (S *)smem;
+  c.Wt = c.X + tile;
+  double *p = (double *)(c.Wt + a.csz);
+  c.tri.d = p; p += a.m * 32;
+  c.tri.e = p; p += a.m * 32;
+  c.tri.Z = p; p += a.m * (a.m + 1);
+  c.tri.ldz = a.m + 1;
+  c.red = (double (*)[kPkWarps])p; p += (2 * kPkNV + 2) * kPkWarps;
+  c.vals = p; p += kPkMaxK;
+  c.alpha = p; p += kMaxM;
+  c.nrm2 = p; p += kMaxM + 1;
+  c.coef = p; p += 4 * kMaxM;
+  c.gco = (S *)(((uintptr_t)p + 15) & ~(uintptr_t)15);
+  c.s0 = (long long)blockIdx.x * a.csz;
+  long long e0 = c.s0 + a.csz;
+  if (e0 > a.g.n) e0 = a.g.n;
+  c.cnt = e0 > c.s0 ? e0 - c.s0 : 0;
+}
+
+// publish ||start||^2, barrier, gather -> nrm2[0]
+template <class S>
+__device__ __forceinline__ bool pk_start_norm(const PkArgs &a, PkCtx<S> &c, GridSync &gs, double (&nrm)[1]) {
+  pk_publish<1>(nrm, a.part, gs.slot, c.red, 0);
+  if (!grid_barrier(gs)) return false;
+  pk_gather(1, a.part, gs.slot ^ 1, a.ncta, c.vals);
+  if (threadIdx.x == 0) c.nrm2[0] = c.vals[0];
+  __syncthreads();
+  return true;
+}
+
+// ---------------------------------------------------------------- NLSE, Strang splitting
+// buffers: u ping-pong (a.u0 current at entry, a.u1), start-vector ping-pong (sv0, sv1)
+template <bool ANISO>
+__global__ void __launch_bounds__(kPkThreads, 1) k_pk_nlse(PkArgs a, double2 *sv0, double2 *sv1) {
+  extern __shared__ __align__(16) unsigned char pk_smem[];
+  PkCtx<double2> c;
+  pk_carve<double2>(a, c, pk_smem);
+  GridSync gs{a.bar, 0u, (unsigned)a.ncta, 0};
+  const int nx = a.g.nx;
+  const NlseParams p{0.5 * a.dt, a.s1, a.s2, a.kappa};
+  double2 *ucur = (double2 *)a.u0, *unext = (double2 *)a.u1;
+  double2 *scur = sv0, *snext = sv1;
+  // start vector of the first step: rho = exp(.5 tau g(u)) u   (nlse_cubic_solver.hpp:62-66)
+  {
+    double nrm[1] = {0.0};
+    for (long long li = threadIdx.x; li < c.cnt; li += kPkThreads) {
+      const long long idx = c.s0 + li;
+      const double2 uv = ucur[idx];
+      double2 r;
+      switch (a.eq) {
+      case NLS_EQ_NLSE_CUBIC: r = nlse_phase<NLS_EQ_NLSE_CUBIC>(p, a.mf[idx], uv, uv, uv); break;
+      case NLS_EQ_NLSE_CQ: r = nlse_phase<NLS_EQ_NLSE_CQ>(p, a.mf[idx], uv, uv, uv); break;
+      default: r = nlse_phase<NLS_EQ_NLSE_SAT>(p, a.mf[idx], uv, uv, uv);
+      }
+      scur[idx] = r;
+      c.X[li + nx] = r;
+      nrm[0] += r.x * r.x + r.y * r.y;
+    }
+    if (!pk_start_norm<double2>(a, c, gs, nrm)) return;
+  }
+  for (int step = 0; step < a.nsteps; ++step) {
+    if (!pk_lanczos<double2, ANISO>(a, c, gs, scur)) return;
+    pk_coefficients<double2>(a, c, 1, NLS_FN_EXP, 0.0, a.dt, 0, 0.0, 0.0); // expm_multiply(L, rho, i dt)
+    double nrm[1] = {0.0};
+#pragma unroll 2
+    for (long long li = threadIdx.x; li < c.cnt; li += kPkThreads) {
+      const long long idx = c.s0 + li;
+      const long long sc = clamp_site(a.g, idx); // fused neumann_bc_no_velocity (boundaries.hpp:40-57)
+      const double2 buf = PkCombine<double2>::eval(a, scur, c.coef, sc);
+      const double mv = a.mf[sc];
+      double2 un;
+      switch (a.eq) {
+      case NLS_EQ_NLSE_CUBIC: un = nlse_phase<NLS_EQ_NLSE_CUBIC>(p, mv, buf, buf, buf); break;
+      case NLS_EQ_NLSE_CQ: un = nlse_phase<NLS_EQ_NLSE_CQ>(p, mv, __ldcg(ucur + sc), buf, buf); break; // old-u density (Q7)
+      default: un = nlse_phase<NLS_EQ_NLSE_SAT>(p, mv, __ldcg(ucur + sc), buf, buf);
+      }
+      unext[idx] = un;
+      double2 r;
+      const double mi = a.mf[idx];
+      switch (a.eq) {
+      case NLS_EQ_NLSE_CUBIC: r = nlse_phase<NLS_EQ_NLSE_CUBIC>(p, mi, un, un, un); break;
+      case NLS_EQ_NLSE_CQ: r = nlse_phase<NLS_EQ_NLSE_CQ>(p, mi, un, un, un); break;
+      default: r = nlse_phase<NLS_EQ_NLSE_SAT>(p, mi, un, un, un);
+      }
+      snext[idx] = r;
+      c.X[li + nx] = r;
+      nrm[0] += r.x * r.x + r.y * r.y;
+    }
+    if (!pk_start_norm<double2>(a, c, gs, nrm)) return;
+    double2 *t = ucur; ucur = unext; unext = t;
+    t = scur; scur = snext; snext = t;
+  }
+}
+
+// ---------------------------------------------------------------- real equations, Gautschi
+// buffers: a.u0 = u (also column 0 of the first Lanczos run), a.u1 = u_past, a.acc, gbuf = start
+// vector of the second run.   sg_single_solver.hpp:43-59, kg_solver.hpp:13-22
+template <bool ANISO>
+__global__ void __launch_bounds__(kPkThreads, 1) k_pk_gautschi(PkArgs a, double *gbuf) {
+  extern __shared__ __align__(16) unsigned char pk_smem[];
+  PkCtx<double> c;
+  pk_carve<double>(a, c, pk_smem);
+  GridSync gs{a.bar, 0u, (unsigned)a.ncta, 0};
+  const int nx = a.g.nx;
+  double *u = (double *)a.u0, *up = (double *)a.u1, *accb = (double *)a.acc;
+  const int filt = a.eq == NLS_EQ_SGE ? NLS_FN_MOD_COSINE : NLS_FN_ID_SQRT;
+  const double tau2 = a.dt * a.dt;
+  {
+    double nrm[1] = {0.0};
+    for (long long li = threadIdx.x; li < c.cnt; li += kPkThreads) {
+      const double v = u[c.s0 + li];
+      c.X[li + nx] = v;
+      nrm[0] += v * v;
+    }
+    if (!pk_start_norm<double>(a, c, gs, nrm)) return;
+  }
+  for (int step = 0; step < a.nsteps; ++step) {
+    if (!pk_lanczos<double, ANISO>(a, c, gs, u)) return;
+    pk_coefficients<double>(a, c, 2, filt, a.dt, 0.0, NLS_FN_COS_SQRT, a.dt, 0.0);
+    {
+      double nrm[1] = {0.0};
+#pragma unroll 2
+      for (long long li = threadIdx.x; li < c.cnt; li += kPkThreads) {
+        const long long idx = c.s0 + li;
+        double sf, sc;
+        PkCombine<double>::eval2(a, u, c.coef, c.coef + 2 * kMaxM, idx, sf, sc);
+        double fv;
+        switch (a.eq) {
+        case NLS_EQ_SGE: fv = f_real<NLS_EQ_SGE>(sf); break;
+        case NLS_EQ_KGE: fv = f_real<NLS_EQ_KGE>(sf); break;
+        case NLS_EQ_PHI4: fv = f_real<NLS_EQ_PHI4>(sf); break;
+        case NLS_EQ_SGE_DOUBLE: fv = f_real<NLS_EQ_SGE_DOUBLE>(sf); break;
+        default: fv = f_real<NLS_EQ_SGE_SINH>(sf);
+        }
+        const double gv = -(a.mf[idx] * fv);
+        gbuf[idx] = gv;
+        c.X[li + nx] = gv;
+        nrm[0] += gv * gv;
+        accb[idx] = 2 * sc - __ldcg(up + idx);
+        up[idx] = __ldcg(u + idx);
+      }
+      if (!pk_start_norm<double>(a, c, gs, nrm)) return;
+    }
+    if (!pk_lanczos<double, ANISO>(a, c, gs, gbuf)) return;
+    pk_coefficients<double>(a, c, 1, NLS_FN_SINC2_HALF, a.dt, 0.0, 0, 0.0, 0.0);
+    {
+      double nrm[1] = {0.0};
+#pragma unroll 2
+      for (long long li = threadIdx.x; li < c.cnt; li += kPkThreads) {
+        const long long idx = c.s0 + li;
+        const long long sc = clamp_site(a.g, idx);
+        const double s = PkCombine<double>::eval(a, gbuf, c.coef, sc);
+        const double un = __ldcg(accb + sc) + tau2 * s;
+        u[idx] = un;
+        c.X[li + nx] = un;
+        nrm[0] += un * un;
+      }
+      if (!pk_start_norm<double>(a, c, gs, nrm)) return;
+    }
+  }
+}
+
+} // namespace nls
