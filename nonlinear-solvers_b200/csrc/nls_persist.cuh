@@ -195,9 +195,13 @@ __device__ __forceinline__ bool pk_tridiag_warp(PkTri &T, int m) {
 
 
 // ---------------------------------------------------------------- shared-memory context
+// per-site neighbour flags, computed once per launch (the index divisions leave the hot loops)
+enum { PF_XM = 1, PF_XP = 2, PF_YM = 4, PF_YP = 8, PF_ZM = 16, PF_ZP = 32, PF_RING = 64 };
+
 template <class S> struct PkCtx {
   S *X;               // stencil tile: sites [s0 - nx, s0 + csz + nx)
   S *Wt;              // w tile: sites [s0, s0 + csz)
+  unsigned char *flag; // [csz] PF_* bits of the owned sites
   PkTri tri;
   double (*red)[kPkWarps]; // [2*kPkNV + 2][kPkWarps]
   double *vals;       // [kPkMaxK] gathered sums
@@ -205,26 +209,91 @@ template <class S> struct PkCtx {
   double *nrm2;       // [kMaxM+1] nrm2[0] = ||start||^2, nrm2[j+1] = ||w_j||^2
   double *coef;       // [2][2*kMaxM] complex coefficients (two function sets)
   S *gco;             // [kMaxM] re-orthogonalisation coefficients of the current iteration
-  long long s0, cnt;  // first owned site, number of owned sites (may be 0)
+  long long s0;       // first owned site
+  int cnt;            // number of owned sites (may be 0)
 };
-
-// tile fetch: shared memory inside [lo, hi), otherwise the global column (z-neighbours)
-template <class S> struct TileFetch {
-  const S *X;
-  const S *col;
-  long long lo, hi;
-  __device__ __forceinline__ S operator()(long long i) const {
-    if (i >= lo && i < hi) return X[i - lo];
-    return __ldcg(col + i);
-  }
-};
-
-template <class S> __device__ __forceinline__ S pk_ldcg(const S *p) { return __ldcg(p); }
 
 // column i of the Krylov basis: i == 0 is the start-vector buffer, i >= 1 lives in V
 template <class S>
 __device__ __forceinline__ S *pk_col(const PkArgs &a, S *start, int i) {
   return i == 0 ? start : (S *)a.V + (size_t)(i - 1) * a.colstride;
+}
+
+__device__ __forceinline__ unsigned char pk_site_flags(const Geom &g, long long idx) {
+  const long long gi = idx + g.goff;
+  const unsigned ugi = (unsigned)gi;
+  const unsigned i = ugi % (unsigned)g.nx;
+  const unsigned jj = ugi / (unsigned)g.nx;
+  unsigned f = 0;
+  if (i != 0) f |= PF_XM;                      // laplacians.hpp:33
+  if (i != (unsigned)(g.nx - 1)) f |= PF_XP;
+  if (gi >= g.nx) f |= PF_YM;                  // flat-index test, no plane check (:39, :140)
+  if (gi + g.nx < g.nglob) f |= PF_YP;
+  bool ring;
+  if (g.dim3) {
+    if (gi >= g.plane) f |= PF_ZM;             // :145
+    if (gi + g.plane < g.nglob) f |= PF_ZP;
+    const unsigned j = jj % (unsigned)g.ny, k = jj / (unsigned)g.ny;
+    ring = i == 0 || i == (unsigned)(g.nx - 1) || j == 0 || j == (unsigned)(g.ny - 1) || k == 0 ||
+           k == (unsigned)(g.nz_glob - 1);
+  } else {
+    ring = i == 0 || i == (unsigned)(g.nx - 1) || jj == 0 || jj == (unsigned)(g.ny - 1);
+  }
+  if (ring) f |= PF_RING;
+  return (unsigned char)f;
+}
+
+// (L x)(site li) from the X tile (x/y neighbours) and the global column (z neighbours).
+// Same rows as stencil_site_f (laplacians.hpp:9-218), neighbours gated by the cached flags.
+template <class S, bool ANISO>
+__device__ __forceinline__ S pk_stencil(const Geom &g, const S *__restrict__ xc, const S *__restrict__ colg,
+                                        const double *__restrict__ cfg, unsigned f, int li) {
+  using T = Sc<S>;
+  const int nx = g.nx;
+  const S z = T::zero();
+  const S xm = (f & PF_XM) ? xc[li - 1] : z;
+  const S xp = (f & PF_XP) ? xc[li + 1] : z;
+  const S ym = (f & PF_YM) ? xc[li - nx] : z;
+  const S yp = (f & PF_YP) ? xc[li + nx] : z;
+  S zm = z, zp = z;
+  if (g.dim3) {
+    if (f & PF_ZM) zm = __ldcg(colg + li - g.plane);
+    if (f & PF_ZP) zp = __ldcg(colg + li + g.plane);
+  }
+  S acc = z;
+  if (!ANISO) {
+    const double dg = g.dim3 ? ((f & PF_RING) ? -5.0 : -6.0) : ((f & PF_RING) ? -3.0 : -4.0);
+    acc = T::fma_r(g.sc, zm, acc);
+    acc = T::fma_r(g.sc, ym, acc);
+    acc = T::fma_r(g.sc, xm, acc);
+    acc = T::fma_r(dg * g.sc, xc[li], acc);
+    acc = T::fma_r(g.sc, xp, acc);
+    acc = T::fma_r(g.sc, yp, acc);
+    acc = T::fma_r(g.sc, zp, acc);
+  } else {
+    const double cc = cfg[li];
+    const double wxm = (f & PF_XM) ? (cfg[li - 1] + cc) / 2.0 : 0.0;
+    const double wxp = (f & PF_XP) ? (cc + cfg[li + 1]) / 2.0 : 0.0;
+    const double wym = (f & PF_YM) ? (cfg[li - nx] + cc) / 2.0 : 0.0;
+    const double wyp = (f & PF_YP) ? (cc + cfg[li + nx]) / 2.0 : 0.0;
+    const double wzm = (f & PF_ZM) ? (cfg[li - g.plane] + cc) / 2.0 : 0.0;
+    const double wzp = (f & PF_ZP) ? (cc + cfg[li + g.plane]) / 2.0 : 0.0;
+    double ds = 0.0;
+    if (f & PF_XM) ds += wxm;
+    if (f & PF_XP) ds += wxp;
+    if (f & PF_YM) ds += wym;
+    if (f & PF_YP) ds += wyp;
+    if (f & PF_ZM) ds += wzm;
+    if (f & PF_ZP) ds += wzp;
+    acc = T::fma_r(wzm * g.sc, zm, acc);
+    acc = T::fma_r(wym * g.sc, ym, acc);
+    acc = T::fma_r(wxm * g.sc, xm, acc);
+    acc = T::fma_r(-ds * g.sc, xc[li], acc);
+    acc = T::fma_r(wxp * g.sc, xp, acc);
+    acc = T::fma_r(wyp * g.sc, yp, acc);
+    acc = T::fma_r(wzp * g.sc, zp, acc);
+  }
+  return acc;
 }
 
 // load the +-nx halo rows of column `col` into the X tile (after a grid barrier)
@@ -235,12 +304,117 @@ __device__ __forceinline__ void pk_load_halo(const PkArgs &a, PkCtx<S> &c, const
     for (int t = threadIdx.x; t < 2 * nx; t += kPkThreads) {
       const bool up = t >= nx;
       const long long idx = up ? c.s0 + c.cnt + (t - nx) : c.s0 - nx + t;
-      const long long xi = up ? nx + c.cnt + (t - nx) : t;
+      const int xi = up ? nx + c.cnt + (t - nx) : t;
       if (idx >= 0 && idx < a.g.n) c.X[xi] = __ldcg(col + idx);
     }
   }
   __syncthreads();
 }
+
+// ---------------------------------------------------------------- Lanczos phases
+// Column roles in iteration j: "others" = columns 0..j-2 (groups of <= kPkNV, pointer per
+// column), column j-1 (recurrence term + dot, loaded once), column j (the X tile).
+// Phase A, group of NC other columns starting at i0.  FIRST: also forms w (stencil + recurrence),
+// stores it to the Wt tile and accumulates the j-1 and j dots.
+template <class S, bool ANISO, int NC, bool FIRST>
+__device__ __forceinline__ void pk_phase_a(const PkArgs &a, PkCtx<S> &c, GridSync &gs, S *start, int j, int i0,
+                                           double inv_bj, double cm) {
+  using T = Sc<S>;
+  constexpr int W = T::W;
+  constexpr int NA = NC > 0 ? NC : 1;
+  const S *p[NA];
+#pragma unroll
+  for (int i = 0; i < NC; ++i) p[i] = pk_col<S>(a, start, i0 + i) + c.s0;
+  const S *colj = pk_col<S>(a, start, j) + c.s0;
+  const S *colm = j > 0 ? pk_col<S>(a, start, j - 1) + c.s0 : colj;
+  const double *cfg = ANISO ? a.cf + c.s0 : nullptr;
+  const S *xc = c.X + a.g.nx;
+  double acc[NA * W], accM[W], accA[W];
+#pragma unroll
+  for (int k = 0; k < NA * W; ++k) acc[k] = 0.0;
+#pragma unroll
+  for (int k = 0; k < W; ++k) accM[k] = accA[k] = 0.0;
+#pragma unroll(W == 1 ? 2 : 1)
+  for (int li = threadIdx.x; li < c.cnt; li += kPkThreads) {
+    S v[NA];
+#pragma unroll
+    for (int i = 0; i < NC; ++i) v[i] = __ldcg(p[i] + li);
+    S w;
+    if (FIRST) {
+      S vm = T::zero();
+      if (j > 0) vm = __ldcg(colm + li);
+      w = T::mulr(pk_stencil<S, ANISO>(a.g, xc, colj, cfg, c.flag[li], li), inv_bj);
+      w = T::fma_r(cm, vm, w); // cm == 0 when j == 0
+      c.Wt[li] = w;
+      T::dot_acc(accA, xc[li], w);
+      T::dot_acc(accM, vm, w);
+    } else {
+      w = c.Wt[li];
+    }
+#pragma unroll
+    for (int i = 0; i < NC; ++i) T::dot_acc(acc + i * W, v[i], w);
+  }
+  if (NC > 0) pk_publish<NA * W>(acc, a.part, gs.slot, c.red, i0 * W);
+  if (FIRST) {
+    if (j > 0) pk_publish<W>(accM, a.part, gs.slot, c.red, (j - 1) * W);
+    pk_publish<W>(accA, a.part, gs.slot, c.red, j * W);
+  }
+}
+
+// Phase B, group of NC other columns.  LAST: also subtracts the j-1 and j terms, accumulates
+// ||w||^2 and stores w to column j+1 (global) and to the X tile centre.
+template <class S, int NC, bool LAST>
+__device__ __forceinline__ void pk_phase_b(const PkArgs &a, PkCtx<S> &c, GridSync &gs, S *start, int j, int i0) {
+  using T = Sc<S>;
+  constexpr int W = T::W;
+  constexpr int NA = NC > 0 ? NC : 1;
+  const S *p[NA];
+  S gc[NA];
+#pragma unroll
+  for (int i = 0; i < NC; ++i) {
+    p[i] = pk_col<S>(a, start, i0 + i) + c.s0;
+    gc[i] = c.gco[i0 + i];
+  }
+  const S *colm = j > 0 ? pk_col<S>(a, start, j - 1) + c.s0 : nullptr;
+  S *coln = pk_col<S>(a, start, j + 1) + c.s0;
+  S *xc = c.X + a.g.nx;
+  const S gm = j > 0 ? c.gco[j - 1] : T::zero(), gj = c.gco[j];
+  double nrm[1] = {0.0};
+#pragma unroll(W == 1 ? 2 : 1)
+  for (int li = threadIdx.x; li < c.cnt; li += kPkThreads) {
+    S v[NA];
+#pragma unroll
+    for (int i = 0; i < NC; ++i) v[i] = __ldcg(p[i] + li);
+    S vm = T::zero();
+    if (LAST && j > 0) vm = __ldcg(colm + li);
+    S w = c.Wt[li];
+#pragma unroll
+    for (int i = 0; i < NC; ++i) w = T::sub(w, T::mul(gc[i], v[i]));
+    if (LAST) {
+      w = T::sub(w, T::mul(gm, vm));
+      w = T::sub(w, T::mul(gj, xc[li]));
+      nrm[0] += T::abs2(w);
+      coln[li] = w;
+      xc[li] = w;
+    } else {
+      c.Wt[li] = w;
+    }
+  }
+  if (LAST) pk_publish<1>(nrm, a.part, gs.slot, c.red, 0);
+}
+
+#define PK_SWITCH_NC(nc, CALL)                                                                     \
+  switch (nc) {                                                                                    \
+  case 0: { constexpr int NC = 0; CALL; } break;                                                   \
+  case 1: { constexpr int NC = 1; CALL; } break;                                                   \
+  case 2: { constexpr int NC = 2; CALL; } break;                                                   \
+  case 3: { constexpr int NC = 3; CALL; } break;                                                   \
+  case 4: { constexpr int NC = 4; CALL; } break;                                                   \
+  case 5: { constexpr int NC = 5; CALL; } break;                                                   \
+  case 6: { constexpr int NC = 6; CALL; } break;                                                   \
+  case 7: { constexpr int NC = 7; CALL; } break;                                                   \
+  default: { constexpr int NC = 8; CALL; } break;                                                  \
+  }
 
 // ---------------------------------------------------------------- one Lanczos run
 // On entry: X centre holds the start vector's owned sites, nrm2[0] = ||start||^2 (gathered),
@@ -250,80 +424,35 @@ template <class S, bool ANISO>
 __device__ bool pk_lanczos(const PkArgs &a, PkCtx<S> &c, GridSync &gs, S *start) {
   using T = Sc<S>;
   constexpr int W = T::W;
-  const Geom &g = a.g;
-  const int nx = g.nx;
-  const double *cb = ANISO ? a.cf : nullptr;
   for (int j = 0; j < a.m - 1; ++j) {
-    S *colj = pk_col<S>(a, start, j);
-    const S *colm = j > 0 ? pk_col<S>(a, start, j - 1) : nullptr;
-    S *coln = pk_col<S>(a, start, j + 1);
-    pk_load_halo<S>(a, c, colj);
+    pk_load_halo<S>(a, c, pk_col<S>(a, start, j));
     const double bj = sqrt(c.nrm2[j]);
     const double inv_bj = 1.0 / bj;
     const double cm = j > 0 ? -bj / sqrt(c.nrm2[j - 1]) : 0.0; // -beta_j * (1/beta_{j-1})
-    TileFetch<S> xf{c.X, colj, c.s0 - nx, c.s0 + c.cnt + nx};
+    const int nother = j > 0 ? j - 1 : 0;
     // ---- phase A: w = L v_j - beta_j v_{j-1};  sums_i = w_i^H w for i <= j
-    const int nprev = j; // columns 0..j-1 come from global memory, column j from the X tile
-    for (int i0 = 0; i0 == 0 || i0 < nprev; i0 += kPkNV) {
-      double acc[kPkNV * W];
-      double accA[W];
-#pragma unroll
-      for (int k = 0; k < kPkNV * W; ++k) acc[k] = 0.0;
-#pragma unroll
-      for (int k = 0; k < W; ++k) accA[k] = 0.0;
-      const int cntc = min(kPkNV, nprev - i0);
-#pragma unroll 2
-      for (long long li = threadIdx.x; li < c.cnt; li += kPkThreads) {
-        const long long idx = c.s0 + li;
-        S w;
-        if (i0 == 0) {
-          w = T::mulr(stencil_site_f<S, ANISO>(g, xf, cb, idx, 1.0), inv_bj);
-          if (j > 0) w = T::fma_r(cm, __ldcg(colm + idx), w);
-          c.Wt[li] = w;
-          T::dot_acc(accA, c.X[li + nx], w);
-        } else {
-          w = c.Wt[li];
-        }
-#pragma unroll
-        for (int i = 0; i < kPkNV; ++i)
-          if (i < cntc) T::dot_acc(acc + i * W, __ldcg(pk_col<S>(a, start, i0 + i) + idx), w);
+    {
+      const int nc0 = min(nother, kPkNV);
+      PK_SWITCH_NC(nc0, (pk_phase_a<S, ANISO, NC, true>(a, c, gs, start, j, 0, inv_bj, cm)));
+      for (int i0 = kPkNV; i0 < nother; i0 += kPkNV) {
+        const int nc = min(nother - i0, kPkNV);
+        PK_SWITCH_NC(nc, (pk_phase_a<S, ANISO, NC, false>(a, c, gs, start, j, i0, inv_bj, cm)));
       }
-      pk_publish<kPkNV * W>(acc, a.part, gs.slot, c.red, i0 * W);
-      if (i0 == 0) pk_publish<W>(accA, a.part, gs.slot, c.red, j * W);
     }
     if (!grid_barrier(gs)) return false;
     pk_gather((j + 1) * W, a.part, gs.slot ^ 1, a.ncta, c.vals);
-    // h_i = sums_i / beta_i ; w -= h_i v_i = (sums_i / beta_i^2) w_i ; alpha = h_j
+    // h_i = sums_i / beta_i ; w -= h_i v_i = (sums_i / beta_i^2) w_i ; alpha = Re h_j
     if (threadIdx.x <= j) {
       const int i = threadIdx.x;
-      const double ib2 = 1.0 / c.nrm2[i];
-      c.gco[i] = T::mulr(T::from(c.vals + i * W), ib2);
-      if (i == j) c.alpha[j] = c.vals[j * W] * inv_bj; // T(j,j) = Re(v_j^H w) = Re(sums_j)/beta_j
+      c.gco[i] = T::mulr(T::from(c.vals + i * W), 1.0 / c.nrm2[i]);
+      if (i == j) c.alpha[j] = c.vals[j * W] * inv_bj; // T(j,j) = Re(v_j^H w)
     }
     __syncthreads();
     // ---- phase B: w -= sum_i g_i w_i ; ||w||^2 ; w -> column j+1 (global) and X centre
     {
-      double nrm[1] = {0.0};
-      const S gj = c.gco[j];
-#pragma unroll 2
-      for (long long li = threadIdx.x; li < c.cnt; li += kPkThreads) {
-        const long long idx = c.s0 + li;
-        S w = c.Wt[li];
-        for (int i0 = 0; i0 < nprev; i0 += kPkNV) {
-          S v[kPkNV];
-#pragma unroll
-          for (int i = 0; i < kPkNV; ++i)
-            if (i0 + i < nprev) v[i] = __ldcg(pk_col<S>(a, start, i0 + i) + idx);
-#pragma unroll
-          for (int i = 0; i < kPkNV; ++i)
-            if (i0 + i < nprev) w = T::sub(w, T::mul(c.gco[i0 + i], v[i]));
-        }
-        w = T::sub(w, T::mul(gj, c.X[li + nx]));
-        nrm[0] += T::abs2(w);
-        coln[idx] = w;
-        c.X[li + nx] = w;
-      }
-      pk_publish<1>(nrm, a.part, gs.slot, c.red, 0);
+      int i0 = 0;
+      for (; nother - i0 > kPkNV; i0 += kPkNV) pk_phase_b<S, kPkNV, false>(a, c, gs, start, j, i0);
+      PK_SWITCH_NC(nother - i0, (pk_phase_b<S, NC, true>(a, c, gs, start, j, i0)));
     }
     if (!grid_barrier(gs)) return false;
     pk_gather(1, a.part, gs.slot ^ 1, a.ncta, c.vals);
@@ -367,10 +496,9 @@ __device__ __forceinline__ void pk_coefficients(const PkArgs &a, PkCtx<S> &c, in
       for (int i = lane; i < m; i += 32) {
         double sr = 0.0, si = 0.0;
         for (int k = 0; k < m; ++k) {
-          const double2 fv = make_double2(T.e[k * 32], T.e[k * 32 + 1]);
           const double zz = T.Z[i * T.ldz + k] * T.Z[k];
-          sr = fma(zz, fv.x, sr);
-          si = fma(zz, fv.y, si);
+          sr = fma(zz, T.e[k * 32], sr);
+          si = fma(zz, T.e[k * 32 + 1], si);
         }
         const double scale = beta0 / sqrt(c.nrm2[i]);
         co[2 * i] = sr * scale;
@@ -381,66 +509,82 @@ __device__ __forceinline__ void pk_coefficients(const PkArgs &a, PkCtx<S> &c, in
   __syncthreads();
 }
 
-// y(site) = sum_i co_i * column_i[site]   (any site: columns are complete in global memory)
-template <class S> struct PkCombine;
-template <> struct PkCombine<double> {
-  __device__ static __forceinline__ double eval(const PkArgs &a, const double *start, const double *co, long long site) {
-    double s = 0.0;
-    for (int i0 = 0; i0 < a.m; i0 += kPkNV) {
-      double v[kPkNV];
+// ---------------------------------------------------------------- recombination
+// y += sum_{q<NC} co[q] * base[q*cs]   (base already points at the site)
+template <int NC>
+__device__ __forceinline__ void pk_comb(const double *base, size_t cs, const double *co, double &y) {
+  double v[NC];
 #pragma unroll
-      for (int i = 0; i < kPkNV; ++i)
-        if (i0 + i < a.m) v[i] = __ldcg(pk_col<double>(a, (double *)start, i0 + i) + site);
+  for (int q = 0; q < NC; ++q) v[q] = __ldcg(base + q * cs);
 #pragma unroll
-      for (int i = 0; i < kPkNV; ++i)
-        if (i0 + i < a.m) s = fma(v[i], co[2 * (i0 + i)], s);
-    }
-    return s;
+  for (int q = 0; q < NC; ++q) y = fma(v[q], co[2 * q], y);
+}
+template <int NC>
+__device__ __forceinline__ void pk_comb(const double2 *base, size_t cs, const double *co, double2 &y) {
+  double2 v[NC];
+#pragma unroll
+  for (int q = 0; q < NC; ++q) v[q] = __ldcg(base + q * cs);
+#pragma unroll
+  for (int q = 0; q < NC; ++q) {
+    const double cr = co[2 * q], ci = co[2 * q + 1];
+    y.x = fma(v[q].x, cr, fma(-v[q].y, ci, y.x));
+    y.y = fma(v[q].x, ci, fma(v[q].y, cr, y.y));
   }
-  // two coefficient sets in one pass
-  __device__ static __forceinline__ void eval2(const PkArgs &a, const double *start, const double *co0,
-                                               const double *co1, long long site, double &y0, double &y1) {
-    y0 = 0.0;
-    y1 = 0.0;
-    for (int i0 = 0; i0 < a.m; i0 += kPkNV) {
-      double v[kPkNV];
+}
+template <int NC>
+__device__ __forceinline__ void pk_comb2(const double *base, size_t cs, const double *co0, const double *co1,
+                                         double &y0, double &y1) {
+  double v[NC];
 #pragma unroll
-      for (int i = 0; i < kPkNV; ++i)
-        if (i0 + i < a.m) v[i] = __ldcg(pk_col<double>(a, (double *)start, i0 + i) + site);
+  for (int q = 0; q < NC; ++q) v[q] = __ldcg(base + q * cs);
 #pragma unroll
-      for (int i = 0; i < kPkNV; ++i)
-        if (i0 + i < a.m) {
-          y0 = fma(v[i], co0[2 * (i0 + i)], y0);
-          y1 = fma(v[i], co1[2 * (i0 + i)], y1);
-        }
-    }
+  for (int q = 0; q < NC; ++q) {
+    y0 = fma(v[q], co0[2 * q], y0);
+    y1 = fma(v[q], co1[2 * q], y1);
   }
-};
-template <> struct PkCombine<double2> {
-  __device__ static __forceinline__ double2 eval(const PkArgs &a, const double2 *start, const double *co, long long site) {
-    double2 s = make_double2(0.0, 0.0);
-    for (int i0 = 0; i0 < a.m; i0 += kPkNV) {
-      double2 v[kPkNV];
-#pragma unroll
-      for (int i = 0; i < kPkNV; ++i)
-        if (i0 + i < a.m) v[i] = __ldcg(pk_col<double2>(a, (double2 *)start, i0 + i) + site);
-#pragma unroll
-      for (int i = 0; i < kPkNV; ++i)
-        if (i0 + i < a.m) {
-          const double cr = co[2 * (i0 + i)], ci = co[2 * (i0 + i) + 1];
-          s.x = fma(v[i].x, cr, fma(-v[i].y, ci, s.x));
-          s.y = fma(v[i].x, ci, fma(v[i].y, cr, s.y));
-        }
-    }
-    return s;
-  }
-};
+}
 
-// shared-memory bytes the kernel needs for (n-chunk, nx, m)
+// y(off) = sum_i co_i * column_i[off]: column 0 = start buffer, columns 1..m-1 strided in V
+template <class S>
+__device__ __forceinline__ S pk_combine(const PkArgs &a, const S *start, const double *co, long long off) {
+  S y = Sc<S>::zero();
+  pk_comb<1>(start + off, 0, co, y);
+  const S *vb = (const S *)a.V + off;
+  const int nv = a.m - 1;
+  int q = 0;
+  for (; q + 4 <= nv; q += 4) pk_comb<4>(vb + (size_t)q * a.colstride, a.colstride, co + 2 * (1 + q), y);
+  switch (nv - q) {
+  case 1: pk_comb<1>(vb + (size_t)q * a.colstride, a.colstride, co + 2 * (1 + q), y); break;
+  case 2: pk_comb<2>(vb + (size_t)q * a.colstride, a.colstride, co + 2 * (1 + q), y); break;
+  case 3: pk_comb<3>(vb + (size_t)q * a.colstride, a.colstride, co + 2 * (1 + q), y); break;
+  default: break;
+  }
+  return y;
+}
+__device__ __forceinline__ void pk_combine2(const PkArgs &a, const double *start, const double *co0,
+                                            const double *co1, long long off, double &y0, double &y1) {
+  y0 = 0.0;
+  y1 = 0.0;
+  pk_comb2<1>(start + off, 0, co0, co1, y0, y1);
+  const double *vb = (const double *)a.V + off;
+  const int nv = a.m - 1;
+  int q = 0;
+  for (; q + 4 <= nv; q += 4)
+    pk_comb2<4>(vb + (size_t)q * a.colstride, a.colstride, co0 + 2 * (1 + q), co1 + 2 * (1 + q), y0, y1);
+  switch (nv - q) {
+  case 1: pk_comb2<1>(vb + (size_t)q * a.colstride, a.colstride, co0 + 2 * (1 + q), co1 + 2 * (1 + q), y0, y1); break;
+  case 2: pk_comb2<2>(vb + (size_t)q * a.colstride, a.colstride, co0 + 2 * (1 + q), co1 + 2 * (1 + q), y0, y1); break;
+  case 3: pk_comb2<3>(vb + (size_t)q * a.colstride, a.colstride, co0 + 2 * (1 + q), co1 + 2 * (1 + q), y0, y1); break;
+  default: break;
+  }
+}
+
+// ---------------------------------------------------------------- kernel set-up
 inline size_t pk_smem_bytes(size_t esz, long long csz, int nx, int m) {
-  size_t b = (size_t)(2 * csz + 2 * nx) * esz;          // X + Wt
-  b += (size_t)m * 32 * 8 * 2 + (size_t)m * (m + 1) * 8; // tridiagonal work space
-  b += (size_t)(2 * kPkNV + 2) * kPkWarps * 8;           // red
+  size_t b = (size_t)(2 * csz + 2 * nx) * esz;           // X + Wt
+  b += ((size_t)csz + 15) / 16 * 16;                      // flags
+  b += (size_t)m * 32 * 8 * 2 + (size_t)m * (m + 1) * 8;  // tridiagonal work space
+  b += (size_t)(2 * kPkNV + 2) * kPkWarps * 8;            // red
   b += (size_t)kPkMaxK * 8 + kMaxM * 8 + (kMaxM + 1) * 8 + 4 * kMaxM * 8 + kMaxM * 16;
   return b + 64;
 }
@@ -450,7 +594,8 @@ __device__ __forceinline__ void pk_carve(const PkArgs &a, PkCtx<S> &c, unsigned 
   const long long tile = a.csz + 2 * a.g.nx;
   c.X = (S *)smem;
   c.Wt = c.X + tile;
-  double *p = (double *)(c.Wt + a.csz);
+  c.flag = (unsigned char *)(c.Wt + a.csz);
+  double *p = (double *)(c.flag + (a.csz + 15) / 16 * 16);
   c.tri.d = p; p += a.m * 32;
   c.tri.e = p; p += a.m * 32;
   c.tri.Z = p; p += a.m * (a.m + 1);
@@ -464,7 +609,9 @@ __device__ __forceinline__ void pk_carve(const PkArgs &a, PkCtx<S> &c, unsigned 
   c.s0 = (long long)blockIdx.x * a.csz;
   long long e0 = c.s0 + a.csz;
   if (e0 > a.g.n) e0 = a.g.n;
-  c.cnt = e0 > c.s0 ? e0 - c.s0 : 0;
+  c.cnt = e0 > c.s0 ? (int)(e0 - c.s0) : 0;
+  for (int li = threadIdx.x; li < c.cnt; li += kPkThreads) c.flag[li] = pk_site_flags(a.g, c.s0 + li);
+  __syncthreads();
 }
 
 // publish ||start||^2, barrier, gather -> nrm2[0]
@@ -478,6 +625,23 @@ __device__ __forceinline__ bool pk_start_norm(const PkArgs &a, PkCtx<S> &c, Grid
   return true;
 }
 
+__device__ __forceinline__ double2 pk_nlse_phase(int eq, const NlseParams &p, double mv, double2 dens, double2 z) {
+  switch (eq) {
+  case NLS_EQ_NLSE_CUBIC: return nlse_phase<NLS_EQ_NLSE_CUBIC>(p, mv, dens, z, z);
+  case NLS_EQ_NLSE_CQ: return nlse_phase<NLS_EQ_NLSE_CQ>(p, mv, dens, z, z);
+  default: return nlse_phase<NLS_EQ_NLSE_SAT>(p, mv, dens, z, z);
+  }
+}
+__device__ __forceinline__ double pk_f_real(int eq, double x) {
+  switch (eq) {
+  case NLS_EQ_SGE: return f_real<NLS_EQ_SGE>(x);
+  case NLS_EQ_KGE: return f_real<NLS_EQ_KGE>(x);
+  case NLS_EQ_PHI4: return f_real<NLS_EQ_PHI4>(x);
+  case NLS_EQ_SGE_DOUBLE: return f_real<NLS_EQ_SGE_DOUBLE>(x);
+  default: return f_real<NLS_EQ_SGE_SINH>(x);
+  }
+}
+
 // ---------------------------------------------------------------- NLSE, Strang splitting
 // buffers: u ping-pong (a.u0 current at entry, a.u1), start-vector ping-pong (sv0, sv1)
 template <bool ANISO>
@@ -486,24 +650,19 @@ __global__ void __launch_bounds__(kPkThreads, 1) k_pk_nlse(PkArgs a, double2 *sv
   PkCtx<double2> c;
   pk_carve<double2>(a, c, pk_smem);
   GridSync gs{a.bar, 0u, (unsigned)a.ncta, 0};
-  const int nx = a.g.nx;
   const NlseParams p{0.5 * a.dt, a.s1, a.s2, a.kappa};
   double2 *ucur = (double2 *)a.u0, *unext = (double2 *)a.u1;
   double2 *scur = sv0, *snext = sv1;
+  double2 *xc = c.X + a.g.nx;
+  const double *mfc = a.mf + c.s0;
   // start vector of the first step: rho = exp(.5 tau g(u)) u   (nlse_cubic_solver.hpp:62-66)
   {
     double nrm[1] = {0.0};
-    for (long long li = threadIdx.x; li < c.cnt; li += kPkThreads) {
-      const long long idx = c.s0 + li;
-      const double2 uv = ucur[idx];
-      double2 r;
-      switch (a.eq) {
-      case NLS_EQ_NLSE_CUBIC: r = nlse_phase<NLS_EQ_NLSE_CUBIC>(p, a.mf[idx], uv, uv, uv); break;
-      case NLS_EQ_NLSE_CQ: r = nlse_phase<NLS_EQ_NLSE_CQ>(p, a.mf[idx], uv, uv, uv); break;
-      default: r = nlse_phase<NLS_EQ_NLSE_SAT>(p, a.mf[idx], uv, uv, uv);
-      }
-      scur[idx] = r;
-      c.X[li + nx] = r;
+    for (int li = threadIdx.x; li < c.cnt; li += kPkThreads) {
+      const double2 uv = ucur[c.s0 + li];
+      const double2 r = pk_nlse_phase(a.eq, p, mfc[li], uv, uv);
+      scur[c.s0 + li] = r;
+      xc[li] = r;
       nrm[0] += r.x * r.x + r.y * r.y;
     }
     if (!pk_start_norm<double2>(a, c, gs, nrm)) return;
@@ -512,28 +671,19 @@ __global__ void __launch_bounds__(kPkThreads, 1) k_pk_nlse(PkArgs a, double2 *sv
     if (!pk_lanczos<double2, ANISO>(a, c, gs, scur)) return;
     pk_coefficients<double2>(a, c, 1, NLS_FN_EXP, 0.0, a.dt, 0, 0.0, 0.0); // expm_multiply(L, rho, i dt)
     double nrm[1] = {0.0};
-#pragma unroll 2
-    for (long long li = threadIdx.x; li < c.cnt; li += kPkThreads) {
+    for (int li = threadIdx.x; li < c.cnt; li += kPkThreads) {
       const long long idx = c.s0 + li;
-      const long long sc = clamp_site(a.g, idx); // fused neumann_bc_no_velocity (boundaries.hpp:40-57)
-      const double2 buf = PkCombine<double2>::eval(a, scur, c.coef, sc);
+      // fused neumann_bc_no_velocity (boundaries.hpp:40-57): boundary sites take the clamped site's value
+      const long long sc = (c.flag[li] & PF_RING) ? clamp_site(a.g, idx) : idx;
+      const double2 buf = pk_combine<double2>(a, scur, c.coef, sc);
       const double mv = a.mf[sc];
       double2 un;
-      switch (a.eq) {
-      case NLS_EQ_NLSE_CUBIC: un = nlse_phase<NLS_EQ_NLSE_CUBIC>(p, mv, buf, buf, buf); break;
-      case NLS_EQ_NLSE_CQ: un = nlse_phase<NLS_EQ_NLSE_CQ>(p, mv, __ldcg(ucur + sc), buf, buf); break; // old-u density (Q7)
-      default: un = nlse_phase<NLS_EQ_NLSE_SAT>(p, mv, __ldcg(ucur + sc), buf, buf);
-      }
+      if (a.eq == NLS_EQ_NLSE_CUBIC) un = nlse_phase<NLS_EQ_NLSE_CUBIC>(p, mv, buf, buf, buf);
+      else un = pk_nlse_phase(a.eq, p, mv, __ldcg(ucur + sc), buf); // old-u density
       unext[idx] = un;
-      double2 r;
-      const double mi = a.mf[idx];
-      switch (a.eq) {
-      case NLS_EQ_NLSE_CUBIC: r = nlse_phase<NLS_EQ_NLSE_CUBIC>(p, mi, un, un, un); break;
-      case NLS_EQ_NLSE_CQ: r = nlse_phase<NLS_EQ_NLSE_CQ>(p, mi, un, un, un); break;
-      default: r = nlse_phase<NLS_EQ_NLSE_SAT>(p, mi, un, un, un);
-      }
+      const double2 r = pk_nlse_phase(a.eq, p, mfc[li], un, un);
       snext[idx] = r;
-      c.X[li + nx] = r;
+      xc[li] = r;
       nrm[0] += r.x * r.x + r.y * r.y;
     }
     if (!pk_start_norm<double2>(a, c, gs, nrm)) return;
@@ -551,15 +701,16 @@ __global__ void __launch_bounds__(kPkThreads, 1) k_pk_gautschi(PkArgs a, double 
   PkCtx<double> c;
   pk_carve<double>(a, c, pk_smem);
   GridSync gs{a.bar, 0u, (unsigned)a.ncta, 0};
-  const int nx = a.g.nx;
-  double *u = (double *)a.u0, *up = (double *)a.u1, *accb = (double *)a.acc;
+  double *u = (double *)a.u0, *up = (double *)a.u1 + c.s0, *accb = (double *)a.acc;
+  double *xc = c.X + a.g.nx;
+  const double *mfc = a.mf + c.s0;
   const int filt = a.eq == NLS_EQ_SGE ? NLS_FN_MOD_COSINE : NLS_FN_ID_SQRT;
   const double tau2 = a.dt * a.dt;
   {
     double nrm[1] = {0.0};
-    for (long long li = threadIdx.x; li < c.cnt; li += kPkThreads) {
+    for (int li = threadIdx.x; li < c.cnt; li += kPkThreads) {
       const double v = u[c.s0 + li];
-      c.X[li + nx] = v;
+      xc[li] = v;
       nrm[0] += v * v;
     }
     if (!pk_start_norm<double>(a, c, gs, nrm)) return;
@@ -570,24 +721,16 @@ __global__ void __launch_bounds__(kPkThreads, 1) k_pk_gautschi(PkArgs a, double 
     {
       double nrm[1] = {0.0};
 #pragma unroll 2
-      for (long long li = threadIdx.x; li < c.cnt; li += kPkThreads) {
+      for (int li = threadIdx.x; li < c.cnt; li += kPkThreads) {
         const long long idx = c.s0 + li;
         double sf, sc;
-        PkCombine<double>::eval2(a, u, c.coef, c.coef + 2 * kMaxM, idx, sf, sc);
-        double fv;
-        switch (a.eq) {
-        case NLS_EQ_SGE: fv = f_real<NLS_EQ_SGE>(sf); break;
-        case NLS_EQ_KGE: fv = f_real<NLS_EQ_KGE>(sf); break;
-        case NLS_EQ_PHI4: fv = f_real<NLS_EQ_PHI4>(sf); break;
-        case NLS_EQ_SGE_DOUBLE: fv = f_real<NLS_EQ_SGE_DOUBLE>(sf); break;
-        default: fv = f_real<NLS_EQ_SGE_SINH>(sf);
-        }
-        const double gv = -(a.mf[idx] * fv);
+        pk_combine2(a, u, c.coef, c.coef + 2 * kMaxM, idx, sf, sc);
+        const double gv = -(mfc[li] * pk_f_real(a.eq, sf));
         gbuf[idx] = gv;
-        c.X[li + nx] = gv;
+        xc[li] = gv;
         nrm[0] += gv * gv;
-        accb[idx] = 2 * sc - __ldcg(up + idx);
-        up[idx] = __ldcg(u + idx);
+        accb[idx] = 2 * sc - __ldcg(up + li);
+        up[li] = __ldcg(u + idx);
       }
       if (!pk_start_norm<double>(a, c, gs, nrm)) return;
     }
@@ -596,13 +739,13 @@ __global__ void __launch_bounds__(kPkThreads, 1) k_pk_gautschi(PkArgs a, double 
     {
       double nrm[1] = {0.0};
 #pragma unroll 2
-      for (long long li = threadIdx.x; li < c.cnt; li += kPkThreads) {
+      for (int li = threadIdx.x; li < c.cnt; li += kPkThreads) {
         const long long idx = c.s0 + li;
-        const long long sc = clamp_site(a.g, idx);
-        const double s = PkCombine<double>::eval(a, gbuf, c.coef, sc);
+        const long long sc = (c.flag[li] & PF_RING) ? clamp_site(a.g, idx) : idx;
+        const double s = pk_combine<double>(a, gbuf, c.coef, sc);
         const double un = __ldcg(accb + sc) + tau2 * s;
         u[idx] = un;
-        c.X[li + nx] = un;
+        xc[li] = un;
         nrm[0] += un * un;
       }
       if (!pk_start_norm<double>(a, c, gs, nrm)) return;
