@@ -53,7 +53,27 @@ WORKLOADS = {
                s1=1.0, s2=-0.1),
     "c4": dict(desc="ensemble of NLSE 2D cubic 512x512 trajectories, m=10 (BASELINE configs[3])",
                n=512, dim=2, L=10.0, eq=EQ.NLSE_CUBIC, integ=INT.SS2, m=10, dt=1e-3, seg=10, batch=64),
+    # weak scaling of the slab decomposition: 1024 x 1024 x (128*G) planes, G = number of GPUs
+    # (G = 8 is the full 1024^3 of BASELINE configs[4]; the full cube does not fit fewer than 2 GPUs)
+    "c5": dict(desc="NLSE 3D cubic 1024x1024x(128*G) complex128, z-slabs over G GPUs, in-kernel NVLink halo + "
+                    "scalar exchange, m=10 (BASELINE configs[4] at G=8)",
+               n=1024, dim=3, L=10.0, eq=EQ.NLSE_CUBIC, integ=INT.SS2, m=10, dt=2e-4, seg=5, slab_planes=128),
 }
+
+
+def slab_ic(n, z0, nz, nzg, L):
+    """seed-free analytic IC for the slab workload: 8 fixed Gaussians, evaluated per slab."""
+    x = np.linspace(-L, L, n)
+    z = np.linspace(-L, L, nzg)[z0:z0 + nz]
+    u = np.zeros((nz, n, n), dtype=np.complex128)
+    for k in range(8):
+        c = 0.5 * L * np.array([np.cos(1.3 * k), np.sin(2.1 * k), np.cos(0.7 * k + 1.0)])
+        s = 0.8 + 0.05 * k
+        gx = np.exp(-(x - c[0]) ** 2 / (2 * s * s)) * np.exp(1j * 0.3 * k * x)
+        gy = np.exp(-(x - c[1]) ** 2 / (2 * s * s))
+        gz = np.exp(-(z - c[2]) ** 2 / (2 * s * s))
+        u += (0.5 + 0.05 * k) * gz[:, None, None] * gy[None, :, None] * gx[None, None, :]
+    return u
 
 
 def bytes_per_site_step(w, reorth_full=True):
@@ -162,6 +182,8 @@ def cpu_baseline(w, budget_s=20.0):
     bounded sample: the same grid and inputs, few steps."""
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import orc
+    if "slab_planes" in w:  # the CPU cannot hold the slab workload: same equation on a 128^3 cube
+        w = dict(w, n=128)
     d = make_desc(w, batch=1)
     u0, v0 = make_state(w, 1)
     o = orc.Oracle(d)
@@ -223,9 +245,22 @@ def run_native(args, w, rank, world, local_rank):
     import torch.distributed as dist
     torch.cuda.set_device(local_rank)
     batch = w.get("batch", 1)
-    d = make_desc(w, batch=batch, device=local_rank)
-    u0, v0 = make_state(w, batch, seed0=rank * batch)
-    eng = Engine(d)
+    if "slab_planes" in w:  # z-slab decomposition: one slab handle per GPU, wired over peer memory
+        from nls_b200 import slabs
+        n, nzg = w["n"], w["slab_planes"] * world
+        dx = 2.0 * w["L"] / (n - 1)
+
+        def mk(nz, nz_global, z0):
+            return Desc.make(n, n, nz, dx=dx, equation=w["eq"], integrator=w["integ"], krylov_m=w["m"],
+                             dt=w["dt"], device=local_rank, nz_global=nz_global, z0=z0)
+        eng, z0, nz = slabs.make_slab_engine(mk, nzg, dist if world > 1 else None, rank, world,
+                                             torch.device("cuda", local_rank))
+        d = eng.desc
+        u0, v0 = slab_ic(n, z0, nz, nzg, w["L"])[None], None
+    else:
+        d = make_desc(w, batch=batch, device=local_rank)
+        u0, v0 = make_state(w, batch, seed0=rank * batch)
+        eng = Engine(d)
     load_state(eng, w, u0, v0)
     dt, K, W = w["dt"], args.steps, args.warmup
     sites = d.n * batch
@@ -289,11 +324,13 @@ def run_native(args, w, rank, world, local_rank):
         "metric": METRIC, "value": value, "unit": "site-steps/s", "n_gpus": world, "steps": K, "warmup": W,
         "ms_per_step": t_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f64", "data": "synthetic",
-        "config": {"workload": args.workload, "description": w["desc"], "grid": [w["n"]] * w["dim"],
+        "config": {"workload": args.workload, "description": w["desc"],
+                   "grid": [w["n"], w["n"], w["slab_planes"] * world] if "slab_planes" in w else [w["n"]] * w["dim"],
                    "trajectories_per_gpu": batch, "krylov_m": w["m"], "dt": dt, "reorth": "full",
                    "l2": "no flush: state+basis working set per step exceeds/approaches L2 and every step "
                          "rewrites it (production access pattern)",
-                   "parallelism": f"ensemble x{world}" if world > 1 else "single GPU"},
+                   "parallelism": (f"z-slabs x{world} (peer-memory halo + in-kernel all-reduce)" if "slab_planes" in w
+                                   else f"ensemble x{world}") if world > 1 else "single GPU"},
         "e2e": {"value": e2e, "unit": "site-steps/s", "h2d_bytes_per_step": h2d / seg,
                 "d2h_bytes_per_step": d2h / seg, "segment_steps": seg,
                 "note": "per segment: pinned-host state -> device, seg steps, state+velocity -> pinned host"},

@@ -174,16 +174,23 @@ void *nls_stream(nls_handle h);
 /* time a run of nsteps steps with CUDA events on the handle's stream; ms returned */
 int nls_step_timed(nls_handle h, double dt, uint32_t nsteps, float *ms);
 
-/* ---- z-slab decomposition across GPUs (one handle per GPU) ---- */
-/* opaque IPC descriptor of this handle's halo mailbox (64-byte cudaIpcMemHandle_t + sizes) */
+/* ---- z-slab decomposition across GPUs (one handle per GPU) ----
+ * A handle created with nz_global > nz owns planes [z0, z0+nz) of the global grid (batch must
+ * be 1, nz >= 2) and keeps one ghost plane per side.  Halo planes and the scalar sums of every
+ * Lanczos reduction travel INSIDE the kernels through peer-mapped memory (NVLink); the host
+ * only wires the handles together once:
+ *   1. every rank calls nls_slab_export and the 128-byte blobs are gathered in rank order
+ *      (rank r owns the r-th slab counting from z = 0), e.g. with an all-gather;
+ *   2. every rank calls nls_slab_connect with all blobs.  Ranks may be processes (CUDA IPC)
+ *      or host threads of one process (direct peer access).
+ * After that nls_set_field(U, C), nls_step, nls_matfunc, nls_lanczos, nls_stencil_apply and
+ * nls_reduce are COLLECTIVE: every rank must issue the same calls in the same order (they
+ * exchange ghost planes / sums; a missing peer makes the call fail after ~3 s instead of
+ * hanging).  Host arrays passed to a slab handle hold the local planes only; reductions and
+ * Lanczos scalars returned are global.  All ranks must be synchronised (nls_sync + a host
+ * barrier) before any of them calls nls_destroy. */
 int nls_slab_export(nls_handle h, void *buf128);
-/* connect to the lower (z0-1) and upper (z0+nz) neighbours; either may be NULL */
-int nls_slab_connect(nls_handle h, const void *lower128, const void *upper128);
-/* install the scalar all-reduce callback used at every Lanczos reduction point:
- * it must sum `count` doubles in place across all slabs (called from the host
- * thread that calls nls_step, with the stream synchronised). */
-typedef void (*nls_allreduce_fn)(double *vals, int count, void *user);
-int nls_slab_set_allreduce(nls_handle h, nls_allreduce_fn fn, void *user);
+int nls_slab_connect(nls_handle h, const void *all_blobs /* nranks*128 bytes */, int rank, int nranks);
 
 #ifdef __cplusplus
 }

@@ -7,3 +7,4 @@ from .binding import (  # noqa: F401
     Desc, Engine, NlsError, load_library, library_path, build_library,
     EQ, INT, LAP, FN, FIELD, RED, REORTH, FLAG_NO_GRAPH, FLAG_NO_PERSISTENT,
 )
+from . import slabs  # noqa: F401,E402

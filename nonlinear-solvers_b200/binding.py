@@ -120,8 +120,7 @@ _SIGS = {
     "nls_stream": (_vp, [_vp]),
     "nls_step_timed": (C.c_int, [_vp, C.c_double, C.c_uint32, C.POINTER(C.c_float)]),
     "nls_slab_export": (C.c_int, [_vp, _vp]),
-    "nls_slab_connect": (C.c_int, [_vp, _vp, _vp]),
-    "nls_slab_set_allreduce": (C.c_int, [_vp, _vp, _vp]),
+    "nls_slab_connect": (C.c_int, [_vp, _vp, C.c_int, C.c_int]),
 }
 EXPORTS = tuple(_SIGS)
 
@@ -233,6 +232,15 @@ class Engine:
         out = np.empty(self.desc.batch, dtype=np.float64)
         self._check(self.lib.nls_reduce(self.h, what, out.ctypes.data_as(_dp)))
         return out
+
+    def slab_export(self):
+        buf = C.create_string_buffer(128)
+        self._check(self.lib.nls_slab_export(self.h, buf))
+        return buf.raw
+
+    def slab_connect(self, blobs, rank, nranks):
+        assert len(blobs) == 128 * nranks
+        self._check(self.lib.nls_slab_connect(self.h, blobs, rank, nranks))
 
     def launch_count(self):
         return int(self.lib.nls_launch_count(self.h))

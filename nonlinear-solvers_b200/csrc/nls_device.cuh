@@ -167,14 +167,93 @@ __device__ __forceinline__ long long clamp_site(const Geom &g, long long idx) {
 //   stage 2: the last CTA of the trajectory to arrive (atomic ticket) sums the partials in
 //            a fixed order and stores the K totals to `dst`; no host round trip, no
 //            floating-point atomics, bit-reproducible for a given launch shape.
+// z-slab decomposition (one handle per GPU): cross-GPU sum of the per-slab totals through
+// peer-mapped mailboxes, entirely inside the producing kernel (no host, no NCCL call):
+//   the last CTA of a slab writes its K totals into slot [seq % kSlabSlots][rank] of EVERY
+//   rank's mailbox (peer stores over NVLink), fences, then release-stores the sequence number
+//   seq+1 into the matching flag; it then spins (acquire loads, LOCAL memory) until all G flags
+//   of its own mailbox carry seq+1 and sums the G contributions in rank order, so every rank
+//   obtains bit-identical scalars.  The same release/acquire chain orders the halo-plane peer
+//   stores of that kernel before the next kernel's stencil reads on the neighbour.
+constexpr int kSlabMaxRanks = 8;
+constexpr int kSlabSlots = 4;
+constexpr int kSlabMaxK = 32;
+struct SlabMailbox { // lives at offset 0 of every rank's exchange arena
+  double red[kSlabSlots][kSlabMaxRanks][kSlabMaxK];
+  unsigned long long flag[kSlabSlots][kSlabMaxRanks];
+  unsigned long long seq;   // reductions completed by the owning rank
+  unsigned abort_flag;      // set once a wait timed out: later waits are skipped
+};
+struct SlabCtx {
+  int rank, nranks;
+  SlabMailbox *box[kSlabMaxRanks]; // box[rank] is local, the others are peer mappings
+  int *status;
+};
+
+template <class S> struct Halo { // peer ghost planes of the vector a kernel produces (or null)
+  S *lo; // lower neighbour's upper ghost plane
+  S *hi; // upper neighbour's lower ghost plane
+};
+template <class S>
+__device__ __forceinline__ void halo_push(const Halo<S> &h, long long n, long long plane, long long idx, S v) {
+  if (h.lo != nullptr && idx < plane) h.lo[idx] = v;
+  if (h.hi != nullptr && idx >= n - plane) h.hi[idx - (n - plane)] = v;
+}
+
+__device__ __forceinline__ void st_release_sys_u64(unsigned long long *p, unsigned long long v) {
+  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_acquire_sys_u64(const unsigned long long *p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+
 struct RedCtx {
   double *partials;  // [batch][gridDim.x][K]
   unsigned *tickets; // [batch]
+  const SlabCtx *slab; // null unless z-slab decomposed (batch == 1 then)
 };
+
+// called by all threads of the last CTA; s_tot[K] holds this slab's totals
+template <int K>
+__device__ __forceinline__ void slab_allreduce(const SlabCtx &sc, double *s_tot, double *dst) {
+  static_assert(K <= kSlabMaxK, "reduction too wide for the slab mailbox");
+  SlabMailbox *mine = sc.box[sc.rank];
+  const unsigned long long seq = *(volatile unsigned long long *)&mine->seq; // written only by this rank's previous reduction
+  const int slot = (int)(seq % kSlabSlots);
+  const int G = sc.nranks;
+  for (int t = threadIdx.x; t < G * K; t += blockDim.x) {
+    const int q = t / K, k = t - q * K;
+    sc.box[q]->red[slot][sc.rank][k] = s_tot[k];
+  }
+  __threadfence_system();
+  __syncthreads();
+  if ((int)threadIdx.x < G) st_release_sys_u64(&sc.box[threadIdx.x]->flag[slot][sc.rank], seq + 1);
+  if ((int)threadIdx.x < G) {
+    const long long t0 = clock64();
+    bool dead = *(volatile unsigned *)&mine->abort_flag != 0u;
+    while (!dead && ld_acquire_sys_u64(&mine->flag[slot][threadIdx.x]) != seq + 1) {
+      if (clock64() - t0 > 6000000000LL) { // ~3 s: a peer died or never launched
+        dead = true;
+        mine->abort_flag = 1u;
+        atomicExch(sc.status, 2);
+      }
+    }
+  }
+  __syncthreads();
+  if ((int)threadIdx.x < K) {
+    double v = 0.0;
+    for (int q = 0; q < G; ++q) v += *(volatile double *)&mine->red[slot][q][threadIdx.x];
+    dst[threadIdx.x] = v;
+  }
+  if (threadIdx.x == 0) mine->seq = seq + 1;
+}
 
 template <int K>
 __device__ __forceinline__ void grid_reduce(double (&acc)[K], const RedCtx &rc, double *dst) {
   __shared__ double s_part[kThreads / 32][K];
+  __shared__ double s_tot[K];
   __shared__ bool s_last;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #pragma unroll
@@ -193,7 +272,9 @@ __device__ __forceinline__ void grid_reduce(double (&acc)[K], const RedCtx &rc, 
     for (int w = 0; w < kThreads / 32; ++w) v += s_part[w][threadIdx.x];
     mine[threadIdx.x] = v;
   }
-  __threadfence();
+  // slab mode: this CTA's halo-plane peer stores must be visible system-wide before the flag
+  if (rc.slab != nullptr) __threadfence_system();
+  else __threadfence();
   __syncthreads();
   if (threadIdx.x == 0) {
     const unsigned t = atomicAdd(&rc.tickets[b], 1u);
@@ -204,12 +285,20 @@ __device__ __forceinline__ void grid_reduce(double (&acc)[K], const RedCtx &rc, 
   if (!s_last) return;
   __threadfence();
   const double *all = rc.partials + (size_t)b * nblk * K;
+  const bool slab = rc.slab != nullptr;
   for (int k = warp; k < K; k += kThreads / 32) {
     double v = 0.0;
     for (int blk = lane; blk < nblk; blk += 32) v += __ldcg(&all[(size_t)blk * K + k]);
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
-    if (lane == 0) dst[k] = v;
+    if (lane == 0) {
+      if (slab) s_tot[k] = v;
+      else dst[k] = v;
+    }
+  }
+  if (slab) {
+    __syncthreads();
+    slab_allreduce<K>(*rc.slab, s_tot, dst);
   }
 }
 

@@ -3,6 +3,8 @@
 // No CPU fallback anywhere: without a CUDA device every entry point returns NLS_ERR_CUDA.
 #include "nls_persist.cuh"
 
+#include <unistd.h>
+
 #include <cmath>
 #include <cstdio>
 #include <cstring>
@@ -47,7 +49,7 @@ struct nls_engine {
   void *acc = nullptr;   // Gautschi accumulator
   double *mf = nullptr, *cf = nullptr;
   double *scalA = nullptr, *scalB = nullptr, *coef = nullptr, *redout = nullptr;
-  RedCtx rc{nullptr, nullptr};
+  RedCtx rc{nullptr, nullptr, nullptr};
   int *status = nullptr;
   size_t colstride = 0;  // scalars between basis columns
   // stepping state
@@ -68,9 +70,17 @@ struct nls_engine {
   double *pk_part = nullptr;
   unsigned *pk_bar = nullptr;
   uint64_t pk_launches = 0;
-  // slabs
-  nls_allreduce_fn allreduce = nullptr;
-  void *allreduce_user = nullptr;
+  // z-slabs: the stencil-input vectors (+ the mailbox) live in one exchange arena that the
+  // other ranks map through CUDA IPC (or address directly when they live in this process)
+  bool slab = false;
+  char *arena = nullptr;
+  size_t slot_bytes = 0;      // bytes per arena slot on THIS rank
+  int rank = 0, nranks = 1;
+  bool connected = false;
+  SlabCtx *slab_dev = nullptr;
+  double *slab_scratch = nullptr;
+  struct Peer { char *base = nullptr; bool ipc = false; uint64_t stride = 0; uint32_t nz = 0; };
+  Peer peers[kSlabMaxRanks];
 
   size_t vec_elems() const { return (size_t)batch * g.stride; }
   size_t vec_bytes() const { return vec_elems() * esz; }
@@ -95,6 +105,51 @@ S *col(nls_engine *e, int j) {
   return (S *)e->V + (size_t)j * e->colstride;
 }
 
+// ---------------------------------------------------------------- z-slab exchange arena
+constexpr int kArenaSlots = 7; // wbuf0, wbuf1, w0, u0, u1, u2, cf
+constexpr size_t kMailboxBytes = (sizeof(SlabMailbox) + 4095) / 4096 * 4096;
+
+struct SlabDesc { // the 128-byte blob of nls_slab_export
+  cudaIpcMemHandle_t ipc; // 64 bytes
+  uint64_t magic, pid, raw, stride;
+  uint32_t nz, z0, nx, ny;
+  int32_t device, esz;
+  uint64_t pad[1];
+};
+static_assert(sizeof(SlabDesc) == 128, "slab descriptor must be 128 bytes");
+constexpr uint64_t kSlabMagic = 0x4e4c53534c414231ull; // "NLSSLAB1"
+
+// peer ghost planes of a local arena vector (null/null when not decomposed or not in the arena)
+template <class S>
+Halo<S> halo_for(nls_engine *e, const void *local) {
+  Halo<S> h{nullptr, nullptr};
+  if (!e->slab || !e->connected || !local) return h;
+  const ptrdiff_t off = (const char *)local - (e->arena + kMailboxBytes);
+  if (off < 0 || (size_t)off >= kArenaSlots * e->slot_bytes || off % (ptrdiff_t)e->slot_bytes) return h;
+  const int slot = (int)(off / (ptrdiff_t)e->slot_bytes);
+  const size_t plane = (size_t)e->g.plane;
+  if (e->rank > 0) {
+    const nls_engine::Peer &p = e->peers[e->rank - 1];
+    const size_t pslot = (p.stride * e->esz + 255) / 256 * 256;
+    h.lo = (S *)(p.base + kMailboxBytes + slot * pslot) + (p.stride - plane); // its upper ghost plane
+  }
+  if (e->rank + 1 < e->nranks) {
+    const nls_engine::Peer &p = e->peers[e->rank + 1];
+    const size_t pslot = (p.stride * e->esz + 255) / 256 * 256;
+    h.hi = (S *)(p.base + kMailboxBytes + slot * pslot); // its lower ghost plane
+  }
+  return h;
+}
+
+// push the boundary planes of an uploaded stencil input to the neighbours (collective)
+template <class S>
+void halo_exchange(nls_engine *e, const void *buf) {
+  if (!e->slab || !e->connected) return;
+  k_halo_exchange<S><<<e->grid(), kThreads, 0, e->stream>>>(e->g, (const S *)buf, e->rc, halo_for<S>(e, buf),
+                                                         e->slab_scratch);
+  e->count();
+}
+
 // ---------------------------------------------------------------- Lanczos (K2)
 template <class S, bool ANISO>
 void lanczos_t(nls_engine *e, const S *start, double *scal) {
@@ -108,7 +163,7 @@ void lanczos_t(nls_engine *e, const S *start, double *scal) {
            e->rc);
     if (e->d.reorth == NLS_REORTH_NONE) {
       LAUNCH(e, (k_lanczos_pc<S, 4, true>), gr, e->g, wout, (const S *)e->V, e->colstride, j, j, 1,
-             scal, kOffAlpha + j * e->W, scal, e->rc);
+             scal, kOffAlpha + j * e->W, scal, e->rc, halo_for<S>(e, wout));
       continue;
     }
     const int nv = j + 1;
@@ -125,8 +180,8 @@ void lanczos_t(nls_engine *e, const S *start, double *scal) {
       const int hoff = kOffH + i0 * e->W;
 #define PC(NV)                                                                                      \
   do {                                                                                              \
-    if (last) LAUNCH(e, (k_lanczos_pc<S, NV, true>), gr, e->g, wout, (const S *)e->V, e->colstride, j, i0, cnt, scal, hoff, scal, e->rc); \
-    else LAUNCH(e, (k_lanczos_pc<S, NV, false>), gr, e->g, wout, (const S *)e->V, e->colstride, j, i0, cnt, scal, hoff, scal, e->rc);     \
+    if (last) LAUNCH(e, (k_lanczos_pc<S, NV, true>), gr, e->g, wout, (const S *)e->V, e->colstride, j, i0, cnt, scal, hoff, scal, e->rc, halo_for<S>(e, wout)); \
+    else LAUNCH(e, (k_lanczos_pc<S, NV, false>), gr, e->g, wout, (const S *)e->V, e->colstride, j, i0, cnt, scal, hoff, scal, e->rc, Halo<S>{nullptr, nullptr});     \
   } while (0)
       if (cnt <= 4) PC(4);
       else if (cnt <= 8) PC(8);
@@ -169,7 +224,8 @@ void nlse_step_t(nls_engine *e, double dt) {
   tridiag(e, e->scalA, 1, NLS_FN_EXP, 0.0, dt, 0, 0, 0); // expm_multiply(L, rho, tau = i dt)
   NlseParams p{0.5 * dt, e->d.s1, e->d.s2, e->d.kappa};
   LAUNCH(e, (k_nlse_finish<EQ>), e->grid(), e->g, (const double2 *)e->V, e->colstride,
-         wlast<double2>(e), e->coef, e->m, uin, e->mf, uout, (double2 *)e->w0, p, e->scalA, e->rc);
+         wlast<double2>(e), e->coef, e->m, uin, e->mf, uout, (double2 *)e->w0, p, e->scalA, e->rc,
+         halo_for<double2>(e, e->w0));
 }
 
 template <int EQ>
@@ -180,11 +236,12 @@ void gautschi_step_t(nls_engine *e, double dt) {
   tridiag(e, e->scalA, 2, filt, dt, 0.0, NLS_FN_COS_SQRT, dt, 0.0);
   LAUNCH(e, (k_gautschi_a<EQ>), e->grid(), e->g, (const double *)e->V, e->colstride,
          wlast<double>(e), e->coef, e->m, u, up, e->mf, (double *)e->w0, (double *)e->acc, e->scalB,
-         e->rc);
+         e->rc, halo_for<double>(e, e->w0));
   lanczos<double>(e, (const double *)e->w0, e->scalB);
   tridiag(e, e->scalB, 1, NLS_FN_SINC2_HALF, dt, 0.0, 0, 0, 0);
   LAUNCH(e, (k_gautschi_b<0>), e->grid(), e->g, (const double *)e->V, e->colstride,
-         wlast<double>(e), e->coef, e->m, (const double *)e->acc, u, dt * dt, e->scalA, e->rc);
+         wlast<double>(e), e->coef, e->m, (const double *)e->acc, u, dt * dt, e->scalA, e->rc,
+         halo_for<double>(e, u));
 }
 
 template <int EQ>
@@ -194,9 +251,11 @@ void sv_step_t(nls_engine *e, double dt) {
   const double *up = (const double *)e->u[(e->phase + 2) % 3];
   double *un = (double *)e->u[(e->phase + 1) % 3];
   if (e->d.laplacian == NLS_LAP_ANISO)
-    LAUNCH(e, (k_sv<EQ, true>), e->grid(), e->g, u, up, e->mf, e->cf, un, dt * dt);
+    LAUNCH(e, (k_sv<EQ, true>), e->grid(), e->g, u, up, e->mf, e->cf, un, dt * dt, e->rc, halo_for<double>(e, un),
+           e->slab_scratch);
   else
-    LAUNCH(e, (k_sv<EQ, false>), e->grid(), e->g, u, up, e->mf, e->cf, un, dt * dt);
+    LAUNCH(e, (k_sv<EQ, false>), e->grid(), e->g, u, up, e->mf, e->cf, un, dt * dt, e->rc, halo_for<double>(e, un),
+           e->slab_scratch);
 }
 
 void issue_step(nls_engine *e, double dt) {
@@ -237,13 +296,16 @@ int ensure_start(nls_engine *e, double dt) {
     const double2 *u = (const double2 *)e->u[e->phase];
     switch (e->d.equation) {
     case NLS_EQ_NLSE_CUBIC:
-      LAUNCH(e, (k_nlse_prephase<NLS_EQ_NLSE_CUBIC>), e->grid(), e->g, u, e->mf, (double2 *)e->w0, p, e->scalA, e->rc);
+      LAUNCH(e, (k_nlse_prephase<NLS_EQ_NLSE_CUBIC>), e->grid(), e->g, u, e->mf, (double2 *)e->w0, p, e->scalA, e->rc,
+             halo_for<double2>(e, e->w0));
       break;
     case NLS_EQ_NLSE_CQ:
-      LAUNCH(e, (k_nlse_prephase<NLS_EQ_NLSE_CQ>), e->grid(), e->g, u, e->mf, (double2 *)e->w0, p, e->scalA, e->rc);
+      LAUNCH(e, (k_nlse_prephase<NLS_EQ_NLSE_CQ>), e->grid(), e->g, u, e->mf, (double2 *)e->w0, p, e->scalA, e->rc,
+             halo_for<double2>(e, e->w0));
       break;
     default:
-      LAUNCH(e, (k_nlse_prephase<NLS_EQ_NLSE_SAT>), e->grid(), e->g, u, e->mf, (double2 *)e->w0, p, e->scalA, e->rc);
+      LAUNCH(e, (k_nlse_prephase<NLS_EQ_NLSE_SAT>), e->grid(), e->g, u, e->mf, (double2 *)e->w0, p, e->scalA, e->rc,
+             halo_for<double2>(e, e->w0));
     }
   } else {
     LAUNCH(e, (k_norm2<double>), e->grid(), e->g, (const double *)e->u[0], e->scalA + kOffNrm2,
@@ -393,6 +455,7 @@ int check_status(nls_engine *e) {
   int st = 0;
   CU(cudaMemcpyAsync(&st, e->status, sizeof(int), cudaMemcpyDeviceToHost, e->stream));
   CU(cudaStreamSynchronize(e->stream));
+  if (st == 2) return fail(NLS_ERR_STATE, "z-slab exchange timed out waiting for a peer rank");
   if (st) return fail(NLS_ERR_STATE, "tridiagonal eigensolver did not converge (non-finite state?)");
   return NLS_OK;
 }
@@ -417,9 +480,15 @@ int nls_destroy(nls_handle e) {
   if (e->stream) cudaStreamSynchronize(e->stream);
   for (auto &ge : e->gexec)
     if (ge) cudaGraphExecDestroy(ge);
+  if (e->arena) { // sub-allocations of the exchange arena
+    e->wbuf[0] = e->wbuf[1] = e->w0 = e->u[0] = e->u[1] = e->u[2] = nullptr;
+    e->cf = nullptr;
+    for (int q = 0; q < e->nranks; ++q)
+      if (e->peers[q].ipc && e->peers[q].base) cudaIpcCloseMemHandle(e->peers[q].base);
+  }
   void *ptrs[] = {e->V, e->wbuf[0], e->wbuf[1], e->w0, e->u[0], e->u[1], e->u[2], e->acc, e->mf, e->cf,
                   e->scalA, e->scalB, e->coef, e->redout, e->rc.partials, e->rc.tickets, e->status,
-                  e->pk_part, e->pk_bar};
+                  e->pk_part, e->pk_bar, e->arena, e->slab_dev, e->slab_scratch};
   for (void *p : ptrs)
     if (p) cudaFree(p);
   if (e->stream) cudaStreamDestroy(e->stream);
@@ -441,6 +510,8 @@ int nls_create(const nls_desc *desc, nls_handle *out) {
   if (!(d.dx > 0) || !(d.dy > 0)) return fail(NLS_ERR_ARG, "dx, dy must be positive");
   const uint32_t nzg = d.nz_global ? d.nz_global : d.nz;
   if (d.nz_global && (d.nz == 1 || d.z0 + d.nz > nzg)) return fail(NLS_ERR_ARG, "bad slab");
+  if (d.nz_global && nzg != d.nz && (d.batch != 1 || d.nz < 2))
+    return fail(NLS_ERR_ARG, "z-slab handles need batch == 1 and at least 2 planes per slab");
   if ((unsigned long long)d.nx * d.ny * nzg >= (1ull << 32)) return fail(NLS_ERR_ARG, "grid too large (2^32 sites)");
   int ndev = 0;
   CU(cudaGetDeviceCount(&ndev));
@@ -483,11 +554,25 @@ int nls_create(const nls_desc *desc, nls_handle *out) {
   const bool krylov = d.integrator != NLS_INT_SV;
   // the Krylov buffers are also used by nls_matfunc / nls_lanczos / nls_stencil_apply
   ok = ok && alloc(&e->V, vb * (e->m - 1));
-  ok = ok && alloc(&e->wbuf[0], vb) && alloc(&e->wbuf[1], vb) && alloc(&e->w0, vb);
-  ok = ok && alloc(&e->u[0], vb) && alloc(&e->u[1], vb);
-  if (d.integrator == NLS_INT_SV) ok = ok && alloc(&e->u[2], vb);
+  e->slab = g.halo != 0;
+  if (e->slab) { // stencil inputs + mailbox in one arena the other ranks can map
+    e->slot_bytes = (g.stride * e->esz + 255) / 256 * 256;
+    ok = ok && alloc((void **)&e->arena, kMailboxBytes + kArenaSlots * e->slot_bytes);
+    if (ok) {
+      char *b = e->arena + kMailboxBytes;
+      e->wbuf[0] = b; e->wbuf[1] = b + e->slot_bytes; e->w0 = b + 2 * e->slot_bytes;
+      e->u[0] = b + 3 * e->slot_bytes; e->u[1] = b + 4 * e->slot_bytes; e->u[2] = b + 5 * e->slot_bytes;
+      e->cf = (double *)(b + 6 * e->slot_bytes);
+    }
+    ok = ok && alloc((void **)&e->slab_dev, sizeof(SlabCtx)) && alloc((void **)&e->slab_scratch, 64);
+    ok = ok && alloc((void **)&e->mf, g.stride * 8);
+  } else {
+    ok = ok && alloc(&e->wbuf[0], vb) && alloc(&e->wbuf[1], vb) && alloc(&e->w0, vb);
+    ok = ok && alloc(&e->u[0], vb) && alloc(&e->u[1], vb);
+    if (d.integrator == NLS_INT_SV) ok = ok && alloc(&e->u[2], vb);
+    ok = ok && alloc((void **)&e->mf, g.stride * 8) && alloc((void **)&e->cf, g.stride * 8);
+  }
   if (d.integrator == NLS_INT_GAUTSCHI) ok = ok && alloc(&e->acc, vb);
-  ok = ok && alloc((void **)&e->mf, g.stride * 8) && alloc((void **)&e->cf, g.stride * 8);
   ok = ok && alloc((void **)&e->scalA, (size_t)e->batch * kScalStride * 8);
   ok = ok && alloc((void **)&e->scalB, (size_t)e->batch * kScalStride * 8);
   ok = ok && alloc((void **)&e->coef, (size_t)e->batch * 2 * kCoefStride * 8);
@@ -546,6 +631,11 @@ static int set_field_impl(nls_handle e, int field, const void *src, size_t bytes
   default: return fail(NLS_ERR_ARG, "bad field");
   }
   if (rc) return rc;
+  if (e->slab && e->connected) { // collective on slab handles: refresh the neighbours' ghost planes
+    if (field == NLS_FIELD_C) halo_exchange<double>(e, e->cf);
+    else if (field == NLS_FIELD_U && !e->cplx) halo_exchange<double>(e, cur_u(e));
+    CU(cudaGetLastError());
+  }
   e->start_valid = false;
   CU(cudaStreamSynchronize(e->stream)); // host buffer may be reused by the caller
   return NLS_OK;
@@ -582,8 +672,14 @@ int nls_set_field_dev(nls_handle h, int f, const void *s, size_t b) { return set
 int nls_get_field(nls_handle h, int f, void *d, size_t b) { return get_field_impl(h, f, d, b, false); }
 int nls_get_field_dev(nls_handle h, int f, void *d, size_t b) { return get_field_impl(h, f, d, b, true); }
 
+static int slab_ready(nls_handle e) {
+  if (e->slab && !e->connected) return fail(NLS_ERR_STATE, "z-slab handle: call nls_slab_connect first");
+  return NLS_OK;
+}
+
 int nls_step(nls_handle e, double dt, uint32_t nsteps) {
   if (!e) return fail(NLS_ERR_ARG, "null handle");
+  if (slab_ready(e)) return NLS_ERR_STATE;
   CU(cudaSetDevice(e->d.device));
   return run_steps(e, dt, nsteps);
 }
@@ -597,6 +693,7 @@ int nls_sync(nls_handle e) {
 
 int nls_step_timed(nls_handle e, double dt, uint32_t nsteps, float *ms) {
   if (!e || !ms) return fail(NLS_ERR_ARG, "null argument");
+  if (slab_ready(e)) return NLS_ERR_STATE;
   CU(cudaSetDevice(e->d.device));
   int rc = ensure_start(e, dt);
   if (rc) return rc;
@@ -619,8 +716,11 @@ void *nls_stream(nls_handle e) { return e ? (void *)e->stream : nullptr; }
 int nls_stencil_apply(nls_handle e, const void *x, void *y) {
   if (!e || !x || !y) return fail(NLS_ERR_ARG, "null argument");
   CU(cudaSetDevice(e->d.device));
+  if (slab_ready(e)) return NLS_ERR_STATE;
   int rc = copy_in(e, e->w0, x, e->esz, e->batch, false);
   if (rc) return rc;
+  if (e->cplx) halo_exchange<double2>(e, e->w0);
+  else halo_exchange<double>(e, e->w0);
   const bool an = e->d.laplacian == NLS_LAP_ANISO;
   if (e->cplx) {
     if (an) LAUNCH(e, (k_stencil<double2, true>), e->grid(), e->g, (const double2 *)e->w0, (double2 *)e->wbuf[0], e->cf);
@@ -636,9 +736,12 @@ int nls_stencil_apply(nls_handle e, const void *x, void *y) {
 
 // upload `in` into w0, ||in||^2 -> scalA.nrm2[0], run the Lanczos process
 static int lanczos_from_host(nls_handle e, const void *in) {
+  if (slab_ready(e)) return NLS_ERR_STATE;
   int rc = copy_in(e, e->w0, in, e->esz, e->batch, false);
   if (rc) return rc;
   e->start_valid = false;
+  if (e->cplx) halo_exchange<double2>(e, e->w0);
+  else halo_exchange<double>(e, e->w0);
   if (e->cplx) {
     LAUNCH(e, (k_norm2<double2>), e->grid(), e->g, (const double2 *)e->w0, e->scalA + kOffNrm2, kScalStride, e->rc);
     lanczos<double2>(e, (const double2 *)e->w0, e->scalA);
@@ -724,14 +827,71 @@ int nls_reduce(nls_handle e, int what, double *out) {
   return NLS_OK;
 }
 
-int nls_slab_export(nls_handle, void *) { return fail(NLS_ERR_STATE, "z-slab exchange not built in this round"); }
-int nls_slab_connect(nls_handle, const void *, const void *) {
-  return fail(NLS_ERR_STATE, "z-slab exchange not built in this round");
+int nls_slab_export(nls_handle e, void *buf128) {
+  if (!e || !buf128) return fail(NLS_ERR_ARG, "null argument");
+  if (!e->slab) return fail(NLS_ERR_STATE, "not a z-slab handle (nz_global == nz)");
+  CU(cudaSetDevice(e->d.device));
+  SlabDesc sd;
+  std::memset(&sd, 0, sizeof sd);
+  CU(cudaIpcGetMemHandle(&sd.ipc, e->arena));
+  sd.magic = kSlabMagic;
+  sd.pid = (uint64_t)getpid();
+  sd.raw = (uint64_t)(uintptr_t)e->arena;
+  sd.stride = (uint64_t)e->g.stride;
+  sd.nz = e->d.nz; sd.z0 = e->d.z0; sd.nx = e->d.nx; sd.ny = e->d.ny;
+  sd.device = e->d.device; sd.esz = (int32_t)e->esz;
+  std::memcpy(buf128, &sd, sizeof sd);
+  return NLS_OK;
 }
-int nls_slab_set_allreduce(nls_handle e, nls_allreduce_fn fn, void *user) {
-  if (!e) return fail(NLS_ERR_ARG, "null handle");
-  e->allreduce = fn;
-  e->allreduce_user = user;
+
+int nls_slab_connect(nls_handle e, const void *descs, int rank, int nranks) {
+  if (!e || !descs) return fail(NLS_ERR_ARG, "null argument");
+  if (!e->slab) return fail(NLS_ERR_STATE, "not a z-slab handle (nz_global == nz)");
+  if (e->connected) return fail(NLS_ERR_STATE, "already connected");
+  if (nranks < 2 || nranks > kSlabMaxRanks || rank < 0 || rank >= nranks)
+    return fail(NLS_ERR_ARG, "need 2..8 ranks and 0 <= rank < nranks");
+  CU(cudaSetDevice(e->d.device));
+  const SlabDesc *sd = (const SlabDesc *)descs;
+  uint32_t z = 0;
+  for (int q = 0; q < nranks; ++q) { // slabs must tile [0, nz_global) in rank order
+    if (sd[q].magic != kSlabMagic) return fail(NLS_ERR_ARG, "bad slab descriptor");
+    if (sd[q].nx != e->d.nx || sd[q].ny != e->d.ny || sd[q].esz != (int32_t)e->esz || sd[q].z0 != z)
+      return fail(NLS_ERR_ARG, "slab descriptors do not tile the global grid in rank order");
+    z += sd[q].nz;
+  }
+  if (z != (uint32_t)e->g.nz_glob || sd[rank].z0 != e->d.z0 || sd[rank].nz != e->d.nz ||
+      sd[rank].raw != (uint64_t)(uintptr_t)e->arena || sd[rank].pid != (uint64_t)getpid())
+    return fail(NLS_ERR_ARG, "descriptor[rank] is not this handle / slabs do not cover nz_global");
+  SlabCtx sc;
+  std::memset(&sc, 0, sizeof sc);
+  sc.rank = rank; sc.nranks = nranks; sc.status = e->status;
+  for (int q = 0; q < nranks; ++q) {
+    nls_engine::Peer &p = e->peers[q];
+    p.stride = sd[q].stride; p.nz = sd[q].nz;
+    if (q == rank) p.base = e->arena;
+    else if (sd[q].pid == (uint64_t)getpid()) { // same process (one host thread per GPU): direct peer access
+      if (sd[q].device != e->d.device) {
+        int can = 0;
+        CU(cudaDeviceCanAccessPeer(&can, e->d.device, sd[q].device));
+        if (!can) return fail(NLS_ERR_CUDA, "no peer access between the slab devices");
+        cudaError_t pe = cudaDeviceEnablePeerAccess(sd[q].device, 0);
+        if (pe != cudaSuccess && pe != cudaErrorPeerAccessAlreadyEnabled)
+          return fail(NLS_ERR_CUDA, std::string("cudaDeviceEnablePeerAccess: ") + cudaGetErrorString(pe));
+        cudaGetLastError();
+      }
+      p.base = (char *)(uintptr_t)sd[q].raw;
+    } else {
+      void *m = nullptr;
+      CU(cudaIpcOpenMemHandle(&m, sd[q].ipc, cudaIpcMemLazyEnablePeerAccess));
+      p.base = (char *)m; p.ipc = true;
+    }
+    sc.box[q] = (SlabMailbox *)p.base;
+  }
+  CU(cudaMemcpy(e->slab_dev, &sc, sizeof sc, cudaMemcpyHostToDevice));
+  e->rank = rank; e->nranks = nranks;
+  e->rc.slab = e->slab_dev;
+  e->connected = true;
+  e->start_valid = false;
   return NLS_OK;
 }
 

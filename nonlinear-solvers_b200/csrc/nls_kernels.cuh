@@ -128,7 +128,7 @@ k_lanczos_pb(Geom g, S *__restrict__ w, const S *__restrict__ V, size_t colstrid
 template <class S, int NV, bool LAST>
 __global__ void __launch_bounds__(kThreads)
 k_lanczos_pc(Geom g, S *__restrict__ w, const S *__restrict__ V, size_t colstride, int j, int i0,
-             int cnt, const double *hsrc_base, int hoff, double *scal, RedCtx rc) {
+             int cnt, const double *hsrc_base, int hoff, double *scal, RedCtx rc, Halo<S> hp) {
   using T = Sc<S>;
   double *sb = scal + (size_t)blockIdx.y * kScalStride;
   const double *hs = hsrc_base + (size_t)blockIdx.y * kScalStride + hoff;
@@ -145,7 +145,10 @@ k_lanczos_pc(Geom g, S *__restrict__ w, const S *__restrict__ V, size_t colstrid
     for (int i = 0; i < NV; ++i)
       if (i < cnt) wv = T::sub(wv, T::mul(h[i], vb[(size_t)(i0 + i) * colstride + idx]));
     wb[idx] = wv;
-    if (LAST) acc[0] += T::abs2(wv);
+    if (LAST) {
+      acc[0] += T::abs2(wv);
+      halo_push<S>(hp, g.n, g.plane, idx, wv); // w_j is the next iteration's stencil input
+    }
   }
   if (LAST) grid_reduce<1>(acc, rc, sb + kOffNrm2 + j + 1);
 }
@@ -369,7 +372,7 @@ __device__ __forceinline__ double2 nlse_phase(const NlseParams &p, double mval, 
 template <int EQ>
 __global__ void __launch_bounds__(kThreads)
 k_nlse_prephase(Geom g, const double2 *__restrict__ u, const double *__restrict__ mf,
-                double2 *__restrict__ rho, NlseParams p, double *scal, RedCtx rc) {
+                double2 *__restrict__ rho, NlseParams p, double *scal, RedCtx rc, Halo<double2> hp) {
   const double2 *ub = traj(u, g);
   double2 *rb = traj(rho, g);
   const double *mb = mf + g.halo;
@@ -379,6 +382,7 @@ k_nlse_prephase(Geom g, const double2 *__restrict__ u, const double *__restrict_
     const double2 uv = ub[idx];
     const double2 r = nlse_phase<EQ>(p, mb[idx], uv, uv, uv);
     rb[idx] = r;
+    halo_push<double2>(hp, g.n, g.plane, idx, r);
     acc[0] += r.x * r.x + r.y * r.y;
   }
   grid_reduce<1>(acc, rc, scal + (size_t)blockIdx.y * kScalStride + kOffNrm2);
@@ -394,7 +398,7 @@ k_nlse_finish(Geom g, const double2 *__restrict__ V, size_t colstride,
               const double2 *__restrict__ wlast, const double *__restrict__ coef, int m,
               const double2 *__restrict__ uold, const double *__restrict__ mf,
               double2 *__restrict__ uout, double2 *__restrict__ rho, NlseParams p, double *scal,
-              RedCtx rc) {
+              RedCtx rc, Halo<double2> hp) {
   __shared__ double co[kCoefStride];
   const double *cg = coef + ((size_t)blockIdx.y * 2) * kCoefStride;
   for (int i = threadIdx.x; i < 2 * m; i += kThreads) co[i] = cg[i];
@@ -413,6 +417,7 @@ k_nlse_finish(Geom g, const double2 *__restrict__ V, size_t colstride,
     un[idx] = unew;
     const double2 r = nlse_phase<EQ>(p, mb[idx], unew, unew, unew);
     rb[idx] = r;
+    halo_push<double2>(hp, g.n, g.plane, idx, r);
     acc[0] += r.x * r.x + r.y * r.y;
   }
   grid_reduce<1>(acc, rc, scal + (size_t)blockIdx.y * kScalStride + kOffNrm2);
@@ -437,7 +442,8 @@ __global__ void __launch_bounds__(kThreads)
 k_gautschi_a(Geom g, const double *__restrict__ V, size_t colstride,
              const double *__restrict__ wlast, const double *__restrict__ coef, int m,
              const double *__restrict__ u, double *__restrict__ upast, const double *__restrict__ mf,
-             double *__restrict__ gout, double *__restrict__ accout, double *scalB, RedCtx rc) {
+             double *__restrict__ gout, double *__restrict__ accout, double *scalB, RedCtx rc,
+             Halo<double> hp) {
   __shared__ double cof[kCoefStride], coc[kCoefStride];
   const double *cg = coef + ((size_t)blockIdx.y * 2) * kCoefStride;
   for (int i = threadIdx.x; i < 2 * m; i += kThreads) {
@@ -462,6 +468,7 @@ k_gautschi_a(Geom g, const double *__restrict__ V, size_t colstride,
     sc = fma(v, coc[2 * (m - 1)], sc);
     const double gv = -(mb[idx] * f_real<EQ>(sf));
     go[idx] = gv;
+    halo_push<double>(hp, g.n, g.plane, idx, gv);
     acc[0] += gv * gv;
     ao[idx] = 2 * sc - up[idx];
     up[idx] = ub[idx];
@@ -475,7 +482,7 @@ __global__ void __launch_bounds__(kThreads)
 k_gautschi_b(Geom g, const double *__restrict__ V, size_t colstride,
              const double *__restrict__ wlast, const double *__restrict__ coef, int m,
              const double *__restrict__ accin, double *__restrict__ u, double tau2, double *scalA,
-             RedCtx rc) {
+             RedCtx rc, Halo<double> hp) {
   __shared__ double co[kCoefStride];
   const double *cg = coef + ((size_t)blockIdx.y * 2) * kCoefStride;
   for (int i = threadIdx.x; i < 2 * m; i += kThreads) co[i] = cg[i];
@@ -489,6 +496,7 @@ k_gautschi_b(Geom g, const double *__restrict__ V, size_t colstride,
     const double s = combine_site<double>(vb, colstride, wl, co, m, sc);
     const double un = ai[sc] + tau2 * s;
     ub[idx] = un;
+    halo_push<double>(hp, g.n, g.plane, idx, un);
     acc[0] += un * un;
   }
   grid_reduce<1>(acc, rc, scalA + (size_t)blockIdx.y * kScalStride + kOffNrm2);
@@ -501,7 +509,7 @@ template <int EQ, bool ANISO>
 __global__ void __launch_bounds__(kThreads)
 k_sv(Geom g, const double *__restrict__ u, const double *__restrict__ upast,
      const double *__restrict__ mf, const double *__restrict__ cf, double *__restrict__ unew,
-     double tau2) {
+     double tau2, RedCtx rc, Halo<double> hp, double *slab_scratch) {
   const double *ub = traj(u, g), *up = traj(upast, g);
   double *un = traj(unew, g);
   const double *mb = mf + g.halo;
@@ -512,8 +520,29 @@ k_sv(Geom g, const double *__restrict__ u, const double *__restrict__ upast,
     const double uc = ub[sc];
     const double lu = stencil_site<double, ANISO>(g, ub, cb, sc, 1.0);
     const double buf = lu - mb[sc] * f_real<EQ>(uc);
-    un[idx] = 2 * uc - up[sc] + tau2 * buf;
+    const double v = 2 * uc - up[sc] + tau2 * buf;
+    un[idx] = v;
+    halo_push<double>(hp, g.n, g.plane, idx, v);
   }
+  if (rc.slab != nullptr) { // cross-slab barrier: ghost planes complete before the next step reads them
+    double acc[1] = {0.0};
+    grid_reduce<1>(acc, rc, slab_scratch);
+  }
+}
+
+// z-slabs: push the first/last owned plane of x into the neighbours' ghost planes, then a
+// cross-slab barrier (used after host uploads of stencil inputs: U, C, matfunc/stencil input)
+template <class S>
+__global__ void __launch_bounds__(kThreads)
+k_halo_exchange(Geom g, const S *__restrict__ x, RedCtx rc, Halo<S> hp, double *slab_scratch) {
+  const S *xb = x + g.halo;
+  for (long long t = (long long)blockIdx.x * kThreads + threadIdx.x; t < 2 * g.plane;
+       t += (long long)gridDim.x * kThreads) {
+    const long long idx = t < g.plane ? t : g.n - 2 * g.plane + t;
+    halo_push<S>(hp, g.n, g.plane, idx, xb[idx]);
+  }
+  double acc[1] = {0.0};
+  grid_reduce<1>(acc, rc, slab_scratch);
 }
 
 // v = (u - u_past)/dt     sg_single_driver.cpp:113
