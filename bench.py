@@ -209,6 +209,8 @@ def run_reference(args, w, rank, world):
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import orc
     cores = orc.Oracle.threads()
+    if "slab_planes" in w:  # the CPU cannot hold the slab workload: same equation on a 128^3 cube
+        w = dict(w, n=128)
     d = make_desc(w, batch=cores)
     u0, v0 = make_state(w, 1)
     u0 = np.repeat(u0, cores, axis=0)

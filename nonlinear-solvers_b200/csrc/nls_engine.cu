@@ -729,6 +729,9 @@ int nls_stencil_apply(nls_handle e, const void *x, void *y) {
     if (an) LAUNCH(e, (k_stencil<double, true>), e->grid(), e->g, (const double *)e->w0, (double *)e->wbuf[0], e->cf);
     else LAUNCH(e, (k_stencil<double, false>), e->grid(), e->g, (const double *)e->w0, (double *)e->wbuf[0], e->cf);
   }
+  // slabs: trailing cross-slab barrier so a peer's next upload cannot overwrite ghost planes still being read
+  if (e->cplx) halo_exchange<double2>(e, e->wbuf[0]);
+  else halo_exchange<double>(e, e->wbuf[0]);
   CU(cudaGetLastError());
   e->start_valid = false; // w0 was overwritten
   return copy_out(e, y, e->wbuf[0], e->esz, e->batch, false);
