@@ -66,7 +66,13 @@ enum {
 enum {
   NLS_INT_SS2 = 0,      /* Strang splitting, NLSE only */
   NLS_INT_GAUTSCHI = 1, /* Gautschi-type, real equations only */
-  NLS_INT_SV = 2        /* Stoermer-Verlet, real equations only */
+  NLS_INT_SV = 2,       /* Stoermer-Verlet, real equations only */
+  NLS_INT_SEWI = 3      /* NLSE two-step symmetric exponential wave integrator ("Gautschi" NLSE):
+                         * u+ = e^{2 tau L} u- - 2 tau e^{tau L} sinc(dt L) B(u), B = -m g(|u|^2) u, tau = i dt
+                         * (nlse_cubic_gautschi_solver_3d.hpp:8-35, nlse_cubic_quintic_gautschi_solver.hpp:11-41,
+                         * nlse_saturating_gautschi_solver.hpp:11-44, device nlse_dev.hpp:205-238); the first
+                         * step after nls_set_field(U) is one SS2 step with u- = u0
+                         * (nlse_cubic_gautschi_driver.cpp:122-125, nlse_dev.hpp:206-209) */
 };
 
 /* Laplacian flavour */
@@ -95,7 +101,7 @@ enum {
 /* fields addressable through nls_set_field / nls_get_field */
 enum {
   NLS_FIELD_U = 0,      /* state u (complex128 for NLSE, float64 otherwise) */
-  NLS_FIELD_U_PAST = 1, /* previous state (real equations) */
+  NLS_FIELD_U_PAST = 1, /* previous state (real equations; NLS_INT_SEWI: u-, setting it skips the SS2 start-up) */
   NLS_FIELD_V = 2,      /* get: (u-u_past)/dt  sg_single_driver.cpp:113; set: u_past = u - dt*v (:70) */
   NLS_FIELD_M = 3,      /* m(x): float64, n values, shared by the whole batch */
   NLS_FIELD_C = 4       /* c(x): float64, n values (NLS_LAP_ANISO only) */
@@ -130,7 +136,10 @@ typedef struct nls_desc {
 
 enum {
   NLS_FLAG_NO_GRAPH = 1u, /* launch kernels directly instead of replaying a CUDA graph */
-  NLS_FLAG_NO_PERSISTENT = 2u /* never use the persistent cooperative step kernel */
+  NLS_FLAG_NO_PERSISTENT = 2u, /* never use the persistent cooperative step kernel */
+  NLS_FLAG_SEWI_HOST2D = 4u /* NLS_INT_SEWI with the sign convention of the 2D cubic HOST solver:
+                             * u+ = e^{-2 tau L} u- + 2 tau e^{-tau L} sinc(dt L) B(u)
+                             * (nlse_cubic_gautschi_solver.hpp:21-39) */
 };
 
 const char *nls_last_error(void);

@@ -39,7 +39,7 @@ inline void check(int rc, const char *what) {
 class Handle {
 public:
   Handle(const Grid &g, int equation, int integrator, uint32_t krylov_m, double dt = 0.0, double s1 = 0.0,
-         double s2 = 0.0, double kappa = 0.0, uint32_t batch = 1, int device = 0) {
+         double s2 = 0.0, double kappa = 0.0, uint32_t batch = 1, int device = 0, uint32_t flags = 0) {
     nls_desc d;
     std::memset(&d, 0, sizeof d);
     d.struct_size = sizeof d;
@@ -50,7 +50,7 @@ public:
     d.reorth = NLS_REORTH_FULL;
     d.krylov_m = krylov_m; d.batch = batch;
     d.s1 = s1; d.s2 = s2; d.kappa = kappa;
-    d.op_sign = g.op_sign; d.dt = dt; d.device = device;
+    d.op_sign = g.op_sign; d.dt = dt; d.device = device; d.flags = flags;
     n_ = g.n(); batch_ = batch;
     cplx_ = equation <= NLS_EQ_NLSE_SAT;
     check(nls_create(&d, &h_), "nls_create");
@@ -93,8 +93,9 @@ struct Parameters { // nlse_dev.hpp:68-76, nlse_cubic_quintic_dev.hpp:17-28, sg_
 template <int EQ> class NLSESolverBase {
 public:
   using Scalar = std::complex<double>;
-  NLSESolverBase(const nls::Grid &g, const Scalar *host_u0, const double *host_m, const Parameters &p)
-      : h_(g, EQ, NLS_INT_SS2, p.krylov_dim, 0.0, p.sigma1, p.sigma2, p.kappa), p_(p), n_(g.n()) {
+  NLSESolverBase(const nls::Grid &g, const Scalar *host_u0, const double *host_m, const Parameters &p,
+                 int integrator = NLS_INT_SS2)
+      : h_(g, EQ, integrator, p.krylov_dim, 0.0, p.sigma1, p.sigma2, p.kappa), p_(p), n_(g.n()) {
     h_.set(NLS_FIELD_U, host_u0, n_ * sizeof(Scalar));
     std::vector<double> ones;
     if (!host_m) { ones.assign(n_, 1.0); host_m = ones.data(); } // nlse_cubic_quintic_driver_dev.cpp:83-85
@@ -116,6 +117,9 @@ public:
       if (idx < p_.num_snapshots) h_.get(NLS_FIELD_U, host_dst + (size_t)idx * n_, n_ * sizeof(Scalar));
     }
   }
+  // sEWI step (nlse_dev.hpp:205-238): construct the solver with sewi = true; the first call is the SS2
+  // start-up step with u- = u0, exactly as the reference's `if (step_number == 1)` branch
+  void step_sewi(const Scalar tau, const uint32_t step_number, Scalar *host_dst) { step(tau, step_number, host_dst); }
   void apply_bc() {} // fused into step()
   void transfer_snapshots(Scalar *dst) { std::memcpy(dst, traj_.data(), traj_.size() * sizeof(Scalar)); }
   void current_state(Scalar *dst) { h_.get(NLS_FIELD_U, dst, n_ * sizeof(Scalar)); }
@@ -132,8 +136,8 @@ protected:
 class NLSESolverDevice : public NLSESolverBase<NLS_EQ_NLSE_CUBIC> { // nlse_dev.hpp:66-361
 public:
   NLSESolverDevice(const nls::Grid &g, const Scalar *host_u0, const double *host_m, const bool & /*is_3d*/,
-                   const Parameters &p = Parameters())
-      : NLSESolverBase(g, host_u0, host_m, p) {}
+                   const Parameters &p = Parameters(), bool sewi = false)
+      : NLSESolverBase(g, host_u0, host_m, p, sewi ? NLS_INT_SEWI : NLS_INT_SS2) {}
   NLSESolverDevice(const nls::Grid &g, const Scalar *host_u0, const Parameters &p = Parameters()) // gen-1
       : NLSESolverBase(g, host_u0, nullptr, p) {}
 };

@@ -217,7 +217,7 @@ struct RedCtx {
 
 // called by all threads of the last CTA; s_tot[K] holds this slab's totals
 template <int K>
-__device__ __forceinline__ void slab_allreduce(const SlabCtx &sc, double *s_tot, double *dst) {
+__device__ __forceinline__ void slab_allreduce(const SlabCtx &sc, double *s_tot, double *dst, double *dst1, int split) {
   static_assert(K <= kSlabMaxK, "reduction too wide for the slab mailbox");
   SlabMailbox *mine = sc.box[sc.rank];
   const unsigned long long seq = *(volatile unsigned long long *)&mine->seq; // written only by this rank's previous reduction
@@ -245,13 +245,14 @@ __device__ __forceinline__ void slab_allreduce(const SlabCtx &sc, double *s_tot,
   if ((int)threadIdx.x < K) {
     double v = 0.0;
     for (int q = 0; q < G; ++q) v += *(volatile double *)&mine->red[slot][q][threadIdx.x];
-    dst[threadIdx.x] = v;
+    if ((int)threadIdx.x < split) dst[threadIdx.x] = v;
+    else dst1[threadIdx.x - split] = v;
   }
   if (threadIdx.x == 0) mine->seq = seq + 1;
 }
 
 template <int K>
-__device__ __forceinline__ void grid_reduce(double (&acc)[K], const RedCtx &rc, double *dst) {
+__device__ __forceinline__ void grid_reduce_impl(double (&acc)[K], const RedCtx &rc, double *dst, double *dst1, int split) {
   __shared__ double s_part[kThreads / 32][K];
   __shared__ double s_tot[K];
   __shared__ bool s_last;
@@ -293,13 +294,24 @@ __device__ __forceinline__ void grid_reduce(double (&acc)[K], const RedCtx &rc, 
     for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
     if (lane == 0) {
       if (slab) s_tot[k] = v;
-      else dst[k] = v;
+      else if (k < split) dst[k] = v;
+      else dst1[k - split] = v;
     }
   }
   if (slab) {
     __syncthreads();
-    slab_allreduce<K>(*rc.slab, s_tot, dst);
+    slab_allreduce<K>(*rc.slab, s_tot, dst, dst1, split);
   }
+}
+
+template <int K>
+__device__ __forceinline__ void grid_reduce(double (&acc)[K], const RedCtx &rc, double *dst) {
+  grid_reduce_impl<K>(acc, rc, dst, dst, K);
+}
+// H+1 values: the first H totals go to dst0[0..H), the last one to dst1[0]
+template <int H>
+__device__ __forceinline__ void grid_reduce2s(double (&acc)[H + 1], const RedCtx &rc, double *dst0, double *dst1) {
+  grid_reduce_impl<H + 1>(acc, rc, dst0, dst1, H);
 }
 
 } // namespace nls

@@ -9,6 +9,7 @@
 #include <cstdio>
 #include <cstring>
 #include <string>
+#include <unordered_map>
 #include <vector>
 
 using namespace nls;
@@ -39,7 +40,8 @@ struct nls_engine {
   size_t esz = 8;
   int m = 10;
   int batch = 1;
-  int nblk = 1;
+  int nblk = 1; // capacity of the partial-sum array (max CTAs per trajectory)
+  int nsm = 148;
   cudaStream_t stream = nullptr;
   // device memory (all n-vectors: [batch][stride] scalars)
   void *V = nullptr;     // m-1 columns
@@ -55,6 +57,7 @@ struct nls_engine {
   // stepping state
   int nphase = 1, phase = 0;
   bool start_valid = false;
+  bool sewi_started = false; // NLS_INT_SEWI: u- is valid (the SS2 start-up step has been taken)
   double start_dt = 0.0;
   cudaGraphExec_t gexec[3] = {nullptr, nullptr, nullptr};
   double gdt[3] = {0, 0, 0};
@@ -89,15 +92,38 @@ struct nls_engine {
     if (capturing) cap_count++;
     else launches++;
   }
-  int ui() const { return cplx ? phase : 0; } // index of the current u buffer (SV: see sv_idx)
+  void *sv(int p) const { return p == 0 ? w0 : wbuf[0]; } // NLSE start vector (rho) of u[p]
 };
 
 namespace {
 
-#define LAUNCH(e, kern, gr, ...)                       \
-  do {                                                 \
-    kern<<<gr, kThreads, 0, (e)->stream>>>(__VA_ARGS__); \
-    (e)->count();                                      \
+// Persistent-style grids: (resident CTAs per SM for THIS kernel) x (number of SMs) CTAs per
+// launch, split over the batch, so every launch is exactly one wave (a fixed 4 CTAs/SM grid ran
+// 1.33 waves for the kernels that need > 64 registers).  Grid-stride loops cover the rest.
+dim3 grid_for(nls_engine *e, const void *fn) {
+  static thread_local std::unordered_map<const void *, int> occ_cache;
+  auto it = occ_cache.find(fn);
+  int occ;
+  if (it == occ_cache.end()) {
+    occ = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn, kThreads, 0) != cudaSuccess || occ < 1) {
+      cudaGetLastError();
+      occ = 1;
+    }
+    occ_cache[fn] = occ;
+  } else occ = it->second;
+  long long per = ((long long)e->nsm * occ) / e->batch;
+  if (per < 1) per = 1;
+  const long long want = (e->g.n + kThreads - 1) / kThreads;
+  if (per > want) per = want;
+  if (per > e->nblk) per = e->nblk;
+  return dim3((unsigned)per, (unsigned)e->batch);
+}
+
+#define LAUNCH(e, kern, gr, ...)                                                   \
+  do {                                                                             \
+    kern<<<grid_for(e, (const void *)kern), kThreads, 0, (e)->stream>>>(__VA_ARGS__); \
+    (e)->count();                                                                  \
   } while (0)
 
 template <class S>
@@ -106,7 +132,7 @@ S *col(nls_engine *e, int j) {
 }
 
 // ---------------------------------------------------------------- z-slab exchange arena
-constexpr int kArenaSlots = 7; // wbuf0, wbuf1, w0, u0, u1, u2, cf
+constexpr int kArenaSlots = 7; // wbuf0, wbuf1, w0, u0, u1, u2, cf; then the m-1 basis columns
 constexpr size_t kMailboxBytes = (sizeof(SlabMailbox) + 4095) / 4096 * 4096;
 
 struct SlabDesc { // the 128-byte blob of nls_slab_export
@@ -125,7 +151,8 @@ Halo<S> halo_for(nls_engine *e, const void *local) {
   Halo<S> h{nullptr, nullptr};
   if (!e->slab || !e->connected || !local) return h;
   const ptrdiff_t off = (const char *)local - (e->arena + kMailboxBytes);
-  if (off < 0 || (size_t)off >= kArenaSlots * e->slot_bytes || off % (ptrdiff_t)e->slot_bytes) return h;
+  if (off < 0 || (size_t)off >= (size_t)(kArenaSlots + e->m - 1) * e->slot_bytes || off % (ptrdiff_t)e->slot_bytes)
+    return h;
   const int slot = (int)(off / (ptrdiff_t)e->slot_bytes);
   const size_t plane = (size_t)e->g.plane;
   if (e->rank > 0) {
@@ -155,39 +182,47 @@ template <class S, bool ANISO>
 void lanczos_t(nls_engine *e, const S *start, double *scal) {
   const int m = e->m;
   const dim3 gr = e->grid();
+  S *V = (S *)e->V;
+  constexpr int kNC = 12; // columns per launch
   for (int j = 0; j < m - 1; ++j) {
-    const S *wprev = j == 0 ? start : (const S *)e->wbuf[(j - 1) & 1];
-    S *wout = (S *)e->wbuf[j & 1];
-    const S *vprev = j > 0 ? col<S>(e, j - 1) : nullptr;
-    LAUNCH(e, (k_lanczos_pa<S, ANISO>), gr, e->g, wprev, vprev, col<S>(e, j), wout, e->cf, scal, j,
-           e->rc);
-    if (e->d.reorth == NLS_REORTH_NONE) {
-      LAUNCH(e, (k_lanczos_pc<S, 4, true>), gr, e->g, wout, (const S *)e->V, e->colstride, j, j, 1,
-             scal, kOffAlpha + j * e->W, scal, e->rc, halo_for<S>(e, wout));
-      continue;
-    }
-    const int nv = j + 1;
-    for (int i0 = 0; i0 < nv; i0 += 16) {
-      const int cnt = nv - i0 < 16 ? nv - i0 : 16;
-      if (cnt <= 4) LAUNCH(e, (k_lanczos_pb<S, 4>), gr, e->g, wout, (const S *)e->V, e->colstride, j, i0, cnt, scal, e->rc);
-      else if (cnt <= 8) LAUNCH(e, (k_lanczos_pb<S, 8>), gr, e->g, wout, (const S *)e->V, e->colstride, j, i0, cnt, scal, e->rc);
-      else if (cnt <= 12) LAUNCH(e, (k_lanczos_pb<S, 12>), gr, e->g, wout, (const S *)e->V, e->colstride, j, i0, cnt, scal, e->rc);
-      else LAUNCH(e, (k_lanczos_pb<S, 16>), gr, e->g, wout, (const S *)e->V, e->colstride, j, i0, cnt, scal, e->rc);
-    }
-    for (int i0 = 0; i0 < nv; i0 += 16) {
-      const int cnt = nv - i0 < 16 ? nv - i0 : 16;
-      const bool last = i0 + 16 >= nv;
-      const int hoff = kOffH + i0 * e->W;
-#define PC(NV)                                                                                      \
-  do {                                                                                              \
-    if (last) LAUNCH(e, (k_lanczos_pc<S, NV, true>), gr, e->g, wout, (const S *)e->V, e->colstride, j, i0, cnt, scal, hoff, scal, e->rc, halo_for<S>(e, wout)); \
-    else LAUNCH(e, (k_lanczos_pc<S, NV, false>), gr, e->g, wout, (const S *)e->V, e->colstride, j, i0, cnt, scal, hoff, scal, e->rc, Halo<S>{nullptr, nullptr});     \
+    // columns taking part in the orthogonalisation: all of 0..j (reference), or only j (3-term)
+    const int c0 = e->d.reorth == NLS_REORTH_NONE ? j : 0;
+    for (int i0 = c0; i0 <= j; i0 += kNC) {
+      const int cnt = j + 1 - i0 < kNC ? j + 1 - i0 : kNC;
+      const bool first = i0 == c0;
+#define LA(NC)                                                                                           \
+  do {                                                                                                   \
+    if (first) LAUNCH(e, (k_lanczos_a<S, ANISO, NC, true>), gr, e->g, start, V, e->colstride, j, i0, cnt, e->cf, scal, e->rc);  \
+    else LAUNCH(e, (k_lanczos_a<S, ANISO, NC, false>), gr, e->g, start, V, e->colstride, j, i0, cnt, e->cf, scal, e->rc);       \
   } while (0)
-      if (cnt <= 4) PC(4);
-      else if (cnt <= 8) PC(8);
-      else if (cnt <= 12) PC(12);
-      else PC(16);
-#undef PC
+      if (cnt <= 2) LA(2);
+      else if (cnt <= 4) LA(4);
+      else if (cnt <= 6) LA(6);
+      else if (cnt <= 8) LA(8);
+      else if (cnt <= 10) LA(10);
+      else LA(12);
+#undef LA
+    }
+    // Gram entries of column j against the columns the LAST chunk of the previous pass B did not hold
+    if (c0 == 0 && j >= 1)
+      for (int i0 = 0; i0 < ((j - 1) / kNC) * kNC; i0 += kNC)
+        LAUNCH(e, (k_lanczos_g<S, kNC>), gr, e->g, start, (const S *)V, e->colstride, j, i0, kNC, scal, e->rc);
+    for (int i0 = c0; i0 <= j; i0 += kNC) {
+      const int cnt = j + 1 - i0 < kNC ? j + 1 - i0 : kNC;
+      const bool last = i0 + kNC > j;
+      const Halo<S> hp = last ? halo_for<S>(e, V + (size_t)j * e->colstride) : Halo<S>{nullptr, nullptr};
+#define LB(NC)                                                                                           \
+  do {                                                                                                   \
+    if (last) LAUNCH(e, (k_lanczos_b<S, NC, true>), gr, e->g, start, V, e->colstride, j, i0, cnt, scal, e->rc, hp);  \
+    else LAUNCH(e, (k_lanczos_b<S, NC, false>), gr, e->g, start, V, e->colstride, j, i0, cnt, scal, e->rc, hp);      \
+  } while (0)
+      if (cnt <= 2) LB(2);
+      else if (cnt <= 4) LB(4);
+      else if (cnt <= 6) LB(6);
+      else if (cnt <= 8) LB(8);
+      else if (cnt <= 10) LB(10);
+      else LB(12);
+#undef LB
     }
   }
 }
@@ -196,11 +231,6 @@ template <class S>
 void lanczos(nls_engine *e, const S *start, double *scal) {
   if (e->d.laplacian == NLS_LAP_ANISO) lanczos_t<S, true>(e, start, scal);
   else lanczos_t<S, false>(e, start, scal);
-}
-
-template <class S>
-const S *wlast(nls_engine *e) {
-  return (const S *)e->wbuf[(e->m - 2) & 1];
 }
 
 void tridiag(nls_engine *e, const double *scal, int nfn, int f0, double t0r, double t0i, int f1,
@@ -217,15 +247,57 @@ void tridiag(nls_engine *e, const double *scal, int nfn, int f0, double t0r, dou
 
 // ---------------------------------------------------------------- one time step
 template <int EQ>
-void nlse_step_t(nls_engine *e, double dt) {
-  const double2 *uin = (const double2 *)e->u[e->phase];
-  double2 *uout = (double2 *)e->u[1 - e->phase];
-  lanczos<double2>(e, (const double2 *)e->w0, e->scalA);
+void nlse_step_bufs(nls_engine *e, double dt, const double2 *uin, double2 *uout, const double2 *scur, double2 *snext) {
+  lanczos<double2>(e, scur, e->scalA);
   tridiag(e, e->scalA, 1, NLS_FN_EXP, 0.0, dt, 0, 0, 0); // expm_multiply(L, rho, tau = i dt)
   NlseParams p{0.5 * dt, e->d.s1, e->d.s2, e->d.kappa};
-  LAUNCH(e, (k_nlse_finish<EQ>), e->grid(), e->g, (const double2 *)e->V, e->colstride,
-         wlast<double2>(e), e->coef, e->m, uin, e->mf, uout, (double2 *)e->w0, p, e->scalA, e->rc,
+  LAUNCH(e, (k_nlse_finish<EQ>), e->grid(), e->g, scur, (const double2 *)e->V, e->colstride,
+         e->coef, e->m, uin, e->mf, uout, snext, p, e->scalA, e->rc, halo_for<double2>(e, snext));
+}
+
+template <int EQ>
+void nlse_step_t(nls_engine *e, double dt) {
+  // start-vector ping-pong (column 0 of the basis is read at clamped sites while the next rho is written)
+  nlse_step_bufs<EQ>(e, dt, (const double2 *)e->u[e->phase], (double2 *)e->u[1 - e->phase],
+                     (const double2 *)e->sv(e->phase), (double2 *)e->sv(1 - e->phase));
+}
+
+// sEWI (NLS_INT_SEWI): three rotating state buffers u = buf[p], u- = buf[(p+2)%3], u+ -> buf[(p+1)%3].
+// First step after a state upload: one SS2 step with u- = u0 (nlse_cubic_gautschi_driver.cpp:122-125).
+template <int EQ>
+void sewi_first_step_t(nls_engine *e, double dt) {
+  NlseParams p{0.5 * dt, e->d.s1, e->d.s2, e->d.kappa};
+  const double2 *u = (const double2 *)e->u[e->phase];
+  LAUNCH(e, (k_nlse_prephase<EQ>), e->grid(), e->g, u, e->mf, (double2 *)e->w0, p, e->scalA, e->rc,
          halo_for<double2>(e, e->w0));
+  nlse_step_bufs<EQ>(e, dt, u, (double2 *)e->u[(e->phase + 1) % 3], (const double2 *)e->w0, (double2 *)e->wbuf[0]);
+}
+
+// u+ = e^{sg 2 tau L} u- - sg 2 tau e^{sg tau L} sinc(dt L) B(u)   (sg = -1: NLS_FLAG_SEWI_HOST2D)
+// nlse_cubic_gautschi_solver_3d.hpp:8-35 / nlse_cubic_gautschi_solver.hpp:21-39 / nlse_dev.hpp:205-238
+template <int EQ>
+void sewi_step_t(nls_engine *e, double dt) {
+  const double sg = (e->d.flags & NLS_FLAG_SEWI_HOST2D) ? -1.0 : 1.0;
+  const double2 *u = (const double2 *)e->u[e->phase];
+  const double2 *uprev = (const double2 *)e->u[(e->phase + 2) % 3];
+  double2 *unew = (double2 *)e->u[(e->phase + 1) % 3];
+  double2 *B = (double2 *)e->w0, *phi = (double2 *)e->wbuf[0], *a = (double2 *)e->acc;
+  const double2 *V = (const double2 *)e->V;
+  NlseParams p{0.5 * dt, e->d.s1, e->d.s2, e->d.kappa};
+  LAUNCH(e, (k_sewi_B<EQ>), e->grid(), e->g, u, e->mf, B, p, e->scalA, e->rc, halo_for<double2>(e, B));
+  lanczos<double2>(e, B, e->scalA);
+  tridiag(e, e->scalA, 1, NLS_FN_SINC, dt, 0.0, 0, 0, 0); // sincm_multiply(L, B, dt)
+  LAUNCH(e, (k_combine_norm<double2>), e->grid(), e->g, (const double2 *)B, V, e->colstride, e->coef, e->m, phi,
+         e->scalA, e->rc, halo_for<double2>(e, phi));
+  lanczos<double2>(e, phi, e->scalA);
+  tridiag(e, e->scalA, 1, NLS_FN_EXP, 0.0, sg * dt, 0, 0, 0); // expm_multiply(L, phi, sg tau)
+  LAUNCH(e, (k_combine<double2>), e->grid(), e->g, (const double2 *)phi, V, e->colstride, e->coef, 0, e->m, a);
+  halo_exchange<double2>(e, uprev); // slabs: u- becomes a stencil input
+  LAUNCH(e, (k_norm2<double2>), e->grid(), e->g, uprev, e->scalA + kOffNrm2, kScalStride, e->rc);
+  lanczos<double2>(e, uprev, e->scalA);
+  tridiag(e, e->scalA, 1, NLS_FN_EXP, 0.0, sg * 2.0 * dt, 0, 0, 0); // expm_multiply(L, u-, sg 2 tau)
+  LAUNCH(e, k_sewi_final, e->grid(), e->g, uprev, V, e->colstride, e->coef, e->m, (const double2 *)a, unew,
+         -sg * 2.0 * dt);
 }
 
 template <int EQ>
@@ -235,12 +307,12 @@ void gautschi_step_t(nls_engine *e, double dt) {
   const int filt = EQ == NLS_EQ_SGE ? NLS_FN_MOD_COSINE : NLS_FN_ID_SQRT;
   tridiag(e, e->scalA, 2, filt, dt, 0.0, NLS_FN_COS_SQRT, dt, 0.0);
   LAUNCH(e, (k_gautschi_a<EQ>), e->grid(), e->g, (const double *)e->V, e->colstride,
-         wlast<double>(e), e->coef, e->m, u, up, e->mf, (double *)e->w0, (double *)e->acc, e->scalB,
+         e->coef, e->m, u, up, e->mf, (double *)e->w0, (double *)e->acc, e->scalB,
          e->rc, halo_for<double>(e, e->w0));
   lanczos<double>(e, (const double *)e->w0, e->scalB);
   tridiag(e, e->scalB, 1, NLS_FN_SINC2_HALF, dt, 0.0, 0, 0, 0);
-  LAUNCH(e, (k_gautschi_b<0>), e->grid(), e->g, (const double *)e->V, e->colstride,
-         wlast<double>(e), e->coef, e->m, (const double *)e->acc, u, dt * dt, e->scalA, e->rc,
+  LAUNCH(e, (k_gautschi_b<0>), e->grid(), e->g, (const double *)e->w0, (const double *)e->V, e->colstride,
+         e->coef, e->m, (const double *)e->acc, u, dt * dt, e->scalA, e->rc,
          halo_for<double>(e, u));
 }
 
@@ -260,6 +332,18 @@ void sv_step_t(nls_engine *e, double dt) {
 
 void issue_step(nls_engine *e, double dt) {
   const int eq = e->d.equation;
+  if (e->cplx && e->d.integrator == NLS_INT_SEWI) {
+    if (!e->sewi_started) {
+      if (eq == NLS_EQ_NLSE_CUBIC) sewi_first_step_t<NLS_EQ_NLSE_CUBIC>(e, dt);
+      else if (eq == NLS_EQ_NLSE_CQ) sewi_first_step_t<NLS_EQ_NLSE_CQ>(e, dt);
+      else sewi_first_step_t<NLS_EQ_NLSE_SAT>(e, dt);
+    } else {
+      if (eq == NLS_EQ_NLSE_CUBIC) sewi_step_t<NLS_EQ_NLSE_CUBIC>(e, dt);
+      else if (eq == NLS_EQ_NLSE_CQ) sewi_step_t<NLS_EQ_NLSE_CQ>(e, dt);
+      else sewi_step_t<NLS_EQ_NLSE_SAT>(e, dt);
+    }
+    return;
+  }
   if (e->cplx) {
     if (eq == NLS_EQ_NLSE_CUBIC) nlse_step_t<NLS_EQ_NLSE_CUBIC>(e, dt);
     else if (eq == NLS_EQ_NLSE_CQ) nlse_step_t<NLS_EQ_NLSE_CQ>(e, dt);
@@ -289,23 +373,23 @@ double *cur_upast(nls_engine *e) {
 
 // make the start vector of the next step valid (first step, or after a state/dt change)
 int ensure_start(nls_engine *e, double dt) {
-  if (e->d.integrator == NLS_INT_SV) return NLS_OK;
+  if (e->d.integrator == NLS_INT_SV || e->d.integrator == NLS_INT_SEWI) return NLS_OK;
   if (e->start_valid && (!e->cplx || e->start_dt == dt)) return NLS_OK;
   if (e->cplx) {
     NlseParams p{0.5 * dt, e->d.s1, e->d.s2, e->d.kappa};
     const double2 *u = (const double2 *)e->u[e->phase];
     switch (e->d.equation) {
     case NLS_EQ_NLSE_CUBIC:
-      LAUNCH(e, (k_nlse_prephase<NLS_EQ_NLSE_CUBIC>), e->grid(), e->g, u, e->mf, (double2 *)e->w0, p, e->scalA, e->rc,
-             halo_for<double2>(e, e->w0));
+      LAUNCH(e, (k_nlse_prephase<NLS_EQ_NLSE_CUBIC>), e->grid(), e->g, u, e->mf, (double2 *)e->sv(e->phase), p, e->scalA, e->rc,
+             halo_for<double2>(e, e->sv(e->phase)));
       break;
     case NLS_EQ_NLSE_CQ:
-      LAUNCH(e, (k_nlse_prephase<NLS_EQ_NLSE_CQ>), e->grid(), e->g, u, e->mf, (double2 *)e->w0, p, e->scalA, e->rc,
-             halo_for<double2>(e, e->w0));
+      LAUNCH(e, (k_nlse_prephase<NLS_EQ_NLSE_CQ>), e->grid(), e->g, u, e->mf, (double2 *)e->sv(e->phase), p, e->scalA, e->rc,
+             halo_for<double2>(e, e->sv(e->phase)));
       break;
     default:
-      LAUNCH(e, (k_nlse_prephase<NLS_EQ_NLSE_SAT>), e->grid(), e->g, u, e->mf, (double2 *)e->w0, p, e->scalA, e->rc,
-             halo_for<double2>(e, e->w0));
+      LAUNCH(e, (k_nlse_prephase<NLS_EQ_NLSE_SAT>), e->grid(), e->g, u, e->mf, (double2 *)e->sv(e->phase), p, e->scalA, e->rc,
+             halo_for<double2>(e, e->sv(e->phase)));
     }
   } else {
     LAUNCH(e, (k_norm2<double>), e->grid(), e->g, (const double *)e->u[0], e->scalA + kOffNrm2,
@@ -327,6 +411,13 @@ int run_steps(nls_engine *e, double dt, uint32_t nsteps) {
   const bool use_graph = !(e->d.flags & NLS_FLAG_NO_GRAPH);
   for (uint32_t s = 0; s < nsteps; ++s) {
     const int p = e->phase;
+    if (e->d.integrator == NLS_INT_SEWI && !e->sewi_started) { // one-off SS2 start-up step, not worth a graph
+      issue_step(e, dt);
+      CU(cudaGetLastError());
+      e->sewi_started = true;
+      e->phase = (p + 1) % e->nphase;
+      continue;
+    }
     if (use_graph) {
       if (e->gexec[p] && e->gdt[p] != dt) {
         cudaGraphExecDestroy(e->gexec[p]);
@@ -481,7 +572,7 @@ int nls_destroy(nls_handle e) {
   for (auto &ge : e->gexec)
     if (ge) cudaGraphExecDestroy(ge);
   if (e->arena) { // sub-allocations of the exchange arena
-    e->wbuf[0] = e->wbuf[1] = e->w0 = e->u[0] = e->u[1] = e->u[2] = nullptr;
+    e->wbuf[0] = e->wbuf[1] = e->w0 = e->u[0] = e->u[1] = e->u[2] = e->V = nullptr;
     e->cf = nullptr;
     for (int q = 0; q < e->nranks; ++q)
       if (e->peers[q].ipc && e->peers[q].base) cudaIpcCloseMemHandle(e->peers[q].base);
@@ -504,7 +595,8 @@ int nls_create(const nls_desc *desc, nls_handle *out) {
     return fail(NLS_ERR_ARG, "bad sizes: need nx,ny>=3, nz==1 or >=3, 2<=m<=64, batch>=1");
   if (d.equation < NLS_EQ_NLSE_CUBIC || d.equation > NLS_EQ_SGE_SINH) return fail(NLS_ERR_ARG, "bad equation");
   const bool cplx = d.equation <= NLS_EQ_NLSE_SAT;
-  if (cplx && d.integrator != NLS_INT_SS2) return fail(NLS_ERR_ARG, "NLSE needs NLS_INT_SS2");
+  if (cplx && d.integrator != NLS_INT_SS2 && d.integrator != NLS_INT_SEWI)
+    return fail(NLS_ERR_ARG, "NLSE needs NLS_INT_SS2 or NLS_INT_SEWI");
   if (!cplx && d.integrator != NLS_INT_GAUTSCHI && d.integrator != NLS_INT_SV)
     return fail(NLS_ERR_ARG, "real equations need NLS_INT_GAUTSCHI or NLS_INT_SV");
   if (!(d.dx > 0) || !(d.dy > 0)) return fail(NLS_ERR_ARG, "dx, dy must be positive");
@@ -537,13 +629,15 @@ int nls_create(const nls_desc *desc, nls_handle *out) {
   const double sgn = d.op_sign == 0.0 ? 1.0 : d.op_sign;
   // L *= 1/(dx*dy) (laplacians.hpp:49); 3D: 1/(dx*dx) (:153)
   g.sc = sgn * (1.0 / (g.dim3 ? d.dx * d.dx : d.dx * d.dy));
+  cudaDeviceGetAttribute(&e->nsm, cudaDevAttrMultiProcessorCount, d.device);
+  if (e->nsm < 1) e->nsm = 148;
   long long want = (g.n + kThreads - 1) / kThreads;
-  long long cap = (148LL * 16 + e->batch - 1) / e->batch;
-  if (cap < 16) cap = 16;
-  if (cap > kMaxBlocksPerTraj) cap = kMaxBlocksPerTraj;
+  long long cap = 8LL * e->nsm; // at most 8 CTAs of 256 threads per SM
   e->nblk = (int)(want < cap ? want : cap);
-  e->colstride = e->vec_elems();
-  e->nphase = cplx ? 2 : (d.integrator == NLS_INT_SV ? 3 : 1);
+  e->slab = g.halo != 0;
+  e->slot_bytes = (g.stride * e->esz + 255) / 256 * 256;
+  e->colstride = e->slab ? e->slot_bytes / e->esz : e->vec_elems();
+  e->nphase = cplx ? (d.integrator == NLS_INT_SEWI ? 3 : 2) : (d.integrator == NLS_INT_SV ? 3 : 1);
 
   auto alloc = [&](void **p, size_t bytes) -> bool {
     if (cudaMalloc(p, bytes) != cudaSuccess) return false;
@@ -553,31 +647,30 @@ int nls_create(const nls_desc *desc, nls_handle *out) {
   const size_t vb = e->vec_bytes();
   const bool krylov = d.integrator != NLS_INT_SV;
   // the Krylov buffers are also used by nls_matfunc / nls_lanczos / nls_stencil_apply
-  ok = ok && alloc(&e->V, vb * (e->m - 1));
-  e->slab = g.halo != 0;
-  if (e->slab) { // stencil inputs + mailbox in one arena the other ranks can map
-    e->slot_bytes = (g.stride * e->esz + 255) / 256 * 256;
-    ok = ok && alloc((void **)&e->arena, kMailboxBytes + kArenaSlots * e->slot_bytes);
+  if (!(g.halo != 0)) ok = ok && alloc(&e->V, vb * (e->m - 1));
+  if (e->slab) { // stencil inputs (incl. the basis columns) + mailbox in one arena the other ranks can map
+    ok = ok && alloc((void **)&e->arena, kMailboxBytes + (size_t)(kArenaSlots + e->m - 1) * e->slot_bytes);
     if (ok) {
       char *b = e->arena + kMailboxBytes;
       e->wbuf[0] = b; e->wbuf[1] = b + e->slot_bytes; e->w0 = b + 2 * e->slot_bytes;
       e->u[0] = b + 3 * e->slot_bytes; e->u[1] = b + 4 * e->slot_bytes; e->u[2] = b + 5 * e->slot_bytes;
       e->cf = (double *)(b + 6 * e->slot_bytes);
+      e->V = b + (size_t)kArenaSlots * e->slot_bytes;
     }
     ok = ok && alloc((void **)&e->slab_dev, sizeof(SlabCtx)) && alloc((void **)&e->slab_scratch, 64);
     ok = ok && alloc((void **)&e->mf, g.stride * 8);
   } else {
     ok = ok && alloc(&e->wbuf[0], vb) && alloc(&e->wbuf[1], vb) && alloc(&e->w0, vb);
     ok = ok && alloc(&e->u[0], vb) && alloc(&e->u[1], vb);
-    if (d.integrator == NLS_INT_SV) ok = ok && alloc(&e->u[2], vb);
+    if (d.integrator == NLS_INT_SV || d.integrator == NLS_INT_SEWI) ok = ok && alloc(&e->u[2], vb);
     ok = ok && alloc((void **)&e->mf, g.stride * 8) && alloc((void **)&e->cf, g.stride * 8);
   }
-  if (d.integrator == NLS_INT_GAUTSCHI) ok = ok && alloc(&e->acc, vb);
+  if (d.integrator == NLS_INT_GAUTSCHI || d.integrator == NLS_INT_SEWI) ok = ok && alloc(&e->acc, vb);
   ok = ok && alloc((void **)&e->scalA, (size_t)e->batch * kScalStride * 8);
   ok = ok && alloc((void **)&e->scalB, (size_t)e->batch * kScalStride * 8);
   ok = ok && alloc((void **)&e->coef, (size_t)e->batch * 2 * kCoefStride * 8);
   ok = ok && alloc((void **)&e->redout, (size_t)e->batch * 8);
-  ok = ok && alloc((void **)&e->rc.partials, (size_t)e->batch * e->nblk * 32 * 8);
+  ok = ok && alloc((void **)&e->rc.partials, (size_t)e->batch * e->nblk * 48 * 8);
   ok = ok && alloc((void **)&e->rc.tickets, (size_t)e->batch * 4);
   ok = ok && alloc((void **)&e->status, 4);
   (void)krylov;
@@ -607,8 +700,15 @@ static int set_field_impl(nls_handle e, int field, const void *src, size_t bytes
     rc = copy_in(e, e->cplx ? e->u[e->phase] : (void *)cur_u(e), src, e->esz, e->batch, dev);
     break;
   case NLS_FIELD_U_PAST:
-    if (e->cplx) return fail(NLS_ERR_STATE, "U_PAST: real equations only");
     if (bytes != sb) return fail(NLS_ERR_ARG, "set U_PAST: size mismatch");
+    if (e->cplx) {
+      if (e->d.integrator != NLS_INT_SEWI) return fail(NLS_ERR_STATE, "U_PAST: real equations or NLS_INT_SEWI only");
+      rc = copy_in(e, e->u[(e->phase + 2) % 3], src, 16, e->batch, dev);
+      if (rc) return rc;
+      CU(cudaStreamSynchronize(e->stream));
+      e->sewi_started = true; // explicit u-: no SS2 start-up step
+      return NLS_OK;
+    }
     rc = copy_in(e, cur_upast(e), src, 8, e->batch, dev);
     break;
   case NLS_FIELD_V: { // u_past = u0 - dt*v0  (sg_single_driver.cpp:70)
@@ -631,6 +731,7 @@ static int set_field_impl(nls_handle e, int field, const void *src, size_t bytes
   default: return fail(NLS_ERR_ARG, "bad field");
   }
   if (rc) return rc;
+  if (field == NLS_FIELD_U) e->sewi_started = false;
   if (e->slab && e->connected) { // collective on slab handles: refresh the neighbours' ghost planes
     if (field == NLS_FIELD_C) halo_exchange<double>(e, e->cf);
     else if (field == NLS_FIELD_U && !e->cplx) halo_exchange<double>(e, cur_u(e));
@@ -652,7 +753,11 @@ static int get_field_impl(nls_handle e, int field, void *dst, size_t bytes, bool
     rc = copy_out(e, dst, e->cplx ? e->u[e->phase] : (void *)cur_u(e), e->esz, e->batch, dev);
     break;
   case NLS_FIELD_U_PAST:
-    if (e->cplx) return fail(NLS_ERR_STATE, "U_PAST: real equations only");
+    if (e->cplx) {
+      if (e->d.integrator != NLS_INT_SEWI) return fail(NLS_ERR_STATE, "U_PAST: real equations or NLS_INT_SEWI only");
+      rc = copy_out(e, dst, e->u[(e->phase + 2) % 3], 16, e->batch, dev);
+      break;
+    }
     rc = copy_out(e, dst, cur_upast(e), 8, e->batch, dev);
     break;
   case NLS_FIELD_V: // v = (u - u_past)/dt  (sg_single_driver.cpp:113)
@@ -765,14 +870,11 @@ int nls_matfunc(nls_handle e, int fn, double t_re, double t_im, const void *in, 
   int rc = lanczos_from_host(e, in);
   if (rc) return rc;
   tridiag(e, e->scalA, 1, fn, t_re, t_im, 0, 0, 0);
-  void *dst = e->u[2] ? e->u[2] : e->acc ? e->acc : e->u[1 - e->phase]; // scratch not holding state
+  void *dst = e->wbuf[1]; // scratch: neither state nor part of the basis
   if (e->cplx)
-    LAUNCH(e, (k_combine<double2>), e->grid(), e->g, (const double2 *)e->V, e->colstride, wlast<double2>(e), e->coef, 0, e->m, (double2 *)dst);
-  else {
-    // real scratch: SV has no spare buffer that is not state -> use wbuf not holding wlast
-    dst = e->wbuf[1 - ((e->m - 2) & 1)];
-    LAUNCH(e, (k_combine<double>), e->grid(), e->g, (const double *)e->V, e->colstride, wlast<double>(e), e->coef, 0, e->m, (double *)dst);
-  }
+    LAUNCH(e, (k_combine<double2>), e->grid(), e->g, (const double2 *)e->w0, (const double2 *)e->V, e->colstride, e->coef, 0, e->m, (double2 *)dst);
+  else
+    LAUNCH(e, (k_combine<double>), e->grid(), e->g, (const double *)e->w0, (const double *)e->V, e->colstride, e->coef, 0, e->m, (double *)dst);
   CU(cudaGetLastError());
   rc = copy_out(e, out, dst, e->esz, e->batch, false);
   return rc ? rc : check_status(e);
@@ -793,17 +895,16 @@ int nls_lanczos(nls_handle e, const void *in, void *hV, void *halpha, double *hb
     std::memset(halpha, 0, (size_t)m * e->esz); // T(m-1,m-1) stays 0
     std::memcpy(halpha, &sc[kOffAlpha], (size_t)(m - 1) * e->esz);
   }
-  if (hV) {
+  if (hV) { // columns are kept un-normalised on the device: V.col(i) = column_i / beta_i (presentation only)
     const size_t nb = (size_t)e->g.n * e->esz;
-    for (int j = 0; j < m - 1; ++j)
-      CU(cudaMemcpy((char *)hV + j * nb, (char *)e->V + ((size_t)j * e->colstride + e->g.halo) * e->esz, nb,
-                    cudaMemcpyDeviceToHost));
-    char *lastc = (char *)hV + (size_t)(m - 1) * nb;
-    CU(cudaMemcpy(lastc, (const char *)e->wbuf[(m - 2) & 1] + e->g.halo * e->esz, nb, cudaMemcpyDeviceToHost));
-    // V.col(m-1) = w / T(m-1,m-2)   (eigen_krylov_complex.hpp:46; presentation only)
-    const double off = std::sqrt(sc[kOffNrm2 + m - 1]);
-    double *p = (double *)lastc;
-    for (size_t i = 0; i < (size_t)e->g.n * e->W; ++i) p[i] /= off;
+    for (int jc = 0; jc < m; ++jc) {
+      const char *src = jc == 0 ? (const char *)e->w0 : (const char *)e->V + (size_t)(jc - 1) * e->colstride * e->esz;
+      char *dstc = (char *)hV + (size_t)jc * nb;
+      CU(cudaMemcpy(dstc, src + e->g.halo * e->esz, nb, cudaMemcpyDeviceToHost));
+      const double inv = 1.0 / std::sqrt(sc[kOffNrm2 + jc]);
+      double *p = (double *)dstc;
+      for (size_t i = 0; i < (size_t)e->g.n * e->W; ++i) p[i] *= inv;
+    }
   }
   return NLS_OK;
 }

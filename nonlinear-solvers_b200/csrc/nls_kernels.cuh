@@ -1,9 +1,10 @@
 // nls_kernels.cuh -- the hot-path kernels (all fp64 SIMT, HBM/L2-bandwidth bound).
 //
 //   K1  k_stencil            y = L x                         (replaces device/spmv.hpp:65-72)
-//   K2  k_lanczos_pa/pb/pc   one Lanczos iteration in three fused passes, scalars stay on
-//                            the device (replaces device/lanczos_complex.hpp:318-551 and the
-//                            host algorithm eigen_krylov_complex.hpp:13-52 / _real.hpp:8-55)
+//   K2  k_lanczos_a/b       one Lanczos iteration in two fused passes over an un-normalised
+//                            basis, scalars stay on the device (replaces
+//                            device/lanczos_complex.hpp:318-551 and the host algorithm
+//                            eigen_krylov_complex.hpp:13-52 / _real.hpp:8-55)
 //   K3  k_tridiag            m x m tridiagonal eigensolve + f(Lambda) -> coefficient vectors
 //                            (replaces cusolverDn{D,Z}{sy,he}evd, device/matfunc_*.hpp)
 //   K4  k_nlse_finish, k_gautschi_a/b, k_combine
@@ -14,7 +15,8 @@
 // Per-trajectory device scalars ("scalar block", doubles):
 //   [0 .. 64]           nrm2[j]  : nrm2[0] = ||start||^2, nrm2[j+1] = ||w_j||^2 = T(j+1,j)^2
 //   [65 .. 65+128)      alpha[j] : T(j,j) (W doubles each)
-//   [193 .. 193+128)    h[i]     : re-orthogonalisation coefficients of the current iteration
+//   [193 .. 193+128)    s[i]     : column_i^H w of the current iteration
+//   [328 .. 328+128)    g[i]     : column_i^H column_j (Gram entries of the newest column)
 #pragma once
 #include "nls_device.cuh"
 #include "../../include/nls.h"
@@ -24,7 +26,8 @@ namespace nls {
 constexpr int kOffNrm2 = 0;
 constexpr int kOffAlpha = 65;
 constexpr int kOffH = 193;
-constexpr int kScalStride = 328;
+constexpr int kOffG = 328;  // g[i] = column_i^H column_j of the current iteration (W doubles each)
+constexpr int kScalStride = 456;
 constexpr int kCoefStride = 2 * kMaxM; // doubles per coefficient vector
 
 // arrays hold [batch][stride] scalars with `halo` ghost elements in front of site 0
@@ -61,96 +64,149 @@ k_norm2(Geom g, const S *__restrict__ x, double *dst, int dst_stride, RedCtx rc)
   grid_reduce<1>(acc, rc, dst + (size_t)blockIdx.y * dst_stride);
 }
 
-// ------------------------------------------------------------------ K2, pass a
-// v_j = wprev / beta ; w = L v_j - beta v_{j-1} ; alpha_j = v_j^H w
-// (eigen_krylov_complex.hpp:22,:25-28,:46; the normalisation of the previous iteration is
-//  fused in so the un-normalised vector is read once, with its stencil halo).
-template <class S, bool ANISO>
-__global__ void __launch_bounds__(kThreads)
-k_lanczos_pa(Geom g, const S *__restrict__ wprev, const S *__restrict__ vprev, S *__restrict__ vj,
-             S *__restrict__ wout, const double *__restrict__ cf, double *scal, int j, RedCtx rc) {
-  using T = Sc<S>;
-  double *sb = scal + (size_t)blockIdx.y * kScalStride;
-  const double beta = sqrt(sb[kOffNrm2 + j]);
-  const double inv = 1.0 / beta;
-  const S *wp = traj(wprev, g);
-  const S *vp = j > 0 ? traj(vprev, g) : nullptr;
-  S *vo = traj(vj, g);
-  S *wo = traj(wout, g);
-  const double *cb = ANISO ? cf + g.halo : nullptr;
-  double acc[T::W];
-#pragma unroll
-  for (int k = 0; k < T::W; ++k) acc[k] = 0.0;
-  for (long long idx = (long long)blockIdx.x * kThreads + threadIdx.x; idx < g.n;
-       idx += (long long)gridDim.x * kThreads) {
-    const S vc = T::mulr(wp[idx], inv);
-    S w = stencil_site<S, ANISO>(g, wp, cb, idx, inv);
-    if (j > 0) w = T::fma_r(-beta, vp[idx], w);
-    vo[idx] = vc;
-    wo[idx] = w;
-    T::dot_acc(acc, vc, w);
-  }
-  grid_reduce<T::W>(acc, rc, sb + kOffAlpha + j * T::W);
+// ------------------------------------------------------------------ K2
+// Basis layout: column 0 is the start-vector buffer, columns 1..m-1 live in V; columns are kept
+// UN-normalised (column i = w_{i-1} as it left the orthogonalisation, v_i = column_i / beta_i,
+// beta_i^2 = nrm2[i]), so every column is written exactly once and never rescaled: the 1/beta
+// factors are folded into the scalar coefficients.  One Lanczos iteration is two passes:
+//   pass A (k_lanczos_a): w = L v_j - beta_j v_{j-1}  (eigen_krylov_complex.hpp:25-27), stored
+//           in column j+1, and in the same sweep the sums s_i = column_i^H w and the Gram
+//           entries g_i = column_i^H column_j for all i <= j.  T(j,j) = Re s_j / beta_j (:28).
+//           The reference subtracts alpha v_j FIRST and takes its re-orthogonalisation dots
+//           from w' = w - alpha v_j (:29,:32-33); column_i^H w' = s_i - (alpha/beta_j) g_i gives
+//           the same dots without a second sweep (without the g term the alpha component leaks
+//           through the existing loss of orthogonality and is amplified by |alpha|/beta per
+//           iteration);
+//   pass B (k_lanczos_b): w -= alpha v_j + sum_i h_i v_i  (:29,:34), ||w||^2 (:38).
+// 2j+5 vector passes per iteration instead of the 2j+10 of "alpha step, then block dots, then
+// block update, then normalise" (SURVEY 8d counts the latter).
+template <class S>
+__device__ __forceinline__ const S *colptr(const S *start, const S *V, size_t colstride, int i) {
+  return i == 0 ? start : V + (size_t)(i - 1) * colstride;
 }
 
-// ------------------------------------------------------------------ K2, pass b
-// w -= alpha_j v_j (first chunk only) ; h_i = v_i^H w for i in [i0, i0+cnt)
-// (eigen_krylov_complex.hpp:29 and the dot products of the sweep :32-33, batched)
-template <class S, int NV>
-__global__ void __launch_bounds__(kThreads)
-k_lanczos_pb(Geom g, S *__restrict__ w, const S *__restrict__ V, size_t colstride, int j, int i0,
-             int cnt, double *scal, RedCtx rc) {
+// columns [i0, i0+cnt) of 0..j.  FIRST: also forms w (stencil of column j + recurrence term).
+template <class S, bool ANISO, int NC, bool FIRST>
+__global__ void __launch_bounds__(kThreads, 2)
+k_lanczos_a(Geom g, const S *__restrict__ start, S *__restrict__ V, size_t colstride, int j, int i0,
+            int cnt, const double *__restrict__ cf, double *scal, RedCtx rc) {
   using T = Sc<S>;
   double *sb = scal + (size_t)blockIdx.y * kScalStride;
-  const S alpha = T::from(sb + kOffAlpha + j * T::W);
-  S *wb = traj(w, g);
-  const S *vb = traj(V, g);
-  double acc[NV * T::W];
+  const S *cj = traj(colptr<S>(start, V, colstride, j), g);
+  const S *cm = j > 0 ? traj(colptr<S>(start, V, colstride, j - 1), g) : nullptr;
+  S *wc = traj(V + (size_t)j * colstride, g); // column j+1
+  const S *cb = traj(colptr<S>(start, V, colstride, i0), g);
+  const size_t cs0 = i0 == 0 ? (size_t)((V + 0) - start) : colstride; // column i0 -> i0+1 distance
+  const double *cfb = ANISO ? cf + g.halo : nullptr;
+  double inv = 0.0, cmul = 0.0;
+  if (FIRST) {
+    const double bj = sqrt(sb[kOffNrm2 + j]);
+    inv = 1.0 / bj;
+    cmul = j > 0 ? -bj / sqrt(sb[kOffNrm2 + j - 1]) : 0.0; // -beta_j * (1/beta_{j-1})
+  }
+  double acc[NC * T::W];
 #pragma unroll
-  for (int k = 0; k < NV * T::W; ++k) acc[k] = 0.0;
+  for (int k = 0; k < NC * T::W; ++k) acc[k] = 0.0;
   for (long long idx = (long long)blockIdx.x * kThreads + threadIdx.x; idx < g.n;
        idx += (long long)gridDim.x * kThreads) {
-    S wv = wb[idx];
-    if (i0 == 0) {
-      wv = T::sub(wv, T::mul(alpha, vb[(size_t)j * colstride + idx]));
-      wb[idx] = wv;
+    S v[NC];
+#pragma unroll
+    for (int i = 0; i < NC; ++i)
+      if (i < cnt) v[i] = (i == 0 ? cb : cb + cs0 + (size_t)(i - 1) * colstride)[idx];
+    S w;
+    if (FIRST) {
+      w = stencil_site<S, ANISO>(g, cj, cfb, idx, inv);
+      if (j > 0) w = T::fma_r(cmul, cm[idx], w);
+      wc[idx] = w;
+    } else {
+      w = wc[idx];
     }
 #pragma unroll
-    for (int i = 0; i < NV; ++i)
-      if (i < cnt) T::dot_acc(acc + i * T::W, vb[(size_t)(i0 + i) * colstride + idx], wv);
+    for (int i = 0; i < NC; ++i)
+      if (i < cnt) T::dot_acc(acc + i * T::W, v[i], w);
   }
-  grid_reduce<NV * T::W>(acc, rc, sb + kOffH + i0 * T::W);
+  grid_reduce<NC * T::W>(acc, rc, sb + kOffH + i0 * T::W);
 }
 
-// ------------------------------------------------------------------ K2, pass c
-// w -= sum_i h_i v_i for i in [i0, i0+cnt) ; if LAST: ||w||^2 -> nrm2[j+1]
-// (eigen_krylov_complex.hpp:34 batched, :38)
-template <class S, int NV, bool LAST>
-__global__ void __launch_bounds__(kThreads)
-k_lanczos_pc(Geom g, S *__restrict__ w, const S *__restrict__ V, size_t colstride, int j, int i0,
-             int cnt, const double *hsrc_base, int hoff, double *scal, RedCtx rc, Halo<S> hp) {
+// columns [i0, i0+cnt).  LAST: ||w||^2 -> nrm2[j+1], T(j,j) -> alpha[j], halo push of column j+1.
+template <class S, int NC, bool LAST>
+__global__ void __launch_bounds__(kThreads, 2)
+k_lanczos_b(Geom g, const S *__restrict__ start, S *__restrict__ V, size_t colstride, int j, int i0,
+            int cnt, double *scal, RedCtx rc, Halo<S> hp) {
   using T = Sc<S>;
   double *sb = scal + (size_t)blockIdx.y * kScalStride;
-  const double *hs = hsrc_base + (size_t)blockIdx.y * kScalStride + hoff;
-  S h[NV];
+  S *wc = traj(V + (size_t)j * colstride, g);
+  const S *cb = traj(colptr<S>(start, V, colstride, i0), g);
+  const size_t cs0 = i0 == 0 ? (size_t)((V + 0) - start) : colstride;
+  __shared__ S h[NC];
+  if ((int)threadIdx.x < NC) { // coefficient of column i: (alpha v_j + h_i v_i) in un-normalised form
+    const int i = threadIdx.x;
+    S hv = T::zero();
+    if (i < cnt) {
+      const int ci = i0 + i;
+      S si = T::from(sb + kOffH + ci * T::W);
+      if (ci < j) { // column_i^H (w - alpha v_j) = s_i - (Re s_j / beta_j^2) g_i
+        const double q = sb[kOffH + j * T::W] / sb[kOffNrm2 + j];
+        si = T::sub(si, T::mulr(T::from(sb + kOffG + ci * T::W), q));
+      }
+      hv = T::mulr(si, 1.0 / sb[kOffNrm2 + ci]);
+    }
+    h[i] = hv;
+  }
+  __syncthreads();
+  // LAST: acc[0 .. NC*W) = g_i = column_i^H column_{j+1} (for the next iteration), acc[NC*W] = ||w||^2
+  constexpr int KA = LAST ? NC * T::W + 1 : 1;
+  double acc[KA];
 #pragma unroll
-  for (int i = 0; i < NV; ++i) h[i] = i < cnt ? T::from(hs + i * T::W) : T::zero();
-  S *wb = traj(w, g);
-  const S *vb = traj(V, g);
-  double acc[1] = {0.0};
+  for (int k = 0; k < KA; ++k) acc[k] = 0.0;
   for (long long idx = (long long)blockIdx.x * kThreads + threadIdx.x; idx < g.n;
        idx += (long long)gridDim.x * kThreads) {
-    S wv = wb[idx];
+    S v[NC];
 #pragma unroll
-    for (int i = 0; i < NV; ++i)
-      if (i < cnt) wv = T::sub(wv, T::mul(h[i], vb[(size_t)(i0 + i) * colstride + idx]));
-    wb[idx] = wv;
+    for (int i = 0; i < NC; ++i)
+      if (i < cnt) v[i] = (i == 0 ? cb : cb + cs0 + (size_t)(i - 1) * colstride)[idx];
+    S wv = wc[idx];
+#pragma unroll
+    for (int i = 0; i < NC; ++i)
+      if (i < cnt) wv = T::sub(wv, T::mul(h[i], v[i]));
+    wc[idx] = wv;
     if (LAST) {
-      acc[0] += T::abs2(wv);
-      halo_push<S>(hp, g.n, g.plane, idx, wv); // w_j is the next iteration's stencil input
+#pragma unroll
+      for (int i = 0; i < NC; ++i)
+        if (i < cnt) T::dot_acc(acc + i * T::W, v[i], wv);
+      acc[KA - 1] += T::abs2(wv);
+      halo_push<S>(hp, g.n, g.plane, idx, wv); // column j+1 is the next iteration's stencil input
     }
   }
-  if (LAST) grid_reduce<1>(acc, rc, sb + kOffNrm2 + j + 1);
+  if (LAST) {
+    if (blockIdx.x == 0 && threadIdx.x == 0) // T(j,j) = Re(v_j^H w) = Re s_j / beta_j
+      sb[kOffAlpha + j * T::W] = sb[kOffH + j * T::W] / sqrt(sb[kOffNrm2 + j]);
+    grid_reduce2s<KA - 1>(acc, rc, sb + kOffG + i0 * T::W, sb + kOffNrm2 + j + 1);
+  }
+}
+
+// Gram entries g_i = column_i^H column_j for the columns [i0, i0+cnt) that the LAST chunk of the
+// previous pass B did not hold (only when more than NC columns take part, i.e. m > NC + 1)
+template <class S, int NC>
+__global__ void __launch_bounds__(kThreads)
+k_lanczos_g(Geom g, const S *__restrict__ start, const S *__restrict__ V, size_t colstride, int j, int i0,
+            int cnt, double *scal, RedCtx rc) {
+  using T = Sc<S>;
+  double *sb = scal + (size_t)blockIdx.y * kScalStride;
+  const S *cj = traj(colptr<S>(start, V, colstride, j), g);
+  const S *cb = traj(colptr<S>(start, V, colstride, i0), g);
+  const size_t cs0 = i0 == 0 ? (size_t)((V + 0) - start) : colstride;
+  double acc[NC * T::W];
+#pragma unroll
+  for (int k = 0; k < NC * T::W; ++k) acc[k] = 0.0;
+  for (long long idx = (long long)blockIdx.x * kThreads + threadIdx.x; idx < g.n;
+       idx += (long long)gridDim.x * kThreads) {
+    const S cv = cj[idx];
+#pragma unroll
+    for (int i = 0; i < NC; ++i)
+      if (i < cnt) T::dot_acc(acc + i * T::W, (i == 0 ? cb : cb + cs0 + (size_t)(i - 1) * colstride)[idx], cv);
+  }
+  grid_reduce<NC * T::W>(acc, rc, sb + kOffG + i0 * T::W);
 }
 
 // ------------------------------------------------------------------ K3
@@ -158,8 +214,7 @@ k_lanczos_pc(Geom g, S *__restrict__ w, const S *__restrict__ V, size_t colstrid
 // (diag = Re alpha_j, alpha_{m-1} = 0 as in the reference; off-diag = sqrt(nrm2[j+1])),
 // eigenvector rows distributed over the lanes, then
 //   coef_i = beta0 * sum_k Z_ik f(t, lambda_k) Z_0k            (beta * V * f(T) * e1, :77-82)
-// with the last coefficient divided by T(m-1,m-2) because column m-1 of the basis is kept
-// un-normalised in the w buffer.  Function tables: eigen_krylov_complex.hpp:70-76,:89-96,
+// with coefficient i divided by beta_i because the basis columns are kept un-normalised.  Function tables: eigen_krylov_complex.hpp:70-76,:89-96,
 // eigen_krylov_real.hpp:79-80,:109-115,:142-144,:161-170,:189-204.
 __device__ __forceinline__ double2 fn_eval(int fn, double tr, double ti, double lam) {
   switch (fn) {
@@ -265,7 +320,6 @@ k_tridiag(const double *__restrict__ scal, double *__restrict__ coef, TridiagArg
   __syncwarp();
   if (!ok && lane == 0) atomicExch(status, 1);
   const double beta0 = sqrt(sb[kOffNrm2 + 0]);
-  const double last = 1.0 / sqrt(sb[kOffNrm2 + m - 1]); // 1 / T(m-1,m-2)
   __shared__ double2 fv[kMaxM];
   for (int f = 0; f < a.nfn; ++f) {
     __syncwarp();
@@ -279,8 +333,7 @@ k_tridiag(const double *__restrict__ scal, double *__restrict__ coef, TridiagArg
         sr = fma(zz, fv[k].x, sr);
         si = fma(zz, fv[k].y, si);
       }
-      double scale = beta0;
-      if (i == m - 1) scale *= last;
+      const double scale = beta0 / sqrt(sb[kOffNrm2 + i]); // columns are un-normalised
       co[2 * i] = sr * scale;
       co[2 * i + 1] = si * scale;
     }
@@ -288,54 +341,53 @@ k_tridiag(const double *__restrict__ scal, double *__restrict__ coef, TridiagArg
 }
 
 // ------------------------------------------------------------------ K4 helpers
-// y(idx) = sum_{i<m-1} coef_i V_i[idx] + coef_{m-1} wlast[idx]
+// y(idx) = coef_0 start[idx] + sum_{1<=i<m} coef_i V_{i-1}[idx]   (column 0 is the start buffer)
 template <class S>
-__device__ __forceinline__ S combine_site(const S *__restrict__ vb, size_t colstride,
-                                          const S *__restrict__ wl, const double *__restrict__ co,
-                                          int m, long long idx);
+__device__ __forceinline__ S combine_site(const S *__restrict__ st, const S *__restrict__ vb,
+                                          size_t colstride, const double *__restrict__ co, int m,
+                                          long long idx);
 template <>
-__device__ __forceinline__ double combine_site<double>(const double *__restrict__ vb, size_t colstride,
-                                                       const double *__restrict__ wl,
+__device__ __forceinline__ double combine_site<double>(const double *__restrict__ st,
+                                                       const double *__restrict__ vb, size_t colstride,
                                                        const double *__restrict__ co, int m,
                                                        long long idx) {
-  double s = 0.0;
-  for (int i = 0; i < m - 1; ++i) s = fma(vb[(size_t)i * colstride + idx], co[2 * i], s);
-  return fma(wl[idx], co[2 * (m - 1)], s);
+  double s = st[idx] * co[0];
+#pragma unroll 4
+  for (int i = 1; i < m; ++i) s = fma(vb[(size_t)(i - 1) * colstride + idx], co[2 * i], s);
+  return s;
 }
 template <>
-__device__ __forceinline__ double2 combine_site<double2>(const double2 *__restrict__ vb,
+__device__ __forceinline__ double2 combine_site<double2>(const double2 *__restrict__ st,
+                                                         const double2 *__restrict__ vb,
                                                          size_t colstride,
-                                                         const double2 *__restrict__ wl,
                                                          const double *__restrict__ co, int m,
                                                          long long idx) {
-  double2 s = make_double2(0.0, 0.0);
-  for (int i = 0; i < m - 1; ++i) {
-    const double2 v = vb[(size_t)i * colstride + idx];
+  const double2 v0 = st[idx];
+  double2 s = make_double2(v0.x * co[0] - v0.y * co[1], v0.x * co[1] + v0.y * co[0]);
+#pragma unroll 4
+  for (int i = 1; i < m; ++i) {
+    const double2 v = vb[(size_t)(i - 1) * colstride + idx];
     const double cr = co[2 * i], ci = co[2 * i + 1];
     s.x = fma(v.x, cr, fma(-v.y, ci, s.x));
     s.y = fma(v.x, ci, fma(v.y, cr, s.y));
   }
-  const double2 v = wl[idx];
-  const double cr = co[2 * (m - 1)], ci = co[2 * (m - 1) + 1];
-  s.x = fma(v.x, cr, fma(-v.y, ci, s.x));
-  s.y = fma(v.x, ci, fma(v.y, cr, s.y));
   return s;
 }
 
 // out = sum coef_i v_i   (nls_matfunc: beta * V * f(T) * e1)
 template <class S>
 __global__ void __launch_bounds__(kThreads)
-k_combine(Geom g, const S *__restrict__ V, size_t colstride, const S *__restrict__ wlast,
+k_combine(Geom g, const S *__restrict__ start, const S *__restrict__ V, size_t colstride,
           const double *__restrict__ coef, int fsel, int m, S *__restrict__ out) {
   __shared__ double co[kCoefStride];
   const double *cg = coef + ((size_t)blockIdx.y * 2 + fsel) * kCoefStride;
   for (int i = threadIdx.x; i < 2 * m; i += kThreads) co[i] = cg[i];
   __syncthreads();
-  const S *vb = traj(V, g), *wl = traj(wlast, g);
+  const S *vb = traj(V, g), *st = traj(start, g);
   S *ob = traj(out, g);
   for (long long idx = (long long)blockIdx.x * kThreads + threadIdx.x; idx < g.n;
        idx += (long long)gridDim.x * kThreads)
-    ob[idx] = combine_site<S>(vb, colstride, wl, co, m, idx);
+    ob[idx] = combine_site<S>(st, vb, colstride, co, m, idx);
 }
 
 // nonlinear half-step phase factor exp(.5*tau*g), tau = i*dt, applied to z.
@@ -394,8 +446,8 @@ k_nlse_prephase(Geom g, const double2 *__restrict__ u, const double *__restrict_
 // new state goes to a second buffer (uout) to stay race-free.
 template <int EQ>
 __global__ void __launch_bounds__(kThreads)
-k_nlse_finish(Geom g, const double2 *__restrict__ V, size_t colstride,
-              const double2 *__restrict__ wlast, const double *__restrict__ coef, int m,
+k_nlse_finish(Geom g, const double2 *__restrict__ start, const double2 *__restrict__ V, size_t colstride,
+              const double *__restrict__ coef, int m,
               const double2 *__restrict__ uold, const double *__restrict__ mf,
               double2 *__restrict__ uout, double2 *__restrict__ rho, NlseParams p, double *scal,
               RedCtx rc, Halo<double2> hp) {
@@ -403,14 +455,14 @@ k_nlse_finish(Geom g, const double2 *__restrict__ V, size_t colstride,
   const double *cg = coef + ((size_t)blockIdx.y * 2) * kCoefStride;
   for (int i = threadIdx.x; i < 2 * m; i += kThreads) co[i] = cg[i];
   __syncthreads();
-  const double2 *vb = traj(V, g), *wl = traj(wlast, g), *uo = traj(uold, g);
+  const double2 *vb = traj(V, g), *st = traj(start, g), *uo = traj(uold, g);
   double2 *un = traj(uout, g), *rb = traj(rho, g);
   const double *mb = mf + g.halo;
   double acc[1] = {0.0};
   for (long long idx = (long long)blockIdx.x * kThreads + threadIdx.x; idx < g.n;
        idx += (long long)gridDim.x * kThreads) {
     const long long sc = clamp_site(g, idx);
-    const double2 buf = combine_site<double2>(vb, colstride, wl, co, m, sc);
+    const double2 buf = combine_site<double2>(st, vb, colstride, co, m, sc);
     double2 unew;
     if (EQ == NLS_EQ_NLSE_CUBIC) unew = nlse_phase<EQ>(p, mb[sc], buf, buf, buf);
     else unew = nlse_phase<EQ>(p, mb[sc], uo[sc], buf, buf); // density from the OLD u (Q7)
@@ -421,6 +473,78 @@ k_nlse_finish(Geom g, const double2 *__restrict__ V, size_t colstride,
     acc[0] += r.x * r.x + r.y * r.y;
   }
   grid_reduce<1>(acc, rc, scal + (size_t)blockIdx.y * kScalStride + kOffNrm2);
+}
+
+// ------------------------------------------------------------------ sEWI (NLS_INT_SEWI)
+// B(u) = -m g(|u|^2) u   (nlse_cubic_gautschi_solver.hpp:27-32, nlse_cubic_quintic_gautschi_solver.hpp:19-26,
+// nlse_saturating_gautschi_solver.hpp:21-30: real denominator 1 + kappa |u|^2 here), ||B||^2 -> nrm2[0]
+template <int EQ>
+__global__ void __launch_bounds__(kThreads)
+k_sewi_B(Geom g, const double2 *__restrict__ u, const double *__restrict__ mf, double2 *__restrict__ out,
+         NlseParams p, double *scal, RedCtx rc, Halo<double2> hp) {
+  const double2 *ub = traj(u, g);
+  double2 *ob = traj(out, g);
+  const double *mb = mf + g.halo;
+  double acc[1] = {0.0};
+  for (long long idx = (long long)blockIdx.x * kThreads + threadIdx.x; idx < g.n;
+       idx += (long long)gridDim.x * kThreads) {
+    const double2 uv = ub[idx];
+    const double r = uv.x * uv.x + uv.y * uv.y;
+    double gg;
+    if (EQ == NLS_EQ_NLSE_CUBIC) gg = mb[idx] * r;
+    else if (EQ == NLS_EQ_NLSE_CQ) gg = mb[idx] * (p.s1 * r + p.s2 * (r * r));
+    else gg = mb[idx] * (r * (1.0 / (1.0 + p.kappa * r)));
+    const double2 b = make_double2(-gg * uv.x, -gg * uv.y);
+    ob[idx] = b;
+    halo_push<double2>(hp, g.n, g.plane, idx, b);
+    acc[0] += b.x * b.x + b.y * b.y;
+  }
+  grid_reduce<1>(acc, rc, scal + (size_t)blockIdx.y * kScalStride + kOffNrm2);
+}
+
+// out = sum coef_i column_i with ||out||^2 -> nrm2[0]: a matrix-function result that is the start
+// vector of the next Lanczos run (phi = sincm_multiply(L, B, dt))
+template <class S>
+__global__ void __launch_bounds__(kThreads)
+k_combine_norm(Geom g, const S *__restrict__ start, const S *__restrict__ V, size_t colstride,
+               const double *__restrict__ coef, int m, S *__restrict__ out, double *scal, RedCtx rc,
+               Halo<S> hp) {
+  __shared__ double co[kCoefStride];
+  const double *cg = coef + ((size_t)blockIdx.y * 2) * kCoefStride;
+  for (int i = threadIdx.x; i < 2 * m; i += kThreads) co[i] = cg[i];
+  __syncthreads();
+  const S *vb = traj(V, g), *st = traj(start, g);
+  S *ob = traj(out, g);
+  double acc[1] = {0.0};
+  for (long long idx = (long long)blockIdx.x * kThreads + threadIdx.x; idx < g.n;
+       idx += (long long)gridDim.x * kThreads) {
+    const S y = combine_site<S>(st, vb, colstride, co, m, idx);
+    ob[idx] = y;
+    halo_push<S>(hp, g.n, g.plane, idx, y);
+    acc[0] += Sc<S>::abs2(y);
+  }
+  grid_reduce<1>(acc, rc, scal + (size_t)blockIdx.y * kScalStride + kOffNrm2);
+}
+
+// u+ = b - sg * 2 tau * a, b = sum coef_i column_i (expm of u-), tau = i dt, followed by the no-flux
+// copy (clamped-site read).  fprime = -sg * 2 * dt.
+__global__ void __launch_bounds__(kThreads)
+k_sewi_final(Geom g, const double2 *__restrict__ start, const double2 *__restrict__ V, size_t colstride,
+             const double *__restrict__ coef, int m, const double2 *__restrict__ a, double2 *__restrict__ unew,
+             double fprime) {
+  __shared__ double co[kCoefStride];
+  const double *cg = coef + ((size_t)blockIdx.y * 2) * kCoefStride;
+  for (int i = threadIdx.x; i < 2 * m; i += kThreads) co[i] = cg[i];
+  __syncthreads();
+  const double2 *vb = traj(V, g), *st = traj(start, g), *ab = traj(a, g);
+  double2 *un = traj(unew, g);
+  for (long long idx = (long long)blockIdx.x * kThreads + threadIdx.x; idx < g.n;
+       idx += (long long)gridDim.x * kThreads) {
+    const long long sc = clamp_site(g, idx);
+    const double2 b = combine_site<double2>(st, vb, colstride, co, m, sc);
+    const double2 av = ab[sc];
+    un[idx] = make_double2(b.x - fprime * av.y, b.y + fprime * av.x); // b + fprime * i * a
+  }
 }
 
 // f(u) of the real equations
@@ -440,7 +564,7 @@ __device__ __forceinline__ double f_real(double x) {
 template <int EQ>
 __global__ void __launch_bounds__(kThreads)
 k_gautschi_a(Geom g, const double *__restrict__ V, size_t colstride,
-             const double *__restrict__ wlast, const double *__restrict__ coef, int m,
+             const double *__restrict__ coef, int m,
              const double *__restrict__ u, double *__restrict__ upast, const double *__restrict__ mf,
              double *__restrict__ gout, double *__restrict__ accout, double *scalB, RedCtx rc,
              Halo<double> hp) {
@@ -451,27 +575,26 @@ k_gautschi_a(Geom g, const double *__restrict__ V, size_t colstride,
     coc[i] = cg[kCoefStride + i];
   }
   __syncthreads();
-  const double *vb = traj(V, g), *wl = traj(wlast, g), *ub = traj(u, g);
+  const double *vb = traj(V, g), *ub = traj(u, g);
   double *up = traj(upast, g), *go = traj(gout, g), *ao = traj(accout, g);
   const double *mb = mf + g.halo;
   double acc[1] = {0.0};
   for (long long idx = (long long)blockIdx.x * kThreads + threadIdx.x; idx < g.n;
        idx += (long long)gridDim.x * kThreads) {
-    double sf = 0.0, sc = 0.0;
-    for (int i = 0; i < m - 1; ++i) {
-      const double v = vb[(size_t)i * colstride + idx];
+    const double uv = ub[idx]; // column 0 of this Lanczos run is u itself
+    double sf = uv * cof[0], sc = uv * coc[0];
+#pragma unroll 4
+    for (int i = 1; i < m; ++i) {
+      const double v = vb[(size_t)(i - 1) * colstride + idx];
       sf = fma(v, cof[2 * i], sf);
       sc = fma(v, coc[2 * i], sc);
     }
-    const double v = wl[idx];
-    sf = fma(v, cof[2 * (m - 1)], sf);
-    sc = fma(v, coc[2 * (m - 1)], sc);
     const double gv = -(mb[idx] * f_real<EQ>(sf));
     go[idx] = gv;
     halo_push<double>(hp, g.n, g.plane, idx, gv);
     acc[0] += gv * gv;
     ao[idx] = 2 * sc - up[idx];
-    up[idx] = ub[idx];
+    up[idx] = uv;
   }
   grid_reduce<1>(acc, rc, scalB + (size_t)blockIdx.y * kScalStride + kOffNrm2);
 }
@@ -479,21 +602,21 @@ k_gautschi_a(Geom g, const double *__restrict__ V, size_t colstride,
 // Gautschi stage B: u = acc + tau^2 * beta V sinc2(T) e1, no-flux copy, ||u||^2 for the next step
 template <int DUMMY>
 __global__ void __launch_bounds__(kThreads)
-k_gautschi_b(Geom g, const double *__restrict__ V, size_t colstride,
-             const double *__restrict__ wlast, const double *__restrict__ coef, int m,
+k_gautschi_b(Geom g, const double *__restrict__ start, const double *__restrict__ V, size_t colstride,
+             const double *__restrict__ coef, int m,
              const double *__restrict__ accin, double *__restrict__ u, double tau2, double *scalA,
              RedCtx rc, Halo<double> hp) {
   __shared__ double co[kCoefStride];
   const double *cg = coef + ((size_t)blockIdx.y * 2) * kCoefStride;
   for (int i = threadIdx.x; i < 2 * m; i += kThreads) co[i] = cg[i];
   __syncthreads();
-  const double *vb = traj(V, g), *wl = traj(wlast, g), *ai = traj(accin, g);
+  const double *vb = traj(V, g), *st = traj(start, g), *ai = traj(accin, g);
   double *ub = traj(u, g);
   double acc[1] = {0.0};
   for (long long idx = (long long)blockIdx.x * kThreads + threadIdx.x; idx < g.n;
        idx += (long long)gridDim.x * kThreads) {
     const long long sc = clamp_site(g, idx);
-    const double s = combine_site<double>(vb, colstride, wl, co, m, sc);
+    const double s = combine_site<double>(st, vb, colstride, co, m, sc);
     const double un = ai[sc] + tau2 * s;
     ub[idx] = un;
     halo_push<double>(hp, g.n, g.plane, idx, un);

@@ -35,6 +35,7 @@ struct Spec {
   double op_sign;   // +1: L, -1: -L
   uint32_t krylov;  // Krylov dimension hard-coded by that driver
   const char *ref;  // reference source
+  uint32_t flags = 0; // NLS_FLAG_*
 };
 
 const Spec kSpecs[] = {
@@ -52,6 +53,12 @@ const Spec kSpecs[] = {
     {"phi4", 2, NLS_EQ_PHI4, NLS_INT_GAUTSCHI, 0, false, 1.0, -1, 10, "phi4_driver.cpp:20-123"},
     {"kg_driver_3d", 3, NLS_EQ_KGE, NLS_INT_GAUTSCHI, 0, true, 1.0, -1, 10, "kg_driver_3d.cpp:20-146"},
     {"kg_sv_driver_3d", 3, NLS_EQ_KGE, NLS_INT_SV, 0, true, 1.0, 1, 10, "kg_sv_driver_3d.cpp:20-146"},
+    // sEWI ("Gautschi" NLSE): one SS2 start-up step, then the two-step integrator
+    {"nlse_cubic_gautschi", 2, NLS_EQ_NLSE_CUBIC, NLS_INT_SEWI, 0, false, 0.0, 1, 10, "nlse_cubic_gautschi_driver.cpp:19-150",
+     NLS_FLAG_SEWI_HOST2D},
+    {"nlse_cubic_gautschi_3d", 3, NLS_EQ_NLSE_CUBIC, NLS_INT_SEWI, 0, true, 0.0, 1, 10, "nlse_cubic_gautschi_driver_3d.cpp:22-150"},
+    {"nlse_sewi_2d_dev", 2, NLS_EQ_NLSE_CUBIC, NLS_INT_SEWI, 0, true, 0.0, 1, 25, "nlse_cubic_sewi_driver_2d.cpp:19-125"},
+    {"nlse_sewi_3d_dev", 3, NLS_EQ_NLSE_CUBIC, NLS_INT_SEWI, 0, true, 0.0, 1, 15, "nlse_cubic_sewi_driver_3d.cpp:19-133"},
     // gen-2 device drivers, nlsolvers/device/drivers/ (names from its CMakeLists.txt:55-73)
     {"nlse_2d_dev", 2, NLS_EQ_NLSE_CUBIC, NLS_INT_SS2, 0, true, 0.0, 1, 20, "nlse_cubic_driver_2d.cpp:19-125"},
     {"nlse_3d_dev", 3, NLS_EQ_NLSE_CUBIC, NLS_INT_SS2, 0, true, 0.0, 1, 25, "nlse_cubic_driver_3d.cpp:19-133"},
@@ -161,7 +168,7 @@ int run(const Spec &s, int argc, char **argv) {
   if (is_nlse(s)) {
     std::vector<cplx> u0;
     if (!load_checked(in_u, want, u0, "Input")) return 1;
-    nls::Handle h(g, s.equation, NLS_INT_SS2, krylov, dt, sc[0], sc[1], sc[0], 1, device);
+    nls::Handle h(g, s.equation, s.integrator, krylov, dt, sc[0], sc[1], sc[0], 1, device, s.flags);
     h.set(NLS_FIELD_M, m.data(), n * 8);
     h.set(NLS_FIELD_U, u0.data(), n * 16);
     std::vector<cplx> traj((size_t)ns * n);

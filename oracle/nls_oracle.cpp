@@ -413,7 +413,8 @@ struct orc_engine {
   bool built = false;
   double sgn = 1.0;
   std::vector<double> m, c;
-  std::vector<cplx> uc;            // batch*n
+  std::vector<cplx> uc, uc_prev;   // batch*n (uc_prev: sEWI u^{n-1})
+  std::vector<char> sewi_started;  // per trajectory
   std::vector<double> ur, ur_past; // batch*n
 
   void build() {
@@ -448,6 +449,45 @@ struct orc_engine {
       // cubic: density from buf; cq/sat: |u_old|^2 (sat: denominator from buf)
       const cplx src = d.equation == NLS_EQ_NLSE_CUBIC ? buf[i] : u[i];
       u[i] = std::exp(.5 * tau * g(src, buf[i], i)) * buf[i];
+    }
+    return true;
+  }
+
+  // sEWI step.  Default convention (NLSEGautschiSolver3d::step nlse_cubic_gautschi_solver_3d.hpp:8-35,
+  // NLSECubicQuinticGautschiSolver::step nlse_cubic_quintic_gautschi_solver.hpp:11-41,
+  // NLSESaturatingGautschiSolver::step nlse_saturating_gautschi_solver.hpp:11-44 [real denominator
+  // 1 + kappa |u|^2 here], device step_sewi nlse_dev.hpp:205-238):
+  //   u+ = expm(L, u-, 2 tau) - 2 tau expm(L, sincm(L, B(u), dt), tau)
+  // NLS_FLAG_SEWI_HOST2D (NLSECubicGautschiSolver::step nlse_cubic_gautschi_solver.hpp:21-39):
+  //   u+ = expm(L, u-, -2 tau) + 2 tau expm(L, sincm(L, B(u), dt), -tau)
+  // First step: one SS2 step with u- = u0 (nlse_cubic_gautschi_driver.cpp:122-125).
+  bool step_sewi(cplx *u, cplx *uprev, char &started, double dt) {
+    if (!started) {
+      std::copy(u, u + n, uprev);
+      started = 1;
+      return step_nlse(u, dt);
+    }
+    const cplx tau(0, dt);
+    const double sg = (d.flags & NLS_FLAG_SEWI_HOST2D) ? -1.0 : 1.0;
+    const int mk = (int)d.krylov_m;
+    std::vector<cplx> B(n), phi(n), a(n), b(n);
+    for (int64_t i = 0; i < n; ++i) {
+      const double r = u[i].real() * u[i].real() + u[i].imag() * u[i].imag();
+      double gg;
+      switch (d.equation) {
+      case NLS_EQ_NLSE_CUBIC: gg = m[i] * r; break;
+      case NLS_EQ_NLSE_CQ: gg = m[i] * (d.s1 * r + d.s2 * (r * r)); break;
+      default: gg = m[i] * (r * (1.0 / (1.0 + d.kappa * r))); break;
+      }
+      B[i] = -gg * u[i];
+    }
+    if (!matfunc_apply(A, sgn, NLS_FN_SINC, cplx(dt, 0.0), B.data(), mk, d.reorth, phi.data())) return false;
+    if (!matfunc_apply(A, sgn, NLS_FN_EXP, sg * tau, phi.data(), mk, d.reorth, a.data())) return false;
+    if (!matfunc_apply(A, sgn, NLS_FN_EXP, sg * 2. * tau, uprev, mk, d.reorth, b.data())) return false;
+    for (int64_t i = 0; i < n; ++i) {
+      const cplx un = b[i] - sg * 2. * tau * a[i];
+      uprev[i] = u[i];
+      u[i] = un;
     }
     return true;
   }
@@ -514,8 +554,11 @@ int orc_create(const nls_desc *desc, orc_handle *out) {
   e->cplx_state = desc->equation <= NLS_EQ_NLSE_SAT;
   e->sgn = desc->op_sign == 0.0 ? 1.0 : desc->op_sign;
   e->m.assign(e->n, 0.0); // nlse_cubic_driver.cpp:63: m defaults to ZERO
-  if (e->cplx_state) e->uc.assign((size_t)e->n * desc->batch, cplx(0));
-  else {
+  if (e->cplx_state) {
+    e->uc.assign((size_t)e->n * desc->batch, cplx(0));
+    e->uc_prev.assign((size_t)e->n * desc->batch, cplx(0));
+    e->sewi_started.assign(desc->batch, 0);
+  } else {
     e->ur.assign((size_t)e->n * desc->batch, 0.0);
     e->ur_past.assign((size_t)e->n * desc->batch, 0.0);
   }
@@ -534,9 +577,16 @@ int orc_set_field(orc_handle e, int field, const void *src, size_t bytes) {
   case NLS_FIELD_U:
     if (bytes != sb) break;
     std::memcpy(e->cplx_state ? (void *)e->uc.data() : (void *)e->ur.data(), src, bytes);
+    if (e->cplx_state) std::fill(e->sewi_started.begin(), e->sewi_started.end(), 0);
     return NLS_OK;
   case NLS_FIELD_U_PAST:
-    if (e->cplx_state || bytes != sb) break;
+    if (bytes != sb) break;
+    if (e->cplx_state) {
+      if (e->d.integrator != NLS_INT_SEWI) break;
+      std::memcpy(e->uc_prev.data(), src, bytes);
+      std::fill(e->sewi_started.begin(), e->sewi_started.end(), 1);
+      return NLS_OK;
+    }
     std::memcpy(e->ur_past.data(), src, bytes);
     return NLS_OK;
   case NLS_FIELD_V: { // u_past = u0 - dt*v0  sg_single_driver.cpp:70
@@ -568,7 +618,12 @@ int orc_get_field(orc_handle e, int field, void *dst, size_t bytes) {
     std::memcpy(dst, e->cplx_state ? (void *)e->uc.data() : (void *)e->ur.data(), bytes);
     return NLS_OK;
   case NLS_FIELD_U_PAST:
-    if (e->cplx_state || bytes != sb) break;
+    if (bytes != sb) break;
+    if (e->cplx_state) {
+      if (e->d.integrator != NLS_INT_SEWI) break;
+      std::memcpy(dst, e->uc_prev.data(), bytes);
+      return NLS_OK;
+    }
     std::memcpy(dst, e->ur_past.data(), bytes);
     return NLS_OK;
   case NLS_FIELD_V: { // v = (u - u_past)/dt  sg_single_driver.cpp:113
@@ -595,7 +650,9 @@ int orc_step(orc_handle e, double dt, uint32_t nsteps) {
       bool ok;
       if (e->cplx_state) {
         cplx *u = &e->uc[(size_t)b * n];
-        ok = e->step_nlse(u, dt);
+        if (e->d.integrator == NLS_INT_SEWI)
+          ok = e->step_sewi(u, &e->uc_prev[(size_t)b * n], e->sewi_started[b], dt);
+        else ok = e->step_nlse(u, dt);
         neumann_bc(u, e->d.nx, e->d.ny, e->d.nz);
       } else {
         double *u = &e->ur[(size_t)b * n], *up = &e->ur_past[(size_t)b * n];

@@ -175,6 +175,25 @@ def nlse_step(A, u, mfield, dt, m=10, kind="cubic", s1=0.0, s2=0.0, kappa=0.0):
     return np.exp(0.5 * tau * g(u, buf)) * buf
 
 
+def sewi_step(A, u, uprev, mfield, dt, m=10, kind="cubic", s1=0.0, s2=0.0, kappa=0.0, host2d=False):
+    """sEWI step (nlse_cubic_gautschi_solver_3d.hpp:8-35 and twins; host2d: the 2D cubic host
+    convention of nlse_cubic_gautschi_solver.hpp:21-39).  Returns (u_new before BC, u_prev_new)."""
+    tau = 1j * dt
+    r = np.abs(u) ** 2
+    if kind == "cubic":
+        g = mfield * r
+    elif kind == "cq":
+        g = mfield * (s1 * r + s2 * r * r)
+    else:
+        g = mfield * (r / (1.0 + kappa * r))
+    B = -g * u
+    sg = -1.0 if host2d else 1.0
+    phi = matfunc(A, B, dt, "sinc", m)
+    a = matfunc(A, phi, sg * tau, "exp", m)
+    b = matfunc(A, uprev, sg * 2 * tau, "exp", m)
+    return b - sg * 2 * tau * a, u.copy()
+
+
 _F = {"sge": np.sin, "kge": lambda x: x ** 3, "phi4": lambda x: x - x ** 3,
       "sge_double": lambda x: np.sin(x) + .6 * np.sin(2. * x), "sge_sinh": np.sinh}
 

@@ -148,6 +148,43 @@ def test_nlse_2d_steps(orc, eq):
     assert e.reduce(RED.NONFINITE)[0] == 0
 
 
+@pytest.mark.parametrize("eq,host2d,dim", [(EQ.NLSE_CUBIC, True, 2), (EQ.NLSE_CUBIC, False, 2), (EQ.NLSE_CQ, False, 2),
+                                           (EQ.NLSE_SAT, False, 2), (EQ.NLSE_CUBIC, False, 3)])
+def test_nlse_sewi_steps(orc, eq, host2d, dim):
+    """sEWI two-step integrator (nlse_cubic_gautschi_solver*.hpp, device step_sewi nlse_dev.hpp:205-238):
+    SS2 start-up step + sEWI steps, issued in pieces; both sign conventions; u- readable/settable."""
+    L, dt = 10.0, 1e-3
+    flags = nls_b200.FLAG_SEWI_HOST2D if host2d else 0
+    if dim == 2:
+        n = 80
+        d = Desc.make(n, n, L=L, equation=eq, integrator=INT.SEWI, krylov_m=10, s1=1.0, s2=-0.1, kappa=0.3, flags=flags)
+        u0 = ics.gaussian_bumps_2d(n, L)
+    else:
+        n = 24
+        d = Desc.make(n, n, n, L=L, equation=eq, integrator=INT.SEWI, laplacian=LAP.ANISO, krylov_m=10, flags=flags)
+        u0 = ics.gaussian_bumps_3d(n, L)
+    mf = 1.0 + 0.2 * np.random.default_rng(1).standard_normal(d.n)
+    e, o = Engine(d), orc.Oracle(d)
+    for s in (e, o):
+        s.set(FIELD.U, u0)
+        s.set(FIELD.M, mf)
+    for k in (1, 3, 2, 6):
+        e.step(dt, k)
+        o.step(dt, k)
+    assert rel_l2(e.get(), o.get()) < 1e-11
+    assert rel_l2(e.get(FIELD.U_PAST), o.get(FIELD.U_PAST)) < 1e-11
+    # restart from (u, u-) through the ABI: continues the same trajectory without the SS2 start-up
+    e2 = Engine(d)
+    e2.set(FIELD.M, mf)
+    e2.set(FIELD.U, e.get())
+    e2.set(FIELD.U_PAST, e.get(FIELD.U_PAST))
+    e.step(dt, 3)
+    e2.step(dt, 3)
+    o.step(dt, 3)
+    assert np.array_equal(e.get(), e2.get())
+    assert rel_l2(e.get(), o.get()) < 1e-11
+
+
 def test_nlse_2d_odd_grid_and_step_splitting(orc):
     """nsteps issued in pieces (graph replay, phase flip) equals one call; odd nx."""
     n, L, dt = 67, 8.0, 1e-3

@@ -138,3 +138,28 @@ def test_batch_is_independent(oracle_lib):
     o1 = oracle_lib.Oracle(d1)
     o1.set(FIELD.U, ub[None]); o1.set(FIELD.M, np.ones(d1.n)); o1.step(1e-3, 3)
     assert np.array_equal(o2.get()[1], o1.get()[0])
+
+
+@pytest.mark.parametrize("eq,kind,host2d", [(EQ.NLSE_CUBIC, "cubic", True), (EQ.NLSE_CUBIC, "cubic", False),
+                                            (EQ.NLSE_CQ, "cq", False), (EQ.NLSE_SAT, "sat", False)])
+def test_sewi_steps_vs_numpy_twin(oracle_lib, eq, kind, host2d):
+    """sEWI two-step integrator: SS2 start-up step, then sEWI steps (nlse_cubic_gautschi_driver.cpp:122-137)."""
+    import nls_b200
+    n, L, dt = 20, 5.0, 1e-3
+    d = Desc.make(n, n, L=L, equation=eq, integrator=INT.SEWI, krylov_m=10, s1=1.0, s2=-0.1, kappa=0.3,
+                  flags=nls_b200.FLAG_SEWI_HOST2D if host2d else 0)
+    o = oracle_lib.Oracle(d)
+    u0 = ics.gaussian_bumps_2d(n, L)
+    mf = 1.0 + 0.1 * np.random.default_rng(4).standard_normal(d.n)
+    o.set(FIELD.U, u0)
+    o.set(FIELD.M, mf)
+    o.step(dt, 5)
+    A = onp.lap2d_uniform(n, n, d.dx, d.dy).astype(complex)
+    u = u0.ravel().copy()
+    uprev = u.copy()
+    u = onp.neumann_bc(onp.nlse_step(A, u, mf, dt, 10, kind, 1.0, -0.1, 0.3).reshape(n, n)).ravel()
+    for _ in range(4):
+        un, uprev = onp.sewi_step(A, u, uprev, mf, dt, 10, kind, 1.0, -0.1, 0.3, host2d)
+        u = onp.neumann_bc(un.reshape(n, n)).ravel()
+    assert rel_l2(o.get()[0], u.reshape(n, n)) < 1e-12
+    assert rel_l2(o.get(FIELD.U_PAST)[0], uprev.reshape(n, n)) < 1e-12
