@@ -27,6 +27,7 @@ RED = SimpleNamespace(MASS=0, NONFINITE=1)
 FLAG_NO_GRAPH = 1
 FLAG_NO_PERSISTENT = 2
 FLAG_SEWI_HOST2D = 4
+FLAG_NO_MARCH = 8
 
 
 class NlsError(RuntimeError):

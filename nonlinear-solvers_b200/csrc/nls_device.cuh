@@ -134,6 +134,76 @@ __device__ __forceinline__ S stencil_site_f(const Geom &g, X x, const double *__
   return acc;
 }
 
+// The same rows from neighbour VALUES (missing neighbours passed as anything, gated by the flags):
+// used by the plane-marching kernels, which keep the z+-1 values in registers and fetch the
+// in-plane neighbours through L1.  Accumulation order identical to stencil_site_f.
+enum { NB_XM = 1, NB_XP = 2, NB_YM = 4, NB_YP = 8, NB_ZM = 16, NB_ZP = 32, NB_RING = 64 };
+template <class S, bool ANISO>
+__device__ __forceinline__ S stencil_vals(const Geom &g, unsigned f, double pre, S xc, S xzm, S xym, S xxm,
+                                          S xxp, S xyp, S xzp, double cc, double czm, double cym,
+                                          double cxm, double cxp, double cyp, double czp) {
+  using T = Sc<S>;
+  S acc = T::zero();
+  xc = T::mulr(xc, pre);
+  if (!ANISO) {
+    const double dg = g.dim3 ? ((f & NB_RING) ? -5.0 : -6.0) : ((f & NB_RING) ? -3.0 : -4.0);
+    if (f & NB_ZM) acc = T::fma_r(g.sc, T::mulr(xzm, pre), acc);
+    if (f & NB_YM) acc = T::fma_r(g.sc, T::mulr(xym, pre), acc);
+    if (f & NB_XM) acc = T::fma_r(g.sc, T::mulr(xxm, pre), acc);
+    acc = T::fma_r(dg * g.sc, xc, acc);
+    if (f & NB_XP) acc = T::fma_r(g.sc, T::mulr(xxp, pre), acc);
+    if (f & NB_YP) acc = T::fma_r(g.sc, T::mulr(xyp, pre), acc);
+    if (f & NB_ZP) acc = T::fma_r(g.sc, T::mulr(xzp, pre), acc);
+  } else {
+    const double wxm = (f & NB_XM) ? (cxm + cc) / 2.0 : 0.0;
+    const double wxp = (f & NB_XP) ? (cc + cxp) / 2.0 : 0.0;
+    const double wym = (f & NB_YM) ? (cym + cc) / 2.0 : 0.0;
+    const double wyp = (f & NB_YP) ? (cc + cyp) / 2.0 : 0.0;
+    const double wzm = (f & NB_ZM) ? (czm + cc) / 2.0 : 0.0;
+    const double wzp = (f & NB_ZP) ? (cc + czp) / 2.0 : 0.0;
+    double ds = 0.0;
+    if (f & NB_XM) ds += wxm;
+    if (f & NB_XP) ds += wxp;
+    if (f & NB_YM) ds += wym;
+    if (f & NB_YP) ds += wyp;
+    if (f & NB_ZM) ds += wzm;
+    if (f & NB_ZP) ds += wzp;
+    if (f & NB_ZM) acc = T::fma_r(wzm * g.sc, T::mulr(xzm, pre), acc);
+    if (f & NB_YM) acc = T::fma_r(wym * g.sc, T::mulr(xym, pre), acc);
+    if (f & NB_XM) acc = T::fma_r(wxm * g.sc, T::mulr(xxm, pre), acc);
+    acc = T::fma_r(-ds * g.sc, xc, acc);
+    if (f & NB_XP) acc = T::fma_r(wxp * g.sc, T::mulr(xxp, pre), acc);
+    if (f & NB_YP) acc = T::fma_r(wyp * g.sc, T::mulr(xyp, pre), acc);
+    if (f & NB_ZP) acc = T::fma_r(wzp * g.sc, T::mulr(xzp, pre), acc);
+  }
+  return acc;
+}
+
+// Plane-marching work decomposition of a 3D slab: a CTA owns a kTileX x kTileY in-plane tile and
+// marches it through kz planes; z+-1 neighbours come from registers, in-plane neighbours from L1
+// (they were fetched as "next plane" values by the neighbouring threads one step earlier), so every
+// stencil input is pulled from L2/HBM about once instead of five times.
+constexpr int kTileX = 32, kTileY = 8; // kTileX * kTileY == kThreads
+struct March {
+  int ntx, nty, nzc, zc; // tiles in x, y; z-chunks; planes per chunk
+  long long units;       // ntx * nty * nzc
+};
+__host__ __device__ inline March make_march(const Geom &g, int target_units) {
+  March m;
+  m.ntx = (g.nx + kTileX - 1) / kTileX;
+  m.nty = (g.ny + kTileY - 1) / kTileY;
+  const long long tiles = (long long)m.ntx * m.nty;
+  long long chunks = (target_units + tiles - 1) / tiles;
+  if (chunks < 1) chunks = 1;
+  int zc = (int)((g.nz_loc + chunks - 1) / chunks);
+  if (zc < 8) zc = 8;
+  if (zc > g.nz_loc) zc = g.nz_loc;
+  m.zc = zc;
+  m.nzc = (g.nz_loc + zc - 1) / zc;
+  m.units = tiles * m.nzc;
+  return m;
+}
+
 template <class S> struct GlobalFetch {
   const S *__restrict__ p;
   __device__ __forceinline__ S operator()(long long i) const { return p[i]; }

@@ -192,7 +192,12 @@ void lanczos_t(nls_engine *e, const S *start, double *scal) {
       const bool first = i0 == c0;
 #define LA(NC)                                                                                           \
   do {                                                                                                   \
-    if (first) LAUNCH(e, (k_lanczos_a<S, ANISO, NC, true>), gr, e->g, start, V, e->colstride, j, i0, cnt, e->cf, scal, e->rc);  \
+    if (first && i0 == 0 && e->g.dim3 && !(e->d.flags & NLS_FLAG_NO_MARCH)) {                            \
+      const dim3 g3 = grid_for(e, (const void *)k_lanczos_a3<S, ANISO, NC>);                             \
+      const March mc = make_march(e->g, 8 * (int)g3.x);                                                  \
+      k_lanczos_a3<S, ANISO, NC><<<g3, kThreads, 0, e->stream>>>(e->g, mc, start, V, e->colstride, j, cnt, e->cf, scal, e->rc); \
+      e->count();                                                                                        \
+    } else if (first) LAUNCH(e, (k_lanczos_a<S, ANISO, NC, true>), gr, e->g, start, V, e->colstride, j, i0, cnt, e->cf, scal, e->rc);  \
     else LAUNCH(e, (k_lanczos_a<S, ANISO, NC, false>), gr, e->g, start, V, e->colstride, j, i0, cnt, e->cf, scal, e->rc);       \
   } while (0)
       if (cnt <= 2) LA(2);

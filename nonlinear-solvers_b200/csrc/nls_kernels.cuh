@@ -128,6 +128,101 @@ k_lanczos_a(Geom g, const S *__restrict__ start, S *__restrict__ V, size_t colst
   grid_reduce<NC * T::W>(acc, rc, sb + kOffH + i0 * T::W);
 }
 
+// streaming (evict-first) loads the scheduler may move freely: basis columns are read once per pass
+__device__ __forceinline__ double ld_stream(const double *p) {
+  double v;
+  asm("ld.global.cs.f64 %0, [%1];" : "=d"(v) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ double2 ld_stream(const double2 *p) {
+  double2 v;
+  asm("ld.global.cs.v2.f64 {%0,%1}, [%2];" : "=d"(v.x), "=d"(v.y) : "l"(p));
+  return v;
+}
+
+// Pass A, FIRST chunk, 3D grids: plane-marching form (see March in nls_device.cuh).  Same
+// arithmetic as k_lanczos_a<.., FIRST = true>; only the order in which sites are visited and
+// where the stencil neighbours come from differ.
+template <class S, bool ANISO, int NC>
+__global__ void __launch_bounds__(kThreads, 2)
+k_lanczos_a3(Geom g, March mc, const S *__restrict__ start, S *__restrict__ V, size_t colstride, int j,
+             int cnt, const double *__restrict__ cf, double *scal, RedCtx rc) {
+  using T = Sc<S>;
+  double *sb = scal + (size_t)blockIdx.y * kScalStride;
+  const S *cj = traj(colptr<S>(start, V, colstride, j), g);
+  const S *cm = j > 0 ? traj(colptr<S>(start, V, colstride, j - 1), g) : nullptr;
+  S *wc = traj(V + (size_t)j * colstride, g); // column j+1
+  const S *cb = traj(start, g);               // column 0; column i >= 1 at traj(V) + (i-1)*colstride
+  const S *vb = traj((const S *)V, g);
+  const double *cfb = ANISO ? cf + g.halo : nullptr;
+  const double bj = sqrt(sb[kOffNrm2 + j]);
+  const double inv = 1.0 / bj;
+  const double cmul = j > 0 ? -bj / sqrt(sb[kOffNrm2 + j - 1]) : 0.0;
+  double acc[NC * T::W];
+#pragma unroll
+  for (int k = 0; k < NC * T::W; ++k) acc[k] = 0.0;
+  const int tx = threadIdx.x % kTileX, ty = threadIdx.x / kTileX;
+  const long long tiles = (long long)mc.ntx * mc.nty;
+  for (long long unit = blockIdx.x; unit < mc.units; unit += gridDim.x) {
+    const int tile = (int)(unit % tiles), zc = (int)(unit / tiles);
+    const int i = (tile % mc.ntx) * kTileX + tx, jj = (tile / mc.ntx) * kTileY + ty;
+    if (i >= g.nx || jj >= g.ny) continue;
+    const int k0 = zc * mc.zc, k1 = min(k0 + mc.zc, g.nz_loc);
+    long long idx = ((long long)k0 * g.ny + jj) * g.nx + i;
+    unsigned fxy = 0;
+    if (i != 0) fxy |= NB_XM;
+    if (i != g.nx - 1) fxy |= NB_XP;
+    const bool ring_xy = i == 0 || i == g.nx - 1 || jj == 0 || jj == g.ny - 1;
+    // z window (ghost planes of a slab sit at idx -+ plane; the flat-index tests gate the global ends)
+    S xc = cj[idx];
+    S xzm = (g.z0 + k0 > 0) ? cj[idx - g.plane] : T::zero();
+    double cc = 0.0, czm = 0.0;
+    if (ANISO) {
+      cc = cfb[idx];
+      czm = (g.z0 + k0 > 0) ? cfb[idx - g.plane] : 0.0;
+    }
+    for (int k = k0; k < k1; ++k, idx += g.plane) {
+      const int kg = g.z0 + k;
+      unsigned f = fxy;
+      if (!(kg == 0 && jj == 0)) f |= NB_YM;                        // gi >= nx
+      if (!(kg == g.nz_glob - 1 && jj == g.ny - 1)) f |= NB_YP;     // gi + nx < nglob (y-wrap quirk kept)
+      if (kg > 0) f |= NB_ZM;
+      if (kg < g.nz_glob - 1) f |= NB_ZP;
+      if (ring_xy || kg == 0 || kg == g.nz_glob - 1) f |= NB_RING;
+      S cmv = T::zero();
+      if (j > 0) cmv = ld_stream(cm + idx);
+      const S xzp = (f & NB_ZP) ? cj[idx + g.plane] : T::zero();
+      const S xym = (f & NB_YM) ? cj[idx - g.nx] : T::zero();
+      const S xyp = (f & NB_YP) ? cj[idx + g.nx] : T::zero();
+      const S xxm = (f & NB_XM) ? cj[idx - 1] : T::zero();
+      const S xxp = (f & NB_XP) ? cj[idx + 1] : T::zero();
+      double czp = 0.0, cym = 0.0, cyp = 0.0, cxm = 0.0, cxp = 0.0;
+      if (ANISO) {
+        czp = (f & NB_ZP) ? cfb[idx + g.plane] : 0.0;
+        cym = (f & NB_YM) ? cfb[idx - g.nx] : 0.0;
+        cyp = (f & NB_YP) ? cfb[idx + g.nx] : 0.0;
+        cxm = (f & NB_XM) ? cfb[idx - 1] : 0.0;
+        cxp = (f & NB_XP) ? cfb[idx + 1] : 0.0;
+      }
+      S w = stencil_vals<S, ANISO>(g, f, inv, xc, xzm, xym, xxm, xxp, xyp, xzp, cc, czm, cym, cxm, cxp, cyp, czp);
+      if (j > 0) w = T::fma_r(cmul, cmv, w);
+      __stcs(wc + idx, w);
+#pragma unroll
+      for (int q = 0; q < NC; ++q)
+        if (q < cnt) {
+          S vq;
+          if (q == j) vq = xc;            // already in the z window
+          else if (q == j - 1) vq = cmv;  // the recurrence term
+          else vq = q == 0 ? ld_stream(cb + idx) : ld_stream(vb + (size_t)(q - 1) * colstride + idx);
+          T::dot_acc(acc + q * T::W, vq, w);
+        }
+      xzm = xc; xc = xzp;
+      czm = cc; cc = czp;
+    }
+  }
+  grid_reduce<NC * T::W>(acc, rc, sb + kOffH);
+}
+
 // columns [i0, i0+cnt).  LAST: ||w||^2 -> nrm2[j+1], T(j,j) -> alpha[j], halo push of column j+1.
 template <class S, int NC, bool LAST>
 __global__ void __launch_bounds__(kThreads, 2)

@@ -368,3 +368,45 @@ def test_persistent_kernel_matches_multikernel_and_oracle(orc, case):
     assert res[1][1] > steps, "multi-kernel path expected"
     assert rel_l2(res[0][0], ref) < 1e-11
     assert rel_l2(res[0][0], res[1][0]) < 1e-11
+
+
+# ---- plane-marching pass A (3D) vs the flat-index pass and the oracle ------------------------
+@pytest.mark.parametrize("dims,eq,lap", [((37, 29, 23), EQ.NLSE_CUBIC, LAP.UNIFORM), ((40, 33, 12), EQ.NLSE_CQ, LAP.ANISO),
+                                         ((64, 64, 64), EQ.NLSE_CUBIC, LAP.ANISO), ((35, 70, 9), EQ.KGE, LAP.ANISO)])
+def test_march_pass_matches_flat_pass_and_oracle(orc, dims, eq, lap):
+    nx, ny, nz = dims
+    real = eq == EQ.KGE
+    kw = dict(equation=eq, integrator=INT.GAUTSCHI if real else INT.SS2, laplacian=lap, krylov_m=12, s1=1.0, s2=-0.1,
+              op_sign=-1.0 if real else 1.0, dt=1e-3)
+    rng = np.random.default_rng(3)
+    cf = 1.0 + 0.1 * rng.standard_normal(nx * ny * nz)
+    mf = 1.0 + 0.2 * rng.standard_normal(nx * ny * nz)
+    big = max(dims)
+    u0 = ics.gaussian_bumps_3d(big, 4.0)[:nz, :ny, :nx]
+    if real:
+        u0 = 0.3 * np.abs(u0)
+    outs = []
+    for flags in (nls_b200.FLAG_NO_PERSISTENT, nls_b200.FLAG_NO_PERSISTENT | nls_b200.FLAG_NO_MARCH):
+        d = Desc.make(nx, ny, nz, dx=0.2, flags=flags, **kw)
+        e = Engine(d)
+        if lap == LAP.ANISO:
+            e.set(FIELD.C, cf)
+        e.set(FIELD.M, mf)
+        x = randn(d, 5)
+        V, a, b = e.lanczos(x)
+        e.set(FIELD.U, u0)
+        if real:
+            e.set(FIELD.V, np.zeros_like(u0))
+        e.step(1e-3, 6)
+        outs.append((V, a, b, e.get()))
+    assert rel_l2(outs[0][0], outs[1][0]) < 1e-12 and np.allclose(outs[0][2], outs[1][2], rtol=1e-13)
+    assert rel_l2(outs[0][3], outs[1][3]) < 1e-13
+    o = orc.Oracle(d)
+    if lap == LAP.ANISO:
+        o.set(FIELD.C, cf)
+    o.set(FIELD.M, mf)
+    o.set(FIELD.U, u0)
+    if real:
+        o.set(FIELD.V, np.zeros_like(u0))
+    o.step(1e-3, 6)
+    assert rel_l2(outs[0][3], o.get()) < 1e-11
