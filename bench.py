@@ -168,6 +168,16 @@ def peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def measured_traffic(workload, steps_per_launch):
+    """ncu-measured DRAM bytes of the dominant kernel per launch (profiles/traffic.json), or None."""
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    try:
+        ent = json.load(open(p)).get(workload)
+        return None if ent is None else ent["bytes_per_step"] * steps_per_launch
+    except (OSError, ValueError, KeyError):
+        return None
+
+
 def pinned_like(a):
     import torch
     t = torch.empty(a.shape, dtype=torch.complex128 if np.iscomplexobj(a) else torch.float64, pin_memory=True)
@@ -339,7 +349,7 @@ def run_native(args, w, rank, world, local_rank):
         "gpu_launches": int(launches),
         "clocks": clocks,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": None, "peak_source": peak_src,
+                     "traffic": measured_traffic(args.workload, K if launches <= 2 else 1), "peak_source": peak_src,
                      "model": f"{bpss:.0f} algorithmic B/site-step (SURVEY 8d, full re-orthogonalisation) x "
                               f"site-steps/s; whole-step graph ({launches // max(K, 1)} kernels/step)"},
     }

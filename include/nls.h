@@ -137,7 +137,10 @@ typedef struct nls_desc {
 enum {
   NLS_FLAG_NO_GRAPH = 1u, /* launch kernels directly instead of replaying a CUDA graph */
   NLS_FLAG_NO_PERSISTENT = 2u, /* never use the persistent cooperative step kernel */
-  NLS_FLAG_NO_MARCH = 8u,   /* 3D: use the flat-index stencil pass instead of the plane-marching one */
+  NLS_FLAG_MARCH = 8u,      /* 3D: plane-marching stencil pass (z window in registers); measured slower than
+                             * the TMA-staged and flat passes on B200, kept as an option */
+  NLS_FLAG_NO_TMA = 16u,    /* never use the TMA-staged Lanczos passes (nls_tma.cuh) */
+  NLS_FLAG_FORCE_TMA = 32u, /* use them below the size threshold too (tests) */
   NLS_FLAG_SEWI_HOST2D = 4u /* NLS_INT_SEWI with the sign convention of the 2D cubic HOST solver:
                              * u+ = e^{-2 tau L} u- + 2 tau e^{-tau L} sinc(dt L) B(u)
                              * (nlse_cubic_gautschi_solver.hpp:21-39) */

@@ -27,7 +27,9 @@ RED = SimpleNamespace(MASS=0, NONFINITE=1)
 FLAG_NO_GRAPH = 1
 FLAG_NO_PERSISTENT = 2
 FLAG_SEWI_HOST2D = 4
-FLAG_NO_MARCH = 8
+FLAG_MARCH = 8
+FLAG_NO_TMA = 16
+FLAG_FORCE_TMA = 32
 
 
 class NlsError(RuntimeError):

@@ -179,6 +179,32 @@ __device__ __forceinline__ S stencil_vals(const Geom &g, unsigned f, double pre,
   return acc;
 }
 
+// NB_* flags of a site from its flat index: the reference's triplet-loop conditions
+// (laplacians.hpp:33-42, :133-148), evaluated once per site
+__device__ __forceinline__ unsigned site_flags(const Geom &g, long long idx) {
+  const long long gi = idx + g.goff;
+  const unsigned ugi = (unsigned)gi;
+  const unsigned i = ugi % (unsigned)g.nx;
+  const unsigned jj = ugi / (unsigned)g.nx;
+  unsigned f = 0;
+  if (i != 0) f |= NB_XM;
+  if (i != (unsigned)(g.nx - 1)) f |= NB_XP;
+  if (gi >= g.nx) f |= NB_YM;
+  if (gi + g.nx < g.nglob) f |= NB_YP;
+  bool ring;
+  if (g.dim3) {
+    if (gi >= g.plane) f |= NB_ZM;
+    if (gi + g.plane < g.nglob) f |= NB_ZP;
+    const unsigned j = jj % (unsigned)g.ny, k = jj / (unsigned)g.ny;
+    ring = i == 0 || i == (unsigned)(g.nx - 1) || j == 0 || j == (unsigned)(g.ny - 1) || k == 0 ||
+           k == (unsigned)(g.nz_glob - 1);
+  } else {
+    ring = i == 0 || i == (unsigned)(g.nx - 1) || jj == 0 || jj == (unsigned)(g.ny - 1);
+  }
+  if (ring) f |= NB_RING;
+  return f;
+}
+
 // Plane-marching work decomposition of a 3D slab: a CTA owns a kTileX x kTileY in-plane tile and
 // marches it through kz planes; z+-1 neighbours come from registers, in-plane neighbours from L1
 // (they were fetched as "next plane" values by the neighbouring threads one step earlier), so every
@@ -286,9 +312,8 @@ struct RedCtx {
 };
 
 // called by all threads of the last CTA; s_tot[K] holds this slab's totals
-template <int K>
-__device__ __forceinline__ void slab_allreduce(const SlabCtx &sc, double *s_tot, double *dst, double *dst1, int split) {
-  static_assert(K <= kSlabMaxK, "reduction too wide for the slab mailbox");
+__device__ __forceinline__ void slab_allreduce_rt(const SlabCtx &sc, int K, double *s_tot, double *dst, double *dst1,
+                                                  int split) {
   SlabMailbox *mine = sc.box[sc.rank];
   const unsigned long long seq = *(volatile unsigned long long *)&mine->seq; // written only by this rank's previous reduction
   const int slot = (int)(seq % kSlabSlots);
@@ -319,6 +344,11 @@ __device__ __forceinline__ void slab_allreduce(const SlabCtx &sc, double *s_tot,
     else dst1[threadIdx.x - split] = v;
   }
   if (threadIdx.x == 0) mine->seq = seq + 1;
+}
+template <int K>
+__device__ __forceinline__ void slab_allreduce(const SlabCtx &sc, double *s_tot, double *dst, double *dst1, int split) {
+  static_assert(K <= kSlabMaxK, "reduction too wide for the slab mailbox");
+  slab_allreduce_rt(sc, K, s_tot, dst, dst1, split);
 }
 
 template <int K>

@@ -2,6 +2,7 @@
 // Owns device memory, one stream per handle, CUDA-graph capture of a whole time step.
 // No CPU fallback anywhere: without a CUDA device every entry point returns NLS_ERR_CUDA.
 #include "nls_persist.cuh"
+#include "nls_tma.cuh"
 
 #include <unistd.h>
 
@@ -42,6 +43,8 @@ struct nls_engine {
   int batch = 1;
   int nblk = 1; // capacity of the partial-sum array (max CTAs per trajectory)
   int nsm = 148;
+  int smem_optin = 0;  // max dynamic shared memory per CTA
+  bool tma_ok = false; // TMA-staged Lanczos passes usable (alignment + size), see tma_setup
   cudaStream_t stream = nullptr;
   // device memory (all n-vectors: [batch][stride] scalars)
   void *V = nullptr;     // m-1 columns
@@ -178,6 +181,72 @@ void halo_exchange(nls_engine *e, const void *buf) {
 }
 
 // ---------------------------------------------------------------- Lanczos (K2)
+// ---------------------------------------------------------------- TMA-staged passes (nls_tma.cuh)
+// Bulk copies need 16-byte aligned addresses and sizes: always true for complex128 vectors; float64
+// vectors (and the c field) need even nx, plane, n and strides.
+void tma_setup(nls_engine *e) {
+  const Geom &g = e->g;
+  e->tma_ok = false;
+  if ((e->d.flags & NLS_FLAG_NO_TMA) || e->batch != 1 || e->smem_optin < 160 * 1024) return;
+  if (g.n < (1LL << 20) && !(e->d.flags & NLS_FLAG_FORCE_TMA)) return; // small grids are launch-bound anyway
+  const bool even = g.nx % 2 == 0 && g.n % 2 == 0 && g.halo % 2 == 0 && g.stride % 2 == 0 &&
+                    (!g.dim3 || g.plane % 2 == 0) && e->colstride % 2 == 0;
+  if (!e->cplx && !even) return;
+  if (e->cplx && e->d.laplacian == NLS_LAP_ANISO && !even) return;
+  e->tma_ok = true;
+}
+
+TmaPlan tma_plan(nls_engine *e, int nseg, size_t extra) {
+  TmaPlan pl;
+  pl.tile = kTmaTileBytes / (int)e->esz;
+  pl.ntile = (int)((e->g.n + pl.tile - 1) / pl.tile);
+  pl.stage_bytes = ((size_t)nseg * kTmaTileBytes + extra + 127) / 128 * 128;
+  long long ns = ((long long)e->smem_optin - kTmaHdrBytes) / (long long)pl.stage_bytes;
+  pl.nstages = (int)(ns > 4 ? 4 : ns);
+  pl.smem_bytes = kTmaHdrBytes + (size_t)pl.nstages * pl.stage_bytes;
+  return pl;
+}
+
+bool tma_attr(const void *fn, int bytes) { // opt in to large dynamic shared memory once per kernel
+  static thread_local std::unordered_map<const void *, bool> done;
+  auto it = done.find(fn);
+  if (it != done.end()) return it->second;
+  const bool ok = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes) == cudaSuccess;
+  if (!ok) cudaGetLastError();
+  done[fn] = ok;
+  return ok;
+}
+
+template <class S, bool ANISO>
+bool launch_a_tma(nls_engine *e, const S *start, S *V, int j, double *scal) {
+  if (!e->tma_ok || j + 1 > kTmaMaxCols || e->d.reorth != NLS_REORTH_FULL) return false;
+  const TmaPlan pl = tma_plan(e, j + 1 + (ANISO ? 10 : 5), 64);
+  const void *fn = (const void *)k_lanczos_a_tma<S, ANISO>;
+  if (pl.nstages < 2 || !tma_attr(fn, e->smem_optin)) return false;
+  const int gx = pl.ntile < e->nsm ? pl.ntile : e->nsm;
+  k_lanczos_a_tma<S, ANISO><<<dim3(gx, 1), kTmaThreads, pl.smem_bytes, e->stream>>>(e->g, pl, start, V, e->colstride, j,
+                                                                                 e->cf, scal, e->rc, e->status);
+  e->count();
+  return true;
+}
+
+template <class S>
+bool launch_b_tma(nls_engine *e, const S *start, S *V, int j, int i0, int cnt, bool last, double *scal, Halo<S> hp) {
+  if (!e->tma_ok || cnt > kTmaMaxCols) return false;
+  const TmaPlan pl = tma_plan(e, cnt + 1, 0);
+  const void *fn = last ? (const void *)k_lanczos_b_tma<S, true> : (const void *)k_lanczos_b_tma<S, false>;
+  if (pl.nstages < 2 || !tma_attr(fn, e->smem_optin)) return false;
+  const int gx = pl.ntile < e->nsm ? pl.ntile : e->nsm;
+  if (last)
+    k_lanczos_b_tma<S, true><<<dim3(gx, 1), kTmaThreads, pl.smem_bytes, e->stream>>>(e->g, pl, start, V, e->colstride, j, i0,
+                                                                                   cnt, scal, e->rc, hp, e->status);
+  else
+    k_lanczos_b_tma<S, false><<<dim3(gx, 1), kTmaThreads, pl.smem_bytes, e->stream>>>(e->g, pl, start, V, e->colstride, j, i0,
+                                                                                    cnt, scal, e->rc, hp, e->status);
+  e->count();
+  return true;
+}
+
 template <class S, bool ANISO>
 void lanczos_t(nls_engine *e, const S *start, double *scal) {
   const int m = e->m;
@@ -190,9 +259,10 @@ void lanczos_t(nls_engine *e, const S *start, double *scal) {
     for (int i0 = c0; i0 <= j; i0 += kNC) {
       const int cnt = j + 1 - i0 < kNC ? j + 1 - i0 : kNC;
       const bool first = i0 == c0;
+      if (first && i0 == 0 && cnt == j + 1 && launch_a_tma<S, ANISO>(e, start, V, j, scal)) continue;
 #define LA(NC)                                                                                           \
   do {                                                                                                   \
-    if (first && i0 == 0 && e->g.dim3 && !(e->d.flags & NLS_FLAG_NO_MARCH)) {                            \
+    if (first && i0 == 0 && e->g.dim3 && (e->d.flags & NLS_FLAG_MARCH)) {                            \
       const dim3 g3 = grid_for(e, (const void *)k_lanczos_a3<S, ANISO, NC>);                             \
       const March mc = make_march(e->g, 8 * (int)g3.x);                                                  \
       k_lanczos_a3<S, ANISO, NC><<<g3, kThreads, 0, e->stream>>>(e->g, mc, start, V, e->colstride, j, cnt, e->cf, scal, e->rc); \
@@ -216,6 +286,7 @@ void lanczos_t(nls_engine *e, const S *start, double *scal) {
       const int cnt = j + 1 - i0 < kNC ? j + 1 - i0 : kNC;
       const bool last = i0 + kNC > j;
       const Halo<S> hp = last ? halo_for<S>(e, V + (size_t)j * e->colstride) : Halo<S>{nullptr, nullptr};
+      if (launch_b_tma<S>(e, start, V, j, i0, cnt, last, scal, hp)) continue;
 #define LB(NC)                                                                                           \
   do {                                                                                                   \
     if (last) LAUNCH(e, (k_lanczos_b<S, NC, true>), gr, e->g, start, V, e->colstride, j, i0, cnt, scal, e->rc, hp);  \
@@ -457,8 +528,9 @@ void pk_setup(nls_engine *e) {
   const nls_desc &d = e->d;
   e->pk_ok = false;
   if (d.flags & NLS_FLAG_NO_PERSISTENT) return;
-  if (e->batch != 1 || e->g.halo != 0 || d.reorth != NLS_REORTH_FULL) return;
-  if (d.integrator != NLS_INT_SS2 && d.integrator != NLS_INT_GAUTSCHI) return;
+  const bool sv = d.integrator == NLS_INT_SV;
+  if (e->batch != 1 || e->g.halo != 0 || (!sv && d.reorth != NLS_REORTH_FULL)) return;
+  if (d.integrator != NLS_INT_SS2 && d.integrator != NLS_INT_GAUTSCHI && !sv) return;
   int dev = d.device, nsm = 0, smem_max = 0, coop = 0;
   cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev);
   cudaDeviceGetAttribute(&smem_max, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
@@ -471,6 +543,7 @@ void pk_setup(nls_engine *e) {
   if (smem > (size_t)smem_max) return;
   const bool an = d.laplacian == NLS_LAP_ANISO;
   const void *fn = e->cplx ? (an ? (const void *)k_pk_nlse<true> : (const void *)k_pk_nlse<false>)
+                   : sv    ? (an ? (const void *)k_pk_sv<true> : (const void *)k_pk_sv<false>)
                            : (an ? (const void *)k_pk_gautschi<true> : (const void *)k_pk_gautschi<false>);
   if (cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) {
     cudaGetLastError();
@@ -509,6 +582,12 @@ int run_steps_pk(nls_engine *e, double dt, uint32_t nsteps) {
     const void *fn = an ? (const void *)k_pk_nlse<true> : (const void *)k_pk_nlse<false>;
     CU(cudaLaunchCooperativeKernel(fn, dim3(a.ncta), dim3(kPkThreads), args, e->pk_smem, e->stream));
     e->phase = (e->phase + (int)(nsteps & 1u)) & 1;
+  } else if (e->d.integrator == NLS_INT_SV) {
+    double *b0 = (double *)e->u[e->phase], *b1 = (double *)e->u[(e->phase + 1) % 3], *b2 = (double *)e->u[(e->phase + 2) % 3];
+    void *args[] = {&a, &b0, &b1, &b2};
+    const void *fn = an ? (const void *)k_pk_sv<true> : (const void *)k_pk_sv<false>;
+    CU(cudaLaunchCooperativeKernel(fn, dim3(a.ncta), dim3(kPkThreads), args, e->pk_smem, e->stream));
+    e->phase = (int)((e->phase + nsteps) % 3u);
   } else {
     a.u0 = e->u[0]; a.u1 = e->u[1];
     double *gb = (double *)e->w0;
@@ -552,6 +631,7 @@ int check_status(nls_engine *e) {
   CU(cudaMemcpyAsync(&st, e->status, sizeof(int), cudaMemcpyDeviceToHost, e->stream));
   CU(cudaStreamSynchronize(e->stream));
   if (st == 2) return fail(NLS_ERR_STATE, "z-slab exchange timed out waiting for a peer rank");
+  if (st == 3) return fail(NLS_ERR_STATE, "TMA pipeline timed out (internal error)");
   if (st) return fail(NLS_ERR_STATE, "tridiagonal eigensolver did not converge (non-finite state?)");
   return NLS_OK;
 }
@@ -635,6 +715,7 @@ int nls_create(const nls_desc *desc, nls_handle *out) {
   // L *= 1/(dx*dy) (laplacians.hpp:49); 3D: 1/(dx*dx) (:153)
   g.sc = sgn * (1.0 / (g.dim3 ? d.dx * d.dx : d.dx * d.dy));
   cudaDeviceGetAttribute(&e->nsm, cudaDevAttrMultiProcessorCount, d.device);
+  cudaDeviceGetAttribute(&e->smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, d.device);
   if (e->nsm < 1) e->nsm = 148;
   long long want = (g.n + kThreads - 1) / kThreads;
   long long cap = 8LL * e->nsm; // at most 8 CTAs of 256 threads per SM
@@ -685,6 +766,7 @@ int nls_create(const nls_desc *desc, nls_handle *out) {
   }
   ok = ok && cudaDeviceSynchronize() == cudaSuccess;
   if (ok) pk_setup(e);
+  if (ok) tma_setup(e);
   if (!ok) {
     std::string msg = std::string("allocation failed: ") + cudaGetErrorString(cudaGetLastError());
     nls_destroy(e);

@@ -753,4 +753,59 @@ __global__ void __launch_bounds__(kPkThreads, 1) k_pk_gautschi(PkArgs a, double 
   }
 }
 
+
+// ---------------------------------------------------------------- real equations, Stoermer-Verlet
+// u+ = 2u - u_past + tau^2 (L u - m f(u)) followed by the no-flux copy (sg_single_sv_solver.hpp:9-19,
+// kg_sv_solver.hpp:13-21, boundaries.hpp:40-57), nsteps steps per launch.  u (with its +-nx halo
+// rows) and u_past stay in shared memory for the whole launch; each step writes u+ once to the
+// rotating global buffers (the neighbours' halo rows and the final state come from there) and
+// costs one grid barrier.  buf[0] = u, buf[2] = u_past at entry; step s writes buf[(s+1)%3].
+template <bool ANISO>
+__global__ void __launch_bounds__(kPkThreads, 1) k_pk_sv(PkArgs a, double *b0, double *b1, double *b2) {
+  extern __shared__ __align__(16) unsigned char pk_smem[];
+  PkCtx<double> c;
+  pk_carve<double>(a, c, pk_smem);
+  GridSync gs{a.bar, 0u, (unsigned)a.ncta, 0};
+  double *buf[3] = {b0, b1, b2};
+  double *xc = c.X + a.g.nx;
+  const double *mfc = a.mf + c.s0;
+  const double *cfg = ANISO ? a.cf + c.s0 : nullptr;
+  const double tau2 = a.dt * a.dt;
+  for (int li = threadIdx.x; li < c.cnt; li += kPkThreads) {
+    xc[li] = buf[0][c.s0 + li];
+    c.Wt[li] = buf[2][c.s0 + li];
+  }
+  __syncthreads();
+  int p = 0;
+  for (int step = 0; step < a.nsteps; ++step) {
+    const double *ucur = buf[p];
+    double *unew = buf[(p + 1) % 3];
+    pk_load_halo<double>(a, c, ucur);
+    for (int li = threadIdx.x; li < c.cnt; li += kPkThreads) {
+      const long long idx = c.s0 + li;
+      const unsigned f = c.flag[li];
+      double un;
+      if (f & PF_RING) { // boundary site: the value the update gives at the clamped (interior) site
+        const long long sc = clamp_site(a.g, idx);
+        const double uc = __ldcg(ucur + sc);
+        const double lu = stencil_site_f<double, ANISO>(a.g, [&](long long q) { return __ldcg(ucur + q); }, a.cf, sc, 1.0);
+        const double upv = sc >= c.s0 && sc < c.s0 + c.cnt ? c.Wt[sc - c.s0] : __ldcg(buf[(p + 2) % 3] + sc);
+        un = 2 * uc - upv + tau2 * (lu - a.mf[sc] * pk_f_real(a.eq, uc));
+      } else {
+        const double uc = xc[li];
+        const double lu = pk_stencil<double, ANISO>(a.g, xc, ucur + c.s0, cfg, f, li);
+        un = 2 * uc - c.Wt[li] + tau2 * (lu - mfc[li] * pk_f_real(a.eq, uc));
+      }
+      unew[idx] = un;
+    }
+    __syncthreads(); // all reads of the tiles are done
+    for (int li = threadIdx.x; li < c.cnt; li += kPkThreads) {
+      c.Wt[li] = xc[li];
+      xc[li] = __ldcg(unew + c.s0 + li); // written by this very thread in the loop above
+    }
+    if (!grid_barrier(gs)) return;
+    p = (p + 1) % 3;
+  }
+}
+
 } // namespace nls
