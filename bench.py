@@ -290,6 +290,7 @@ def run_native(args, w, rank, world, local_rank):
     l0 = eng.launch_count()
     ms = eng.step_timed(dt, K)
     launches = eng.launch_count() - l0
+    tma_launches = eng.tma_launch_count()
     barrier()
     # ---- end to end through the C ABI with pinned HOST buffers: per segment of `seg` steps,
     # H2D of the state (u, u_past / u) and D2H of the result (u, v / u)
@@ -346,7 +347,7 @@ def run_native(args, w, rank, world, local_rank):
         "e2e": {"value": e2e, "unit": "site-steps/s", "h2d_bytes_per_step": h2d / seg,
                 "d2h_bytes_per_step": d2h / seg, "segment_steps": seg,
                 "note": "per segment: pinned-host state -> device, seg steps, state+velocity -> pinned host"},
-        "gpu_launches": int(launches),
+        "gpu_launches": int(launches), "tma_staged_launches_total": int(tma_launches),
         "clocks": clocks,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": measured_traffic(args.workload, K if launches <= 2 else 1), "peak_source": peak_src,

@@ -139,8 +139,11 @@ enum {
   NLS_FLAG_NO_PERSISTENT = 2u, /* never use the persistent cooperative step kernel */
   NLS_FLAG_MARCH = 8u,      /* 3D: plane-marching stencil pass (z window in registers); measured slower than
                              * the TMA-staged and flat passes on B200, kept as an option */
-  NLS_FLAG_NO_TMA = 16u,    /* never use the TMA-staged Lanczos passes (nls_tma.cuh) */
-  NLS_FLAG_FORCE_TMA = 32u, /* use them below the size threshold too (tests) */
+  NLS_FLAG_TMA = 32u,       /* TMA-staged Lanczos passes (nls_tma.cuh: cp.async.bulk + mbarrier ring, arithmetic from
+                             * shared memory).  Correct and tested, but measured slower than the register-staged
+                             * passes on B200 so far, hence opt-in */
+  NLS_FLAG_PK_SV = 64u,     /* Stoermer-Verlet through the persistent kernel (k_pk_sv); off by default: at
+                             * 1024^2 one grid barrier per step (15.7 us) costs more than a k_sv launch (11-14 us) */
   NLS_FLAG_SEWI_HOST2D = 4u /* NLS_INT_SEWI with the sign convention of the 2D cubic HOST solver:
                              * u+ = e^{-2 tau L} u- + 2 tau e^{-tau L} sinc(dt L) B(u)
                              * (nlse_cubic_gautschi_solver.hpp:21-39) */
@@ -182,6 +185,8 @@ int nls_reduce(nls_handle h, int what, double *out);
 
 /* number of kernel launches issued (directly or through graph replays) since creation */
 uint64_t nls_launch_count(nls_handle h);
+/* how many of them were TMA-staged Lanczos passes (nls_tma.cuh) */
+uint64_t nls_tma_launch_count(nls_handle h);
 /* the CUDA stream (cudaStream_t) the handle launches on */
 void *nls_stream(nls_handle h);
 /* time a run of nsteps steps with CUDA events on the handle's stream; ms returned */

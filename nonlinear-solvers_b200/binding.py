@@ -28,8 +28,8 @@ FLAG_NO_GRAPH = 1
 FLAG_NO_PERSISTENT = 2
 FLAG_SEWI_HOST2D = 4
 FLAG_MARCH = 8
-FLAG_NO_TMA = 16
-FLAG_FORCE_TMA = 32
+FLAG_TMA = 32
+FLAG_PK_SV = 64
 
 
 class NlsError(RuntimeError):
@@ -121,6 +121,7 @@ _SIGS = {
     "nls_lanczos": (C.c_int, [_vp, _vp, _vp, _vp, _dp]),
     "nls_reduce": (C.c_int, [_vp, C.c_int, _dp]),
     "nls_launch_count": (C.c_uint64, [_vp]),
+    "nls_tma_launch_count": (C.c_uint64, [_vp]),
     "nls_stream": (_vp, [_vp]),
     "nls_step_timed": (C.c_int, [_vp, C.c_double, C.c_uint32, C.POINTER(C.c_float)]),
     "nls_slab_export": (C.c_int, [_vp, _vp]),
@@ -248,3 +249,6 @@ class Engine:
 
     def launch_count(self):
         return int(self.lib.nls_launch_count(self.h))
+
+    def tma_launch_count(self):
+        return int(self.lib.nls_tma_launch_count(self.h))

@@ -64,8 +64,8 @@ struct nls_engine {
   double start_dt = 0.0;
   cudaGraphExec_t gexec[3] = {nullptr, nullptr, nullptr};
   double gdt[3] = {0, 0, 0};
-  uint64_t glaunch[3] = {0, 0, 0};
-  uint64_t launches = 0;
+  uint64_t glaunch[3] = {0, 0, 0}, gtma[3] = {0, 0, 0};
+  uint64_t launches = 0, tma_launches = 0, cap_tma = 0;
   bool capturing = false;
   uint64_t cap_count = 0;
   // persistent cooperative kernel (nls_persist.cuh)
@@ -91,9 +91,9 @@ struct nls_engine {
   size_t vec_elems() const { return (size_t)batch * g.stride; }
   size_t vec_bytes() const { return vec_elems() * esz; }
   dim3 grid() const { return dim3((unsigned)nblk, (unsigned)batch); }
-  void count() {
-    if (capturing) cap_count++;
-    else launches++;
+  void count(bool tma = false) {
+    if (capturing) { cap_count++; cap_tma += tma; }
+    else { launches++; tma_launches += tma; }
   }
   void *sv(int p) const { return p == 0 ? w0 : wbuf[0]; } // NLSE start vector (rho) of u[p]
 };
@@ -182,18 +182,43 @@ void halo_exchange(nls_engine *e, const void *buf) {
 
 // ---------------------------------------------------------------- Lanczos (K2)
 // ---------------------------------------------------------------- TMA-staged passes (nls_tma.cuh)
+bool tma_attr(const void *fn, int bytes) { // opt in to large dynamic shared memory once per kernel
+  static thread_local std::unordered_map<const void *, bool> done;
+  auto it = done.find(fn);
+  if (it != done.end()) return it->second;
+  const bool ok = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes) == cudaSuccess;
+  if (!ok) cudaGetLastError();
+  done[fn] = ok;
+  return ok;
+}
+
+
 // Bulk copies need 16-byte aligned addresses and sizes: always true for complex128 vectors; float64
 // vectors (and the c field) need even nx, plane, n and strides.
 void tma_setup(nls_engine *e) {
   const Geom &g = e->g;
   e->tma_ok = false;
-  if ((e->d.flags & NLS_FLAG_NO_TMA) || e->batch != 1 || e->smem_optin < 160 * 1024) return;
-  if (g.n < (1LL << 20) && !(e->d.flags & NLS_FLAG_FORCE_TMA)) return; // small grids are launch-bound anyway
+  // opt-in: on B200 the register-staged passes are faster (256^3 complex, 12 columns: pass B 4.1 vs 3.8-6.6 TB/s,
+  // pass A 0.6-2.2 vs 2.1-4.5 TB/s; profiles/r01e_launches_c3_tma.csv) -- the per-tile overhead of the
+  // 256-site tiles that fit a multi-stage ring beside 12 columns is not yet hidden
+  if (!(e->d.flags & NLS_FLAG_TMA) || e->batch != 1 || e->smem_optin < 160 * 1024) return;
   const bool even = g.nx % 2 == 0 && g.n % 2 == 0 && g.halo % 2 == 0 && g.stride % 2 == 0 &&
                     (!g.dim3 || g.plane % 2 == 0) && e->colstride % 2 == 0;
   if (!e->cplx && !even) return;
   if (e->cplx && e->d.laplacian == NLS_LAP_ANISO && !even) return;
-  e->tma_ok = true;
+  // opt in to the large dynamic shared memory now: not allowed later, inside a stream capture
+  bool ok;
+  if (e->cplx)
+    ok = tma_attr((const void *)k_lanczos_a_tma<double2, false>, e->smem_optin) &&
+         tma_attr((const void *)k_lanczos_a_tma<double2, true>, e->smem_optin) &&
+         tma_attr((const void *)k_lanczos_b_tma<double2, false>, e->smem_optin) &&
+         tma_attr((const void *)k_lanczos_b_tma<double2, true>, e->smem_optin);
+  else
+    ok = tma_attr((const void *)k_lanczos_a_tma<double, false>, e->smem_optin) &&
+         tma_attr((const void *)k_lanczos_a_tma<double, true>, e->smem_optin) &&
+         tma_attr((const void *)k_lanczos_b_tma<double, false>, e->smem_optin) &&
+         tma_attr((const void *)k_lanczos_b_tma<double, true>, e->smem_optin);
+  e->tma_ok = ok;
 }
 
 TmaPlan tma_plan(nls_engine *e, int nseg, size_t extra) {
@@ -207,16 +232,6 @@ TmaPlan tma_plan(nls_engine *e, int nseg, size_t extra) {
   return pl;
 }
 
-bool tma_attr(const void *fn, int bytes) { // opt in to large dynamic shared memory once per kernel
-  static thread_local std::unordered_map<const void *, bool> done;
-  auto it = done.find(fn);
-  if (it != done.end()) return it->second;
-  const bool ok = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes) == cudaSuccess;
-  if (!ok) cudaGetLastError();
-  done[fn] = ok;
-  return ok;
-}
-
 template <class S, bool ANISO>
 bool launch_a_tma(nls_engine *e, const S *start, S *V, int j, double *scal) {
   if (!e->tma_ok || j + 1 > kTmaMaxCols || e->d.reorth != NLS_REORTH_FULL) return false;
@@ -226,7 +241,7 @@ bool launch_a_tma(nls_engine *e, const S *start, S *V, int j, double *scal) {
   const int gx = pl.ntile < e->nsm ? pl.ntile : e->nsm;
   k_lanczos_a_tma<S, ANISO><<<dim3(gx, 1), kTmaThreads, pl.smem_bytes, e->stream>>>(e->g, pl, start, V, e->colstride, j,
                                                                                  e->cf, scal, e->rc, e->status);
-  e->count();
+  e->count(true);
   return true;
 }
 
@@ -243,7 +258,7 @@ bool launch_b_tma(nls_engine *e, const S *start, S *V, int j, int i0, int cnt, b
   else
     k_lanczos_b_tma<S, false><<<dim3(gx, 1), kTmaThreads, pl.smem_bytes, e->stream>>>(e->g, pl, start, V, e->colstride, j, i0,
                                                                                     cnt, scal, e->rc, hp, e->status);
-  e->count();
+  e->count(true);
   return true;
 }
 
@@ -256,9 +271,13 @@ void lanczos_t(nls_engine *e, const S *start, double *scal) {
   for (int j = 0; j < m - 1; ++j) {
     // columns taking part in the orthogonalisation: all of 0..j (reference), or only j (3-term)
     const int c0 = e->d.reorth == NLS_REORTH_NONE ? j : 0;
-    for (int i0 = c0; i0 <= j; i0 += kNC) {
-      const int cnt = j + 1 - i0 < kNC ? j + 1 - i0 : kNC;
+    // pass A chunks: the stencil-carrying first chunk takes at most kFirst columns (complex: beyond 6
+    // the 128-register budget of 2 CTAs/SM costs more than re-reading w once in a second, dots-only chunk)
+    constexpr int kFirst = sizeof(S) == 16 ? 6 : kNC;
+    for (int i0 = c0, cnt = 0; i0 <= j; i0 += cnt) {
       const bool first = i0 == c0;
+      const int cap = first ? kFirst : kNC;
+      cnt = j + 1 - i0 < cap ? j + 1 - i0 : cap;
       if (first && i0 == 0 && cnt == j + 1 && launch_a_tma<S, ANISO>(e, start, V, j, scal)) continue;
 #define LA(NC)                                                                                           \
   do {                                                                                                   \
@@ -504,6 +523,7 @@ int run_steps(nls_engine *e, double dt, uint32_t nsteps) {
         CU(cudaStreamBeginCapture(e->stream, cudaStreamCaptureModeThreadLocal));
         e->capturing = true;
         e->cap_count = 0;
+        e->cap_tma = 0;
         issue_step(e, dt);
         e->capturing = false;
         CU(cudaStreamEndCapture(e->stream, &graph));
@@ -511,9 +531,11 @@ int run_steps(nls_engine *e, double dt, uint32_t nsteps) {
         cudaGraphDestroy(graph);
         e->gdt[p] = dt;
         e->glaunch[p] = e->cap_count;
+        e->gtma[p] = e->cap_tma;
       }
       CU(cudaGraphLaunch(e->gexec[p], e->stream));
       e->launches += e->glaunch[p];
+      e->tma_launches += e->gtma[p];
     } else {
       issue_step(e, dt);
       CU(cudaGetLastError());
@@ -529,6 +551,7 @@ void pk_setup(nls_engine *e) {
   e->pk_ok = false;
   if (d.flags & NLS_FLAG_NO_PERSISTENT) return;
   const bool sv = d.integrator == NLS_INT_SV;
+  if (sv && !(d.flags & NLS_FLAG_PK_SV)) return; // measured: one barrier per step costs more than a k_sv launch
   if (e->batch != 1 || e->g.halo != 0 || (!sv && d.reorth != NLS_REORTH_FULL)) return;
   if (d.integrator != NLS_INT_SS2 && d.integrator != NLS_INT_GAUTSCHI && !sv) return;
   int dev = d.device, nsm = 0, smem_max = 0, coop = 0;
@@ -716,6 +739,7 @@ int nls_create(const nls_desc *desc, nls_handle *out) {
   g.sc = sgn * (1.0 / (g.dim3 ? d.dx * d.dx : d.dx * d.dy));
   cudaDeviceGetAttribute(&e->nsm, cudaDevAttrMultiProcessorCount, d.device);
   cudaDeviceGetAttribute(&e->smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, d.device);
+  e->smem_optin -= 4096; // dynamic budget: leave room for the kernels' static shared memory
   if (e->nsm < 1) e->nsm = 148;
   long long want = (g.n + kThreads - 1) / kThreads;
   long long cap = 8LL * e->nsm; // at most 8 CTAs of 256 threads per SM
@@ -903,6 +927,7 @@ int nls_step_timed(nls_handle e, double dt, uint32_t nsteps, float *ms) {
 }
 
 uint64_t nls_launch_count(nls_handle e) { return e ? e->launches : 0; }
+uint64_t nls_tma_launch_count(nls_handle e) { return e ? e->tma_launches : 0; }
 void *nls_stream(nls_handle e) { return e ? (void *)e->stream : nullptr; }
 
 int nls_stencil_apply(nls_handle e, const void *x, void *y) {

@@ -114,7 +114,7 @@ def main():
          6, 5e-4, False, 1e-11)
     case("nlse 3-term", 16, 18, dict(equation=EQ.NLSE_CUBIC, krylov_m=8, reorth=1), 5, 1e-3, False, 1e-11)
     case("nlse cq 3D aniso, TMA passes", 32, 28, dict(equation=EQ.NLSE_CQ, laplacian=LAP.ANISO, krylov_m=12, s1=1.0, s2=-0.1,
-                                                     flags=nls_b200.FLAG_FORCE_TMA), 5, 5e-4, False, 1e-11)
+                                                     flags=nls_b200.FLAG_TMA), 5, 5e-4, False, 1e-11)
     case("nlse sewi 3D", 18, 20, dict(equation=EQ.NLSE_CUBIC, integrator=INT.SEWI, krylov_m=8), 5, 1e-3, False, 1e-11)
     case("kge 3D gautschi aniso", 20, 22, dict(equation=EQ.KGE, integrator=INT.GAUTSCHI, laplacian=LAP.ANISO,
                                                krylov_m=10, op_sign=-1.0), 6, 1e-3, True, 1e-11)

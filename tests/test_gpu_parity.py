@@ -329,7 +329,7 @@ def test_linearity_and_norm_preservation_full_size():
 # ---- persistent cooperative kernel vs the multi-kernel path -------------------------------
 @pytest.mark.parametrize("case", ["nlse2d", "nlse2d_odd", "cq3d_aniso", "sge", "kge_neg", "nlse_m20", "sge_sv", "kge_sv_3d"])
 def test_persistent_kernel_matches_multikernel_and_oracle(orc, case):
-    kw, steps, dt = {}, 12, 1e-3
+    kw, steps, dt, pk_flag = {}, 12, 1e-3, 0
     if case == "nlse2d":
         n, L = 128, 10.0
         dims, u0, v0 = (n, n, 1), ics.gaussian_bumps_2d(n, L), None
@@ -351,11 +351,13 @@ def test_persistent_kernel_matches_multikernel_and_oracle(orc, case):
         dims, u0 = (n, n, 1), ics.kink_2d(n, L)
         v0 = 0.05 * np.cos(u0)
         kw = dict(equation=EQ.SGE, integrator=INT.SV, dt=dt)
+        pk_flag = nls_b200.FLAG_PK_SV
     elif case == "kge_sv_3d":
         n, L, steps = 26, 4.0, 30
         dims, u0 = (n, n, n), 0.3 * np.abs(ics.gaussian_bumps_3d(n, L))
         v0 = 0.05 * np.cos(u0)
         kw = dict(equation=EQ.KGE, integrator=INT.SV, laplacian=LAP.ANISO, dt=dt)
+        pk_flag = nls_b200.FLAG_PK_SV
     elif case == "sge":
         n, L = 160, 10.0
         dims, u0 = (n, n, 1), ics.kink_2d(n, L)
@@ -367,7 +369,7 @@ def test_persistent_kernel_matches_multikernel_and_oracle(orc, case):
         v0 = 0.05 * np.cos(u0)
         kw = dict(equation=EQ.KGE, integrator=INT.GAUTSCHI, krylov_m=10, dt=dt, op_sign=-1.0)
     res = []
-    for flags in (0, nls_b200.FLAG_NO_PERSISTENT):
+    for flags in (pk_flag, nls_b200.FLAG_NO_PERSISTENT):
         d = Desc.make(dims[0], dims[1], dims[2], L=L, flags=flags, **kw)
         cf = 1.0 + 0.1 * np.random.default_rng(2).standard_normal(d.n) if d.laplacian == LAP.ANISO else None
         mf = 1.0 + 0.2 * np.random.default_rng(1).standard_normal(d.n)
@@ -453,7 +455,7 @@ def test_tma_passes_match_register_passes_and_oracle(orc, case):
         u0 = 0.3 * np.abs(u0)
     base = nls_b200.FLAG_NO_PERSISTENT
     outs = []
-    for flags in (base | nls_b200.FLAG_FORCE_TMA, base | nls_b200.FLAG_NO_TMA):
+    for flags in (base | nls_b200.FLAG_TMA, base):
         d = Desc.make(nx, ny, nz, dx=0.2, flags=flags, krylov_m=m, reorth=reorth, dt=dt, **kw)
         e = Engine(d)
         if d.laplacian == LAP.ANISO:
@@ -464,7 +466,8 @@ def test_tma_passes_match_register_passes_and_oracle(orc, case):
         if real:
             e.set(FIELD.V, np.zeros_like(u0))
         e.step(dt, steps)
-        outs.append((V, a, b, e.get(), e.launch_count()))
+        outs.append((V, a, b, e.get(), e.tma_launch_count()))
+    assert outs[0][4] > 0 and outs[1][4] == 0, "first handle must have run the TMA-staged passes, second must not"
     assert rel_l2(outs[0][0][:6], outs[1][0][:6]) < 1e-12 and np.allclose(outs[0][2], outs[1][2], rtol=1e-12)
     G = outs[0][0].conj() @ outs[0][0].T
     assert np.abs(G - np.eye(m)).max() < 1e-11
