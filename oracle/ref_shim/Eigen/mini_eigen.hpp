@@ -65,6 +65,8 @@ public:
   std::vector<T> v;
   VectorX() {}
   explicit VectorX(long n) : v(n) {}
+  template <class U, class = typename std::enable_if<!std::is_same<U, T>::value && std::is_convertible<U, T>::value>::type>
+  VectorX(const VectorX<U> &o) : v(o.v.begin(), o.v.end()) {} // e.g. real expression assigned to a complex vector
   VectorX(const Strided<T> &s) : v(s.n) { for (long i = 0; i < s.n; ++i) v[i] = s.p[i * s.stride]; }
   static VectorX Zero(long n) { VectorX r(n); std::fill(r.v.begin(), r.v.end(), T(0)); return r; }
   static VectorX Ones(long n) { VectorX r(n); std::fill(r.v.begin(), r.v.end(), T(1)); return r; }

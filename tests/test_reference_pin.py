@@ -1,0 +1,135 @@
+"""Pins the CPU oracle (oracle/nls_oracle.cpp) against the REFERENCE'S OWN host sources, compiled
+unmodified into oracle/_ref/libnls_ref.so (oracle/ref_harness.cpp + the mini-Eigen stand-in).
+What this covers: matrix assembly incl. its quirks, Lanczos operation order, every matrix-function
+table, the SS2 / sEWI / Gautschi / Stoermer-Verlet step formulas and the boundary copies -- i.e.
+the reference's source text.  What it cannot cover: Eigen's own arithmetic (absent dependency)."""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+from conftest import rel_l2
+import ics
+import nls_b200
+from nls_b200 import Desc, EQ, INT, LAP, FN, FIELD
+
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle"))
+import ref as refmod  # noqa: E402
+
+pytestmark = pytest.mark.skipif(not refmod.available(), reason="oracle/_ref not built and /root/reference absent")
+
+
+@pytest.fixture(scope="module")
+def R():
+    refmod.build()
+    return refmod.Reference
+
+
+def randn(n, cplx, seed=42):
+    rng = np.random.default_rng(seed)
+    x = rng.standard_normal(n)
+    return x + 1j * rng.standard_normal(n) if cplx else x
+
+
+@pytest.mark.parametrize("dims,aniso", [((14, 14, 1), False), ((12, 12, 1), True), ((7, 7, 7), False), ((6, 6, 6), True)])
+def test_assembled_matrices_are_identical(oracle_lib, R, dims, aniso):
+    nx, ny, nz = dims
+    d = Desc.make(nx, ny, nz, L=3.0, laplacian=LAP.ANISO if aniso else LAP.UNIFORM)
+    c = np.random.default_rng(3).uniform(0.5, 1.5, d.n)
+    o = oracle_lib.Oracle(d)
+    if aniso:
+        o.set(FIELD.C, c)
+    A, B = o.csr(), R(nx, ny, nz, d.dx, aniso, c if aniso else None).matrix()
+    assert A.nnz == B.nnz and abs(A - B).max() <= 1e-13 * abs(B).max()
+    if not aniso:
+        assert abs(A - B).max() == 0  # quirks included: corner rows (2D), y-wrap coupling (3D)
+
+
+@pytest.mark.parametrize("cplx", [False, True])
+@pytest.mark.parametrize("m", [5, 10, 20])
+def test_lanczos_matches_reference_source(oracle_lib, R, cplx, m):
+    n = 40
+    d = Desc.make(n, n, L=5.0, equation=EQ.NLSE_CUBIC if cplx else EQ.SGE, integrator=INT.SS2 if cplx else INT.GAUTSCHI,
+                  krylov_m=m)
+    x = randn(d.n, cplx)
+    V, a, b = oracle_lib.Oracle(d).lanczos(x)
+    Vr, Tr, br = R(n, n, 1, d.dx).lanczos(x, m)
+    assert abs(b[0] - br) <= 1e-14 * br
+    assert np.allclose(a, np.diag(Tr), rtol=1e-12, atol=1e-12 * abs(np.diag(Tr)).max())
+    assert np.allclose(b[1:], np.real(np.diag(Tr, -1)), rtol=1e-12)
+    assert Tr[m - 1, m - 1] == 0  # the last diagonal entry is never computed
+    assert rel_l2(V, Vr) < 1e-9
+
+
+@pytest.mark.parametrize("fn,t,cplx", [(FN.EXP, 1e-2j, True), (FN.EXP, -2e-2j, True), (FN.SINC, 1e-2, True),
+                                       (FN.COS_SQRT, 1e-2, False), (FN.SINC2_SQRT, 1e-2, False), (FN.ID_SQRT, 1e-2, False),
+                                       (FN.SINC2_HALF, 1e-2, False), (FN.MOD_COSINE, 1e-2, False)])
+def test_matrix_functions_match_reference_source(oracle_lib, R, fn, t, cplx):
+    n = 36
+    d = Desc.make(n, n, L=5.0, equation=EQ.NLSE_CUBIC if cplx else EQ.SGE, integrator=INT.SS2 if cplx else INT.GAUTSCHI,
+                  krylov_m=10, op_sign=1.0 if cplx else -1.0)
+    x = randn(d.n, cplx, 7)
+    got = oracle_lib.Oracle(d).matfunc(fn, t, x)
+    ref = R(n, n, 1, d.dx, sign=1.0 if cplx else -1.0).matfunc(fn, t, x)
+    assert rel_l2(got, ref) < 1e-12
+
+
+@pytest.mark.parametrize("eq,kind,dims", [(EQ.NLSE_CUBIC, 0, (32, 32, 1)), (EQ.NLSE_CQ, 1, (28, 28, 1)),
+                                          (EQ.NLSE_SAT, 2, (28, 28, 1))])
+def test_ss2_steps_match_reference_source(oracle_lib, R, eq, kind, dims):
+    nx, ny, nz = dims
+    dt, steps = 1e-3, 12
+    d = Desc.make(nx, ny, nz, L=10.0, equation=eq, krylov_m=10, s1=1.0, s2=-0.1, kappa=0.3)
+    u0 = ics.gaussian_bumps_2d(nx, 10.0)
+    mf = 1.0 + 0.2 * np.random.default_rng(1).standard_normal(d.n)
+    o = oracle_lib.Oracle(d)
+    o.set(FIELD.U, u0); o.set(FIELD.M, mf); o.step(dt, steps)
+    ref = R(nx, ny, nz, d.dx).nlse_steps(kind, u0.ravel(), mf, dt, steps, s1=1.0, s2=-0.1, kappa=0.3)
+    assert rel_l2(o.get(), ref) < 1e-12
+
+
+def test_ss2_3d_aniso_steps_match_reference_source(oracle_lib, R):
+    n, dt, steps = 12, 5e-4, 6
+    d = Desc.make(n, n, n, L=6.0, equation=EQ.NLSE_CUBIC, laplacian=LAP.ANISO, krylov_m=10)
+    c = 1.0 + 0.1 * np.random.default_rng(2).standard_normal(d.n)
+    mf = 1.0 + 0.2 * np.random.default_rng(1).standard_normal(d.n)
+    u0 = ics.gaussian_bumps_3d(n, 6.0)
+    o = oracle_lib.Oracle(d)
+    o.set(FIELD.C, c); o.set(FIELD.U, u0); o.set(FIELD.M, mf); o.step(dt, steps)
+    ref = R(n, n, n, d.dx, True, c).nlse_steps(0, u0.ravel(), mf, dt, steps)
+    assert rel_l2(o.get(), ref) < 1e-12
+
+
+@pytest.mark.parametrize("eq,ss2,sewi,flags,dims", [(EQ.NLSE_CUBIC, 0, 10, nls_b200.FLAG_SEWI_HOST2D, (28, 28, 1)),
+                                                    (EQ.NLSE_CUBIC, 0, 11, 0, (10, 10, 10)),
+                                                    (EQ.NLSE_CQ, 1, 12, 0, (24, 24, 1)), (EQ.NLSE_SAT, 2, 13, 0, (24, 24, 1))])
+def test_sewi_steps_match_reference_source(oracle_lib, R, eq, ss2, sewi, flags, dims):
+    """SS2 start-up step, then sEWI steps, as nlse_cubic_gautschi_driver.cpp:122-137 drives them"""
+    nx, ny, nz = dims
+    dt, steps = 1e-3, 6
+    d = Desc.make(nx, ny, nz, L=10.0, equation=eq, integrator=INT.SEWI, krylov_m=10, s1=1.0, s2=-0.1, kappa=0.3, flags=flags)
+    u0 = ics.gaussian_bumps_3d(nx, 10.0) if nz > 1 else ics.gaussian_bumps_2d(nx, 10.0)
+    mf = 1.0 + 0.2 * np.random.default_rng(1).standard_normal(d.n)
+    o = oracle_lib.Oracle(d)
+    o.set(FIELD.U, u0); o.set(FIELD.M, mf); o.step(dt, 1 + steps)
+    r = R(nx, ny, nz, d.dx)
+    u1 = r.nlse_steps(ss2, u0.ravel(), mf, dt, 1, s1=1.0, s2=-0.1, kappa=0.3)
+    u, up = r.nlse_steps(sewi, u1, mf, dt, steps, uprev=u0.ravel(), s1=1.0, s2=-0.1, kappa=0.3)
+    assert rel_l2(o.get(), u) < 1e-12
+    assert rel_l2(o.get(FIELD.U_PAST), up) < 1e-12
+
+
+@pytest.mark.parametrize("eq,integ,kind,sign", [(EQ.SGE, INT.GAUTSCHI, 0, 1.0), (EQ.SGE, INT.SV, 1, 1.0),
+                                                (EQ.KGE, INT.GAUTSCHI, 2, -1.0), (EQ.KGE, INT.SV, 3, 1.0)])
+def test_real_steps_match_reference_source(oracle_lib, R, eq, integ, kind, sign):
+    n, dt, steps = 32, 1e-3, 10 if integ == INT.GAUTSCHI else 60
+    d = Desc.make(n, n, L=10.0, equation=eq, integrator=integ, krylov_m=10, dt=dt, op_sign=sign)
+    u0 = ics.kink_2d(n, 10.0) * (0.2 if eq == EQ.KGE else 1.0)
+    v0 = 0.05 * np.cos(u0)
+    mf = 1.0 + 0.2 * np.random.default_rng(1).standard_normal(d.n)
+    o = oracle_lib.Oracle(d)
+    o.set(FIELD.U, u0); o.set(FIELD.V, v0); o.set(FIELD.M, mf); o.step(dt, steps)
+    u, up = R(n, n, 1, d.dx, sign=sign).real_steps(kind, u0.ravel(), (u0 - dt * v0).ravel(), mf, dt, steps)
+    assert rel_l2(o.get(), u) < 1e-12
+    assert rel_l2(o.get(FIELD.U_PAST), up) < 1e-12
