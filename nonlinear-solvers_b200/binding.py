@@ -135,7 +135,7 @@ def load_library(path=None):
     global _lib
     if _lib is not None and path is None:
         return _lib
-    p = path or _LIB
+    p = path or os.environ.get("NLS_B200_LIB") or _LIB  # the env override is for A/B builds of the same source tree
     if not os.path.exists(p):
         raise NlsError(f"{p} not built: run `python -c 'import __graft_entry__ as g; g.build()'` "
                        "(there is no CPU fallback)")

@@ -8,6 +8,7 @@
 
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <unordered_map>
@@ -44,6 +45,7 @@ struct nls_engine {
   int nblk = 1; // capacity of the partial-sum array (max CTAs per trajectory)
   int nsm = 148;
   int smem_optin = 0;  // max dynamic shared memory per CTA
+  int first_cap = 0;   // complex pass A: columns in the stencil-carrying first chunk (0 = rule in lanczos_t)
   bool tma_ok = false; // TMA-staged Lanczos passes usable (alignment + size), see tma_setup
   cudaStream_t stream = nullptr;
   // device memory (all n-vectors: [batch][stride] scalars)
@@ -273,7 +275,7 @@ void lanczos_t(nls_engine *e, const S *start, double *scal) {
     const int c0 = e->d.reorth == NLS_REORTH_NONE ? j : 0;
     // pass A chunks: the stencil-carrying first chunk takes at most kFirst columns (complex: beyond 6
     // the 128-register budget of 2 CTAs/SM costs more than re-reading w once in a second, dots-only chunk)
-    constexpr int kFirst = sizeof(S) == 16 ? 6 : kNC;
+    const int kFirst = sizeof(S) == 16 ? (e->first_cap >= 2 && e->first_cap <= kNC ? e->first_cap : 6) : kNC;
     for (int i0 = c0, cnt = 0; i0 <= j; i0 += cnt) {
       const bool first = i0 == c0;
       const int cap = first ? kFirst : kNC;
@@ -741,6 +743,7 @@ int nls_create(const nls_desc *desc, nls_handle *out) {
   cudaDeviceGetAttribute(&e->smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, d.device);
   e->smem_optin -= 4096; // dynamic budget: leave room for the kernels' static shared memory
   if (e->nsm < 1) e->nsm = 148;
+  if (const char *fc = getenv("NLS_FIRST_CAP")) e->first_cap = atoi(fc); // tuning knob (2..12), not API
   long long want = (g.n + kThreads - 1) / kThreads;
   long long cap = 8LL * e->nsm; // at most 8 CTAs of 256 threads per SM
   e->nblk = (int)(want < cap ? want : cap);

@@ -203,7 +203,7 @@ template <class S> struct PkCtx {
   S *Wt;              // w tile: sites [s0, s0 + csz)
   unsigned char *flag; // [csz] PF_* bits of the owned sites
   PkTri tri;
-  double (*red)[kPkWarps]; // [2*kPkNV + 2][kPkWarps]
+  double (*red)[kPkWarps]; // [2*kPkNV + 4][kPkWarps]
   double *vals;       // [kPkMaxK] gathered sums
   double *alpha;      // [kMaxM]   T(j,j)
   double *nrm2;       // [kMaxM+1] nrm2[0] = ||start||^2, nrm2[j+1] = ||w_j||^2
@@ -311,13 +311,19 @@ __device__ __forceinline__ void pk_load_halo(const PkArgs &a, PkCtx<S> &c, const
   __syncthreads();
 }
 
+// sites per two-stage block: about 16 doubles of loads in flight per thread (128-register budget)
+__host__ __device__ constexpr int pk_block(int nloads, int w) {
+  const int per = (nloads > 0 ? nloads : 1) * w;
+  return per <= 1 ? 14 : per <= 2 ? 7 : per <= 4 ? 4 : per <= 8 ? 2 : 1;
+}
+
 // ---------------------------------------------------------------- Lanczos phases
 // Column roles in iteration j: "others" = columns 0..j-2 (groups of <= kPkNV, pointer per
 // column), column j-1 (recurrence term + dot, loaded once), column j (the X tile).
 // Phase A, group of NC other columns starting at i0.  FIRST: also forms w (stencil + recurrence),
 // stores it to the Wt tile and accumulates the j-1 and j dots.
 template <class S, bool ANISO, int NC, bool FIRST>
-__device__ __forceinline__ void pk_phase_a(const PkArgs &a, PkCtx<S> &c, GridSync &gs, S *start, int j, int i0,
+__device__ __noinline__ void pk_phase_a(const PkArgs &a, PkCtx<S> &c, GridSync &gs, S *start, int j, int i0,
                                            double inv_bj, double cm) {
   using T = Sc<S>;
   constexpr int W = T::W;
@@ -334,25 +340,53 @@ __device__ __forceinline__ void pk_phase_a(const PkArgs &a, PkCtx<S> &c, GridSyn
   for (int k = 0; k < NA * W; ++k) acc[k] = 0.0;
 #pragma unroll
   for (int k = 0; k < W; ++k) accM[k] = accA[k] = 0.0;
-#pragma unroll(W == 1 ? 2 : 1)
-  for (int li = threadIdx.x; li < c.cnt; li += kPkThreads) {
-    S v[NA];
+  // two-stage blocks: all global loads of U sites are issued before the first use, so a phase costs
+  // ceil(sites per thread / U) memory round trips instead of one per site (the basis is L2-resident at
+  // these sizes; the loops are latency-, not bandwidth-bound).  Site order per thread is unchanged.
+  constexpr int U = pk_block(NC + (FIRST ? 1 : 0), W);
+  for (int l0 = threadIdx.x; l0 < c.cnt; l0 += U * kPkThreads) {
+    S v[U][NA], vm[U];
 #pragma unroll
-    for (int i = 0; i < NC; ++i) v[i] = __ldcg(p[i] + li);
-    S w;
-    if (FIRST) {
-      S vm = T::zero();
-      if (j > 0) vm = __ldcg(colm + li);
-      w = T::mulr(pk_stencil<S, ANISO>(a.g, xc, colj, cfg, c.flag[li], li), inv_bj);
-      w = T::fma_r(cm, vm, w); // cm == 0 when j == 0
-      c.Wt[li] = w;
-      T::dot_acc(accA, xc[li], w);
-      T::dot_acc(accM, vm, w);
-    } else {
-      w = c.Wt[li];
+    for (int u = 0; u < U; ++u) {
+      const int li = l0 + u * kPkThreads;
+      vm[u] = T::zero();
+      if (li < c.cnt) {
+#pragma unroll
+        for (int i = 0; i < NC; ++i) v[u][i] = __ldcg(p[i] + li);
+        if (FIRST && j > 0) vm[u] = __ldcg(colm + li);
+      }
     }
 #pragma unroll
-    for (int i = 0; i < NC; ++i) T::dot_acc(acc + i * W, v[i], w);
+    for (int u = 0; u < U; ++u) {
+      const int li = l0 + u * kPkThreads;
+      if (li < c.cnt) {
+        S w;
+        if (FIRST) {
+          w = T::mulr(pk_stencil<S, ANISO>(a.g, xc, colj, cfg, c.flag[li], li), inv_bj);
+          w = T::fma_r(cm, vm[u], w); // cm == 0 when j == 0
+          c.Wt[li] = w;
+          T::dot_acc(accA, xc[li], w);
+          T::dot_acc(accM, vm[u], w);
+        } else {
+          w = c.Wt[li];
+        }
+#pragma unroll
+        for (int i = 0; i < NC; ++i) T::dot_acc(acc + i * W, v[u][i], w);
+      }
+    }
+  }
+  if (FIRST && j > 0 && NC == j - 1) {
+    // the usual case (all other columns in this group): slots 0..j are contiguous -> one publish
+    double all[(NC + 2) * W];
+#pragma unroll
+    for (int k = 0; k < NC * W; ++k) all[k] = acc[k];
+#pragma unroll
+    for (int k = 0; k < W; ++k) {
+      all[NC * W + k] = accM[k];
+      all[(NC + 1) * W + k] = accA[k];
+    }
+    pk_publish<(NC + 2) * W>(all, a.part, gs.slot, c.red, 0);
+    return;
   }
   if (NC > 0) pk_publish<NA * W>(acc, a.part, gs.slot, c.red, i0 * W);
   if (FIRST) {
@@ -364,7 +398,7 @@ __device__ __forceinline__ void pk_phase_a(const PkArgs &a, PkCtx<S> &c, GridSyn
 // Phase B, group of NC other columns.  LAST: also subtracts the j-1 and j terms, accumulates
 // ||w||^2 and stores w to column j+1 (global) and to the X tile centre.
 template <class S, int NC, bool LAST>
-__device__ __forceinline__ void pk_phase_b(const PkArgs &a, PkCtx<S> &c, GridSync &gs, S *start, int j, int i0) {
+__device__ __noinline__ void pk_phase_b(const PkArgs &a, PkCtx<S> &c, GridSync &gs, S *start, int j, int i0) {
   using T = Sc<S>;
   constexpr int W = T::W;
   constexpr int NA = NC > 0 ? NC : 1;
@@ -380,24 +414,36 @@ __device__ __forceinline__ void pk_phase_b(const PkArgs &a, PkCtx<S> &c, GridSyn
   S *xc = c.X + a.g.nx;
   const S gm = j > 0 ? c.gco[j - 1] : T::zero(), gj = c.gco[j];
   double nrm[1] = {0.0};
-#pragma unroll(W == 1 ? 2 : 1)
-  for (int li = threadIdx.x; li < c.cnt; li += kPkThreads) {
-    S v[NA];
+  constexpr int U = pk_block(NC + (LAST ? 1 : 0), W);
+  for (int l0 = threadIdx.x; l0 < c.cnt; l0 += U * kPkThreads) {
+    S v[U][NA], vm[U];
 #pragma unroll
-    for (int i = 0; i < NC; ++i) v[i] = __ldcg(p[i] + li);
-    S vm = T::zero();
-    if (LAST && j > 0) vm = __ldcg(colm + li);
-    S w = c.Wt[li];
+    for (int u = 0; u < U; ++u) {
+      const int li = l0 + u * kPkThreads;
+      vm[u] = T::zero();
+      if (li < c.cnt) {
 #pragma unroll
-    for (int i = 0; i < NC; ++i) w = T::sub(w, T::mul(gc[i], v[i]));
-    if (LAST) {
-      w = T::sub(w, T::mul(gm, vm));
-      w = T::sub(w, T::mul(gj, xc[li]));
-      nrm[0] += T::abs2(w);
-      coln[li] = w;
-      xc[li] = w;
-    } else {
-      c.Wt[li] = w;
+        for (int i = 0; i < NC; ++i) v[u][i] = __ldcg(p[i] + li);
+        if (LAST && j > 0) vm[u] = __ldcg(colm + li);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int li = l0 + u * kPkThreads;
+      if (li < c.cnt) {
+        S w = c.Wt[li];
+#pragma unroll
+        for (int i = 0; i < NC; ++i) w = T::sub(w, T::mul(gc[i], v[u][i]));
+        if (LAST) {
+          w = T::sub(w, T::mul(gm, vm[u]));
+          w = T::sub(w, T::mul(gj, xc[li]));
+          nrm[0] += T::abs2(w);
+          coln[li] = w;
+          xc[li] = w;
+        } else {
+          c.Wt[li] = w;
+        }
+      }
     }
   }
   if (LAST) pk_publish<1>(nrm, a.part, gs.slot, c.red, 0);
@@ -584,7 +630,7 @@ inline size_t pk_smem_bytes(size_t esz, long long csz, int nx, int m) {
   size_t b = (size_t)(2 * csz + 2 * nx) * esz;           // X + Wt
   b += ((size_t)csz + 15) / 16 * 16;                      // flags
   b += (size_t)m * 32 * 8 * 2 + (size_t)m * (m + 1) * 8;  // tridiagonal work space
-  b += (size_t)(2 * kPkNV + 2) * kPkWarps * 8;            // red
+  b += (size_t)(2 * kPkNV + 4) * kPkWarps * 8;            // red
   b += (size_t)kPkMaxK * 8 + kMaxM * 8 + (kMaxM + 1) * 8 + 4 * kMaxM * 8 + kMaxM * 16;
   return b + 64;
 }
@@ -600,7 +646,7 @@ __device__ __forceinline__ void pk_carve(const PkArgs &a, PkCtx<S> &c, unsigned 
   c.tri.e = p; p += a.m * 32;
   c.tri.Z = p; p += a.m * (a.m + 1);
   c.tri.ldz = a.m + 1;
-  c.red = (double (*)[kPkWarps])p; p += (2 * kPkNV + 2) * kPkWarps;
+  c.red = (double (*)[kPkWarps])p; p += (2 * kPkNV + 4) * kPkWarps;
   c.vals = p; p += kPkMaxK;
   c.alpha = p; p += kMaxM;
   c.nrm2 = p; p += kMaxM + 1;

@@ -1,6 +1,7 @@
 // nls_oracle.cpp -- CPU restatement of the reference host algorithm.
-// TEST INFRASTRUCTURE ONLY (see nls_oracle.h).  "parity unpinned" at the Eigen
-// boundary; anchored by scipy expm_multiply + numpy twin (tests/test_oracle.py).
+// TEST INFRASTRUCTURE ONLY (see nls_oracle.h).  Pinned against the reference's own host
+// sources (oracle/_ref, tests/test_reference_pin.py); Eigen's arithmetic itself is substituted
+// ("parity unpinned" only there); also anchored by scipy expm_multiply + numpy twin.
 //
 // Every function cites the reference file:line it restates (paths relative to
 // the reference checkout, nlsolvers/ tree is canonical per SURVEY.md 8c).

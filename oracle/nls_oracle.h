@@ -6,11 +6,17 @@
  * bench.py's cpu_baseline / --impl reference legs use it, as the checker or
  * the timed CPU baseline -- never as the product path.
  *
- * PARITY STATUS: "parity unpinned" at the Eigen boundary.  The reference's own
- * CPU code cannot be compiled here (it needs Eigen3, which is neither vendored
- * nor installed) and the reference ships no golden
- * vectors.  The restatement is pinned instead by (i) the reference's own
- * external check, scipy.sparse.linalg.expm_multiply
+ * PARITY STATUS: pinned against the reference's own host sources; Eigen's
+ * arithmetic substituted.  The reference's CPU headers are compiled UNMODIFIED,
+ * where they lie, against a mini-Eigen stand-in (oracle/ref_shim, Eigen3 itself
+ * is neither vendored nor installed) into
+ * oracle/_ref/libnls_ref.so (oracle/ref_harness.cpp, oracle/Makefile), and
+ * tests/test_reference_pin.py checks this restatement against it: matrices
+ * identical, Lanczos / matrix functions / all step functions <= 1e-12.
+ * Unpinned remainder: Eigen's own floating-point behaviour (dot summation order,
+ * its eigensolver) -- the reference ships no golden vectors.  Independent
+ * anchors: (i) the reference's own external check,
+ * scipy.sparse.linalg.expm_multiply
  * (nlsolvers/scipy-test/check_krylov_compute.py:41-49), (ii) an independent
  * numpy/scipy twin (oracle/oracle_np.py) and (iii) dense eigh-based evaluation
  * of f(tL)u on small grids; see tests/test_oracle.py.

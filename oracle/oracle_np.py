@@ -2,8 +2,8 @@
 
 Restates the same reference functions as oracle/nls_oracle.cpp with different machinery
 (scipy.sparse COO assembly, numpy.linalg.eigh on the full m x m T) so that a slip in one
-restatement shows up as a disagreement between the two.  "parity unpinned" at the Eigen
-boundary -- see oracle/nls_oracle.h.  Small grids only (pure-Python assembly loops).
+restatement shows up as a disagreement between the two.  Parity status: see oracle/nls_oracle.h
+(pinned against the reference sources via oracle/_ref; Eigen's own arithmetic substituted).  Small grids only (pure-Python assembly loops).
 """
 import numpy as np
 import scipy.sparse as sp
