@@ -273,9 +273,11 @@ void lanczos_t(nls_engine *e, const S *start, double *scal) {
   for (int j = 0; j < m - 1; ++j) {
     // columns taking part in the orthogonalisation: all of 0..j (reference), or only j (3-term)
     const int c0 = e->d.reorth == NLS_REORTH_NONE ? j : 0;
-    // pass A chunks: the stencil-carrying first chunk takes at most kFirst columns (complex: beyond 6
-    // the 128-register budget of 2 CTAs/SM costs more than re-reading w once in a second, dots-only chunk)
-    const int kFirst = sizeof(S) == 16 ? (e->first_cap >= 2 && e->first_cap <= kNC ? e->first_cap : 6) : kNC;
+    // pass A chunks: the stencil-carrying first chunk of a complex sweep takes at most kFirst columns;
+    // beyond that the 128-register budget of 2 CTAs/SM costs more than re-reading w once in a second,
+    // dots-only chunk.  Measured on B200 (profiles/r01f_firstcap.txt): div(c grad) stencil 6 (C3 12.0 ->
+    // 10.8 ms/step), uniform stencil 10 (C4/C5 lose 3% with 6).  NLS_FIRST_CAP overrides for tuning.
+    const int kFirst = sizeof(S) == 16 ? (e->first_cap >= 2 && e->first_cap <= kNC ? e->first_cap : (ANISO ? 6 : 10)) : kNC;
     for (int i0 = c0, cnt = 0; i0 <= j; i0 += cnt) {
       const bool first = i0 == c0;
       const int cap = first ? kFirst : kNC;

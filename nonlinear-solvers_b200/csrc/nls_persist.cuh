@@ -23,10 +23,31 @@
 
 namespace nls {
 
-constexpr int kPkThreads = 512;
+// Address-space hints (experimental, -DPK_SHARED_HINTS / -DPK_GLOBAL_HINTS): with them every access through
+// the context compiles to LDS/STS instead of generic LD/ST (1449 LDS vs 1402 LD in k_pk_gautschi), but on
+// B200 that bought nothing measurable (C1 0.1061 vs 0.1057 ms/step, C2 0.571 vs 0.575) and the shared hints
+// miscompile k_pk_gautschi (illegal address; k_pk_nlse passes) with nvcc 12.9 -- off by default.
+#ifdef PK_SHARED_HINTS
+#define PK_SHARED(p) __builtin_assume(__isShared(p))
+#else
+#define PK_SHARED(p) do { } while (0)
+#endif
+#ifdef PK_GLOBAL_HINTS
+#define PK_GLOBAL(p) __builtin_assume(__isGlobal(p))
+#else
+#define PK_GLOBAL(p) do { } while (0)
+#endif
+
+#ifndef PK_THREADS
+#define PK_THREADS 512
+#endif
+#ifndef PK_NV
+#define PK_NV 8
+#endif
+constexpr int kPkThreads = PK_THREADS;
 constexpr int kPkWarps = kPkThreads / 32;
 constexpr int kPkMaxK = 2 * kMaxM + 2;   // doubles per reduction (complex h for up to kMaxM columns)
-constexpr int kPkNV = 8;                 // columns per unrolled group
+constexpr int kPkNV = PK_NV;             // columns per unrolled group
 constexpr int kPkPartStride = 160;       // >= max CTAs, padded
 
 struct PkArgs {
@@ -43,6 +64,39 @@ struct PkArgs {
   unsigned *bar;       // [0] arrival counter, [1] abort flag   (zeroed before every launch)
   int *status;
 };
+
+// Phase timing trace (debug builds only, -DPK_TRACE): thread 0 of a CTA stamps clock64() at phase
+// boundaries into shared memory; CTAs 0, ncta/2 and ncta-1 print the deltas at kernel exit.
+#ifdef PK_TRACE
+} // namespace nls
+#include <cstdio>
+namespace nls {
+__shared__ long long pk_tr_t[1024];
+__shared__ int pk_tr_tag[1024];
+__shared__ int pk_tr_n;
+#define PKT(tag)                                                                  \
+  do {                                                                            \
+    if (threadIdx.x == 0 && pk_tr_n < 1024) {                                     \
+      pk_tr_t[pk_tr_n] = clock64();                                               \
+      pk_tr_tag[pk_tr_n++] = (tag);                                               \
+    }                                                                             \
+  } while (0)
+#define PKT_INIT()                                                                \
+  do {                                                                            \
+    if (threadIdx.x == 0) pk_tr_n = 0;                                            \
+    __syncthreads();                                                              \
+  } while (0)
+#define PKT_DUMP(ncta)                                                            \
+  do {                                                                            \
+    if (threadIdx.x == 0 && (blockIdx.x == 0 || blockIdx.x == (ncta) / 2 || blockIdx.x == (ncta)-1))  \
+      for (int q = 1; q < pk_tr_n; ++q)                                           \
+        printf("PKT %d %d %d %lld\n", blockIdx.x, q, pk_tr_tag[q], pk_tr_t[q] - pk_tr_t[q - 1]);     \
+  } while (0)
+#else
+#define PKT(tag) do { } while (0)
+#define PKT_INIT() do { } while (0)
+#define PKT_DUMP(ncta) do { } while (0)
+#endif
 
 // ---------------------------------------------------------------- grid barrier
 struct GridSync {
@@ -91,6 +145,8 @@ __device__ __forceinline__ bool grid_barrier(GridSync &gs) {
 // Must be followed by grid_barrier and then pk_gather.
 template <int K>
 __device__ __forceinline__ void pk_publish(double (&acc)[K], double *part, int slot, double (*s_red)[kPkWarps], int koff = 0) {
+  PK_SHARED(s_red);
+  PK_GLOBAL(part);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #pragma unroll
   for (int k = 0; k < K; ++k) {
@@ -109,17 +165,31 @@ __device__ __forceinline__ void pk_publish(double (&acc)[K], double *part, int s
   __syncthreads(); // s_red may be reused by the next publish
 }
 
-// after the barrier: every CTA sums the partials of all CTAs in the same order -> s_out[k]
-__device__ __forceinline__ void pk_gather(int K, const double *part, int slot, int ncta, double *s_out) {
+// after the barrier: every CTA sums the partials of all CTAs in the same order -> s_out[k].
+// The (<= 5) loads of a lane are issued together: one L2 round trip per value, not one per load.
+__device__ __forceinline__ void pk_gather_nosync(int K, const double *part, int slot, int ncta, double *s_out) {
+  PK_SHARED(s_out);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  constexpr int kPer = (kPkPartStride + 31) / 32;
   for (int k = warp; k < K; k += kPkWarps) {
     const double *p = part + ((size_t)slot * kPkMaxK + k) * kPkPartStride;
+    double t[kPer];
+#pragma unroll
+    for (int q = 0; q < kPer; ++q) {
+      const int c = lane + 32 * q;
+      t[q] = c < ncta ? __ldcg(p + c) : 0.0;
+    }
     double v = 0.0;
-    for (int c = lane; c < ncta; c += 32) v += __ldcg(p + c);
+#pragma unroll
+    for (int q = 0; q < kPer; ++q)
+      if (lane + 32 * q < ncta) v += t[q];
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
     if (lane == 0) s_out[k] = v;
   }
+}
+__device__ __forceinline__ void pk_gather(int K, const double *part, int slot, int ncta, double *s_out) {
+  pk_gather_nosync(K, part, slot, ncta, s_out);
   __syncthreads();
 }
 
@@ -137,8 +207,13 @@ struct PkTri {
 
 __device__ __forceinline__ bool pk_tridiag_warp(PkTri &T, int m) {
   const int lane = threadIdx.x & 31;
-#define D(i) T.d[(i) * 32 + lane]
-#define E(i) T.e[(i) * 32 + lane]
+  double *const td = T.d, *const te = T.e, *const tz = T.Z;
+  PK_SHARED(td);
+  PK_SHARED(te);
+  PK_SHARED(tz);
+  const int ldz = T.ldz;
+#define D(i) td[(i) * 32 + lane]
+#define E(i) te[(i) * 32 + lane]
   bool ok = true;
   for (int l = 0; l < m && ok; ++l) {
     int iter = 0, mm;
@@ -153,33 +228,54 @@ __device__ __forceinline__ bool pk_tridiag_warp(PkTri &T, int m) {
         double r = sqrt(fma(g, g, 1.0));
         g = D(mm) - D(l) + E(l) / (g + copysign(r, g));
         double s = 1.0, c = 1.0, p = 0.0;
-        int i;
+        int i = mm - 1;
         bool early = false;
-        for (i = mm - 1; i >= l; --i) {
-          double f = s * E(i);
-          const double b = c * E(i);
-          r = sqrt(fma(f, f, g * g));
+        // Serial rotation chain with everything it needs next already in registers: D(i+1) of the next
+        // rotation is this one's D(i), the next E/D pair is fetched a rotation ahead, and column i+1 of a
+        // lane's eigenvector rows is carried in a register (each rotation loads one new column, stores one
+        // finished column) -- no shared-memory round trip sits on the dependency chain.
+        const int k0 = lane, k1 = lane + 32;
+        double e_i = E(i), d_i = D(i), d_hi = D(mm);
+        double zh0 = k0 < m ? tz[k0 * ldz + mm] : 0.0, zh1 = k1 < m ? tz[k1 * ldz + mm] : 0.0;
+        for (; i >= l; --i) {
+          double e_n = 0.0, d_n = 0.0;
+          if (i > l) {
+            e_n = E(i - 1);
+            d_n = D(i - 1);
+          }
+          const double zl0 = k0 < m ? tz[k0 * ldz + i] : 0.0, zl1 = k1 < m ? tz[k1 * ldz + i] : 0.0;
+          const double f = s * e_i;
+          const double b = c * e_i;
+          const double t2 = fma(f, f, g * g);
+          const double ir = rsqrt(t2); // one reciprocal square root instead of sqrt + divide
+          r = t2 == 0.0 ? 0.0 : t2 * ir;
           E(i + 1) = r;
           if (r == 0.0) {
-            D(i + 1) -= p;
+            D(i + 1) = d_hi - p;
             E(mm) = 0.0;
+            if (k0 < m) tz[k0 * ldz + i + 1] = zh0;
+            if (k1 < m) tz[k1 * ldz + i + 1] = zh1;
             early = true;
             break;
           }
-          const double ir = 1.0 / r;
           s = f * ir;
           c = g * ir;
-          g = D(i + 1) - p;
-          r = (D(i) - g) * s + 2.0 * c * b;
+          g = d_hi - p;
+          r = (d_i - g) * s + 2.0 * c * b;
           p = s * r;
           D(i + 1) = g + p;
           g = c * r - b;
-          for (int k = lane; k < m; k += 32) { // rotate columns i, i+1 of Z (rows over lanes)
-            double *zr = T.Z + k * T.ldz + i;
-            const double z1 = zr[1], z0 = zr[0];
-            zr[1] = s * z0 + c * z1;
-            zr[0] = c * z0 - s * z1;
-          }
+          if (k0 < m) tz[k0 * ldz + i + 1] = s * zl0 + c * zh0;
+          if (k1 < m) tz[k1 * ldz + i + 1] = s * zl1 + c * zh1;
+          zh0 = c * zl0 - s * zh0;
+          zh1 = c * zl1 - s * zh1;
+          d_hi = d_i;
+          d_i = d_n;
+          e_i = e_n;
+        }
+        if (!early) {
+          if (k0 < m) tz[k0 * ldz + l] = zh0;
+          if (k1 < m) tz[k1 * ldz + l] = zh1;
         }
         if (early) continue;
         D(l) -= p;
@@ -198,19 +294,28 @@ __device__ __forceinline__ bool pk_tridiag_warp(PkTri &T, int m) {
 // per-site neighbour flags, computed once per launch (the index divisions leave the hot loops)
 enum { PF_XM = 1, PF_XP = 2, PF_YM = 4, PF_YP = 8, PF_ZM = 16, PF_ZP = 32, PF_RING = 64 };
 
+// Shared-memory pointers are handed out through accessors (hook for the address-space hints above).
+#define PK_ACC(type, name)                                   \
+  type name##_;                                              \
+  __device__ __forceinline__ type name() const {             \
+    type p = name##_;                                        \
+    PK_SHARED(p);                                            \
+    return p;                                                \
+  }
 template <class S> struct PkCtx {
-  S *X;               // stencil tile: sites [s0 - nx, s0 + csz + nx)
-  S *Wt;              // w tile: sites [s0, s0 + csz)
-  unsigned char *flag; // [csz] PF_* bits of the owned sites
+  PK_ACC(S *, X)                // stencil tile: sites [s0 - nx, s0 + csz + nx)
+  PK_ACC(S *, Wt)               // w tile: sites [s0, s0 + csz)
+  PK_ACC(unsigned char *, flag) // [csz] PF_* bits of the owned sites
   PkTri tri;
-  double (*red)[kPkWarps]; // [2*kPkNV + 4][kPkWarps]
-  double *vals;       // [kPkMaxK] gathered sums
-  double *alpha;      // [kMaxM]   T(j,j)
-  double *nrm2;       // [kMaxM+1] nrm2[0] = ||start||^2, nrm2[j+1] = ||w_j||^2
-  double *coef;       // [2][2*kMaxM] complex coefficients (two function sets)
-  S *gco;             // [kMaxM] re-orthogonalisation coefficients of the current iteration
-  long long s0;       // first owned site
-  int cnt;            // number of owned sites (may be 0)
+  typedef double (*RedPtr)[kPkWarps];
+  PK_ACC(RedPtr, red)           // [2*kPkNV + 2][kPkWarps]
+  PK_ACC(double *, vals)        // [kPkMaxK] gathered sums
+  PK_ACC(double *, alpha)       // [kMaxM]   T(j,j)
+  PK_ACC(double *, nrm2)        // [kMaxM+1] nrm2[0] = ||start||^2, nrm2[j+1] = ||w_j||^2
+  PK_ACC(double *, coef)        // [2][2*kMaxM] complex coefficients (two function sets)
+  PK_ACC(S *, gco)              // [kMaxM] re-orthogonalisation coefficients of the current iteration
+  long long s0;                 // first owned site
+  int cnt;                      // number of owned sites (may be 0)
 };
 
 // column i of the Krylov basis: i == 0 is the start-vector buffer, i >= 1 lives in V
@@ -249,6 +354,7 @@ template <class S, bool ANISO>
 __device__ __forceinline__ S pk_stencil(const Geom &g, const S *__restrict__ xc, const S *__restrict__ colg,
                                         const double *__restrict__ cfg, unsigned f, int li) {
   using T = Sc<S>;
+  PK_SHARED(xc);
   const int nx = g.nx;
   const S z = T::zero();
   const S xm = (f & PF_XM) ? xc[li - 1] : z;
@@ -296,25 +402,54 @@ __device__ __forceinline__ S pk_stencil(const Geom &g, const S *__restrict__ xc,
   return acc;
 }
 
-// load the +-nx halo rows of column `col` into the X tile (after a grid barrier)
+// load the +-nx halo rows of column `col` into the X tile (after a grid barrier).  Up to 4 elements
+// per thread are loaded before the first shared-memory store (one L2 round trip for nx <= 1200).
 template <class S>
-__device__ __forceinline__ void pk_load_halo(const PkArgs &a, PkCtx<S> &c, const S *col) {
+__device__ __forceinline__ void pk_load_halo_part(const PkArgs &a, PkCtx<S> &c, const S *col, int tid, int nth) {
   const int nx = a.g.nx;
+  constexpr int kQ = 5;
   if (c.cnt > 0) {
-    for (int t = threadIdx.x; t < 2 * nx; t += kPkThreads) {
-      const bool up = t >= nx;
-      const long long idx = up ? c.s0 + c.cnt + (t - nx) : c.s0 - nx + t;
-      const int xi = up ? nx + c.cnt + (t - nx) : t;
-      if (idx >= 0 && idx < a.g.n) c.X[xi] = __ldcg(col + idx);
+    for (int t0 = tid; t0 < 2 * nx; t0 += kQ * nth) {
+      S v[kQ];
+      int xi[kQ];
+#pragma unroll
+      for (int q = 0; q < kQ; ++q) {
+        const int t = t0 + q * nth;
+        const bool up = t >= nx;
+        const long long idx = up ? c.s0 + c.cnt + (t - nx) : c.s0 - nx + t;
+        xi[q] = -1;
+        if (t < 2 * nx && idx >= 0 && idx < a.g.n) {
+          xi[q] = up ? nx + c.cnt + (t - nx) : t;
+          v[q] = __ldcg(col + idx);
+        }
+      }
+#pragma unroll
+      for (int q = 0; q < kQ; ++q)
+        if (xi[q] >= 0) c.X()[xi[q]] = v[q];
     }
   }
+}
+template <class S>
+__device__ __forceinline__ void pk_load_halo_nosync(const PkArgs &a, PkCtx<S> &c, const S *col) {
+  pk_load_halo_part<S>(a, c, col, threadIdx.x, kPkThreads);
+}
+template <class S>
+__device__ __forceinline__ void pk_load_halo(const PkArgs &a, PkCtx<S> &c, const S *col) {
+  pk_load_halo_nosync<S>(a, c, col);
   __syncthreads();
 }
 
-// sites per two-stage block: about 16 doubles of loads in flight per thread (128-register budget)
-__host__ __device__ constexpr int pk_block(int nloads, int w) {
-  const int per = (nloads > 0 ? nloads : 1) * w;
-  return per <= 1 ? 14 : per <= 2 ? 7 : per <= 4 ? 4 : per <= 8 ? 2 : 1;
+#ifndef PK_COMB_UNROLL
+#define PK_COMB_UNROLL 2
+#endif
+constexpr int kPkCombUnroll = PK_COMB_UNROLL; // sites per unrolled group in the recombination loops of k_pk_gautschi
+// unroll factor of the phase loops (the compiler interleaves the loads of the unrolled sites)
+__host__ __device__ constexpr int pk_unroll(int nc, int w) {
+#ifdef PK_UNROLL_TUNE
+  return w == 1 ? (nc <= 1 ? 8 : nc <= 4 ? 4 : 2) : (nc <= 1 ? 4 : nc <= 3 ? 2 : 1);
+#else
+  return w == 1 ? 2 : 1;
+#endif
 }
 
 // ---------------------------------------------------------------- Lanczos phases
@@ -323,7 +458,7 @@ __host__ __device__ constexpr int pk_block(int nloads, int w) {
 // Phase A, group of NC other columns starting at i0.  FIRST: also forms w (stencil + recurrence),
 // stores it to the Wt tile and accumulates the j-1 and j dots.
 template <class S, bool ANISO, int NC, bool FIRST>
-__device__ __noinline__ void pk_phase_a(const PkArgs &a, PkCtx<S> &c, GridSync &gs, S *start, int j, int i0,
+__device__ __forceinline__ void pk_phase_a(const PkArgs &a, PkCtx<S> &c, GridSync &gs, S *start, int j, int i0,
                                            double inv_bj, double cm) {
   using T = Sc<S>;
   constexpr int W = T::W;
@@ -334,71 +469,43 @@ __device__ __noinline__ void pk_phase_a(const PkArgs &a, PkCtx<S> &c, GridSync &
   const S *colj = pk_col<S>(a, start, j) + c.s0;
   const S *colm = j > 0 ? pk_col<S>(a, start, j - 1) + c.s0 : colj;
   const double *cfg = ANISO ? a.cf + c.s0 : nullptr;
-  const S *xc = c.X + a.g.nx;
+  const S *xc = c.X() + a.g.nx;
   double acc[NA * W], accM[W], accA[W];
 #pragma unroll
   for (int k = 0; k < NA * W; ++k) acc[k] = 0.0;
 #pragma unroll
   for (int k = 0; k < W; ++k) accM[k] = accA[k] = 0.0;
-  // two-stage blocks: all global loads of U sites are issued before the first use, so a phase costs
-  // ceil(sites per thread / U) memory round trips instead of one per site (the basis is L2-resident at
-  // these sizes; the loops are latency-, not bandwidth-bound).  Site order per thread is unchanged.
-  constexpr int U = pk_block(NC + (FIRST ? 1 : 0), W);
-  for (int l0 = threadIdx.x; l0 < c.cnt; l0 += U * kPkThreads) {
-    S v[U][NA], vm[U];
+#pragma unroll(pk_unroll(NC, W))
+  for (int li = threadIdx.x; li < c.cnt; li += kPkThreads) {
+    S v[NA];
 #pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const int li = l0 + u * kPkThreads;
-      vm[u] = T::zero();
-      if (li < c.cnt) {
-#pragma unroll
-        for (int i = 0; i < NC; ++i) v[u][i] = __ldcg(p[i] + li);
-        if (FIRST && j > 0) vm[u] = __ldcg(colm + li);
-      }
+    for (int i = 0; i < NC; ++i) v[i] = __ldcg(p[i] + li);
+    S w;
+    if (FIRST) {
+      S vm = T::zero();
+      if (j > 0) vm = __ldcg(colm + li);
+      w = T::mulr(pk_stencil<S, ANISO>(a.g, xc, colj, cfg, c.flag()[li], li), inv_bj);
+      w = T::fma_r(cm, vm, w); // cm == 0 when j == 0
+      c.Wt()[li] = w;
+      T::dot_acc(accA, xc[li], w);
+      T::dot_acc(accM, vm, w);
+    } else {
+      w = c.Wt()[li];
     }
 #pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const int li = l0 + u * kPkThreads;
-      if (li < c.cnt) {
-        S w;
-        if (FIRST) {
-          w = T::mulr(pk_stencil<S, ANISO>(a.g, xc, colj, cfg, c.flag[li], li), inv_bj);
-          w = T::fma_r(cm, vm[u], w); // cm == 0 when j == 0
-          c.Wt[li] = w;
-          T::dot_acc(accA, xc[li], w);
-          T::dot_acc(accM, vm[u], w);
-        } else {
-          w = c.Wt[li];
-        }
-#pragma unroll
-        for (int i = 0; i < NC; ++i) T::dot_acc(acc + i * W, v[u][i], w);
-      }
-    }
+    for (int i = 0; i < NC; ++i) T::dot_acc(acc + i * W, v[i], w);
   }
-  if (FIRST && j > 0 && NC == j - 1) {
-    // the usual case (all other columns in this group): slots 0..j are contiguous -> one publish
-    double all[(NC + 2) * W];
-#pragma unroll
-    for (int k = 0; k < NC * W; ++k) all[k] = acc[k];
-#pragma unroll
-    for (int k = 0; k < W; ++k) {
-      all[NC * W + k] = accM[k];
-      all[(NC + 1) * W + k] = accA[k];
-    }
-    pk_publish<(NC + 2) * W>(all, a.part, gs.slot, c.red, 0);
-    return;
-  }
-  if (NC > 0) pk_publish<NA * W>(acc, a.part, gs.slot, c.red, i0 * W);
+  if (NC > 0) pk_publish<NA * W>(acc, a.part, gs.slot, c.red(), i0 * W);
   if (FIRST) {
-    if (j > 0) pk_publish<W>(accM, a.part, gs.slot, c.red, (j - 1) * W);
-    pk_publish<W>(accA, a.part, gs.slot, c.red, j * W);
+    if (j > 0) pk_publish<W>(accM, a.part, gs.slot, c.red(), (j - 1) * W);
+    pk_publish<W>(accA, a.part, gs.slot, c.red(), j * W);
   }
 }
 
 // Phase B, group of NC other columns.  LAST: also subtracts the j-1 and j terms, accumulates
 // ||w||^2 and stores w to column j+1 (global) and to the X tile centre.
 template <class S, int NC, bool LAST>
-__device__ __noinline__ void pk_phase_b(const PkArgs &a, PkCtx<S> &c, GridSync &gs, S *start, int j, int i0) {
+__device__ __forceinline__ void pk_phase_b(const PkArgs &a, PkCtx<S> &c, GridSync &gs, S *start, int j, int i0) {
   using T = Sc<S>;
   constexpr int W = T::W;
   constexpr int NA = NC > 0 ? NC : 1;
@@ -407,46 +514,35 @@ __device__ __noinline__ void pk_phase_b(const PkArgs &a, PkCtx<S> &c, GridSync &
 #pragma unroll
   for (int i = 0; i < NC; ++i) {
     p[i] = pk_col<S>(a, start, i0 + i) + c.s0;
-    gc[i] = c.gco[i0 + i];
+    gc[i] = c.gco()[i0 + i];
   }
   const S *colm = j > 0 ? pk_col<S>(a, start, j - 1) + c.s0 : nullptr;
   S *coln = pk_col<S>(a, start, j + 1) + c.s0;
-  S *xc = c.X + a.g.nx;
-  const S gm = j > 0 ? c.gco[j - 1] : T::zero(), gj = c.gco[j];
+  PK_GLOBAL(coln);
+  S *xc = c.X() + a.g.nx;
+  const S gm = j > 0 ? c.gco()[j - 1] : T::zero(), gj = c.gco()[j];
   double nrm[1] = {0.0};
-  constexpr int U = pk_block(NC + (LAST ? 1 : 0), W);
-  for (int l0 = threadIdx.x; l0 < c.cnt; l0 += U * kPkThreads) {
-    S v[U][NA], vm[U];
+#pragma unroll(pk_unroll(NC, W))
+  for (int li = threadIdx.x; li < c.cnt; li += kPkThreads) {
+    S v[NA];
 #pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const int li = l0 + u * kPkThreads;
-      vm[u] = T::zero();
-      if (li < c.cnt) {
+    for (int i = 0; i < NC; ++i) v[i] = __ldcg(p[i] + li);
+    S vm = T::zero();
+    if (LAST && j > 0) vm = __ldcg(colm + li);
+    S w = c.Wt()[li];
 #pragma unroll
-        for (int i = 0; i < NC; ++i) v[u][i] = __ldcg(p[i] + li);
-        if (LAST && j > 0) vm[u] = __ldcg(colm + li);
-      }
-    }
-#pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const int li = l0 + u * kPkThreads;
-      if (li < c.cnt) {
-        S w = c.Wt[li];
-#pragma unroll
-        for (int i = 0; i < NC; ++i) w = T::sub(w, T::mul(gc[i], v[u][i]));
-        if (LAST) {
-          w = T::sub(w, T::mul(gm, vm[u]));
-          w = T::sub(w, T::mul(gj, xc[li]));
-          nrm[0] += T::abs2(w);
-          coln[li] = w;
-          xc[li] = w;
-        } else {
-          c.Wt[li] = w;
-        }
-      }
+    for (int i = 0; i < NC; ++i) w = T::sub(w, T::mul(gc[i], v[i]));
+    if (LAST) {
+      w = T::sub(w, T::mul(gm, vm));
+      w = T::sub(w, T::mul(gj, xc[li]));
+      nrm[0] += T::abs2(w);
+      coln[li] = w;
+      xc[li] = w;
+    } else {
+      c.Wt()[li] = w;
     }
   }
-  if (LAST) pk_publish<1>(nrm, a.part, gs.slot, c.red, 0);
+  if (LAST) pk_publish<1>(nrm, a.part, gs.slot, c.red(), 0);
 }
 
 #define PK_SWITCH_NC(nc, CALL)                                                                     \
@@ -471,10 +567,11 @@ __device__ bool pk_lanczos(const PkArgs &a, PkCtx<S> &c, GridSync &gs, S *start)
   using T = Sc<S>;
   constexpr int W = T::W;
   for (int j = 0; j < a.m - 1; ++j) {
-    pk_load_halo<S>(a, c, pk_col<S>(a, start, j));
-    const double bj = sqrt(c.nrm2[j]);
+    if (j == 0) pk_load_halo<S>(a, c, pk_col<S>(a, start, 0)); // later iterations: loaded with the norm gather
+    PKT(100 + j); // halo loaded
+    const double bj = sqrt(c.nrm2()[j]);
     const double inv_bj = 1.0 / bj;
-    const double cm = j > 0 ? -bj / sqrt(c.nrm2[j - 1]) : 0.0; // -beta_j * (1/beta_{j-1})
+    const double cm = j > 0 ? -bj / sqrt(c.nrm2()[j - 1]) : 0.0; // -beta_j * (1/beta_{j-1})
     const int nother = j > 0 ? j - 1 : 0;
     // ---- phase A: w = L v_j - beta_j v_{j-1};  sums_i = w_i^H w for i <= j
     {
@@ -485,25 +582,35 @@ __device__ bool pk_lanczos(const PkArgs &a, PkCtx<S> &c, GridSync &gs, S *start)
         PK_SWITCH_NC(nc, (pk_phase_a<S, ANISO, NC, false>(a, c, gs, start, j, i0, inv_bj, cm)));
       }
     }
+    PKT(200 + j); // phase A done (loop + publish)
     if (!grid_barrier(gs)) return false;
-    pk_gather((j + 1) * W, a.part, gs.slot ^ 1, a.ncta, c.vals);
+    PKT(300 + j); // barrier passed
+    pk_gather((j + 1) * W, a.part, gs.slot ^ 1, a.ncta, c.vals());
     // h_i = sums_i / beta_i ; w -= h_i v_i = (sums_i / beta_i^2) w_i ; alpha = Re h_j
     if (threadIdx.x <= j) {
       const int i = threadIdx.x;
-      c.gco[i] = T::mulr(T::from(c.vals + i * W), 1.0 / c.nrm2[i]);
-      if (i == j) c.alpha[j] = c.vals[j * W] * inv_bj; // T(j,j) = Re(v_j^H w)
+      c.gco()[i] = T::mulr(T::from(c.vals() + i * W), 1.0 / c.nrm2()[i]);
+      if (i == j) c.alpha()[j] = c.vals()[j * W] * inv_bj; // T(j,j) = Re(v_j^H w)
     }
     __syncthreads();
+    PKT(400 + j); // gathered
     // ---- phase B: w -= sum_i g_i w_i ; ||w||^2 ; w -> column j+1 (global) and X centre
     {
       int i0 = 0;
       for (; nother - i0 > kPkNV; i0 += kPkNV) pk_phase_b<S, kPkNV, false>(a, c, gs, start, j, i0);
       PK_SWITCH_NC(nother - i0, (pk_phase_b<S, NC, true>(a, c, gs, start, j, i0)));
     }
+    PKT(500 + j); // phase B done
     if (!grid_barrier(gs)) return false;
-    pk_gather(1, a.part, gs.slot ^ 1, a.ncta, c.vals);
-    if (threadIdx.x == 0) c.nrm2[j + 1] = c.vals[0];
+    PKT(600 + j); // barrier passed
+    // one latency window: warp 0 gathers ||w||^2 while warps 1.. fetch the next iteration's halo rows
+    if (j + 1 < a.m - 1 && threadIdx.x >= 32)
+      pk_load_halo_part<S>(a, c, pk_col<S>(a, start, j + 1), threadIdx.x - 32, kPkThreads - 32);
+    else
+      pk_gather_nosync(1, a.part, gs.slot ^ 1, a.ncta, c.vals());
+    if (threadIdx.x == 0) c.nrm2()[j + 1] = c.vals()[0];
     __syncthreads();
+    PKT(700 + j); // gathered
   }
   return true;
 }
@@ -517,36 +624,41 @@ __device__ __forceinline__ void pk_coefficients(const PkArgs &a, PkCtx<S> &c, in
   if (threadIdx.x < 32) {
     const int lane = threadIdx.x;
     PkTri &T = c.tri;
+    double *const td = T.d, *const te = T.e, *const tz = T.Z;
+    PK_SHARED(td);
+    PK_SHARED(te);
+    PK_SHARED(tz);
+    const int ldz = T.ldz;
     for (int i = 0; i < m; ++i) {
-      T.d[i * 32 + lane] = i < m - 1 ? c.alpha[i] : 0.0; // T(m-1,m-1) = 0
-      T.e[i * 32 + lane] = i < m - 1 ? sqrt(c.nrm2[i + 1]) : 0.0;
+      td[i * 32 + lane] = i < m - 1 ? c.alpha()[i] : 0.0; // T(m-1,m-1) = 0
+      te[i * 32 + lane] = i < m - 1 ? sqrt(c.nrm2()[i + 1]) : 0.0;
     }
     for (int i = lane; i < m; i += 32)
-      for (int k = 0; k < m; ++k) T.Z[i * T.ldz + k] = i == k ? 1.0 : 0.0;
+      for (int k = 0; k < m; ++k) tz[i * ldz + k] = i == k ? 1.0 : 0.0;
     __syncwarp();
     const bool ok = pk_tridiag_warp(T, m);
     __syncwarp();
     if (!ok && lane == 0) atomicExch(a.status, 1);
-    const double beta0 = sqrt(c.nrm2[0]);
+    const double beta0 = sqrt(c.nrm2()[0]);
     for (int f = 0; f < nfn; ++f) {
       const int fn = f ? f1 : f0;
       const double tr = f ? t1r : t0r, ti = f ? t1i : t0i;
-      double *co = c.coef + f * 2 * kMaxM;
+      double *co = c.coef() + f * 2 * kMaxM;
       __syncwarp();
       for (int k = lane; k < m; k += 32) { // f(t lambda_k) -> e[k][0..1] (e is free after QL)
-        const double2 fv = fn_eval(fn, tr, ti, T.d[k * 32 + lane]);
-        T.e[k * 32] = fv.x;
-        T.e[k * 32 + 1] = fv.y;
+        const double2 fv = fn_eval(fn, tr, ti, td[k * 32 + lane]);
+        te[k * 32] = fv.x;
+        te[k * 32 + 1] = fv.y;
       }
       __syncwarp();
       for (int i = lane; i < m; i += 32) {
         double sr = 0.0, si = 0.0;
         for (int k = 0; k < m; ++k) {
-          const double zz = T.Z[i * T.ldz + k] * T.Z[k];
-          sr = fma(zz, T.e[k * 32], sr);
-          si = fma(zz, T.e[k * 32 + 1], si);
+          const double zz = tz[i * ldz + k] * tz[k];
+          sr = fma(zz, te[k * 32], sr);
+          si = fma(zz, te[k * 32 + 1], si);
         }
-        const double scale = beta0 / sqrt(c.nrm2[i]);
+        const double scale = beta0 / sqrt(c.nrm2()[i]);
         co[2 * i] = sr * scale;
         co[2 * i + 1] = si * scale;
       }
@@ -630,7 +742,7 @@ inline size_t pk_smem_bytes(size_t esz, long long csz, int nx, int m) {
   size_t b = (size_t)(2 * csz + 2 * nx) * esz;           // X + Wt
   b += ((size_t)csz + 15) / 16 * 16;                      // flags
   b += (size_t)m * 32 * 8 * 2 + (size_t)m * (m + 1) * 8;  // tridiagonal work space
-  b += (size_t)(2 * kPkNV + 4) * kPkWarps * 8;            // red
+  b += (size_t)(2 * kPkNV + 2) * kPkWarps * 8;            // red
   b += (size_t)kPkMaxK * 8 + kMaxM * 8 + (kMaxM + 1) * 8 + 4 * kMaxM * 8 + kMaxM * 16;
   return b + 64;
 }
@@ -638,35 +750,35 @@ inline size_t pk_smem_bytes(size_t esz, long long csz, int nx, int m) {
 template <class S>
 __device__ __forceinline__ void pk_carve(const PkArgs &a, PkCtx<S> &c, unsigned char *smem) {
   const long long tile = a.csz + 2 * a.g.nx;
-  c.X = (S *)smem;
-  c.Wt = c.X + tile;
-  c.flag = (unsigned char *)(c.Wt + a.csz);
-  double *p = (double *)(c.flag + (a.csz + 15) / 16 * 16);
+  c.X_ = (S *)smem;
+  c.Wt_ = c.X_ + tile;
+  c.flag_ = (unsigned char *)(c.Wt_ + a.csz);
+  double *p = (double *)(c.flag() + (a.csz + 15) / 16 * 16);
   c.tri.d = p; p += a.m * 32;
   c.tri.e = p; p += a.m * 32;
   c.tri.Z = p; p += a.m * (a.m + 1);
   c.tri.ldz = a.m + 1;
-  c.red = (double (*)[kPkWarps])p; p += (2 * kPkNV + 4) * kPkWarps;
-  c.vals = p; p += kPkMaxK;
-  c.alpha = p; p += kMaxM;
-  c.nrm2 = p; p += kMaxM + 1;
-  c.coef = p; p += 4 * kMaxM;
-  c.gco = (S *)(((uintptr_t)p + 15) & ~(uintptr_t)15);
+  c.red_ = (double (*)[kPkWarps])p; p += (2 * kPkNV + 2) * kPkWarps;
+  c.vals_ = p; p += kPkMaxK;
+  c.alpha_ = p; p += kMaxM;
+  c.nrm2_ = p; p += kMaxM + 1;
+  c.coef_ = p; p += 4 * kMaxM;
+  c.gco_ = (S *)(((uintptr_t)p + 15) & ~(uintptr_t)15);
   c.s0 = (long long)blockIdx.x * a.csz;
   long long e0 = c.s0 + a.csz;
   if (e0 > a.g.n) e0 = a.g.n;
   c.cnt = e0 > c.s0 ? (int)(e0 - c.s0) : 0;
-  for (int li = threadIdx.x; li < c.cnt; li += kPkThreads) c.flag[li] = pk_site_flags(a.g, c.s0 + li);
+  for (int li = threadIdx.x; li < c.cnt; li += kPkThreads) c.flag()[li] = pk_site_flags(a.g, c.s0 + li);
   __syncthreads();
 }
 
 // publish ||start||^2, barrier, gather -> nrm2[0]
 template <class S>
 __device__ __forceinline__ bool pk_start_norm(const PkArgs &a, PkCtx<S> &c, GridSync &gs, double (&nrm)[1]) {
-  pk_publish<1>(nrm, a.part, gs.slot, c.red, 0);
+  pk_publish<1>(nrm, a.part, gs.slot, c.red(), 0);
   if (!grid_barrier(gs)) return false;
-  pk_gather(1, a.part, gs.slot ^ 1, a.ncta, c.vals);
-  if (threadIdx.x == 0) c.nrm2[0] = c.vals[0];
+  pk_gather(1, a.part, gs.slot ^ 1, a.ncta, c.vals());
+  if (threadIdx.x == 0) c.nrm2()[0] = c.vals()[0];
   __syncthreads();
   return true;
 }
@@ -699,7 +811,11 @@ __global__ void __launch_bounds__(kPkThreads, 1) k_pk_nlse(PkArgs a, double2 *sv
   const NlseParams p{0.5 * a.dt, a.s1, a.s2, a.kappa};
   double2 *ucur = (double2 *)a.u0, *unext = (double2 *)a.u1;
   double2 *scur = sv0, *snext = sv1;
-  double2 *xc = c.X + a.g.nx;
+  PK_GLOBAL(ucur);
+  PK_GLOBAL(unext);
+  PK_GLOBAL(scur);
+  PK_GLOBAL(snext);
+  double2 *xc = c.X() + a.g.nx;
   const double *mfc = a.mf + c.s0;
   // start vector of the first step: rho = exp(.5 tau g(u)) u   (nlse_cubic_solver.hpp:62-66)
   {
@@ -720,8 +836,8 @@ __global__ void __launch_bounds__(kPkThreads, 1) k_pk_nlse(PkArgs a, double2 *sv
     for (int li = threadIdx.x; li < c.cnt; li += kPkThreads) {
       const long long idx = c.s0 + li;
       // fused neumann_bc_no_velocity (boundaries.hpp:40-57): boundary sites take the clamped site's value
-      const long long sc = (c.flag[li] & PF_RING) ? clamp_site(a.g, idx) : idx;
-      const double2 buf = pk_combine<double2>(a, scur, c.coef, sc);
+      const long long sc = (c.flag()[li] & PF_RING) ? clamp_site(a.g, idx) : idx;
+      const double2 buf = pk_combine<double2>(a, scur, c.coef(), sc);
       const double mv = a.mf[sc];
       double2 un;
       if (a.eq == NLS_EQ_NLSE_CUBIC) un = nlse_phase<NLS_EQ_NLSE_CUBIC>(p, mv, buf, buf, buf);
@@ -748,7 +864,11 @@ __global__ void __launch_bounds__(kPkThreads, 1) k_pk_gautschi(PkArgs a, double 
   pk_carve<double>(a, c, pk_smem);
   GridSync gs{a.bar, 0u, (unsigned)a.ncta, 0};
   double *u = (double *)a.u0, *up = (double *)a.u1 + c.s0, *accb = (double *)a.acc;
-  double *xc = c.X + a.g.nx;
+  PK_GLOBAL(u);
+  PK_GLOBAL(up);
+  PK_GLOBAL(accb);
+  PK_GLOBAL(gbuf);
+  double *xc = c.X() + a.g.nx;
   const double *mfc = a.mf + c.s0;
   const int filt = a.eq == NLS_EQ_SGE ? NLS_FN_MOD_COSINE : NLS_FN_ID_SQRT;
   const double tau2 = a.dt * a.dt;
@@ -762,15 +882,19 @@ __global__ void __launch_bounds__(kPkThreads, 1) k_pk_gautschi(PkArgs a, double 
     if (!pk_start_norm<double>(a, c, gs, nrm)) return;
   }
   for (int step = 0; step < a.nsteps; ++step) {
+    if (step == a.nsteps - 1) PKT_INIT();
+    PKT(1);
     if (!pk_lanczos<double, ANISO>(a, c, gs, u)) return;
+    PKT(2); // first Lanczos run done
     pk_coefficients<double>(a, c, 2, filt, a.dt, 0.0, NLS_FN_COS_SQRT, a.dt, 0.0);
+    PKT(3); // tridiagonal solve + coefficients
     {
       double nrm[1] = {0.0};
-#pragma unroll 2
+#pragma unroll(kPkCombUnroll)
       for (int li = threadIdx.x; li < c.cnt; li += kPkThreads) {
         const long long idx = c.s0 + li;
         double sf, sc;
-        pk_combine2(a, u, c.coef, c.coef + 2 * kMaxM, idx, sf, sc);
+        pk_combine2(a, u, c.coef(), c.coef() + 2 * kMaxM, idx, sf, sc);
         const double gv = -(mfc[li] * pk_f_real(a.eq, sf));
         gbuf[idx] = gv;
         xc[li] = gv;
@@ -780,15 +904,18 @@ __global__ void __launch_bounds__(kPkThreads, 1) k_pk_gautschi(PkArgs a, double 
       }
       if (!pk_start_norm<double>(a, c, gs, nrm)) return;
     }
+    PKT(4); // combine 1 + start norm
     if (!pk_lanczos<double, ANISO>(a, c, gs, gbuf)) return;
+    PKT(5);
     pk_coefficients<double>(a, c, 1, NLS_FN_SINC2_HALF, a.dt, 0.0, 0, 0.0, 0.0);
+    PKT(6);
     {
       double nrm[1] = {0.0};
-#pragma unroll 2
+#pragma unroll(kPkCombUnroll)
       for (int li = threadIdx.x; li < c.cnt; li += kPkThreads) {
         const long long idx = c.s0 + li;
-        const long long sc = (c.flag[li] & PF_RING) ? clamp_site(a.g, idx) : idx;
-        const double s = pk_combine<double>(a, gbuf, c.coef, sc);
+        const long long sc = (c.flag()[li] & PF_RING) ? clamp_site(a.g, idx) : idx;
+        const double s = pk_combine<double>(a, gbuf, c.coef(), sc);
         const double un = __ldcg(accb + sc) + tau2 * s;
         u[idx] = un;
         xc[li] = un;
@@ -796,7 +923,9 @@ __global__ void __launch_bounds__(kPkThreads, 1) k_pk_gautschi(PkArgs a, double 
       }
       if (!pk_start_norm<double>(a, c, gs, nrm)) return;
     }
+    PKT(7); // combine 2 + start norm
   }
+  PKT_DUMP(a.ncta);
 }
 
 
@@ -813,13 +942,13 @@ __global__ void __launch_bounds__(kPkThreads, 1) k_pk_sv(PkArgs a, double *b0, d
   pk_carve<double>(a, c, pk_smem);
   GridSync gs{a.bar, 0u, (unsigned)a.ncta, 0};
   double *buf[3] = {b0, b1, b2};
-  double *xc = c.X + a.g.nx;
+  double *xc = c.X() + a.g.nx;
   const double *mfc = a.mf + c.s0;
   const double *cfg = ANISO ? a.cf + c.s0 : nullptr;
   const double tau2 = a.dt * a.dt;
   for (int li = threadIdx.x; li < c.cnt; li += kPkThreads) {
     xc[li] = buf[0][c.s0 + li];
-    c.Wt[li] = buf[2][c.s0 + li];
+    c.Wt()[li] = buf[2][c.s0 + li];
   }
   __syncthreads();
   int p = 0;
@@ -829,24 +958,24 @@ __global__ void __launch_bounds__(kPkThreads, 1) k_pk_sv(PkArgs a, double *b0, d
     pk_load_halo<double>(a, c, ucur);
     for (int li = threadIdx.x; li < c.cnt; li += kPkThreads) {
       const long long idx = c.s0 + li;
-      const unsigned f = c.flag[li];
+      const unsigned f = c.flag()[li];
       double un;
       if (f & PF_RING) { // boundary site: the value the update gives at the clamped (interior) site
         const long long sc = clamp_site(a.g, idx);
         const double uc = __ldcg(ucur + sc);
         const double lu = stencil_site_f<double, ANISO>(a.g, [&](long long q) { return __ldcg(ucur + q); }, a.cf, sc, 1.0);
-        const double upv = sc >= c.s0 && sc < c.s0 + c.cnt ? c.Wt[sc - c.s0] : __ldcg(buf[(p + 2) % 3] + sc);
+        const double upv = sc >= c.s0 && sc < c.s0 + c.cnt ? c.Wt()[sc - c.s0] : __ldcg(buf[(p + 2) % 3] + sc);
         un = 2 * uc - upv + tau2 * (lu - a.mf[sc] * pk_f_real(a.eq, uc));
       } else {
         const double uc = xc[li];
         const double lu = pk_stencil<double, ANISO>(a.g, xc, ucur + c.s0, cfg, f, li);
-        un = 2 * uc - c.Wt[li] + tau2 * (lu - mfc[li] * pk_f_real(a.eq, uc));
+        un = 2 * uc - c.Wt()[li] + tau2 * (lu - mfc[li] * pk_f_real(a.eq, uc));
       }
       unew[idx] = un;
     }
     __syncthreads(); // all reads of the tiles are done
     for (int li = threadIdx.x; li < c.cnt; li += kPkThreads) {
-      c.Wt[li] = xc[li];
+      c.Wt()[li] = xc[li];
       xc[li] = __ldcg(unew + c.s0 + li); // written by this very thread in the loop above
     }
     if (!grid_barrier(gs)) return;
