@@ -442,6 +442,7 @@ __device__ __forceinline__ void pk_load_halo(const PkArgs &a, PkCtx<S> &c, const
 #ifndef PK_COMB_UNROLL
 #define PK_COMB_UNROLL 2
 #endif
+constexpr int kPkCoefRegs = 12;           // recombination keeps the coefficients in registers for m <= 12
 constexpr int kPkCombUnroll = PK_COMB_UNROLL; // sites per unrolled group in the recombination loops of k_pk_gautschi
 // unroll factor of the phase loops (the compiler interleaves the loads of the unrolled sites)
 __host__ __device__ constexpr int pk_unroll(int nc, int w) {
@@ -457,26 +458,39 @@ __host__ __device__ constexpr int pk_unroll(int nc, int w) {
 // column), column j-1 (recurrence term + dot, loaded once), column j (the X tile).
 // Phase A, group of NC other columns starting at i0.  FIRST: also forms w (stencil + recurrence),
 // stores it to the Wt tile and accumulates the j-1 and j dots.
+// The site loops live in functions whose pointer parameters are __restrict__ and whose scalars are passed
+// by value: inside the kernels the context struct sits in local memory and every store through a generic
+// pointer forced the compiler to reload it (loop bound included) and to keep the next site's loads behind the
+// current site's stores -- one full memory round trip per site (profiles/r01f_pk_gautschi_phase_trace.txt).
+// column k of the basis for a chunk: k == 0 -> startp, k >= 1 -> vbase + (k-1)*cs
+template <class S>
+__device__ __forceinline__ const S *pk_colp(const S *startp, const S *vbase, size_t cs, int k) {
+  return k == 0 ? startp : vbase + (size_t)(k - 1) * cs;
+}
+
 template <class S, bool ANISO, int NC, bool FIRST>
-__device__ __forceinline__ void pk_phase_a(const PkArgs &a, PkCtx<S> &c, GridSync &gs, S *start, int j, int i0,
-                                           double inv_bj, double cm) {
+__device__ __forceinline__ void pk_loop_a(const Geom &g, const int cnt, const int j, const int i0,
+                                          const S *__restrict__ xc, S *__restrict__ Wt,
+                                          const unsigned char *__restrict__ flag, const S *__restrict__ startp,
+                                          const S *__restrict__ vbase, const size_t cs,
+                                          const double *__restrict__ cfg, const double inv_bj, const double cm,
+                                          double *__restrict__ acc, double *__restrict__ accM,
+                                          double *__restrict__ accA) {
   using T = Sc<S>;
   constexpr int W = T::W;
   constexpr int NA = NC > 0 ? NC : 1;
   const S *p[NA];
 #pragma unroll
-  for (int i = 0; i < NC; ++i) p[i] = pk_col<S>(a, start, i0 + i) + c.s0;
-  const S *colj = pk_col<S>(a, start, j) + c.s0;
-  const S *colm = j > 0 ? pk_col<S>(a, start, j - 1) + c.s0 : colj;
-  const double *cfg = ANISO ? a.cf + c.s0 : nullptr;
-  const S *xc = c.X() + a.g.nx;
-  double acc[NA * W], accM[W], accA[W];
+  for (int i = 0; i < NC; ++i) p[i] = pk_colp<S>(startp, vbase, cs, i0 + i);
+  const S *colj = pk_colp<S>(startp, vbase, cs, j);
+  const S *colm = j > 0 ? pk_colp<S>(startp, vbase, cs, j - 1) : colj;
+  double la[NA * W], lm[W], lj[W];
 #pragma unroll
-  for (int k = 0; k < NA * W; ++k) acc[k] = 0.0;
+  for (int k = 0; k < NA * W; ++k) la[k] = 0.0;
 #pragma unroll
-  for (int k = 0; k < W; ++k) accM[k] = accA[k] = 0.0;
+  for (int k = 0; k < W; ++k) lm[k] = lj[k] = 0.0;
 #pragma unroll(pk_unroll(NC, W))
-  for (int li = threadIdx.x; li < c.cnt; li += kPkThreads) {
+  for (int li = threadIdx.x; li < cnt; li += kPkThreads) {
     S v[NA];
 #pragma unroll
     for (int i = 0; i < NC; ++i) v[i] = __ldcg(p[i] + li);
@@ -484,17 +498,37 @@ __device__ __forceinline__ void pk_phase_a(const PkArgs &a, PkCtx<S> &c, GridSyn
     if (FIRST) {
       S vm = T::zero();
       if (j > 0) vm = __ldcg(colm + li);
-      w = T::mulr(pk_stencil<S, ANISO>(a.g, xc, colj, cfg, c.flag()[li], li), inv_bj);
+      w = T::mulr(pk_stencil<S, ANISO>(g, xc, colj, cfg, flag[li], li), inv_bj);
       w = T::fma_r(cm, vm, w); // cm == 0 when j == 0
-      c.Wt()[li] = w;
-      T::dot_acc(accA, xc[li], w);
-      T::dot_acc(accM, vm, w);
+      Wt[li] = w;
+      T::dot_acc(lj, xc[li], w);
+      T::dot_acc(lm, vm, w);
     } else {
-      w = c.Wt()[li];
+      w = Wt[li];
     }
 #pragma unroll
-    for (int i = 0; i < NC; ++i) T::dot_acc(acc + i * W, v[i], w);
+    for (int i = 0; i < NC; ++i) T::dot_acc(la + i * W, v[i], w);
   }
+#pragma unroll
+  for (int k = 0; k < NA * W; ++k) acc[k] = la[k];
+#pragma unroll
+  for (int k = 0; k < W; ++k) {
+    accM[k] = lm[k];
+    accA[k] = lj[k];
+  }
+}
+
+template <class S, bool ANISO, int NC, bool FIRST>
+__device__ __forceinline__ void pk_phase_a(const PkArgs &a, PkCtx<S> &c, GridSync &gs, S *start, int j, int i0,
+                                           double inv_bj, double cm) {
+  using T = Sc<S>;
+  constexpr int W = T::W;
+  constexpr int NA = NC > 0 ? NC : 1;
+  double acc[NA * W], accM[W], accA[W];
+  pk_loop_a<S, ANISO, NC, FIRST>(a.g, c.cnt, j, i0, c.X() + a.g.nx, c.Wt(), c.flag(), start + c.s0,
+                                 (const S *)a.V + c.s0, a.colstride, ANISO ? a.cf + c.s0 : nullptr, inv_bj, cm,
+                                 acc, accM, accA);
+  PKT(900 + j); // phase A site loop done
   if (NC > 0) pk_publish<NA * W>(acc, a.part, gs.slot, c.red(), i0 * W);
   if (FIRST) {
     if (j > 0) pk_publish<W>(accM, a.part, gs.slot, c.red(), (j - 1) * W);
@@ -505,7 +539,10 @@ __device__ __forceinline__ void pk_phase_a(const PkArgs &a, PkCtx<S> &c, GridSyn
 // Phase B, group of NC other columns.  LAST: also subtracts the j-1 and j terms, accumulates
 // ||w||^2 and stores w to column j+1 (global) and to the X tile centre.
 template <class S, int NC, bool LAST>
-__device__ __forceinline__ void pk_phase_b(const PkArgs &a, PkCtx<S> &c, GridSync &gs, S *start, int j, int i0) {
+__device__ __forceinline__ double pk_loop_b(const int cnt, const int j, const int i0, S *__restrict__ xc,
+                                            S *__restrict__ Wt, const S *__restrict__ startp,
+                                            const S *__restrict__ vbase, const size_t cs, S *__restrict__ coln,
+                                            const S *__restrict__ gco) {
   using T = Sc<S>;
   constexpr int W = T::W;
   constexpr int NA = NC > 0 ? NC : 1;
@@ -513,35 +550,41 @@ __device__ __forceinline__ void pk_phase_b(const PkArgs &a, PkCtx<S> &c, GridSyn
   S gc[NA];
 #pragma unroll
   for (int i = 0; i < NC; ++i) {
-    p[i] = pk_col<S>(a, start, i0 + i) + c.s0;
-    gc[i] = c.gco()[i0 + i];
+    p[i] = pk_colp<S>(startp, vbase, cs, i0 + i);
+    gc[i] = gco[i0 + i];
   }
-  const S *colm = j > 0 ? pk_col<S>(a, start, j - 1) + c.s0 : nullptr;
-  S *coln = pk_col<S>(a, start, j + 1) + c.s0;
-  PK_GLOBAL(coln);
-  S *xc = c.X() + a.g.nx;
-  const S gm = j > 0 ? c.gco()[j - 1] : T::zero(), gj = c.gco()[j];
-  double nrm[1] = {0.0};
+  const S *colm = j > 0 ? pk_colp<S>(startp, vbase, cs, j - 1) : startp;
+  const S gm = j > 0 ? gco[j - 1] : T::zero(), gj = gco[j];
+  double nrm = 0.0;
 #pragma unroll(pk_unroll(NC, W))
-  for (int li = threadIdx.x; li < c.cnt; li += kPkThreads) {
+  for (int li = threadIdx.x; li < cnt; li += kPkThreads) {
     S v[NA];
 #pragma unroll
     for (int i = 0; i < NC; ++i) v[i] = __ldcg(p[i] + li);
     S vm = T::zero();
     if (LAST && j > 0) vm = __ldcg(colm + li);
-    S w = c.Wt()[li];
+    S w = Wt[li];
 #pragma unroll
     for (int i = 0; i < NC; ++i) w = T::sub(w, T::mul(gc[i], v[i]));
     if (LAST) {
       w = T::sub(w, T::mul(gm, vm));
       w = T::sub(w, T::mul(gj, xc[li]));
-      nrm[0] += T::abs2(w);
+      nrm += T::abs2(w);
       coln[li] = w;
       xc[li] = w;
     } else {
-      c.Wt()[li] = w;
+      Wt[li] = w;
     }
   }
+  return nrm;
+}
+
+template <class S, int NC, bool LAST>
+__device__ __forceinline__ void pk_phase_b(const PkArgs &a, PkCtx<S> &c, GridSync &gs, S *start, int j, int i0) {
+  double nrm[1];
+  nrm[0] = pk_loop_b<S, NC, LAST>(c.cnt, j, i0, c.X() + a.g.nx, c.Wt(), start + c.s0, (const S *)a.V + c.s0,
+                                  a.colstride, (S *)a.V + (size_t)j * a.colstride + c.s0, c.gco());
+  PKT(800 + j); // phase B site loop done
   if (LAST) pk_publish<1>(nrm, a.part, gs.slot, c.red(), 0);
 }
 
@@ -743,7 +786,7 @@ inline size_t pk_smem_bytes(size_t esz, long long csz, int nx, int m) {
   b += ((size_t)csz + 15) / 16 * 16;                      // flags
   b += (size_t)m * 32 * 8 * 2 + (size_t)m * (m + 1) * 8;  // tridiagonal work space
   b += (size_t)(2 * kPkNV + 2) * kPkWarps * 8;            // red
-  b += (size_t)kPkMaxK * 8 + kMaxM * 8 + (kMaxM + 1) * 8 + 4 * kMaxM * 8 + kMaxM * 16;
+  b += (size_t)kPkMaxK * 8 + kMaxM * 8 + (kMaxM + 2) * 8 + 4 * kMaxM * 8 + kMaxM * 16;
   return b + 64;
 }
 
@@ -761,9 +804,9 @@ __device__ __forceinline__ void pk_carve(const PkArgs &a, PkCtx<S> &c, unsigned 
   c.red_ = (double (*)[kPkWarps])p; p += (2 * kPkNV + 2) * kPkWarps;
   c.vals_ = p; p += kPkMaxK;
   c.alpha_ = p; p += kMaxM;
-  c.nrm2_ = p; p += kMaxM + 1;
+  c.nrm2_ = p; p += kMaxM + 2; // even count: keeps the complex gco array 16-byte aligned without integer casts
   c.coef_ = p; p += 4 * kMaxM;
-  c.gco_ = (S *)(((uintptr_t)p + 15) & ~(uintptr_t)15);
+  c.gco_ = (S *)p;
   c.s0 = (long long)blockIdx.x * a.csz;
   long long e0 = c.s0 + a.csz;
   if (e0 > a.g.n) e0 = a.g.n;
@@ -854,6 +897,87 @@ __global__ void __launch_bounds__(kPkThreads, 1) k_pk_nlse(PkArgs a, double2 *sv
   }
 }
 
+// Site loops of the Gautschi step (restrict parameters, see pk_loop_a).
+// mid: two coefficient sets in one pass over the basis; g = -m f(filter u) -> gbuf + X tile, ||g||^2,
+//      acc = 2 cos(.)u - u_past, u_past <- u                      (sg_single_solver.hpp:46-52)
+__device__ __forceinline__ double pk_gautschi_mid(const PkArgs &a, const int cnt, const long long s0,
+                                                  const double *__restrict__ u, const double *__restrict__ V,
+                                                  const double *__restrict__ coef, const double *__restrict__ mfc,
+                                                  double *__restrict__ gbuf, double *__restrict__ xc,
+                                                  double *__restrict__ accb, double *__restrict__ up) {
+  const int m = a.m, eq = a.eq;
+  const size_t cs = a.colstride;
+  double co0[2 * kPkCoefRegs], co1[2 * kPkCoefRegs]; // unused beyond m; m <= kPkCoefRegs uses registers
+  const bool inreg = m <= kPkCoefRegs;
+#pragma unroll
+  for (int q = 0; q < kPkCoefRegs; ++q) {
+    co0[q] = q < m ? coef[2 * q] : 0.0;
+    co1[q] = q < m ? coef[2 * kMaxM + 2 * q] : 0.0;
+  }
+  double nrm = 0.0;
+#pragma unroll(kPkCombUnroll)
+  for (int li = threadIdx.x; li < cnt; li += kPkThreads) {
+    const long long idx = s0 + li;
+    double sf = 0.0, sc = 0.0;
+    if (inreg) {
+      double v[kPkCoefRegs];
+      v[0] = __ldcg(u + idx);
+#pragma unroll
+      for (int q = 1; q < kPkCoefRegs; ++q) v[q] = q < m ? __ldcg(V + (size_t)(q - 1) * cs + idx) : 0.0;
+#pragma unroll
+      for (int q = 0; q < kPkCoefRegs; ++q) {
+        sf = fma(v[q], co0[q], sf);
+        sc = fma(v[q], co1[q], sc);
+      }
+    } else {
+      pk_combine2(a, u, coef, coef + 2 * kMaxM, idx, sf, sc);
+    }
+    const double gv = -(mfc[li] * pk_f_real(eq, sf));
+    gbuf[idx] = gv;
+    xc[li] = gv;
+    nrm += gv * gv;
+    accb[idx] = 2 * sc - __ldcg(up + li);
+    up[li] = __ldcg(u + idx);
+  }
+  return nrm;
+}
+// tail: u+ = acc + tau^2 sinc^2(.) g at the clamped site (fused no-flux copy), ||u+||^2   (:53-57, boundaries.hpp:40-57)
+__device__ __forceinline__ double pk_gautschi_tail(const PkArgs &a, const int cnt, const long long s0,
+                                                   const double *__restrict__ gbuf, const double *__restrict__ V,
+                                                   const double *__restrict__ coef,
+                                                   const unsigned char *__restrict__ flag,
+                                                   const double *__restrict__ accb, double *__restrict__ u,
+                                                   double *__restrict__ xc, const double tau2) {
+  const int m = a.m;
+  const size_t cs = a.colstride;
+  double co[kPkCoefRegs];
+  const bool inreg = m <= kPkCoefRegs;
+#pragma unroll
+  for (int q = 0; q < kPkCoefRegs; ++q) co[q] = q < m ? coef[2 * q] : 0.0;
+  double nrm = 0.0;
+#pragma unroll(kPkCombUnroll)
+  for (int li = threadIdx.x; li < cnt; li += kPkThreads) {
+    const long long idx = s0 + li;
+    const long long sc = (flag[li] & PF_RING) ? clamp_site(a.g, idx) : idx;
+    double s = 0.0;
+    if (inreg) {
+      double v[kPkCoefRegs];
+      v[0] = __ldcg(gbuf + sc);
+#pragma unroll
+      for (int q = 1; q < kPkCoefRegs; ++q) v[q] = q < m ? __ldcg(V + (size_t)(q - 1) * cs + sc) : 0.0;
+#pragma unroll
+      for (int q = 0; q < kPkCoefRegs; ++q) s = fma(v[q], co[q], s);
+    } else {
+      s = pk_combine<double>(a, gbuf, coef, sc);
+    }
+    const double un = __ldcg(accb + sc) + tau2 * s;
+    u[idx] = un;
+    xc[li] = un;
+    nrm += un * un;
+  }
+  return nrm;
+}
+
 // ---------------------------------------------------------------- real equations, Gautschi
 // buffers: a.u0 = u (also column 0 of the first Lanczos run), a.u1 = u_past, a.acc, gbuf = start
 // vector of the second run.   sg_single_solver.hpp:43-59, kg_solver.hpp:13-22
@@ -889,19 +1013,8 @@ __global__ void __launch_bounds__(kPkThreads, 1) k_pk_gautschi(PkArgs a, double 
     pk_coefficients<double>(a, c, 2, filt, a.dt, 0.0, NLS_FN_COS_SQRT, a.dt, 0.0);
     PKT(3); // tridiagonal solve + coefficients
     {
-      double nrm[1] = {0.0};
-#pragma unroll(kPkCombUnroll)
-      for (int li = threadIdx.x; li < c.cnt; li += kPkThreads) {
-        const long long idx = c.s0 + li;
-        double sf, sc;
-        pk_combine2(a, u, c.coef(), c.coef() + 2 * kMaxM, idx, sf, sc);
-        const double gv = -(mfc[li] * pk_f_real(a.eq, sf));
-        gbuf[idx] = gv;
-        xc[li] = gv;
-        nrm[0] += gv * gv;
-        accb[idx] = 2 * sc - __ldcg(up + li);
-        up[li] = __ldcg(u + idx);
-      }
+      double nrm[1];
+      nrm[0] = pk_gautschi_mid(a, c.cnt, c.s0, u, (const double *)a.V, c.coef(), mfc, gbuf, xc, accb, up);
       if (!pk_start_norm<double>(a, c, gs, nrm)) return;
     }
     PKT(4); // combine 1 + start norm
@@ -910,17 +1023,8 @@ __global__ void __launch_bounds__(kPkThreads, 1) k_pk_gautschi(PkArgs a, double 
     pk_coefficients<double>(a, c, 1, NLS_FN_SINC2_HALF, a.dt, 0.0, 0, 0.0, 0.0);
     PKT(6);
     {
-      double nrm[1] = {0.0};
-#pragma unroll(kPkCombUnroll)
-      for (int li = threadIdx.x; li < c.cnt; li += kPkThreads) {
-        const long long idx = c.s0 + li;
-        const long long sc = (c.flag()[li] & PF_RING) ? clamp_site(a.g, idx) : idx;
-        const double s = pk_combine<double>(a, gbuf, c.coef(), sc);
-        const double un = __ldcg(accb + sc) + tau2 * s;
-        u[idx] = un;
-        xc[li] = un;
-        nrm[0] += un * un;
-      }
+      double nrm[1];
+      nrm[0] = pk_gautschi_tail(a, c.cnt, c.s0, gbuf, (const double *)a.V, c.coef(), c.flag(), accb, u, xc, tau2);
       if (!pk_start_norm<double>(a, c, gs, nrm)) return;
     }
     PKT(7); // combine 2 + start norm
