@@ -1,0 +1,13 @@
+#!/bin/bash
+# GPU session 19: restrict-parameter site loops in the persistent kernels
+set -x
+mkdir -p gpurun_out
+V=$PWD/nonlinear-solvers_b200/variants
+timeout 900 python -m pytest tests/test_gpu_parity.py -m gpu -q > gpurun_out/r19_pytest_gpu.log 2>&1; echo "pytest rc=$?" >> gpurun_out/r19_pytest_gpu.log
+for w in c2_gautschi c1; do
+  timeout 300 python bench.py --workload $w --steps 500 --warmup 20 --no-cpu > gpurun_out/r19_bench_${w}_base.log 2>&1
+  NLS_B200_LIB=$V/libnls_unroll.so timeout 300 python bench.py --workload $w --steps 500 --warmup 20 --no-cpu > gpurun_out/r19_bench_${w}_unroll.log 2>&1
+done
+NLS_B200_LIB=$V/libnls_unroll.so timeout 900 python -m pytest tests/test_gpu_parity.py -m gpu -q > gpurun_out/r19_pytest_unroll.log 2>&1; echo "pytest rc=$?" >> gpurun_out/r19_pytest_unroll.log
+NLS_B200_LIB=$V/libnls_trace.so timeout 300 python tools/pk_trace.py > gpurun_out/r19_pk_trace.txt 2>&1
+grep -h -o '"ms_per_step": [0-9.]*' gpurun_out/r19_bench_*.log
