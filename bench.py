@@ -91,7 +91,8 @@ def make_desc(w, batch=None, device=0):
     n = w["n"]
     return Desc.make(n, n, n if w["dim"] == 3 else 1, L=w["L"], equation=w["eq"], integrator=w["integ"],
                      laplacian=w.get("lap", LAP.UNIFORM), krylov_m=w["m"], batch=batch or w.get("batch", 1),
-                     s1=w.get("s1", 0.0), s2=w.get("s2", 0.0), dt=w["dt"], device=device)
+                     s1=w.get("s1", 0.0), s2=w.get("s2", 0.0), dt=w["dt"], device=device,
+                     flags=int(os.environ.get("NLS_BENCH_FLAGS", w.get("flags", 0))))
 
 
 def make_state(w, batch, seed0=0):

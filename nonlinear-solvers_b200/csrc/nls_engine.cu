@@ -566,7 +566,7 @@ void pk_setup(nls_engine *e) {
   long long csz = (e->g.n + nsm - 1) / nsm;
   if (csz < 64) csz = 64;
   const int ncta = (int)((e->g.n + csz - 1) / csz);
-  const size_t smem = pk_smem_bytes(e->esz, csz, e->g.nx, e->m);
+  const size_t smem = pk_smem_bytes(e->esz, csz, e->g.nx, e->m, sv ? 2 * e->g.nx : 0);
   if (smem > (size_t)smem_max) return;
   const bool an = d.laplacian == NLS_LAP_ANISO;
   const void *fn = e->cplx ? (an ? (const void *)k_pk_nlse<true> : (const void *)k_pk_nlse<false>)

@@ -19,6 +19,7 @@
 // nls_kernels.cuh up to re-orthogonalisation rounding (one block Gram-Schmidt pass including
 // the alpha term, instead of alpha step + block pass).
 #pragma once
+#include <climits>
 #include "nls_kernels.cuh"
 
 namespace nls {
@@ -803,8 +804,8 @@ __device__ __forceinline__ void pk_combine2(const PkArgs &a, const double *start
 }
 
 // ---------------------------------------------------------------- kernel set-up
-inline size_t pk_smem_bytes(size_t esz, long long csz, int nx, int m) {
-  size_t b = (size_t)(2 * csz + 2 * nx) * esz;           // X + Wt
+inline size_t pk_smem_bytes(size_t esz, long long csz, int nx, int m, int wt_halo = 0) {
+  size_t b = (size_t)(2 * csz + 2 * nx + wt_halo) * esz; // X + Wt (+ halo rows of the Wt tile, Stoermer-Verlet)
   b += ((size_t)csz + 15) / 16 * 16;                      // flags
   b += (size_t)m * 32 * 8 * 2 + (size_t)m * (m + 1) * 8;  // tridiagonal work space
   b += (size_t)(2 * kPkNV + 2) * kPkWarps * 8;            // red
@@ -813,11 +814,11 @@ inline size_t pk_smem_bytes(size_t esz, long long csz, int nx, int m) {
 }
 
 template <class S>
-__device__ __forceinline__ void pk_carve(const PkArgs &a, PkCtx<S> &c, unsigned char *smem) {
+__device__ __forceinline__ void pk_carve(const PkArgs &a, PkCtx<S> &c, unsigned char *smem, int wt_halo = 0) {
   const long long tile = a.csz + 2 * a.g.nx;
   c.X_ = (S *)smem;
   c.Wt_ = c.X_ + tile;
-  c.flag_ = (unsigned char *)(c.Wt_ + a.csz);
+  c.flag_ = (unsigned char *)(c.Wt_ + a.csz + wt_halo);
   double *p = (double *)(c.flag() + (a.csz + 15) / 16 * 16);
   c.tri.d = p; p += a.m * 32;
   c.tri.e = p; p += a.m * 32;
@@ -1067,50 +1068,89 @@ __global__ void __launch_bounds__(kPkThreads, 1) k_pk_gautschi(PkArgs a, double 
 // rows) and u_past stay in shared memory for the whole launch; each step writes u+ once to the
 // rotating global buffers (the neighbours' halo rows and the final state come from there) and
 // costs one grid barrier.  buf[0] = u, buf[2] = u_past at entry; step s writes buf[(s+1)%3].
+// one Stoermer-Verlet step over a chunk (restrict parameters, see pk_loop_a): reads the u tile (with halo
+// rows) and u_past in place, writes u+ over u_past in shared memory and to the rotating global buffer
+template <bool ANISO>
+__device__ __forceinline__ void pk_sv_loop(const PkArgs &a, const int cnt, const long long s0,
+                                           const double *__restrict__ xc, double *__restrict__ pc,
+                                           const unsigned char *__restrict__ flag,
+                                           const double *__restrict__ ucur, const double *__restrict__ upast,
+                                           double *__restrict__ unew, const double *__restrict__ mf,
+                                           const double *__restrict__ cfg, const double tau2) {
+  PK_LSH(xc); PK_LSH(pc); PK_LSH(flag); PK_LGL(unew);
+  const int eq = a.eq;
+#pragma unroll 2
+  for (int li = threadIdx.x; li < cnt; li += kPkThreads) {
+    const long long idx = s0 + li;
+    const unsigned f = flag[li];
+    double un;
+    if (f & PF_RING) { // boundary site: the value the update gives at the clamped (interior) site
+      const long long sc = clamp_site(a.g, idx);
+      const double uc = __ldcg(ucur + sc);
+      const double lu = stencil_site_f<double, ANISO>(a.g, [&](long long q) { return __ldcg(ucur + q); }, a.cf, sc, 1.0);
+      un = 2 * uc - __ldcg(upast + sc) + tau2 * (lu - mf[sc] * pk_f_real(eq, uc));
+    } else {
+      const double uc = xc[li];
+      const double lu = pk_stencil<double, ANISO>(a.g, xc, ucur + s0, cfg, f, li);
+      un = 2 * uc - pc[li] + tau2 * (lu - mf[idx] * pk_f_real(eq, uc));
+    }
+    pc[li] = un;
+    unew[idx] = un;
+  }
+}
+
+// halo rows of `col` into the tile whose centre is xc (tile = xc - nx)
+__device__ __forceinline__ void pk_sv_halo(const PkArgs &a, const int cnt, const long long s0, double *xc,
+                                           const double *col) {
+  const int nx = a.g.nx;
+  constexpr int kQ = 4;
+  if (cnt > 0) {
+    for (int t0 = threadIdx.x; t0 < 2 * nx; t0 += kQ * kPkThreads) {
+      double v[kQ];
+      int xi[kQ];
+#pragma unroll
+      for (int q = 0; q < kQ; ++q) {
+        const int t = t0 + q * kPkThreads;
+        const bool up = t >= nx;
+        const long long idx = up ? s0 + cnt + (t - nx) : s0 - nx + t;
+        xi[q] = INT_MIN;
+        if (t < 2 * nx && idx >= 0 && idx < a.g.n) {
+          xi[q] = up ? cnt + (t - nx) : t - nx;
+          v[q] = __ldcg(col + idx);
+        }
+      }
+#pragma unroll
+      for (int q = 0; q < kQ; ++q)
+        if (xi[q] != INT_MIN) xc[xi[q]] = v[q];
+    }
+  }
+  __syncthreads();
+}
+
 template <bool ANISO>
 __global__ void __launch_bounds__(kPkThreads, 1) k_pk_sv(PkArgs a, double *b0, double *b1, double *b2) {
   extern __shared__ __align__(16) unsigned char pk_smem[];
   PkCtx<double> c;
-  pk_carve<double>(a, c, pk_smem);
+  pk_carve<double>(a, c, pk_smem, 2 * a.g.nx); // both tiles carry halo rows: they swap roles every step
   GridSync gs{a.bar, 0u, (unsigned)a.ncta, 0};
   double *buf[3] = {b0, b1, b2};
-  double *xc = c.X() + a.g.nx;
-  const double *mfc = a.mf + c.s0;
+  double *xc = c.X() + a.g.nx, *pc = c.Wt() + a.g.nx; // u tile centre, u_past tile centre
   const double *cfg = ANISO ? a.cf + c.s0 : nullptr;
   const double tau2 = a.dt * a.dt;
-  for (int li = threadIdx.x; li < c.cnt; li += kPkThreads) {
-    xc[li] = buf[0][c.s0 + li];
-    c.Wt()[li] = buf[2][c.s0 + li];
+  const int cnt = c.cnt;
+  const long long s0 = c.s0;
+  for (int li = threadIdx.x; li < cnt; li += kPkThreads) {
+    xc[li] = buf[0][s0 + li];
+    pc[li] = buf[2][s0 + li];
   }
   __syncthreads();
   int p = 0;
   for (int step = 0; step < a.nsteps; ++step) {
     const double *ucur = buf[p];
-    double *unew = buf[(p + 1) % 3];
-    pk_load_halo<double>(a, c, ucur);
-    for (int li = threadIdx.x; li < c.cnt; li += kPkThreads) {
-      const long long idx = c.s0 + li;
-      const unsigned f = c.flag()[li];
-      double un;
-      if (f & PF_RING) { // boundary site: the value the update gives at the clamped (interior) site
-        const long long sc = clamp_site(a.g, idx);
-        const double uc = __ldcg(ucur + sc);
-        const double lu = stencil_site_f<double, ANISO>(a.g, [&](long long q) { return __ldcg(ucur + q); }, a.cf, sc, 1.0);
-        const double upv = sc >= c.s0 && sc < c.s0 + c.cnt ? c.Wt()[sc - c.s0] : __ldcg(buf[(p + 2) % 3] + sc);
-        un = 2 * uc - upv + tau2 * (lu - a.mf[sc] * pk_f_real(a.eq, uc));
-      } else {
-        const double uc = xc[li];
-        const double lu = pk_stencil<double, ANISO>(a.g, xc, ucur + c.s0, cfg, f, li);
-        un = 2 * uc - c.Wt()[li] + tau2 * (lu - mfc[li] * pk_f_real(a.eq, uc));
-      }
-      unew[idx] = un;
-    }
-    __syncthreads(); // all reads of the tiles are done
-    for (int li = threadIdx.x; li < c.cnt; li += kPkThreads) {
-      c.Wt()[li] = xc[li];
-      xc[li] = __ldcg(unew + c.s0 + li); // written by this very thread in the loop above
-    }
-    if (!grid_barrier(gs)) return;
+    pk_sv_halo(a, cnt, s0, xc, ucur);
+    pk_sv_loop<ANISO>(a, cnt, s0, xc, pc, c.flag(), ucur, buf[(p + 2) % 3], buf[(p + 1) % 3], a.mf, cfg, tau2);
+    double *t = xc; xc = pc; pc = t; // u+ (written over u_past) becomes u, u becomes u_past
+    if (!grid_barrier(gs)) return;   // starts with __syncthreads: all tile reads of this step are done
     p = (p + 1) % 3;
   }
 }
