@@ -219,6 +219,7 @@ def run_reference(args, w, rank, world):
         return
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import orc
+    orc.Oracle.set_threads(len(os.sched_getaffinity(0)))  # torchrun exports OMP_NUM_THREADS=1
     cores = orc.Oracle.threads()
     if "slab_planes" in w:  # the CPU cannot hold the slab workload: same equation on a 128^3 cube
         w = dict(w, n=128)

@@ -539,6 +539,15 @@ int orc_threads(void) {
 #endif
 }
 
+// launchers such as torchrun export OMP_NUM_THREADS=1; the timed CPU baseline asks for all cores explicitly
+void orc_set_threads(int n) {
+#ifdef _OPENMP
+  if (n > 0) omp_set_num_threads(n);
+#else
+  (void)n;
+#endif
+}
+
 int orc_create(const nls_desc *desc, orc_handle *out) {
   if (!desc || !out || desc->struct_size != sizeof(nls_desc)) {
     g_err = "bad descriptor";

@@ -48,6 +48,7 @@ int orc_reduce(orc_handle h, int what, double *out);
 int orc_csr(orc_handle h, int64_t *nnz, int64_t *rowptr, int32_t *col, double *val);
 /* number of OpenMP threads the batch loop will use */
 int orc_threads(void);
+void orc_set_threads(int n);
 const char *orc_last_error(void);
 
 #ifdef __cplusplus

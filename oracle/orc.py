@@ -127,3 +127,7 @@ class Oracle:
     @staticmethod
     def threads():
         return lib().orc_threads()
+
+    @staticmethod
+    def set_threads(n):
+        lib().orc_set_threads(int(n))
