@@ -315,7 +315,7 @@ template <class S> struct PkCtx {
   PK_ACC(unsigned char *, flag) // [csz] PF_* bits of the owned sites
   PkTri tri;
   typedef double (*RedPtr)[kPkWarps];
-  PK_ACC(RedPtr, red)           // [2*kPkNV + 2][kPkWarps]
+  PK_ACC(RedPtr, red)           // [2*kPkNV + 4][kPkWarps]
   PK_ACC(double *, vals)        // [kPkMaxK] gathered sums
   PK_ACC(double *, alpha)       // [kMaxM]   T(j,j)
   PK_ACC(double *, nrm2)        // [kMaxM+1] nrm2[0] = ||start||^2, nrm2[j+1] = ||w_j||^2
@@ -549,6 +549,19 @@ __device__ __forceinline__ void pk_phase_a(const PkArgs &a, PkCtx<S> &c, GridSyn
                                  (const S *)a.V + c.s0, a.colstride, ANISO ? a.cf + c.s0 : nullptr, inv_bj, cm,
                                  acc, accM, accA);
   PKT(900 + j); // phase A site loop done
+  if (FIRST && j > 0 && NC == j - 1) {
+    // the usual case (all other columns in this group): partial-sum slots 0..j are contiguous -> one publish
+    double all[(NC + 2) * W];
+#pragma unroll
+    for (int k = 0; k < NC * W; ++k) all[k] = acc[k];
+#pragma unroll
+    for (int k = 0; k < W; ++k) {
+      all[NC * W + k] = accM[k];
+      all[(NC + 1) * W + k] = accA[k];
+    }
+    pk_publish<(NC + 2) * W>(all, a.part, gs.slot, c.red(), 0);
+    return;
+  }
   if (NC > 0) pk_publish<NA * W>(acc, a.part, gs.slot, c.red(), i0 * W);
   if (FIRST) {
     if (j > 0) pk_publish<W>(accM, a.part, gs.slot, c.red(), (j - 1) * W);
@@ -808,7 +821,7 @@ inline size_t pk_smem_bytes(size_t esz, long long csz, int nx, int m, int wt_hal
   size_t b = (size_t)(2 * csz + 2 * nx + wt_halo) * esz; // X + Wt (+ halo rows of the Wt tile, Stoermer-Verlet)
   b += ((size_t)csz + 15) / 16 * 16;                      // flags
   b += (size_t)m * 32 * 8 * 2 + (size_t)m * (m + 1) * 8;  // tridiagonal work space
-  b += (size_t)(2 * kPkNV + 2) * kPkWarps * 8;            // red
+  b += (size_t)(2 * kPkNV + 4) * kPkWarps * 8;            // red
   b += (size_t)kPkMaxK * 8 + kMaxM * 8 + (kMaxM + 2) * 8 + 4 * kMaxM * 8 + kMaxM * 16;
   return b + 64;
 }
@@ -824,7 +837,7 @@ __device__ __forceinline__ void pk_carve(const PkArgs &a, PkCtx<S> &c, unsigned 
   c.tri.e = p; p += a.m * 32;
   c.tri.Z = p; p += a.m * (a.m + 1);
   c.tri.ldz = a.m + 1;
-  c.red_ = (double (*)[kPkWarps])p; p += (2 * kPkNV + 2) * kPkWarps;
+  c.red_ = (double (*)[kPkWarps])p; p += (2 * kPkNV + 4) * kPkWarps;
   c.vals_ = p; p += kPkMaxK;
   c.alpha_ = p; p += kMaxM;
   c.nrm2_ = p; p += kMaxM + 2; // even count: keeps the complex gco array 16-byte aligned without integer casts
