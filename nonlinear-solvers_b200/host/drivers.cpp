@@ -9,7 +9,11 @@
 //   (ny,nx) / (nz,ny,nx) in and (ns,[nz,]ny,nx) out, default m when no file is given,
 //   the sign of the operator (+L or -L) and the hard-coded Krylov dimension.
 // Optional trailing flags (not in the reference; ignored by its launchers):
-//   --m K   Krylov dimension      --device D   CUDA device ordinal
+//   --m K   Krylov dimension      --device D   first CUDA device ordinal
+//   --devices G   spread an ensemble file over devices D..D+G-1 (one host thread each)
+// Ensemble input: when u0.npy [and v0.npy] carry one extra leading dimension
+// `(B, [nz,] ny, nx)`, all B trajectories advance in batched handles and the trajectory files
+// get the shape `(B, num_snapshots, ...)`; `nlse_ensemble_driver` is the cubic-NLSE alias for it.
 #include "../../include/nls/solvers.hpp"
 #include "npy.hpp"
 
@@ -17,6 +21,8 @@
 #include <cstdlib>
 #include <iostream>
 #include <libgen.h>
+#include <thread>
+#include <algorithm>
 
 using nls_host::read_npy;
 using nls_host::write_npy;
@@ -53,6 +59,9 @@ const Spec kSpecs[] = {
     {"phi4", 2, NLS_EQ_PHI4, NLS_INT_GAUTSCHI, 0, false, 1.0, -1, 10, "phi4_driver.cpp:20-123"},
     {"kg_driver_3d", 3, NLS_EQ_KGE, NLS_INT_GAUTSCHI, 0, true, 1.0, -1, 10, "kg_driver_3d.cpp:20-146"},
     {"kg_sv_driver_3d", 3, NLS_EQ_KGE, NLS_INT_SV, 0, true, 1.0, 1, 10, "kg_sv_driver_3d.cpp:20-146"},
+    // in-process ensemble alias (N3): the nlse_cubic contract with m == 1 when no m file is given,
+    // like the trajectories of device/nlse_driver_omp.cpp:103-121 (u_t = i(Lu + |u|^2 u))
+    {"nlse_ensemble_driver", 2, NLS_EQ_NLSE_CUBIC, NLS_INT_SS2, 0, false, 1.0, 1, 10, "nlse_driver_omp.cpp:56-121"},
     // sEWI ("Gautschi" NLSE): one SS2 start-up step, then the two-step integrator
     {"nlse_cubic_gautschi", 2, NLS_EQ_NLSE_CUBIC, NLS_INT_SEWI, 0, false, 0.0, 1, 10, "nlse_cubic_gautschi_driver.cpp:19-150",
      NLS_FLAG_SEWI_HOST2D},
@@ -80,7 +89,8 @@ int usage(const Spec &s, const char *argv0) {
   if (is_nlse(s)) std::cerr << " input_u0.npy output_traj.npy";
   else std::cerr << " input_u0.npy input_v0.npy output_traj.npy output_vel.npy";
   std::cerr << " T nt num_snapshots" << (s.fields_req ? " input_m.npy input_c.npy" : " [input_m.npy]")
-            << " [--m K] [--device D]\n";
+            << " [--m K] [--device D] [--devices G]\n"
+            << "  (u0/v0 may be ensemble files of shape (B, ...): output is (B, num_snapshots, ...))\n";
   return 1;
 }
 
@@ -97,16 +107,124 @@ bool load_checked(const std::string &file, const std::vector<uint64_t> &want, st
   return false;
 }
 
+// Shape check that also accepts a leading ensemble dimension: `(B, [nz,] ny, nx)` holds B
+// independent initial conditions (the reference runs one process, or one OpenMP
+// thread with its own solver, per trajectory: device/submit_nlse.py:117-129,
+// device/nlse_driver_omp.cpp:103-121).  B = 0 on return means "not an ensemble file".
+template <class T>
+bool load_state(const std::string &file, const std::vector<uint64_t> &want, std::vector<T> &out, const char *what,
+                uint64_t &B) {
+  std::vector<uint64_t> shape;
+  out = read_npy<T>(file, shape);
+  if (shape == want) { B = 0; return true; }
+  if (shape.size() == want.size() + 1 && shape[0] >= 1 && std::equal(want.begin(), want.end(), shape.begin() + 1)) {
+    B = shape[0];
+    return true;
+  }
+  std::cerr << "Error: " << what << " array dimensions mismatch\nExpected:";
+  for (auto v : want) std::cerr << " " << v;
+  std::cerr << "\nGot:";
+  for (auto v : shape) std::cerr << " " << v;
+  std::cerr << "\n";
+  return false;
+}
+
+// The time loop of every driver (nlse_cubic_driver.cpp:96-105, sg_single_driver.cpp:104-121) for
+// one trajectory or for an ensemble file.  The B trajectories are block-partitioned over the
+// devices (`[g*B/G, (g+1)*B/G)`), one host thread and one batched handle per
+// device, no communication.  Output: `(ns, ...)` for a plain input, `(B, ns, ...)` for an
+// ensemble input, trajectory b identical to what the single-trajectory driver writes for IC b.
+template <class T>
+bool run_ensemble(const Spec &s, const nls::Grid &g, uint32_t krylov, double dt, const double *sc, uint32_t nt,
+                  uint32_t ns, uint32_t freq, const std::vector<uint64_t> &want, const std::vector<double> &m,
+                  const std::string &in_u, const std::string &in_v, const std::string &out_u,
+                  const std::string &out_v, const std::vector<int> &devices, uint64_t &B_out) {
+  const bool real = !in_v.empty();
+  const size_t n = g.n();
+  std::vector<T> u0, v0;
+  uint64_t Bu = 0, Bv = 0;
+  if (!load_state(in_u, want, u0, "Input", Bu)) return false;
+  if (real && !load_state(in_v, want, v0, "Input velocity", Bv)) return false;
+  if (real && Bu != Bv) {
+    std::cerr << "Error: u0 and v0 hold a different number of trajectories (" << Bu << " vs " << Bv << ")\n";
+    return false;
+  }
+  const uint64_t B = Bu ? Bu : 1;
+  B_out = B;
+  if (devices.size() > 1) { // a single device is left to nls_create to validate, like every other driver
+    const int have = std::max(0, nls_device_count());
+    if (devices.back() >= have) {
+      std::cerr << "Error: --device " << devices.front() << " --devices " << devices.size() << " but " << have
+                << " CUDA device(s) are visible\n";
+      return false;
+    }
+  }
+  std::vector<uint64_t> oshape = want;
+  oshape.insert(oshape.begin(), ns);
+  if (Bu) oshape.insert(oshape.begin(), B);
+  std::vector<T> tu((size_t)B * ns * n), tv(real ? (size_t)B * ns * n : 0);
+  for (uint64_t b = 0; b < B; ++b) {
+    std::copy(u0.begin() + b * n, u0.begin() + (b + 1) * n, tu.begin() + b * ns * n);
+    if (real) std::copy(v0.begin() + b * n, v0.begin() + (b + 1) * n, tv.begin() + b * ns * n);
+  }
+
+  const size_t G = std::min<size_t>(devices.size(), B);
+  std::vector<std::string> errors(G);
+  auto worker = [&](size_t gi) {
+    try {
+      const uint64_t b0 = gi * B / G, b1 = (gi + 1) * B / G, nb = b1 - b0;
+      nls::Handle h(g, s.equation, s.integrator, krylov, dt, sc[0], sc[1], sc[0], (uint32_t)nb, devices[gi], s.flags);
+      h.set(NLS_FIELD_M, m.data(), n * 8);
+      h.set(NLS_FIELD_U, u0.data() + b0 * n, nb * n * sizeof(T));
+      if (real) h.set(NLS_FIELD_V, v0.data() + b0 * n, nb * n * sizeof(T));
+      std::vector<T> su(nb > 1 ? nb * n : 0), sv(real && nb > 1 ? nb * n : 0);
+      // run up to the next snapshot step in one asynchronous call; same steps, same snapshots
+      for (uint32_t i = 1; i < nt;) {
+        uint32_t next = (i / freq + (i % freq ? 1 : 0)) * freq; // first multiple of freq >= i
+        if (next >= nt) next = nt - 1;
+        h.step(dt, next - i + 1);
+        i = next + 1;
+        if (next % freq != 0 || next / freq >= ns) continue;
+        const size_t snap = next / freq;
+        if (nb == 1) { // straight into the trajectory
+          h.get(NLS_FIELD_U, tu.data() + (b0 * ns + snap) * n, n * sizeof(T));
+          if (real) h.get(NLS_FIELD_V, tv.data() + (b0 * ns + snap) * n, n * sizeof(T));
+          continue;
+        }
+        h.get(NLS_FIELD_U, su.data(), nb * n * sizeof(T));
+        if (real) h.get(NLS_FIELD_V, sv.data(), nb * n * sizeof(T));
+        for (uint64_t b = 0; b < nb; ++b) {
+          std::copy(su.begin() + b * n, su.begin() + (b + 1) * n, tu.begin() + ((b0 + b) * ns + snap) * n);
+          if (real) std::copy(sv.begin() + b * n, sv.begin() + (b + 1) * n, tv.begin() + ((b0 + b) * ns + snap) * n);
+        }
+      }
+      h.sync();
+    } catch (const std::exception &e) { errors[gi] = e.what(); }
+  };
+  if (G == 1) worker(0);
+  else {
+    std::vector<std::thread> th;
+    for (size_t gi = 0; gi < G; ++gi) th.emplace_back(worker, gi);
+    for (auto &t : th) t.join();
+  }
+  for (const auto &e : errors)
+    if (!e.empty()) throw std::runtime_error(e); // CUDA/engine errors abort like the reference
+  write_npy(out_u, tu.data(), oshape);
+  if (real) write_npy(out_v, tv.data(), oshape);
+  return true;
+}
+
 int run(const Spec &s, int argc, char **argv) {
   // strip the optional trailing flags
   uint32_t krylov = s.krylov;
-  int device = 0;
+  int device = 0, ndev = 1;
   if (const char *e = std::getenv("NLS_KRYLOV_M")) krylov = (uint32_t)std::stoul(e);
   std::vector<char *> av(argv, argv + argc);
   for (size_t i = 1; i + 1 < av.size();) {
     const std::string a = av[i];
     if (a == "--m") { krylov = (uint32_t)std::stoul(av[i + 1]); av.erase(av.begin() + i, av.begin() + i + 2); }
     else if (a == "--device") { device = std::stoi(av[i + 1]); av.erase(av.begin() + i, av.begin() + i + 2); }
+    else if (a == "--devices") { ndev = std::stoi(av[i + 1]); av.erase(av.begin() + i, av.begin() + i + 2); }
     else ++i;
   }
   const int ac = (int)av.size();
@@ -143,8 +261,13 @@ int run(const Spec &s, int argc, char **argv) {
   const uint32_t freq = nt / ns;
   const size_t n = g.n();
   std::vector<uint64_t> want = s.dim == 3 ? std::vector<uint64_t>{nz, ny, nx} : std::vector<uint64_t>{ny, nx};
-  std::vector<uint64_t> oshape = want;
-  oshape.insert(oshape.begin(), ns);
+  if (ndev < 1 || device < 0) {
+    std::cerr << "Error: need --device >= 0 and --devices >= 1\n";
+    return 1;
+  }
+  std::vector<int> devices;
+  for (int k = 0; k < ndev; ++k) devices.push_back(device + k);
+  uint64_t B = 1;
 
   std::vector<double> m(n, s.m_default), c;
   if (!m_file.empty()) {
@@ -166,51 +289,13 @@ int run(const Spec &s, int argc, char **argv) {
 
   const auto t0 = std::chrono::steady_clock::now();
   if (is_nlse(s)) {
-    std::vector<cplx> u0;
-    if (!load_checked(in_u, want, u0, "Input")) return 1;
-    nls::Handle h(g, s.equation, s.integrator, krylov, dt, sc[0], sc[1], sc[0], 1, device, s.flags);
-    h.set(NLS_FIELD_M, m.data(), n * 8);
-    h.set(NLS_FIELD_U, u0.data(), n * 16);
-    std::vector<cplx> traj((size_t)ns * n);
-    std::copy(u0.begin(), u0.end(), traj.begin());
-    // run up to the next snapshot step in one asynchronous call; same steps, same snapshots
-    for (uint32_t i = 1; i < nt;) {
-      uint32_t next = (i / freq + (i % freq ? 1 : 0)) * freq; // first multiple of freq >= i
-      if (next >= nt) next = nt - 1;
-      h.step(dt, next - i + 1);
-      i = next + 1;
-      if (next % freq == 0 && next / freq < ns) h.get(NLS_FIELD_U, traj.data() + (size_t)(next / freq) * n, n * 16);
-    }
-    h.sync();
-    write_npy(out_u, traj.data(), oshape);
+    if (!run_ensemble<cplx>(s, g, krylov, dt, sc, nt, ns, freq, want, m, in_u, "", out_u, "", devices, B)) return 1;
   } else {
-    std::vector<double> u0, v0;
-    if (!load_checked(in_u, want, u0, "Input") || !load_checked(in_v, want, v0, "Input velocity")) return 1;
-    nls::Handle h(g, s.equation, s.integrator, krylov, dt, 0, 0, 0, 1, device);
-    h.set(NLS_FIELD_M, m.data(), n * 8);
-    h.set(NLS_FIELD_U, u0.data(), n * 8);
-    h.set(NLS_FIELD_V, v0.data(), n * 8);
-    std::vector<double> tu((size_t)ns * n), tv((size_t)ns * n);
-    std::copy(u0.begin(), u0.end(), tu.begin());
-    std::copy(v0.begin(), v0.end(), tv.begin());
-    for (uint32_t i = 1; i < nt;) {
-      uint32_t next = (i / freq + (i % freq ? 1 : 0)) * freq;
-      if (next >= nt) next = nt - 1;
-      h.step(dt, next - i + 1);
-      i = next + 1;
-      if (next % freq == 0 && next / freq < ns) {
-        h.get(NLS_FIELD_U, tu.data() + (size_t)(next / freq) * n, n * 8);
-        h.get(NLS_FIELD_V, tv.data() + (size_t)(next / freq) * n, n * 8);
-      }
-    }
-    h.sync();
-    write_npy(out_u, tu.data(), oshape);
-    write_npy(out_v, tv.data(), oshape);
+    if (!run_ensemble<double>(s, g, krylov, dt, sc, nt, ns, freq, want, m, in_u, in_v, out_u, out_v, devices, B)) return 1;
   }
   if (std::getenv("NLS_VERBOSE")) {
     const double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
-    std::cerr << s.name << " [" << s.ref << "]: " << (nt - 1) << " steps of " << n << " sites in " << sec
-              << " s (" << (double)n * (nt - 1) / sec << " site-steps/s incl. I/O staging), krylov m=" << krylov << "\n";
+    std::cerr << s.name << " [" << s.ref << "]: " << (nt - 1) << " steps of " << n << " sites" << (double)n * (nt - 1) / sec << " site-steps/s incl. I/O staging), krylov m=" << krylov << "\n";
   }
   return 0;
 }

@@ -151,3 +151,105 @@ def test_3d_device_driver_cli(drivers, oracle_lib, tmp_path):
     got = np.load(tmp_path / "traj.npy")
     assert got.shape == (ns, n, n, n)
     assert rel_l2(got, ref) < 1e-11
+
+
+# ---------------------------------------------------------------- ensemble files
+def test_ensemble_velocity_count_mismatch_returns_1(drivers, tmp_path):
+    """u0 and v0 must hold the same number of trajectories; checked before any CUDA call."""
+    np.save(tmp_path / "u0.npy", np.zeros((3, 16, 16)))
+    np.save(tmp_path / "v0.npy", np.zeros((2, 16, 16)))
+    r = run(drivers, "sg_single", 16, 16, 5.0, 5.0, tmp_path / "u0.npy", tmp_path / "v0.npy", tmp_path / "tu.npy",
+            tmp_path / "tv.npy", 0.01, 10, 5)
+    assert r.returncode == 1 and "different number of trajectories" in r.stderr
+
+
+def test_ensemble_bad_inner_shape_returns_1(drivers, tmp_path):
+    np.save(tmp_path / "u0.npy", np.zeros((3, 16, 15), dtype=np.complex128))
+    r = run(drivers, "nlse_ensemble_driver", 16, 16, 5.0, 5.0, tmp_path / "u0.npy", tmp_path / "o.npy", 0.01, 10, 5)
+    assert r.returncode == 1 and "dimensions mismatch" in r.stderr
+
+
+def test_ensemble_too_many_devices_returns_1(drivers, tmp_path):
+    np.save(tmp_path / "u0.npy", np.zeros((3, 16, 16), dtype=np.complex128))
+    r = run(drivers, "nlse_ensemble_driver", 16, 16, 5.0, 5.0, tmp_path / "u0.npy", tmp_path / "o.npy", 0.01, 10, 5,
+            "--devices", 64)
+    assert r.returncode == 1 and "CUDA device(s) are visible" in r.stderr and not (tmp_path / "o.npy").exists()
+
+
+def random_bumps(B, n, L, seed=7):
+    """B distinct smooth complex ICs: the sampler's random-IC ensemble at test size."""
+    rng = np.random.default_rng(seed)
+    x = np.linspace(-L, L, n)
+    X, Y = np.meshgrid(x, x)
+    out = np.empty((B, n, n), dtype=np.complex128)
+    for b in range(B):
+        cx, cy, kx, ky = rng.uniform(-2, 2, 4)
+        out[b] = np.exp(-((X - cx) ** 2 + (Y - cy) ** 2)) * np.exp(1j * (kx * X + ky * Y))
+    return out
+
+
+@pytest.mark.gpu
+def test_nlse_ensemble_cli(drivers, oracle_lib, tmp_path):
+    """One (B,ny,nx) file -> (B,ns,ny,nx): every trajectory equals the oracle's and, bit for bit,
+    what the single-trajectory driver writes for the same initial condition."""
+    B, n, L, T, nt, ns = 5, 40, 5.0, 0.04, 40, 8
+    u0 = random_bumps(B, n, L)
+    m = 1.0 + 0.1 * np.cos(np.arange(n * n) / 3.0)
+    np.save(tmp_path / "u0.npy", u0)
+    np.save(tmp_path / "m.npy", m.reshape(n, n))
+    run(drivers, "nlse_ensemble_driver", n, n, L, L, tmp_path / "u0.npy", tmp_path / "traj.npy", T, nt, ns,
+        tmp_path / "m.npy", check=True)
+    got = np.load(tmp_path / "traj.npy")
+    assert got.shape == (B, ns, n, n) and got.dtype == np.complex128
+    d = Desc.make(n, n, L=L, equation=EQ.NLSE_CUBIC, krylov_m=10)
+    for b in range(B):
+        ref, _ = oracle_trajectory(oracle_lib, d, u0[b], None, m, None, T, nt, ns)
+        assert np.array_equal(got[b, 0], u0[b])
+        assert rel_l2(got[b], ref) < 1e-11, b
+    for b in (0, B - 1):
+        np.save(tmp_path / "one.npy", u0[b])
+        run(drivers, "nlse_cubic", n, n, L, L, tmp_path / "one.npy", tmp_path / "one_traj.npy", T, nt, ns,
+            tmp_path / "m.npy", check=True)
+        assert rel_l2(got[b], np.load(tmp_path / "one_traj.npy")) < 1e-13
+    # default m == 1 for the ensemble alias (nlse_cubic keeps the reference's m == 0)
+    run(drivers, "nlse_ensemble_driver", n, n, L, L, tmp_path / "u0.npy", tmp_path / "t1.npy", T, nt, ns, check=True)
+    ref, _ = oracle_trajectory(oracle_lib, d, u0[1], None, np.ones(n * n), None, T, nt, ns)
+    assert rel_l2(np.load(tmp_path / "t1.npy")[1], ref) < 1e-11
+
+
+@pytest.mark.gpu
+def test_real_ensemble_cli(drivers, oracle_lib, tmp_path):
+    """Ensemble files through a real-valued driver (sine-Gordon Gautschi): u and velocity trajectories."""
+    B, n, L, T, nt, ns = 3, 40, 6.0, 0.2, 40, 8
+    base = 0.3 * ics.kink_2d(n, L)
+    u0 = np.stack([base * (1 + 0.2 * b) for b in range(B)])
+    v0 = 0.05 * np.cos(u0)
+    np.save(tmp_path / "u0.npy", u0)
+    np.save(tmp_path / "v0.npy", v0)
+    m = 1.0 + 0.2 * np.sin(np.arange(n * n) / 7.0)
+    np.save(tmp_path / "m.npy", m.reshape(n, n))
+    run(drivers, "sg_single", n, n, L, L, tmp_path / "u0.npy", tmp_path / "v0.npy", tmp_path / "tu.npy",
+        tmp_path / "tv.npy", T, nt, ns, tmp_path / "m.npy", check=True)
+    gu, gv = np.load(tmp_path / "tu.npy"), np.load(tmp_path / "tv.npy")
+    assert gu.shape == (B, ns, n, n) and gv.shape == (B, ns, n, n)
+    d = Desc.make(n, n, L=L, equation=EQ.SGE, integrator=INT.GAUTSCHI, krylov_m=10, dt=T / nt)
+    for b in range(B):
+        ru, rv = oracle_trajectory(oracle_lib, d, u0[b], v0[b], m, None, T, nt, ns)
+        assert rel_l2(gu[b], ru) < 1e-11
+        assert rel_l2(gv[b], rv) < 1e-8
+
+
+@pytest.mark.gpu
+def test_ensemble_cli_device_split(drivers, tmp_path):
+    """--devices G block-partitions the trajectories; the result does not depend on G."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    B, n, L, T, nt, ns = 5, 40, 5.0, 0.04, 40, 8
+    np.save(tmp_path / "u0.npy", random_bumps(B, n, L))
+    outs = []
+    for G in (1, 2):
+        run(drivers, "nlse_ensemble_driver", n, n, L, L, tmp_path / "u0.npy", tmp_path / f"t{G}.npy", T, nt, ns,
+            "--devices", G, check=True)
+        outs.append(np.load(tmp_path / f"t{G}.npy"))
+    assert rel_l2(outs[1], outs[0]) < 1e-13
