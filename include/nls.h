@@ -110,7 +110,14 @@ enum {
 /* reductions */
 enum {
   NLS_RED_MASS = 0,     /* sum |u|^2 * dx*dy[*dz] (per trajectory) */
-  NLS_RED_NONFINITE = 1 /* number of non-finite entries of u */
+  NLS_RED_NONFINITE = 1, /* number of non-finite entries of u */
+  /* the energy of the reference's drift scripts, per trajectory (not on z-slab handles):
+   *  complex state: finalized_scripts/compare_utils_complex_2d.py:134-151 -- centred differences
+   *    on the interior sites, sum(|u_x|^2+|u_y|^2[+|u_z|^2]) dV - 1/2 sum(|u|^4) dV (m_eff = 1);
+   *  real state: energy_sge.py:6-14 -- numpy.gradient differences (one-sided on the faces; the
+   *    script passes dx for array axis 0 and dy for axis 1, kept), v = (u-u_past)/dt,
+   *    1/2 dV sum 1/2(|grad u|^2 + v^2 + 2(1-cos u)).  3D uses (dz,dy,dx) for (z,y,x). */
+  NLS_RED_ENERGY = 2
 };
 
 typedef struct nls_desc {

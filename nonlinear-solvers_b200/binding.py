@@ -23,7 +23,7 @@ LAP = SimpleNamespace(UNIFORM=0, ANISO=1)
 REORTH = SimpleNamespace(FULL=0, NONE=1)
 FN = SimpleNamespace(EXP=0, SINC=1, COS_SQRT=2, SINC2_SQRT=3, ID_SQRT=4, SINC2_HALF=5, MOD_COSINE=6)
 FIELD = SimpleNamespace(U=0, U_PAST=1, V=2, M=3, C=4)
-RED = SimpleNamespace(MASS=0, NONFINITE=1)
+RED = SimpleNamespace(MASS=0, NONFINITE=1, ENERGY=2)
 FLAG_NO_GRAPH = 1
 FLAG_NO_PERSISTENT = 2
 FLAG_SEWI_HOST2D = 4

@@ -1029,7 +1029,22 @@ int nls_lanczos(nls_handle e, const void *in, void *hV, void *halpha, double *hb
 int nls_reduce(nls_handle e, int what, double *out) {
   if (!e || !out) return fail(NLS_ERR_ARG, "null argument");
   CU(cudaSetDevice(e->d.device));
-  if (e->cplx) {
+  if (what != NLS_RED_MASS && what != NLS_RED_NONFINITE && what != NLS_RED_ENERGY) return fail(NLS_ERR_ARG, "bad reduction");
+  if (what == NLS_RED_ENERGY) {
+    if (e->slab) return fail(NLS_ERR_STATE, "NLS_RED_ENERGY is not available on z-slab handles");
+    // x, y, z spacings as the scripts use them: compare_utils_complex_2d.py:136-137 (dx for x, dy for y);
+    // energy_sge.py:7-8 hands dx to array axis 0 (= y) and dy to axis 1 (= x) in 2D
+    const bool swap = !e->cplx && !e->g.dim3;
+    const double h0 = swap ? e->d.dy : e->d.dx, h1 = swap ? e->d.dx : e->d.dy, h2 = e->d.dz;
+    if (e->cplx)
+      LAUNCH(e, k_reduce_energy<double2>, e->grid(), e->g, (const double2 *)e->u[e->phase], (const double *)nullptr, 0.0,
+             h0, h1, h2, e->redout, e->rc);
+    else {
+      if (!(e->d.dt > 0)) return fail(NLS_ERR_STATE, "NLS_RED_ENERGY on a real state needs desc.dt > 0 (v = (u-u_past)/dt)");
+      LAUNCH(e, k_reduce_energy<double>, e->grid(), e->g, (const double *)cur_u(e), (const double *)cur_upast(e),
+             1.0 / e->d.dt, h0, h1, h2, e->redout, e->rc);
+    }
+  } else if (e->cplx) {
     const double2 *u = (const double2 *)e->u[e->phase];
     if (what == NLS_RED_MASS) LAUNCH(e, (k_reduce_state<double2, NLS_RED_MASS>), e->grid(), e->g, u, e->redout, e->rc);
     else LAUNCH(e, (k_reduce_state<double2, NLS_RED_NONFINITE>), e->grid(), e->g, u, e->redout, e->rc);
@@ -1041,8 +1056,9 @@ int nls_reduce(nls_handle e, int what, double *out) {
   CU(cudaGetLastError());
   CU(cudaMemcpyAsync(out, e->redout, (size_t)e->batch * 8, cudaMemcpyDeviceToHost, e->stream));
   CU(cudaStreamSynchronize(e->stream));
-  if (what == NLS_RED_MASS) {
-    const double cell = e->g.dim3 ? e->d.dx * e->d.dy * e->d.dz : e->d.dx * e->d.dy;
+  if (what == NLS_RED_MASS || what == NLS_RED_ENERGY) {
+    double cell = e->g.dim3 ? e->d.dx * e->d.dy * e->d.dz : e->d.dx * e->d.dy;
+    if (what == NLS_RED_ENERGY && !e->cplx) cell *= 0.5; // energy_sge.py:14
     for (int b = 0; b < e->batch; ++b) out[b] *= cell;
   }
   return NLS_OK;

@@ -800,4 +800,55 @@ k_reduce_state(Geom g, const S *__restrict__ u, double *dst, RedCtx rc) {
   grid_reduce<1>(acc, rc, dst + blockIdx.y);
 }
 
+// NLS_RED_ENERGY (nls.h): the drift scripts' energies in one pass over u (neighbours through L1/L2).
+//   complex: compare_utils_complex_2d.py:134-151, real: energy_sge.py:6-14 (numpy.gradient edges).
+// h0/h1/h2: spacing used along x / y / z.  upast, inv_dt: real states only.
+template <class S>
+__global__ void __launch_bounds__(kThreads)
+k_reduce_energy(Geom g, const S *__restrict__ u, const double *__restrict__ upast, double inv_dt, double h0,
+                double h1, double h2, double *dst, RedCtx rc) {
+  using T = Sc<S>;
+  constexpr bool CPLX = T::W == 2;
+  const S *ub = traj(u, g);
+  const double *up = CPLX ? nullptr : traj(upast, g);
+  const long long nx = g.nx, pl = (long long)g.nx * g.ny;
+  const int nz = g.dim3 ? g.nz_loc : 1;
+  double acc[1] = {0.0};
+  for (long long idx = (long long)blockIdx.x * kThreads + threadIdx.x; idx < g.n;
+       idx += (long long)gridDim.x * kThreads) {
+    const int i = (int)(idx % nx);
+    const long long r = idx / nx;
+    const int j = (int)(r % g.ny), k = (int)(r / g.ny);
+    const S c = ub[idx];
+    const double a2 = T::abs2(c);
+    if (CPLX) {
+      double e = -0.5 * a2 * a2;
+      if (i > 0 && i < g.nx - 1 && j > 0 && j < g.ny - 1 && (nz == 1 || (k > 0 && k < nz - 1))) {
+        e += T::abs2(T::sub(ub[idx + 1], ub[idx - 1])) / (4.0 * h0 * h0);
+        e += T::abs2(T::sub(ub[idx + nx], ub[idx - nx])) / (4.0 * h1 * h1);
+        if (nz > 1) e += T::abs2(T::sub(ub[idx + pl], ub[idx - pl])) / (4.0 * h2 * h2);
+      }
+      acc[0] += e;
+    } else {
+      // numpy.gradient: centred inside, first-order one-sided on the faces
+      const long long xm = i > 0 ? 1 : 0, xp = i < g.nx - 1 ? 1 : 0;
+      const long long ym = j > 0 ? nx : 0, yp = j < g.ny - 1 ? nx : 0;
+      const double gx = Sc<double>::from((const double *)&ub[idx + xp]) - Sc<double>::from((const double *)&ub[idx - xm]);
+      const double gy = Sc<double>::from((const double *)&ub[idx + yp]) - Sc<double>::from((const double *)&ub[idx - ym]);
+      const double dgx = gx / (h0 * (double)(xm + xp)), dgy = gy / (h1 * (double)((ym + yp) / nx));
+      double e = dgx * dgx + dgy * dgy;
+      if (nz > 1) {
+        const long long zm = k > 0 ? pl : 0, zp = k < nz - 1 ? pl : 0;
+        const double gz = Sc<double>::from((const double *)&ub[idx + zp]) - Sc<double>::from((const double *)&ub[idx - zm]);
+        const double dgz = gz / (h2 * (double)((zm + zp) / pl));
+        e += dgz * dgz;
+      }
+      const double uc = Sc<double>::from((const double *)&c);
+      const double v = (uc - up[idx]) * inv_dt;
+      acc[0] += 0.5 * (e + v * v + 2.0 * (1.0 - cos(uc)));
+    }
+  }
+  grid_reduce<1>(acc, rc, dst + blockIdx.y);
+}
+
 } // namespace nls

@@ -10,6 +10,9 @@
 //   the sign of the operator (+L or -L) and the hard-coded Krylov dimension.
 // Optional trailing flags (not in the reference; ignored by its launchers):
 //   --m K   Krylov dimension      --device D   first CUDA device ordinal
+//   --diag d.npy  also write [mass, energy] of every stored snapshot, shape (num_snapshots, 2)
+//                 [(B, num_snapshots, 2)]: NLS_RED_MASS / NLS_RED_ENERGY, the quantities of
+//                 compare_utils_complex_2d.py:134-151 and energy_sge.py:6-14, reduced on the device
 //   --devices G   spread an ensemble file over devices D..D+G-1 (one host thread each)
 // Ensemble input: when u0.npy [and v0.npy] carry one extra leading dimension
 // `(B, [nz,] ny, nx)`, all B trajectories advance in batched handles and the trajectory files
@@ -89,7 +92,7 @@ int usage(const Spec &s, const char *argv0) {
   if (is_nlse(s)) std::cerr << " input_u0.npy output_traj.npy";
   else std::cerr << " input_u0.npy input_v0.npy output_traj.npy output_vel.npy";
   std::cerr << " T nt num_snapshots" << (s.fields_req ? " input_m.npy input_c.npy" : " [input_m.npy]")
-            << " [--m K] [--device D] [--devices G]\n"
+            << " [--m K] [--device D] [--devices G] [--diag d.npy]\n"
             << "  (u0/v0 may be ensemble files of shape (B, ...): output is (B, num_snapshots, ...))\n";
   return 1;
 }
@@ -138,7 +141,8 @@ template <class T>
 bool run_ensemble(const Spec &s, const nls::Grid &g, uint32_t krylov, double dt, const double *sc, uint32_t nt,
                   uint32_t ns, uint32_t freq, const std::vector<uint64_t> &want, const std::vector<double> &m,
                   const std::string &in_u, const std::string &in_v, const std::string &out_u,
-                  const std::string &out_v, const std::vector<int> &devices, uint64_t &B_out) {
+                  const std::string &out_v, const std::vector<int> &devices, uint64_t &B_out,
+                  const std::string &diag_file) {
   const bool real = !in_v.empty();
   const size_t n = g.n();
   std::vector<T> u0, v0;
@@ -168,6 +172,9 @@ bool run_ensemble(const Spec &s, const nls::Grid &g, uint32_t krylov, double dt,
     if (real) std::copy(v0.begin() + b * n, v0.begin() + (b + 1) * n, tv.begin() + b * ns * n);
   }
 
+  // --diag: [mass, energy] of every stored snapshot, reduced on the device (nls_reduce)
+  const bool diag = !diag_file.empty();
+  std::vector<double> dg(diag ? (size_t)B * ns * 2 : 0);
   const size_t G = std::min<size_t>(devices.size(), B);
   std::vector<std::string> errors(G);
   auto worker = [&](size_t gi) {
@@ -178,6 +185,15 @@ bool run_ensemble(const Spec &s, const nls::Grid &g, uint32_t krylov, double dt,
       h.set(NLS_FIELD_U, u0.data() + b0 * n, nb * n * sizeof(T));
       if (real) h.set(NLS_FIELD_V, v0.data() + b0 * n, nb * n * sizeof(T));
       std::vector<T> su(nb > 1 ? nb * n : 0), sv(real && nb > 1 ? nb * n : 0);
+      std::vector<double> red(nb);
+      auto diagnose = [&](size_t snap) {
+        if (!diag) return;
+        for (int q = 0; q < 2; ++q) {
+          nls::check(nls_reduce(h.raw(), q == 0 ? NLS_RED_MASS : NLS_RED_ENERGY, red.data()), "nls_reduce");
+          for (uint64_t b = 0; b < nb; ++b) dg[((b0 + b) * ns + snap) * 2 + q] = red[b];
+        }
+      };
+      diagnose(0);
       // run up to the next snapshot step in one asynchronous call; same steps, same snapshots
       for (uint32_t i = 1; i < nt;) {
         uint32_t next = (i / freq + (i % freq ? 1 : 0)) * freq; // first multiple of freq >= i
@@ -186,6 +202,7 @@ bool run_ensemble(const Spec &s, const nls::Grid &g, uint32_t krylov, double dt,
         i = next + 1;
         if (next % freq != 0 || next / freq >= ns) continue;
         const size_t snap = next / freq;
+        diagnose(snap);
         if (nb == 1) { // straight into the trajectory
           h.get(NLS_FIELD_U, tu.data() + (b0 * ns + snap) * n, n * sizeof(T));
           if (real) h.get(NLS_FIELD_V, tv.data() + (b0 * ns + snap) * n, n * sizeof(T));
@@ -211,6 +228,11 @@ bool run_ensemble(const Spec &s, const nls::Grid &g, uint32_t krylov, double dt,
     if (!e.empty()) throw std::runtime_error(e); // CUDA/engine errors abort like the reference
   write_npy(out_u, tu.data(), oshape);
   if (real) write_npy(out_v, tv.data(), oshape);
+  if (diag) {
+    std::vector<uint64_t> dshape = {ns, 2};
+    if (Bu) dshape.insert(dshape.begin(), B);
+    write_npy(diag_file, dg.data(), dshape);
+  }
   return true;
 }
 
@@ -218,12 +240,14 @@ int run(const Spec &s, int argc, char **argv) {
   // strip the optional trailing flags
   uint32_t krylov = s.krylov;
   int device = 0, ndev = 1;
+  std::string diag_file;
   if (const char *e = std::getenv("NLS_KRYLOV_M")) krylov = (uint32_t)std::stoul(e);
   std::vector<char *> av(argv, argv + argc);
   for (size_t i = 1; i + 1 < av.size();) {
     const std::string a = av[i];
     if (a == "--m") { krylov = (uint32_t)std::stoul(av[i + 1]); av.erase(av.begin() + i, av.begin() + i + 2); }
     else if (a == "--device") { device = std::stoi(av[i + 1]); av.erase(av.begin() + i, av.begin() + i + 2); }
+    else if (a == "--diag") { diag_file = av[i + 1]; av.erase(av.begin() + i, av.begin() + i + 2); }
     else if (a == "--devices") { ndev = std::stoi(av[i + 1]); av.erase(av.begin() + i, av.begin() + i + 2); }
     else ++i;
   }
@@ -289,13 +313,15 @@ int run(const Spec &s, int argc, char **argv) {
 
   const auto t0 = std::chrono::steady_clock::now();
   if (is_nlse(s)) {
-    if (!run_ensemble<cplx>(s, g, krylov, dt, sc, nt, ns, freq, want, m, in_u, "", out_u, "", devices, B)) return 1;
+    if (!run_ensemble<cplx>(s, g, krylov, dt, sc, nt, ns, freq, want, m, in_u, "", out_u, "", devices, B, diag_file)) return 1;
   } else {
-    if (!run_ensemble<double>(s, g, krylov, dt, sc, nt, ns, freq, want, m, in_u, in_v, out_u, out_v, devices, B)) return 1;
+    if (!run_ensemble<double>(s, g, krylov, dt, sc, nt, ns, freq, want, m, in_u, in_v, out_u, out_v, devices, B, diag_file)) return 1;
   }
   if (std::getenv("NLS_VERBOSE")) {
     const double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
-    std::cerr << s.name << " [" << s.ref << "]: " << (nt - 1) << " steps of " << n << " sites" << (double)n * (nt - 1) / sec << " site-steps/s incl. I/O staging), krylov m=" << krylov << "\n";
+    std::cerr << s.name << " [" << s.ref << "]: " << (nt - 1) << " steps of " << n << " sites x " << B
+              << " trajectories in " << sec << " s (" << (double)n * B * (nt - 1) / sec
+              << " site-steps/s incl. file I/O and staging), krylov m=" << krylov << "\n";
   }
   return 0;
 }

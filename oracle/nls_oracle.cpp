@@ -728,8 +728,57 @@ int orc_lanczos(orc_handle e, const void *in, void *V, void *alpha, double *beta
   return NLS_OK;
 }
 
+// numpy.gradient along one axis (first-order one-sided at both ends, centred inside), times 1:
+// returns (f[p+] - f[p-]) / (h * #steps)                      energy_sge.py:7-8
+static double np_gradient(const double *f, int64_t pos, int64_t len, int64_t stride, double h) {
+  const int64_t lo = pos > 0 ? 1 : 0, hi = pos < len - 1 ? 1 : 0;
+  return (f[hi * stride] - f[-lo * stride]) / (h * (double)(lo + hi));
+}
+
 int orc_reduce(orc_handle e, int what, double *out) {
   const double cell = e->d.nz == 1 ? e->d.dx * e->d.dy : e->d.dx * e->d.dy * e->d.dz;
+  const int64_t nx = e->d.nx, ny = e->d.ny, nz = e->d.nz, pl = nx * ny;
+  if (what == NLS_RED_ENERGY) {
+    if (!e->cplx_state && !(e->d.dt > 0)) return NLS_ERR_STATE;
+    for (uint32_t b = 0; b < e->d.batch; ++b) {
+      double s = 0.0;
+      if (e->cplx_state) {
+        // finalized_scripts/compare_utils_complex_2d.py:134-151: centred differences on the interior
+        // sites only (ux: x neighbours / 2dx, uy: y neighbours / 2dy), potential -1/2 |u|^4, m_eff = 1
+        const cplx *u = &e->uc[(size_t)b * e->n];
+        for (int64_t k = 0; k < nz; ++k)
+          for (int64_t j = 0; j < ny; ++j)
+            for (int64_t i = 0; i < nx; ++i) {
+              const int64_t p = (k * ny + j) * nx + i;
+              const double a2 = abs2_s(u[p]);
+              s += -0.5 * a2 * a2;
+              if (i == 0 || i == nx - 1 || j == 0 || j == ny - 1 || (nz > 1 && (k == 0 || k == nz - 1))) continue;
+              s += abs2_s(u[p + 1] - u[p - 1]) / (4.0 * e->d.dx * e->d.dx);
+              s += abs2_s(u[p + nx] - u[p - nx]) / (4.0 * e->d.dy * e->d.dy);
+              if (nz > 1) s += abs2_s(u[p + pl] - u[p - pl]) / (4.0 * e->d.dz * e->d.dz);
+            }
+        out[b] = s * cell;
+      } else {
+        // energy_sge.py:6-14: np.gradient(u, dx, axis=0), np.gradient(u, dy, axis=1) on the (ny,nx)
+        // array -- dx goes with the y index and dy with the x index (kept); 3D: (dz,dy,dx) for (z,y,x)
+        const double *u = &e->ur[(size_t)b * e->n], *up = &e->ur_past[(size_t)b * e->n];
+        const double hx = nz == 1 ? e->d.dy : e->d.dx, hy = nz == 1 ? e->d.dx : e->d.dy;
+        for (int64_t k = 0; k < nz; ++k)
+          for (int64_t j = 0; j < ny; ++j)
+            for (int64_t i = 0; i < nx; ++i) {
+              const int64_t p = (k * ny + j) * nx + i;
+              const double gx = np_gradient(u + p, i, nx, 1, hx), gy = np_gradient(u + p, j, ny, nx, hy);
+              double g2 = gx * gx + gy * gy;
+              if (nz > 1) { const double gz = np_gradient(u + p, k, nz, pl, e->d.dz); g2 += gz * gz; }
+              const double v = (u[p] - up[p]) / e->d.dt; // sg_single_driver.cpp:113
+              s += 0.5 * (g2 + v * v + 2.0 * (1.0 - std::cos(u[p])));
+            }
+        out[b] = 0.5 * cell * s;
+      }
+    }
+    return NLS_OK;
+  }
+  if (what != NLS_RED_MASS && what != NLS_RED_NONFINITE) return NLS_ERR_ARG;
   for (uint32_t b = 0; b < e->d.batch; ++b) {
     double s = 0.0;
     for (int64_t i = 0; i < e->n; ++i) {

@@ -253,3 +253,32 @@ def test_ensemble_cli_device_split(drivers, tmp_path):
             "--devices", G, check=True)
         outs.append(np.load(tmp_path / f"t{G}.npy"))
     assert rel_l2(outs[1], outs[0]) < 1e-13
+
+
+@pytest.mark.gpu
+def test_cli_diagnostics_file(drivers, tmp_path):
+    """--diag: mass and energy of every stored snapshot equal the reference scripts' formulas applied
+    to the trajectory files (compare_utils_complex_2d.py:134-151, energy_sge.py:6-14)."""
+    from test_energy import nlse_hamiltonian_script, sge_energy_script
+    B, n, L, T, nt, ns = 3, 40, 5.0, 0.04, 40, 8
+    dx = 2 * L / (n - 1)
+    np.save(tmp_path / "u0.npy", random_bumps(B, n, L))
+    run(drivers, "nlse_ensemble_driver", n, n, L, L, tmp_path / "u0.npy", tmp_path / "t.npy", T, nt, ns,
+        "--diag", tmp_path / "d.npy", check=True)
+    tr, dg = np.load(tmp_path / "t.npy"), np.load(tmp_path / "d.npy")
+    assert dg.shape == (B, ns, 2)
+    for b in range(B):
+        for s in range(ns):
+            assert dg[b, s, 0] == pytest.approx(np.sum(np.abs(tr[b, s]) ** 2) * dx * dx, rel=1e-12)
+            assert dg[b, s, 1] == pytest.approx(nlse_hamiltonian_script(tr[b, s], dx, dx), rel=1e-11)
+    assert np.max(np.abs(dg[:, :, 0] / dg[:, :1, 0] - 1)) < 1e-6  # SS2 conserves mass up to the BC copy
+
+    u0 = 0.3 * ics.kink_2d(n, L)
+    np.save(tmp_path / "ru.npy", u0)
+    np.save(tmp_path / "rv.npy", 0.05 * np.cos(u0))
+    run(drivers, "sg_single", n, n, L, L, tmp_path / "ru.npy", tmp_path / "rv.npy", tmp_path / "tu.npy",
+        tmp_path / "tv.npy", 0.2, 40, 8, "--diag", tmp_path / "rd.npy", check=True)
+    tu, tv, rd = np.load(tmp_path / "tu.npy"), np.load(tmp_path / "tv.npy"), np.load(tmp_path / "rd.npy")
+    assert rd.shape == (8, 2)
+    for s in range(8):
+        assert rd[s, 1] == pytest.approx(sge_energy_script(tu[s], tv[s], dx, dx), rel=1e-9)
