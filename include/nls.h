@@ -190,6 +190,17 @@ int nls_lanczos(nls_handle h, const void *host_in, void *host_V, void *host_alph
 /* out[batch] */
 int nls_reduce(nls_handle h, int what, double *out);
 
+/* Snapshot egress with on-device downsampling: the field (NLS_FIELD_U, or NLS_FIELD_V
+ * for real equations) is resampled on the device to tnx x tny [x tnz] points per trajectory with the
+ * launcher's `downsample_interpolation` (finalized_scripts/downsampling.py:68-104, 3D :215-258:
+ * scipy RegularGridInterpolator(method="linear") from linspace(-L,L,n) onto linspace(-L,L,t) per axis,
+ * i.e. multilinear interpolation at index position k*(n-1)/(t-1)), and only the small result crosses
+ * PCIe.  host_dst: [batch][tnz][tny][tnx] scalars, bytes must match; tnz must be 1 for 2D handles;
+ * every target extent must be >= 2 (or equal to 1 together with the source extent).  Not on z-slab
+ * handles. */
+int nls_get_field_resampled(nls_handle h, int field, uint32_t tnx, uint32_t tny, uint32_t tnz, void *host_dst,
+                            size_t bytes);
+
 /* number of kernel launches issued (directly or through graph replays) since creation */
 uint64_t nls_launch_count(nls_handle h);
 /* how many of them were TMA-staged Lanczos passes (nls_tma.cuh) */

@@ -112,6 +112,7 @@ _SIGS = {
     "nls_destroy": (C.c_int, [_vp]),
     "nls_set_field": (C.c_int, [_vp, C.c_int, _vp, _sz]),
     "nls_get_field": (C.c_int, [_vp, C.c_int, _vp, _sz]),
+    "nls_get_field_resampled": (C.c_int, [_vp, C.c_int, C.c_uint32, C.c_uint32, C.c_uint32, _vp, _sz]),
     "nls_set_field_dev": (C.c_int, [_vp, C.c_int, _vp, _sz]),
     "nls_get_field_dev": (C.c_int, [_vp, C.c_int, _vp, _sz]),
     "nls_step": (C.c_int, [_vp, C.c_double, C.c_uint32]),
@@ -189,6 +190,13 @@ class Engine:
     def get(self, field=FIELD.U):
         out = np.empty(self._state_shape(), dtype=self.desc.dtype)
         self._check(self.lib.nls_get_field(self.h, field, _ptr(out), out.nbytes))
+        return out
+
+    def get_resampled(self, tnx, tny, tnz=1, field=FIELD.U):
+        """field resampled on the device to (batch, [tnz,] tny, tnx) (downsampling.py:68-104)."""
+        shape = (self.desc.batch, tnz, tny, tnx) if self.desc.nz > 1 else (self.desc.batch, tny, tnx)
+        out = np.empty(shape, dtype=self.desc.dtype)
+        self._check(self.lib.nls_get_field_resampled(self.h, field, tnx, tny, tnz, _ptr(out), out.nbytes))
         return out
 
     def get_into(self, field, out):

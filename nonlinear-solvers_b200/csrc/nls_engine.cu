@@ -51,6 +51,8 @@ struct nls_engine {
   // device memory (all n-vectors: [batch][stride] scalars)
   void *V = nullptr;     // m-1 columns
   void *wbuf[2] = {nullptr, nullptr};
+  void *rs = nullptr;   // dense output of nls_get_field_resampled (allocated on first use)
+  size_t rs_bytes = 0;
   void *w0 = nullptr;    // start vector (rho / g / matfunc input)
   void *u[3] = {nullptr, nullptr, nullptr};
   void *acc = nullptr;   // Gautschi accumulator
@@ -691,7 +693,7 @@ int nls_destroy(nls_handle e) {
   }
   void *ptrs[] = {e->V, e->wbuf[0], e->wbuf[1], e->w0, e->u[0], e->u[1], e->u[2], e->acc, e->mf, e->cf,
                   e->scalA, e->scalB, e->coef, e->redout, e->rc.partials, e->rc.tickets, e->status,
-                  e->pk_part, e->pk_bar, e->arena, e->slab_dev, e->slab_scratch};
+                  e->pk_part, e->pk_bar, e->arena, e->slab_dev, e->slab_scratch, e->rs};
   for (void *p : ptrs)
     if (p) cudaFree(p);
   if (e->stream) cudaStreamDestroy(e->stream);
@@ -885,6 +887,42 @@ static int get_field_impl(nls_handle e, int field, void *dst, size_t bytes, bool
   default: return fail(NLS_ERR_ARG, "bad field");
   }
   if (rc) return rc;
+  return check_status(e);
+}
+
+int nls_get_field_resampled(nls_handle e, int field, uint32_t tnx, uint32_t tny, uint32_t tnz, void *dst, size_t bytes) {
+  if (!e || !dst) return fail(NLS_ERR_ARG, "null argument");
+  if (e->slab) return fail(NLS_ERR_STATE, "nls_get_field_resampled is not available on z-slab handles");
+  if (field != NLS_FIELD_U && field != NLS_FIELD_V) return fail(NLS_ERR_ARG, "resampled: NLS_FIELD_U or NLS_FIELD_V");
+  if (field == NLS_FIELD_V && e->cplx) return fail(NLS_ERR_STATE, "V: real equations only");
+  if (field == NLS_FIELD_V && !(e->d.dt > 0)) return fail(NLS_ERR_STATE, "V needs desc.dt > 0");
+  const uint32_t nz = e->g.dim3 ? (uint32_t)e->g.nz_loc : 1u;
+  if (tnx < 2 || tny < 2 || (nz == 1 ? tnz != 1 : tnz < 2) || tnx > (1u << 20) || tny > (1u << 20) || tnz > (1u << 20))
+    return fail(NLS_ERR_ARG, "resampled: target extents must be >= 2 (tnz == 1 for 2D handles)");
+  const size_t tot = (size_t)tnx * tny * tnz, need = tot * e->batch * e->esz;
+  if (bytes != need) return fail(NLS_ERR_ARG, "resampled: size mismatch");
+  CU(cudaSetDevice(e->d.device));
+  if (e->rs_bytes < need) {
+    if (e->rs) CU(cudaFree(e->rs));
+    e->rs = nullptr; e->rs_bytes = 0;
+    CU(cudaMalloc(&e->rs, need));
+    e->rs_bytes = need;
+  }
+  const unsigned gx = (unsigned)std::min<size_t>((tot + kThreads - 1) / kThreads, (size_t)e->nsm * 8);
+  const dim3 gr(gx, (unsigned)e->batch);
+  if (e->cplx)
+    k_resample<double2, false><<<gr, kThreads, 0, e->stream>>>(e->g, (const double2 *)e->u[e->phase], nullptr, 0.0,
+                                                               (int)tnx, (int)tny, (int)tnz, (double2 *)e->rs);
+  else if (field == NLS_FIELD_U)
+    k_resample<double, false><<<gr, kThreads, 0, e->stream>>>(e->g, (const double *)cur_u(e), nullptr, 0.0, (int)tnx,
+                                                              (int)tny, (int)tnz, (double *)e->rs);
+  else
+    k_resample<double, true><<<gr, kThreads, 0, e->stream>>>(e->g, (const double *)cur_u(e), (const double *)cur_upast(e),
+                                                             1.0 / e->d.dt, (int)tnx, (int)tny, (int)tnz, (double *)e->rs);
+  e->count();
+  CU(cudaGetLastError());
+  CU(cudaMemcpyAsync(dst, e->rs, need, cudaMemcpyDeviceToHost, e->stream));
+  CU(cudaStreamSynchronize(e->stream));
   return check_status(e);
 }
 

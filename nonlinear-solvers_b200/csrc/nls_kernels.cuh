@@ -851,4 +851,47 @@ k_reduce_energy(Geom g, const S *__restrict__ u, const double *__restrict__ upas
   grid_reduce<1>(acc, rc, dst + blockIdx.y);
 }
 
+// Multilinear resampling of a state onto a coarser linspace grid (nls_get_field_resampled):
+// downsampling.py:68-104 / :215-258.  One thread per target point; out is dense [batch][tz][ty][tx].
+// VEL: sample v = (u - u_past)/dt instead of u (real states).
+__device__ __forceinline__ void resample_axis(int a, int t, int n, int &i0, double &f) {
+  const double pos = t > 1 ? (double)a * (double)(n - 1) / (double)(t - 1) : 0.0;
+  i0 = min((int)pos, n - 2);
+  i0 = max(i0, 0);
+  f = n > 1 ? pos - (double)i0 : 0.0;
+}
+template <class S, bool VEL>
+__global__ void __launch_bounds__(kThreads)
+k_resample(Geom g, const S *__restrict__ u, const double *__restrict__ upast, double inv_dt, int tx, int ty,
+           int tz, S *__restrict__ out) {
+  using T = Sc<S>;
+  const S *ub = traj(u, g);
+  const double *up = VEL ? traj(upast, g) : nullptr;
+  const int nz = g.dim3 ? g.nz_loc : 1;
+  const long long nx = g.nx, pl = (long long)g.nx * g.ny, tot = (long long)tx * ty * tz;
+  S *ob = out + (size_t)blockIdx.y * tot;
+  auto at = [&](long long p) -> S {
+    if (VEL) return T::mulr(T::sub(ub[p], T::from((const double *)&up[p])), inv_dt);
+    return ub[p];
+  };
+  for (long long o = (long long)blockIdx.x * kThreads + threadIdx.x; o < tot; o += (long long)gridDim.x * kThreads) {
+    const int a = (int)(o % tx), b = (int)((o / tx) % ty), c = (int)(o / ((long long)tx * ty));
+    int i, j, k;
+    double fx, fy, fz;
+    resample_axis(a, tx, g.nx, i, fx);
+    resample_axis(b, ty, g.ny, j, fy);
+    resample_axis(c, tz, nz, k, fz);
+    const long long dxs = g.nx > 1 ? 1 : 0, dys = g.ny > 1 ? nx : 0, dzs = nz > 1 ? pl : 0;
+    const long long p = ((long long)k * g.ny + j) * nx + i;
+    auto plane = [&](long long q) -> S {
+      const S r0 = T::add(T::mulr(at(q), 1.0 - fx), T::mulr(at(q + dxs), fx));
+      const S r1 = T::add(T::mulr(at(q + dys), 1.0 - fx), T::mulr(at(q + dys + dxs), fx));
+      return T::add(T::mulr(r0, 1.0 - fy), T::mulr(r1, fy));
+    };
+    S v = plane(p);
+    if (nz > 1) v = T::add(T::mulr(v, 1.0 - fz), T::mulr(plane(p + dzs), fz));
+    ob[o] = v;
+  }
+}
+
 } // namespace nls

@@ -13,6 +13,9 @@
 //   --diag d.npy  also write [mass, energy] of every stored snapshot, shape (num_snapshots, 2)
 //                 [(B, num_snapshots, 2)]: NLS_RED_MASS / NLS_RED_ENERGY, the quantities of
 //                 compare_utils_complex_2d.py:134-151 and energy_sge.py:6-14, reduced on the device
+//   --downsample N  store every snapshot resampled on the device to N x N [x N] points with the launcher's
+//                 downsample_interpolation (finalized_scripts/downsampling.py:68-104, :215-258); the
+//                 trajectory files then have shape ([B,] num_snapshots, N, N[, N])
 //   --devices G   spread an ensemble file over devices D..D+G-1 (one host thread each)
 // Ensemble input: when u0.npy [and v0.npy] carry one extra leading dimension
 // `(B, [nz,] ny, nx)`, all B trajectories advance in batched handles and the trajectory files
@@ -92,7 +95,7 @@ int usage(const Spec &s, const char *argv0) {
   if (is_nlse(s)) std::cerr << " input_u0.npy output_traj.npy";
   else std::cerr << " input_u0.npy input_v0.npy output_traj.npy output_vel.npy";
   std::cerr << " T nt num_snapshots" << (s.fields_req ? " input_m.npy input_c.npy" : " [input_m.npy]")
-            << " [--m K] [--device D] [--devices G] [--diag d.npy]\n"
+            << " [--m K] [--device D] [--devices G] [--diag d.npy] [--downsample N]\n"
             << "  (u0/v0 may be ensemble files of shape (B, ...): output is (B, num_snapshots, ...))\n";
   return 1;
 }
@@ -142,7 +145,7 @@ bool run_ensemble(const Spec &s, const nls::Grid &g, uint32_t krylov, double dt,
                   uint32_t ns, uint32_t freq, const std::vector<uint64_t> &want, const std::vector<double> &m,
                   const std::string &in_u, const std::string &in_v, const std::string &out_u,
                   const std::string &out_v, const std::vector<int> &devices, uint64_t &B_out,
-                  const std::string &diag_file) {
+                  const std::string &diag_file, uint32_t ds) {
   const bool real = !in_v.empty();
   const size_t n = g.n();
   std::vector<T> u0, v0;
@@ -163,14 +166,20 @@ bool run_ensemble(const Spec &s, const nls::Grid &g, uint32_t krylov, double dt,
       return false;
     }
   }
+  // --downsample N: every stored snapshot (snapshot 0 included) is resampled on the device to N^dim
+  // points (nls_get_field_resampled = downsampling.py:68-104) and only that crosses PCIe / hits the file
+  const uint32_t dtz = g.nz > 1 ? ds : 1;
+  const size_t no = ds ? (size_t)ds * ds * dtz : n; // scalars per stored snapshot
   std::vector<uint64_t> oshape = want;
+  if (ds) oshape.assign(want.size(), ds);
   oshape.insert(oshape.begin(), ns);
   if (Bu) oshape.insert(oshape.begin(), B);
-  std::vector<T> tu((size_t)B * ns * n), tv(real ? (size_t)B * ns * n : 0);
-  for (uint64_t b = 0; b < B; ++b) {
-    std::copy(u0.begin() + b * n, u0.begin() + (b + 1) * n, tu.begin() + b * ns * n);
-    if (real) std::copy(v0.begin() + b * n, v0.begin() + (b + 1) * n, tv.begin() + b * ns * n);
-  }
+  std::vector<T> tu((size_t)B * ns * no), tv(real ? (size_t)B * ns * no : 0);
+  if (!ds)
+    for (uint64_t b = 0; b < B; ++b) {
+      std::copy(u0.begin() + b * n, u0.begin() + (b + 1) * n, tu.begin() + b * ns * n);
+      if (real) std::copy(v0.begin() + b * n, v0.begin() + (b + 1) * n, tv.begin() + b * ns * n);
+    }
 
   // --diag: [mass, energy] of every stored snapshot, reduced on the device (nls_reduce)
   const bool diag = !diag_file.empty();
@@ -184,7 +193,7 @@ bool run_ensemble(const Spec &s, const nls::Grid &g, uint32_t krylov, double dt,
       h.set(NLS_FIELD_M, m.data(), n * 8);
       h.set(NLS_FIELD_U, u0.data() + b0 * n, nb * n * sizeof(T));
       if (real) h.set(NLS_FIELD_V, v0.data() + b0 * n, nb * n * sizeof(T));
-      std::vector<T> su(nb > 1 ? nb * n : 0), sv(real && nb > 1 ? nb * n : 0);
+      std::vector<T> su(nb > 1 || ds ? nb * no : 0), sv(real && (nb > 1 || ds) ? nb * no : 0);
       std::vector<double> red(nb);
       auto diagnose = [&](size_t snap) {
         if (!diag) return;
@@ -193,27 +202,35 @@ bool run_ensemble(const Spec &s, const nls::Grid &g, uint32_t krylov, double dt,
           for (uint64_t b = 0; b < nb; ++b) dg[((b0 + b) * ns + snap) * 2 + q] = red[b];
         }
       };
-      diagnose(0);
+      auto store = [&](size_t snap) {
+        diagnose(snap);
+        if (!ds && nb == 1) { // straight into the trajectory
+          h.get(NLS_FIELD_U, tu.data() + (b0 * ns + snap) * n, n * sizeof(T));
+          if (real) h.get(NLS_FIELD_V, tv.data() + (b0 * ns + snap) * n, n * sizeof(T));
+          return;
+        }
+        if (ds) {
+          nls::check(nls_get_field_resampled(h.raw(), NLS_FIELD_U, ds, ds, dtz, su.data(), nb * no * sizeof(T)), "nls_get_field_resampled");
+          if (real)
+            nls::check(nls_get_field_resampled(h.raw(), NLS_FIELD_V, ds, ds, dtz, sv.data(), nb * no * sizeof(T)), "nls_get_field_resampled");
+        } else {
+          h.get(NLS_FIELD_U, su.data(), nb * n * sizeof(T));
+          if (real) h.get(NLS_FIELD_V, sv.data(), nb * n * sizeof(T));
+        }
+        for (uint64_t b = 0; b < nb; ++b) {
+          std::copy(su.begin() + b * no, su.begin() + (b + 1) * no, tu.begin() + ((b0 + b) * ns + snap) * no);
+          if (real) std::copy(sv.begin() + b * no, sv.begin() + (b + 1) * no, tv.begin() + ((b0 + b) * ns + snap) * no);
+        }
+      };
+      if (ds) store(0);
+      else diagnose(0);
       // run up to the next snapshot step in one asynchronous call; same steps, same snapshots
       for (uint32_t i = 1; i < nt;) {
         uint32_t next = (i / freq + (i % freq ? 1 : 0)) * freq; // first multiple of freq >= i
         if (next >= nt) next = nt - 1;
         h.step(dt, next - i + 1);
         i = next + 1;
-        if (next % freq != 0 || next / freq >= ns) continue;
-        const size_t snap = next / freq;
-        diagnose(snap);
-        if (nb == 1) { // straight into the trajectory
-          h.get(NLS_FIELD_U, tu.data() + (b0 * ns + snap) * n, n * sizeof(T));
-          if (real) h.get(NLS_FIELD_V, tv.data() + (b0 * ns + snap) * n, n * sizeof(T));
-          continue;
-        }
-        h.get(NLS_FIELD_U, su.data(), nb * n * sizeof(T));
-        if (real) h.get(NLS_FIELD_V, sv.data(), nb * n * sizeof(T));
-        for (uint64_t b = 0; b < nb; ++b) {
-          std::copy(su.begin() + b * n, su.begin() + (b + 1) * n, tu.begin() + ((b0 + b) * ns + snap) * n);
-          if (real) std::copy(sv.begin() + b * n, sv.begin() + (b + 1) * n, tv.begin() + ((b0 + b) * ns + snap) * n);
-        }
+        if (next % freq == 0 && next / freq < ns) store(next / freq);
       }
       h.sync();
     } catch (const std::exception &e) { errors[gi] = e.what(); }
@@ -241,12 +258,14 @@ int run(const Spec &s, int argc, char **argv) {
   uint32_t krylov = s.krylov;
   int device = 0, ndev = 1;
   std::string diag_file;
+  uint32_t ds = 0;
   if (const char *e = std::getenv("NLS_KRYLOV_M")) krylov = (uint32_t)std::stoul(e);
   std::vector<char *> av(argv, argv + argc);
   for (size_t i = 1; i + 1 < av.size();) {
     const std::string a = av[i];
     if (a == "--m") { krylov = (uint32_t)std::stoul(av[i + 1]); av.erase(av.begin() + i, av.begin() + i + 2); }
     else if (a == "--device") { device = std::stoi(av[i + 1]); av.erase(av.begin() + i, av.begin() + i + 2); }
+    else if (a == "--downsample") { ds = (uint32_t)std::stoul(av[i + 1]); av.erase(av.begin() + i, av.begin() + i + 2); }
     else if (a == "--diag") { diag_file = av[i + 1]; av.erase(av.begin() + i, av.begin() + i + 2); }
     else if (a == "--devices") { ndev = std::stoi(av[i + 1]); av.erase(av.begin() + i, av.begin() + i + 2); }
     else ++i;
@@ -285,6 +304,10 @@ int run(const Spec &s, int argc, char **argv) {
   const uint32_t freq = nt / ns;
   const size_t n = g.n();
   std::vector<uint64_t> want = s.dim == 3 ? std::vector<uint64_t>{nz, ny, nx} : std::vector<uint64_t>{ny, nx};
+  if (ds == 1) {
+    std::cerr << "Error: --downsample needs N >= 2\n";
+    return 1;
+  }
   if (ndev < 1 || device < 0) {
     std::cerr << "Error: need --device >= 0 and --devices >= 1\n";
     return 1;
@@ -313,9 +336,9 @@ int run(const Spec &s, int argc, char **argv) {
 
   const auto t0 = std::chrono::steady_clock::now();
   if (is_nlse(s)) {
-    if (!run_ensemble<cplx>(s, g, krylov, dt, sc, nt, ns, freq, want, m, in_u, "", out_u, "", devices, B, diag_file)) return 1;
+    if (!run_ensemble<cplx>(s, g, krylov, dt, sc, nt, ns, freq, want, m, in_u, "", out_u, "", devices, B, diag_file, ds)) return 1;
   } else {
-    if (!run_ensemble<double>(s, g, krylov, dt, sc, nt, ns, freq, want, m, in_u, in_v, out_u, out_v, devices, B, diag_file)) return 1;
+    if (!run_ensemble<double>(s, g, krylov, dt, sc, nt, ns, freq, want, m, in_u, in_v, out_u, out_v, devices, B, diag_file, ds)) return 1;
   }
   if (std::getenv("NLS_VERBOSE")) {
     const double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();

@@ -795,6 +795,58 @@ int orc_reduce(orc_handle e, int what, double *out) {
   return NLS_OK;
 }
 
+} // extern "C"
+
+// finalized_scripts/downsampling.py:68-104 (2D) and :215-258 (3D): RegularGridInterpolator(method="linear")
+// from linspace(-L,L,n) onto linspace(-L,L,t) along every axis = multilinear interpolation at index position
+// k*(n-1)/(t-1).  dst: [batch][tnz][tny][tnx].  field: NLS_FIELD_U, or NLS_FIELD_V (real states).
+template <class T, class F>
+static void resample_state(const orc_engine *e, F at, uint32_t tx, uint32_t ty, uint32_t tz, T *dst) {
+  const int64_t nx = e->d.nx, ny = e->d.ny, nz = e->d.nz;
+  auto axis = [](int64_t a, int64_t t, int64_t n, int64_t &i0, double &f) {
+    const double pos = t > 1 ? (double)a * (double)(n - 1) / (double)(t - 1) : 0.0;
+    i0 = std::max<int64_t>(0, std::min<int64_t>((int64_t)pos, n - 2));
+    f = n > 1 ? pos - (double)i0 : 0.0;
+  };
+  for (uint32_t b = 0; b < e->d.batch; ++b)
+    for (int64_t c = 0; c < tz; ++c)
+      for (int64_t bb = 0; bb < ty; ++bb)
+        for (int64_t a = 0; a < tx; ++a) {
+          int64_t i, j, k;
+          double fx, fy, fz;
+          axis(a, tx, nx, i, fx); axis(bb, ty, ny, j, fy); axis(c, tz, nz, k, fz);
+          const int64_t dxs = nx > 1 ? 1 : 0, dys = ny > 1 ? nx : 0, dzs = nz > 1 ? nx * ny : 0;
+          const int64_t p = (int64_t)b * e->n + (k * ny + j) * nx + i;
+          auto plane = [&](int64_t q) {
+            const T r0 = at(q) * (1.0 - fx) + at(q + dxs) * fx;
+            const T r1 = at(q + dys) * (1.0 - fx) + at(q + dys + dxs) * fx;
+            return r0 * (1.0 - fy) + r1 * fy;
+          };
+          T v = plane(p);
+          if (nz > 1) v = v * (1.0 - fz) + plane(p + dzs) * fz;
+          dst[(((size_t)b * tz + c) * ty + bb) * tx + a] = v;
+        }
+}
+
+extern "C" {
+
+int orc_get_field_resampled(orc_handle e, int field, uint32_t tx, uint32_t ty, uint32_t tz, void *dst, size_t bytes) {
+  if (field != NLS_FIELD_U && field != NLS_FIELD_V) return NLS_ERR_ARG;
+  if (tx < 2 || ty < 2 || (e->d.nz == 1 ? tz != 1 : tz < 2)) return NLS_ERR_ARG;
+  if (bytes != (size_t)tx * ty * tz * e->d.batch * (e->cplx_state ? 16 : 8)) return NLS_ERR_ARG;
+  if (e->cplx_state) {
+    if (field != NLS_FIELD_U) return NLS_ERR_STATE;
+    resample_state<cplx>(e, [&](int64_t q) { return e->uc[q]; }, tx, ty, tz, (cplx *)dst);
+  } else if (field == NLS_FIELD_U) {
+    resample_state<double>(e, [&](int64_t q) { return e->ur[q]; }, tx, ty, tz, (double *)dst);
+  } else {
+    if (!(e->d.dt > 0)) return NLS_ERR_STATE;
+    const double inv_dt = 1.0 / e->d.dt;
+    resample_state<double>(e, [&](int64_t q) { return (e->ur[q] - e->ur_past[q]) * inv_dt; }, tx, ty, tz, (double *)dst);
+  }
+  return NLS_OK;
+}
+
 int orc_csr(orc_handle e, int64_t *nnz, int64_t *rowptr, int32_t *col, double *val) {
   e->build();
   if (nnz) *nnz = (int64_t)e->A.val.size();

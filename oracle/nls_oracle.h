@@ -43,6 +43,7 @@ int orc_stencil_apply(orc_handle h, const void *x, void *y);
 int orc_matfunc(orc_handle h, int fn, double t_re, double t_im, const void *in, void *out);
 int orc_lanczos(orc_handle h, const void *in, void *V, void *alpha, double *beta);
 int orc_reduce(orc_handle h, int what, double *out);
+int orc_get_field_resampled(orc_handle h, int field, uint32_t tnx, uint32_t tny, uint32_t tnz, void *dst, size_t bytes);
 /* CSR of the assembled operator (for the scipy anchor): nnz returned through *nnz;
  * pass NULL arrays to query sizes. values are real (the stencil weights). */
 int orc_csr(orc_handle h, int64_t *nnz, int64_t *rowptr, int32_t *col, double *val);

@@ -42,6 +42,7 @@ def lib():
         L.orc_matfunc.argtypes = [_vp, C.c_int, C.c_double, C.c_double, _vp, _vp]
         L.orc_lanczos.argtypes = [_vp, _vp, _vp, _vp, _dp]
         L.orc_reduce.argtypes = [_vp, C.c_int, _dp]
+        L.orc_get_field_resampled.argtypes = [_vp, C.c_int, C.c_uint32, C.c_uint32, C.c_uint32, _vp, C.c_size_t]
         L.orc_csr.argtypes = [_vp, C.POINTER(C.c_int64), _vp, _vp, _vp]
         _lib = L
     return _lib
@@ -81,6 +82,12 @@ class Oracle:
     def get(self, field=FIELD.U):
         out = np.empty(self._state_shape(), dtype=self.desc.dtype)
         self._check(self.lib.orc_get_field(self.h, field, _ptr(out), out.nbytes))
+        return out
+
+    def get_resampled(self, tnx, tny, tnz=1, field=FIELD.U):
+        shape = (self.desc.batch, tnz, tny, tnx) if self.desc.nz > 1 else (self.desc.batch, tny, tnx)
+        out = np.empty(shape, dtype=self.desc.dtype)
+        self._check(self.lib.orc_get_field_resampled(self.h, field, tnx, tny, tnz, _ptr(out), out.nbytes))
         return out
 
     def step(self, dt, nsteps=1, sync=True):

@@ -282,3 +282,41 @@ def test_cli_diagnostics_file(drivers, tmp_path):
     assert rd.shape == (8, 2)
     for s in range(8):
         assert rd[s, 1] == pytest.approx(sge_energy_script(tu[s], tv[s], dx, dx), rel=1e-9)
+
+
+def test_downsample_flag_validation(drivers, tmp_path):
+    np.save(tmp_path / "u0.npy", np.zeros((16, 16), dtype=np.complex128))
+    r = run(drivers, "nlse_cubic", 16, 16, 5.0, 5.0, tmp_path / "u0.npy", tmp_path / "o.npy", 0.01, 10, 5,
+            "--downsample", 1)
+    assert r.returncode == 1 and "--downsample" in r.stderr
+
+
+@pytest.mark.gpu
+def test_cli_downsampled_trajectory(drivers, tmp_path):
+    """--downsample N stores what the launcher's downsample_interpolation makes of the full-resolution
+    trajectory (complex_launcher_2d.py:176-191 -> downsampling.py:68-104), for ensemble and real drivers."""
+    from test_downsample import script_downsample_2d
+    B, n, N, L, T, nt, ns = 3, 48, 16, 5.0, 0.04, 40, 8
+    np.save(tmp_path / "u0.npy", random_bumps(B, n, L))
+    common = [n, n, L, L, tmp_path / "u0.npy"]
+    run(drivers, "nlse_ensemble_driver", *common, tmp_path / "full.npy", T, nt, ns, check=True)
+    run(drivers, "nlse_ensemble_driver", *common, tmp_path / "small.npy", T, nt, ns, "--downsample", N, check=True)
+    full, small = np.load(tmp_path / "full.npy"), np.load(tmp_path / "small.npy")
+    assert small.shape == (B, ns, N, N) and small.dtype == np.complex128
+    for b in range(B):
+        for s in range(ns):
+            ref = script_downsample_2d(full[b, s], (N, N), L, L)
+            assert np.max(np.abs(small[b, s] - ref)) < 1e-13 * max(1.0, np.max(np.abs(ref)))
+
+    u0 = 0.3 * ics.kink_2d(n, L)
+    np.save(tmp_path / "ru.npy", u0)
+    np.save(tmp_path / "rv.npy", 0.05 * np.cos(u0))
+    rc = [n, n, L, L, tmp_path / "ru.npy", tmp_path / "rv.npy"]
+    run(drivers, "sg_single", *rc, tmp_path / "fu.npy", tmp_path / "fv.npy", 0.2, 40, 8, check=True)
+    run(drivers, "sg_single", *rc, tmp_path / "su.npy", tmp_path / "sv.npy", 0.2, 40, 8, "--downsample", N, check=True)
+    fu, fv = np.load(tmp_path / "fu.npy"), np.load(tmp_path / "fv.npy")
+    su, sv = np.load(tmp_path / "su.npy"), np.load(tmp_path / "sv.npy")
+    assert su.shape == (8, N, N) and sv.shape == (8, N, N)
+    for s in range(8):
+        assert np.max(np.abs(su[s] - script_downsample_2d(fu[s], (N, N), L, L))) < 1e-12
+        assert np.max(np.abs(sv[s] - script_downsample_2d(fv[s], (N, N), L, L))) < 1e-9
