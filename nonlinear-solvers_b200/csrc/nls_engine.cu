@@ -704,7 +704,8 @@ int nls_destroy(nls_handle e) {
 int nls_create(const nls_desc *desc, nls_handle *out) {
   if (!desc || !out || desc->struct_size != sizeof(nls_desc)) return fail(NLS_ERR_ARG, "bad descriptor");
   const nls_desc &d = *desc;
-  if (d.nx < 3 || d.ny < 3 || d.nz == 0 || d.nz == 2 || d.krylov_m < 2 || d.krylov_m > (uint32_t)kMaxM ||
+  const bool slab_req = d.nz_global && d.nz_global != d.nz; // a slab may hold just 2 planes of a taller grid
+  if (d.nx < 3 || d.ny < 3 || d.nz == 0 || (d.nz == 2 && !slab_req) || d.krylov_m < 2 || d.krylov_m > (uint32_t)kMaxM ||
       d.batch < 1)
     return fail(NLS_ERR_ARG, "bad sizes: need nx,ny>=3, nz==1 or >=3, 2<=m<=64, batch>=1");
   if (d.equation < NLS_EQ_NLSE_CUBIC || d.equation > NLS_EQ_SGE_SINH) return fail(NLS_ERR_ARG, "bad equation");

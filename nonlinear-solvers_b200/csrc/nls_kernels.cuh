@@ -816,9 +816,16 @@ k_reduce_energy(Geom g, const S *__restrict__ u, const double *__restrict__ upas
   double acc[1] = {0.0};
   for (long long idx = (long long)blockIdx.x * kThreads + threadIdx.x; idx < g.n;
        idx += (long long)gridDim.x * kThreads) {
-    const int i = (int)(idx % nx);
-    const long long r = idx / nx;
-    const int j = (int)(r % g.ny), k = (int)(r / g.ny);
+    int i, j, k;
+    if (g.n <= 0xffffffffLL) { // 32-bit divisions (the 64-bit ones cost more than the loads)
+      const unsigned ui = (unsigned)idx, r = ui / (unsigned)g.nx;
+      i = (int)(ui - r * (unsigned)g.nx);
+      k = (int)(r / (unsigned)g.ny);
+      j = (int)(r - (unsigned)k * (unsigned)g.ny);
+    } else {
+      const long long r = idx / nx;
+      i = (int)(idx % nx); j = (int)(r % g.ny); k = (int)(r / g.ny);
+    }
     const S c = ub[idx];
     const double a2 = T::abs2(c);
     if (CPLX) {

@@ -109,16 +109,23 @@ def main():
                     failures.append((name, what, err))
         dist.barrier()
 
+    def Z(base):  # at least 3 planes on every rank, and not a multiple of the rank count
+        return max(base, 3 * world + 1 + base % 2)
+
     case("nlse cubic 3D uniform", 20, 20 + world, dict(equation=EQ.NLSE_CUBIC, krylov_m=10), 8, 1e-3, False, 1e-11)
-    case("nlse cq 3D aniso m=12", 24, 26, dict(equation=EQ.NLSE_CQ, laplacian=LAP.ANISO, krylov_m=12, s1=1.0, s2=-0.1),
+    case("nlse cq 3D aniso m=12", 24, Z(26), dict(equation=EQ.NLSE_CQ, laplacian=LAP.ANISO, krylov_m=12, s1=1.0, s2=-0.1),
          6, 5e-4, False, 1e-11)
-    case("nlse 3-term", 16, 18, dict(equation=EQ.NLSE_CUBIC, krylov_m=8, reorth=1), 5, 1e-3, False, 1e-11)
-    case("nlse cq 3D aniso, TMA passes", 32, 28, dict(equation=EQ.NLSE_CQ, laplacian=LAP.ANISO, krylov_m=12, s1=1.0, s2=-0.1,
+    case("nlse 3-term", 16, Z(18), dict(equation=EQ.NLSE_CUBIC, krylov_m=8, reorth=1), 5, 1e-3, False, 1e-11)
+    case("nlse cq 3D aniso, TMA passes", 32, Z(28), dict(equation=EQ.NLSE_CQ, laplacian=LAP.ANISO, krylov_m=12, s1=1.0, s2=-0.1,
                                                      flags=nls_b200.FLAG_TMA), 5, 5e-4, False, 1e-11)
-    case("nlse sewi 3D", 18, 20, dict(equation=EQ.NLSE_CUBIC, integrator=INT.SEWI, krylov_m=8), 5, 1e-3, False, 1e-11)
-    case("kge 3D gautschi aniso", 20, 22, dict(equation=EQ.KGE, integrator=INT.GAUTSCHI, laplacian=LAP.ANISO,
+    case("nlse sewi 3D", 18, Z(20), dict(equation=EQ.NLSE_CUBIC, integrator=INT.SEWI, krylov_m=8), 5, 1e-3, False, 1e-11)
+    case("kge 3D gautschi aniso", 20, Z(22), dict(equation=EQ.KGE, integrator=INT.GAUTSCHI, laplacian=LAP.ANISO,
                                                krylov_m=10, op_sign=-1.0), 6, 1e-3, True, 1e-11)
-    case("sge 3D stoermer-verlet", 20, 23, dict(equation=EQ.SGE, integrator=INT.SV), 40, 1e-3, True, 1e-11)
+    case("sge 3D stoermer-verlet", 20, Z(23), dict(equation=EQ.SGE, integrator=INT.SV), 40, 1e-3, True, 1e-11)
+    if world > 1:  # thinnest legal decomposition: 2 planes on all ranks but one
+        case("thin slabs, 2 planes per rank", 16, 2 * world + 1, dict(equation=EQ.NLSE_CUBIC, krylov_m=8), 5, 1e-3, False, 1e-11)
+        case("thin slabs, kge gautschi", 16, 2 * world + 1, dict(equation=EQ.KGE, integrator=INT.GAUTSCHI, krylov_m=8,
+                                                               op_sign=-1.0), 5, 1e-3, True, 1e-11)
     if rank == 0:
         print("SLAB_FAIL" if failures else "SLAB_OK", failures, flush=True)
     dist.destroy_process_group()
