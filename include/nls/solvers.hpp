@@ -62,6 +62,16 @@ public:
 
   void set(int field, const void *src, size_t bytes) { check(nls_set_field(h_, field, src, bytes), "nls_set_field"); }
   void get(int field, void *dst, size_t bytes) { check(nls_get_field(h_, field, dst, bytes), "nls_get_field"); }
+  // field resampled on the device to tnx x tny [x tnz] points per trajectory (downsampling.py:68-104)
+  void get_resampled(int field, uint32_t tnx, uint32_t tny, uint32_t tnz, void *dst, size_t bytes) {
+    check(nls_get_field_resampled(h_, field, tnx, tny, tnz, dst, bytes), "nls_get_field_resampled");
+  }
+  // NLS_RED_MASS / NLS_RED_ENERGY / NLS_RED_NONFINITE, one value per trajectory
+  std::vector<double> reduce(int what) {
+    std::vector<double> out(batch_);
+    check(nls_reduce(h_, what, out.data()), "nls_reduce");
+    return out;
+  }
   void step(double dt, uint32_t nsteps = 1) { check(nls_step(h_, dt, nsteps), "nls_step"); }
   void sync() { check(nls_sync(h_), "nls_sync"); }
   nls_handle raw() const { return h_; }

@@ -198,7 +198,7 @@ bool run_ensemble(const Spec &s, const nls::Grid &g, uint32_t krylov, double dt,
       auto diagnose = [&](size_t snap) {
         if (!diag) return;
         for (int q = 0; q < 2; ++q) {
-          nls::check(nls_reduce(h.raw(), q == 0 ? NLS_RED_MASS : NLS_RED_ENERGY, red.data()), "nls_reduce");
+          red = h.reduce(q == 0 ? NLS_RED_MASS : NLS_RED_ENERGY);
           for (uint64_t b = 0; b < nb; ++b) dg[((b0 + b) * ns + snap) * 2 + q] = red[b];
         }
       };
@@ -210,9 +210,8 @@ bool run_ensemble(const Spec &s, const nls::Grid &g, uint32_t krylov, double dt,
           return;
         }
         if (ds) {
-          nls::check(nls_get_field_resampled(h.raw(), NLS_FIELD_U, ds, ds, dtz, su.data(), nb * no * sizeof(T)), "nls_get_field_resampled");
-          if (real)
-            nls::check(nls_get_field_resampled(h.raw(), NLS_FIELD_V, ds, ds, dtz, sv.data(), nb * no * sizeof(T)), "nls_get_field_resampled");
+          h.get_resampled(NLS_FIELD_U, ds, ds, dtz, su.data(), nb * no * sizeof(T));
+          if (real) h.get_resampled(NLS_FIELD_V, ds, ds, dtz, sv.data(), nb * no * sizeof(T));
         } else {
           h.get(NLS_FIELD_U, su.data(), nb * n * sizeof(T));
           if (real) h.get(NLS_FIELD_V, sv.data(), nb * n * sizeof(T));
