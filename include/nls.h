@@ -47,8 +47,12 @@ enum {
   NLS_ERR_ARG = -1,      /* bad descriptor / argument */
   NLS_ERR_CUDA = -2,     /* CUDA runtime error (incl. "no device") */
   NLS_ERR_STATE = -3,    /* call not valid for this handle's equation/integrator */
-  NLS_ERR_NONFINITE = -4 /* reserved */
+  NLS_ERR_NONFINITE = -4 /* the on-device tridiagonal eigensolve did not converge (non-finite state) */
 };
+/* Device-side failures (eigensolver non-convergence -> NLS_ERR_NONFINITE; grid-barrier / z-slab peer /
+ * TMA pipeline time-out -> NLS_ERR_CUDA) are detected by the next nls_sync / nls_get_field* / nls_reduce /
+ * nls_step_timed / nls_matfunc and are STICKY: the state was only partially advanced, so the handle is
+ * poisoned and every later call except nls_destroy returns the same error. */
 
 /* equation = pointwise nonlinearity */
 enum {
@@ -151,6 +155,8 @@ enum {
                              * passes on B200 so far, hence opt-in */
   NLS_FLAG_PK_SV = 64u,     /* Stoermer-Verlet through the persistent kernel (k_pk_sv); off by default: at
                              * 1024^2 one grid barrier per step (15.7 us) costs more than a k_sv launch (11-14 us) */
+  NLS_FLAG_DEBUG_PK_FAULT = 0x80000000u, /* test hook: one CTA of the persistent kernel never reaches its first
+                             * grid barrier, so the barrier times out (~2 s) and the abort path is exercised */
   NLS_FLAG_SEWI_HOST2D = 4u /* NLS_INT_SEWI with the sign convention of the 2D cubic HOST solver:
                              * u+ = e^{-2 tau L} u- + 2 tau e^{-tau L} sinc(dt L) B(u)
                              * (nlse_cubic_gautschi_solver.hpp:21-39) */

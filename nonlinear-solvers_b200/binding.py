@@ -30,6 +30,7 @@ FLAG_SEWI_HOST2D = 4
 FLAG_MARCH = 8
 FLAG_TMA = 32
 FLAG_PK_SV = 64
+FLAG_DEBUG_PK_FAULT = 0x80000000
 
 
 class NlsError(RuntimeError):

@@ -60,6 +60,7 @@ struct nls_engine {
   double *scalA = nullptr, *scalB = nullptr, *coef = nullptr, *redout = nullptr;
   RedCtx rc{nullptr, nullptr, nullptr};
   int *status = nullptr;
+  int poison = 0;        // first non-zero device status seen: the handle's state is unusable from then on (sticky)
   size_t colstride = 0;  // scalars between basis columns
   // stepping state
   int nphase = 1, phase = 0;
@@ -186,13 +187,17 @@ void halo_exchange(nls_engine *e, const void *buf) {
 
 // ---------------------------------------------------------------- Lanczos (K2)
 // ---------------------------------------------------------------- TMA-staged passes (nls_tma.cuh)
-bool tma_attr(const void *fn, int bytes) { // opt in to large dynamic shared memory once per kernel
-  static thread_local std::unordered_map<const void *, bool> done;
-  auto it = done.find(fn);
+bool tma_attr(const void *fn, int bytes) { // opt in to large dynamic shared memory once per (device, kernel)
+  static thread_local std::unordered_map<uint64_t, bool> done_map;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  const uint64_t key = (uint64_t)(uintptr_t)fn * 64u + (uint64_t)dev; // function addresses are >= 64-byte apart
+  auto &done = done_map;
+  auto it = done.find(key);
   if (it != done.end()) return it->second;
   const bool ok = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes) == cudaSuccess;
   if (!ok) cudaGetLastError();
-  done[fn] = ok;
+  done[key] = ok;
   return ok;
 }
 
@@ -592,11 +597,26 @@ void pk_setup(nls_engine *e) {
   e->pk_ok = true;
 }
 
+int run_steps_pk_once(nls_engine *e, double dt, uint32_t nsteps);
+// The grid-barrier counter is 32-bit and only grows within a launch (ncta arrivals per barrier, ~40 barriers
+// per step): split long runs so it can never wrap (148 CTAs x 40 barriers x 65536 steps = 3.9e8 < 2^32).
 int run_steps_pk(nls_engine *e, double dt, uint32_t nsteps) {
+  constexpr uint32_t kMaxStepsPerLaunch = 65536u / 2;
+  while (nsteps) {
+    const uint32_t k = nsteps < kMaxStepsPerLaunch ? nsteps : kMaxStepsPerLaunch;
+    const int rc = run_steps_pk_once(e, dt, k);
+    if (rc) return rc;
+    nsteps -= k;
+  }
+  return NLS_OK;
+}
+
+int run_steps_pk_once(nls_engine *e, double dt, uint32_t nsteps) {
   PkArgs a;
   a.g = e->g;
   a.m = e->m; a.eq = e->d.equation; a.integ = e->d.integrator;
   a.aniso = e->d.laplacian == NLS_LAP_ANISO;
+  a.debug_fault = (e->d.flags & NLS_FLAG_DEBUG_PK_FAULT) ? 1 : 0;
   a.nsteps = (int)nsteps; a.ncta = e->pk_ncta; a.csz = e->pk_csz;
   a.dt = dt; a.s1 = e->d.s1; a.s2 = e->d.s2; a.kappa = e->d.kappa;
   a.V = e->V; a.colstride = e->colstride;
@@ -655,14 +675,25 @@ int copy_out(nls_engine *e, void *host, const void *dev, size_t esz, int nb, boo
   return NLS_OK;
 }
 
+// Device-side failures are STICKY: the first non-zero status word poisons the handle (its state was only
+// partially advanced), every later step / get / sync / reduce returns the same error; only nls_destroy is valid.
+int poisoned(nls_engine *e) {
+  switch (e->poison) {
+  case 0: return NLS_OK;
+  case 2: return fail(NLS_ERR_CUDA, "z-slab exchange timed out waiting for a peer rank (handle poisoned)");
+  case 3: return fail(NLS_ERR_CUDA, "TMA pipeline timed out (internal error; handle poisoned)");
+  case 4: return fail(NLS_ERR_CUDA, "persistent kernel: grid barrier timed out or was aborted; the state is inconsistent (handle poisoned)");
+  default: return fail(NLS_ERR_NONFINITE, "tridiagonal eigensolver did not converge (non-finite state?; handle poisoned)");
+  }
+}
+
 int check_status(nls_engine *e) {
+  if (e->poison) return poisoned(e);
   int st = 0;
   CU(cudaMemcpyAsync(&st, e->status, sizeof(int), cudaMemcpyDeviceToHost, e->stream));
   CU(cudaStreamSynchronize(e->stream));
-  if (st == 2) return fail(NLS_ERR_STATE, "z-slab exchange timed out waiting for a peer rank");
-  if (st == 3) return fail(NLS_ERR_STATE, "TMA pipeline timed out (internal error)");
-  if (st) return fail(NLS_ERR_STATE, "tridiagonal eigensolver did not converge (non-finite state?)");
-  return NLS_OK;
+  e->poison = st;
+  return poisoned(e);
 }
 
 } // namespace
@@ -810,6 +841,7 @@ int nls_create(const nls_desc *desc, nls_handle *out) {
 
 static int set_field_impl(nls_handle e, int field, const void *src, size_t bytes, bool dev) {
   if (!e || !src) return fail(NLS_ERR_ARG, "null argument");
+  if (e->poison) return poisoned(e);
   CU(cudaSetDevice(e->d.device));
   const size_t sb = (size_t)e->batch * e->g.n * e->esz, fb = (size_t)e->g.n * 8;
   int rc;
@@ -940,6 +972,7 @@ static int slab_ready(nls_handle e) {
 int nls_step(nls_handle e, double dt, uint32_t nsteps) {
   if (!e) return fail(NLS_ERR_ARG, "null handle");
   if (slab_ready(e)) return NLS_ERR_STATE;
+  if (e->poison) return poisoned(e);
   CU(cudaSetDevice(e->d.device));
   return run_steps(e, dt, nsteps);
 }
@@ -1067,6 +1100,7 @@ int nls_lanczos(nls_handle e, const void *in, void *hV, void *halpha, double *hb
 
 int nls_reduce(nls_handle e, int what, double *out) {
   if (!e || !out) return fail(NLS_ERR_ARG, "null argument");
+  if (e->poison) return poisoned(e);
   CU(cudaSetDevice(e->d.device));
   if (what != NLS_RED_MASS && what != NLS_RED_NONFINITE && what != NLS_RED_ENERGY) return fail(NLS_ERR_ARG, "bad reduction");
   if (what == NLS_RED_ENERGY) {

@@ -60,6 +60,7 @@ constexpr int kPkPartStride = 160;       // >= max CTAs, padded
 struct PkArgs {
   Geom g;
   int m, eq, integ, aniso, nsteps, ncta;
+  int debug_fault;     // NLS_FLAG_DEBUG_PK_FAULT: the last CTA exits before its first barrier (abort-path test)
   long long csz;       // sites per chunk (chunk c = sites [c*csz, min((c+1)*csz, n)))
   double dt, s1, s2, kappa;
   void *V;             // m columns; column i at V + i*colstride (scalars)
@@ -111,6 +112,7 @@ struct GridSync {
   unsigned target; // arrivals expected at the next barrier
   unsigned ncta;
   int slot;        // parity of the barrier count: which partial-sum slot is live
+  int *status;     // device status word of the handle: 4 = a grid barrier timed out / was aborted
 };
 
 __device__ __forceinline__ unsigned ld_acquire_u32(const unsigned *p) {
@@ -135,6 +137,7 @@ __device__ __forceinline__ bool grid_barrier(GridSync &gs) {
     while (ld_acquire_u32(gs.ctr) < gs.target) {
       if (clock64() - t0 > 4000000000LL || ld_acquire_u32(gs.ctr + 1) != 0u) { // ~2 s
         atomicExch(gs.ctr + 1, 1u);
+        atomicExch(gs.status, 4); // reported by nls_sync / nls_get_field: the state is NOT advanced consistently
         ok = 0;
         break;
       }
@@ -886,7 +889,8 @@ __global__ void __launch_bounds__(kPkThreads, 1) k_pk_nlse(PkArgs a, double2 *sv
   extern __shared__ __align__(16) unsigned char pk_smem[];
   PkCtx<double2> c;
   pk_carve<double2>(a, c, pk_smem);
-  GridSync gs{a.bar, 0u, (unsigned)a.ncta, 0};
+  GridSync gs{a.bar, 0u, (unsigned)a.ncta, 0, a.status};
+  if (a.debug_fault && blockIdx.x == (unsigned)a.ncta - 1u) return; // test hook: one CTA never arrives
   const NlseParams p{0.5 * a.dt, a.s1, a.s2, a.kappa};
   double2 *ucur = (double2 *)a.u0, *unext = (double2 *)a.u1;
   double2 *scur = sv0, *snext = sv1;
@@ -1028,7 +1032,8 @@ __global__ void __launch_bounds__(kPkThreads, 1) k_pk_gautschi(PkArgs a, double 
   extern __shared__ __align__(16) unsigned char pk_smem[];
   PkCtx<double> c;
   pk_carve<double>(a, c, pk_smem);
-  GridSync gs{a.bar, 0u, (unsigned)a.ncta, 0};
+  GridSync gs{a.bar, 0u, (unsigned)a.ncta, 0, a.status};
+  if (a.debug_fault && blockIdx.x == (unsigned)a.ncta - 1u) return; // test hook: one CTA never arrives
   double *u = (double *)a.u0, *up = (double *)a.u1 + c.s0, *accb = (double *)a.acc;
   PK_GLOBAL(u);
   PK_GLOBAL(up);
@@ -1145,7 +1150,8 @@ __global__ void __launch_bounds__(kPkThreads, 1) k_pk_sv(PkArgs a, double *b0, d
   extern __shared__ __align__(16) unsigned char pk_smem[];
   PkCtx<double> c;
   pk_carve<double>(a, c, pk_smem, 2 * a.g.nx); // both tiles carry halo rows: they swap roles every step
-  GridSync gs{a.bar, 0u, (unsigned)a.ncta, 0};
+  GridSync gs{a.bar, 0u, (unsigned)a.ncta, 0, a.status};
+  if (a.debug_fault && blockIdx.x == (unsigned)a.ncta - 1u) return; // test hook: one CTA never arrives
   double *buf[3] = {b0, b1, b2};
   double *xc = c.X() + a.g.nx, *pc = c.Wt() + a.g.nx; // u tile centre, u_past tile centre
   const double *cfg = ANISO ? a.cf + c.s0 : nullptr;

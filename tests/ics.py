@@ -46,3 +46,18 @@ def kink_2d(n, L, seed=77, bumps=3):
         s = rng.uniform(0.5, 1.0)
         u += 0.1 * np.exp(-((X - x0) ** 2 + (Y - y0) ** 2) / (2 * s * s))
     return u
+
+
+def slab_ic(n, z0, nz, nzg, L):
+    """seed-free analytic IC of the C5 workload (same formula as bench.py): 8 fixed Gaussians."""
+    x = np.linspace(-L, L, n)
+    z = np.linspace(-L, L, nzg)[z0:z0 + nz]
+    u = np.zeros((nz, n, n), dtype=np.complex128)
+    for k in range(8):
+        c = 0.5 * L * np.array([np.cos(1.3 * k), np.sin(2.1 * k), np.cos(0.7 * k + 1.0)])
+        s = 0.8 + 0.05 * k
+        gx = np.exp(-(x - c[0]) ** 2 / (2 * s * s)) * np.exp(1j * 0.3 * k * x)
+        gy = np.exp(-(x - c[1]) ** 2 / (2 * s * s))
+        gz = np.exp(-(z - c[2]) ** 2 / (2 * s * s))
+        u += (0.5 + 0.05 * k) * gz[:, None, None] * gy[None, :, None] * gx[None, None, :]
+    return u

@@ -273,7 +273,8 @@ def test_three_term_mode(orc):
 
 def test_config1_full_trajectory_parity(orc):
     """BASELINE config 1: NLSE 2D cubic focusing 256x256, dt=1e-3, nt=1000 (999 steps), m=10,
-    100 snapshots; rel-L2 of every snapshot <= 1e-10 and mass series to 1e-8."""
+    100 snapshots; rel-L2 of every snapshot <= 1e-10, mass AND energy series to 1e-8 (definitions of
+    finalized_scripts/compare_utils_complex_2d.py:134-151, computed by NLS_RED_ENERGY on both sides)."""
     n, L, T, nt, ns = 256, 10.0, 1.0, 1000, 100
     dt, freq = T / nt, nt // ns
     d = Desc.make(n, n, L=L, equation=EQ.NLSE_CUBIC, krylov_m=10)
@@ -282,7 +283,7 @@ def test_config1_full_trajectory_parity(orc):
     for s in (e, o):
         s.set(FIELD.U, u0)
         s.set(FIELD.M, np.ones(d.n))
-    worst, worst_mass = 0.0, 0.0
+    worst, worst_mass, worst_en = 0.0, 0.0, 0.0
     done = 0  # driver loop i=1..nt-1; snapshot when i % freq == 0 (nlse_cubic_driver.cpp:96-105)
     while done < nt - 1:
         k = min(freq - done % freq, nt - 1 - done)
@@ -293,9 +294,12 @@ def test_config1_full_trajectory_parity(orc):
             worst = max(worst, rel_l2(e.get(), o.get()))
             me, mo = e.reduce(RED.MASS)[0], o.reduce(RED.MASS)[0]
             worst_mass = max(worst_mass, abs(me - mo) / mo)
-    print(f"C1 worst snapshot rel-L2 {worst:.3e}, worst mass mismatch {worst_mass:.3e}")
+            ee, eo = e.reduce(RED.ENERGY)[0], o.reduce(RED.ENERGY)[0]
+            worst_en = max(worst_en, abs(ee - eo) / abs(eo))
+    print(f"C1 worst snapshot rel-L2 {worst:.3e}, worst mass mismatch {worst_mass:.3e}, worst energy mismatch {worst_en:.3e}")
     assert worst <= 1e-10
     assert worst_mass <= 1e-8
+    assert worst_en <= 1e-8
 
 
 def test_config2_sge_256_parity(orc):
