@@ -12,6 +12,7 @@
 #include <cstring>
 #include <string>
 #include <unordered_map>
+#include <utility>
 #include <vector>
 
 using namespace nls;
@@ -81,6 +82,10 @@ struct nls_engine {
   double *pk_part = nullptr;
   unsigned *pk_bar = nullptr;
   uint64_t pk_launches = 0;
+  // temporally blocked 2D Stoermer-Verlet kernel (k_pk_sv2)
+  bool sv2_ok = false;
+  Sv2Plan sv2{};
+  unsigned long long *sv2_prog = nullptr; // [ncta] progress counters, then one abort word
   // z-slabs: the stencil-input vectors (+ the mailbox) live in one exchange arena that the
   // other ranks map through CUDA IPC (or address directly when they live in this process)
   bool slab = false;
@@ -508,9 +513,11 @@ int ensure_start(nls_engine *e, double dt) {
 }
 
 int run_steps_pk(nls_engine *e, double dt, uint32_t nsteps);
+int run_steps_sv2(nls_engine *e, double dt, uint32_t nsteps);
 
 int run_steps(nls_engine *e, double dt, uint32_t nsteps) {
   if (nsteps == 0) return NLS_OK;
+  if (e->sv2_ok) return run_steps_sv2(e, dt, nsteps);
   if (e->pk_ok) return run_steps_pk(e, dt, nsteps);
   int rc = ensure_start(e, dt);
   if (rc) return rc;
@@ -588,9 +595,8 @@ void pk_setup(nls_engine *e) {
     cudaGetLastError();
     return;
   }
-  if (cudaMalloc((void **)&e->pk_part, (size_t)2 * kPkMaxK * kPkPartStride * 8) != cudaSuccess) return;
+  if (cudaMalloc((void **)&e->pk_part, (size_t)kPkSlots * kPkMaxK * kPkPartStride * 8) != cudaSuccess) return;
   if (cudaMalloc((void **)&e->pk_bar, 16) != cudaSuccess) return;
-  cudaMemset(e->pk_part, 0, (size_t)2 * kPkMaxK * kPkPartStride * 8);
   e->pk_ncta = ncta;
   e->pk_csz = csz;
   e->pk_smem = smem;
@@ -623,6 +629,7 @@ int run_steps_pk_once(nls_engine *e, double dt, uint32_t nsteps) {
   a.acc = e->acc; a.mf = e->mf; a.cf = e->cf;
   a.part = e->pk_part; a.bar = e->pk_bar; a.status = e->status;
   CU(cudaMemsetAsync(e->pk_bar, 0, 16, e->stream));
+  CU(cudaMemsetAsync(e->pk_part, 0xff, (size_t)kPkSlots * kPkMaxK * kPkPartStride * 8, e->stream)); // sentinel-arm every slot
   const bool an = a.aniso;
   if (e->cplx) {
     a.u0 = e->u[e->phase]; a.u1 = e->u[1 - e->phase];
@@ -646,6 +653,81 @@ int run_steps_pk_once(nls_engine *e, double dt, uint32_t nsteps) {
   }
   e->launches += 1;
   e->start_valid = false; // the multi-kernel path's start vector / norms are stale now
+  return NLS_OK;
+}
+
+// ---- temporally blocked Stoermer-Verlet (2D, uniform Laplacian, one trajectory): default for every grid whose
+// tiles fit in shared memory; NLS_FLAG_PK_SV selects the older 1-D-chunk kernel instead, NLS_FLAG_NO_PERSISTENT the
+// one-kernel-per-step graph
+template <int EQ> const void *sv2_fn() { return (const void *)k_pk_sv2<EQ>; }
+const void *sv2_kernel(int eq) {
+  switch (eq) {
+  case NLS_EQ_SGE: return sv2_fn<NLS_EQ_SGE>();
+  case NLS_EQ_KGE: return sv2_fn<NLS_EQ_KGE>();
+  case NLS_EQ_PHI4: return sv2_fn<NLS_EQ_PHI4>();
+  case NLS_EQ_SGE_DOUBLE: return sv2_fn<NLS_EQ_SGE_DOUBLE>();
+  default: return sv2_fn<NLS_EQ_SGE_SINH>();
+  }
+}
+
+void sv2_setup(nls_engine *e) {
+  const nls_desc &d = e->d;
+  e->sv2_ok = false;
+  if (d.integrator != NLS_INT_SV || (d.flags & (NLS_FLAG_NO_PERSISTENT | NLS_FLAG_PK_SV))) return;
+  if (e->batch != 1 || e->g.dim3 || e->slab || d.laplacian != NLS_LAP_UNIFORM) return;
+  int dev = d.device, nsm = 0, smem_max = 0, coop = 0;
+  cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev);
+  cudaDeviceGetAttribute(&smem_max, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+  cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
+  if (!coop || nsm <= 0) return;
+  Sv2Plan pl;
+  if (!sv2_plan(e->g.nx, e->g.ny, nsm, (size_t)smem_max - 1024, pl)) return;
+  if (const char *ms = getenv("NLS_SV2_MAX_S")) { // tuning knob, not API: cap the temporal block depth
+    const int cap = atoi(ms);
+    if (cap >= 1 && pl.s > cap) { pl.s = cap; pl.smem = sv2_smem_bytes(pl.w, pl.h, pl.s); }
+  }
+  const void *fn = sv2_kernel(d.equation);
+  if (cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem) != cudaSuccess) {
+    cudaGetLastError();
+    return;
+  }
+  int occ = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn, kPkThreads, pl.smem) != cudaSuccess || occ < 1) {
+    cudaGetLastError();
+    return;
+  }
+  if (pl.px * pl.py > nsm * occ) return;
+  if (cudaMalloc((void **)&e->sv2_prog, (size_t)(pl.px * pl.py + 2) * 8) != cudaSuccess) return;
+  e->sv2 = pl;
+  e->sv2_ok = true;
+}
+
+int run_steps_sv2(nls_engine *e, double dt, uint32_t nsteps) {
+  const Sv2Plan &pl = e->sv2;
+  const int ncta = pl.px * pl.py;
+  const int p = e->phase, pp = (p + 2) % 3, pn = (p + 1) % 3;
+  Sv2Args a;
+  a.nx = e->g.nx; a.ny = e->g.ny; a.nsteps = (int)nsteps; a.pl = pl;
+  a.sc = e->g.sc; a.tau2 = dt * dt; a.mf = e->mf;
+  // buffer sets: [0] = current (u, u_past); [1], [2] = ping-pong outputs (spare state buffer + Krylov work vectors)
+  void **slot_u[3] = {&e->u[p], &e->u[pn], &e->wbuf[1]};
+  void **slot_p[3] = {&e->u[pp], &e->wbuf[0], &e->w0};
+  for (int q = 0; q < 3; ++q) { a.su[q] = (double *)*slot_u[q]; a.sp[q] = (double *)*slot_p[q]; }
+  a.prog = e->sv2_prog;
+  a.abort_flag = (unsigned *)(e->sv2_prog + ncta);
+  a.status = e->status;
+  a.debug_fault = (e->d.flags & NLS_FLAG_DEBUG_PK_FAULT) ? 1 : 0;
+  CU(cudaMemsetAsync(e->sv2_prog, 0, (size_t)(ncta + 2) * 8, e->stream));
+  void *args[] = {&a};
+  CU(cudaLaunchCooperativeKernel(sv2_kernel(e->d.equation), dim3(ncta), dim3(kPkThreads), args, pl.smem, e->stream));
+  e->launches += 1;
+  // the last block (index nb-1) stored the final state in set 1 + (nb-1) % 2: make it the current state by
+  // exchanging buffer roles (pointers only)
+  const int nb = ((int)nsteps + pl.s - 1) / pl.s;
+  const int fs = 1 + ((nb - 1) & 1);
+  std::swap(*slot_u[0], *slot_u[fs]);
+  std::swap(*slot_p[0], *slot_p[fs]);
+  e->start_valid = false;
   return NLS_OK;
 }
 
@@ -724,7 +806,7 @@ int nls_destroy(nls_handle e) {
   }
   void *ptrs[] = {e->V, e->wbuf[0], e->wbuf[1], e->w0, e->u[0], e->u[1], e->u[2], e->acc, e->mf, e->cf,
                   e->scalA, e->scalB, e->coef, e->redout, e->rc.partials, e->rc.tickets, e->status,
-                  e->pk_part, e->pk_bar, e->arena, e->slab_dev, e->slab_scratch, e->rs};
+                  e->pk_part, e->pk_bar, e->sv2_prog, e->arena, e->slab_dev, e->slab_scratch, e->rs};
   for (void *p : ptrs)
     if (p) cudaFree(p);
   if (e->stream) cudaStreamDestroy(e->stream);
@@ -829,6 +911,7 @@ int nls_create(const nls_desc *desc, nls_handle *out) {
   }
   ok = ok && cudaDeviceSynchronize() == cudaSuccess;
   if (ok) pk_setup(e);
+  if (ok) sv2_setup(e);
   if (ok) tma_setup(e);
   if (!ok) {
     std::string msg = std::string("allocation failed: ") + cudaGetErrorString(cudaGetLastError());

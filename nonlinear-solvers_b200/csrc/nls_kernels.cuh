@@ -353,11 +353,128 @@ struct TridiagArgs {
   double tr[2], ti[2];
 };
 
+// Warp-cooperative implicit-shift QL (tql2) for m <= 32 with the tridiagonal in REGISTERS: lane i owns d_i and
+// e_i (e_i couples i and i+1; e_{m-1} = 0), every lane runs the same scalar recurrence on values broadcast by
+// shuffles (fetched one rotation ahead, so no memory round trip sits on the serial rotation chain), the
+// deflation scan is one ballot, and lane k owns row k of the eigenvector matrix Z (shared memory, leading
+// dimension ldz, must hold the identity on entry).  On exit d (lane k) = lambda_k, column k of Z its eigenvector.
+// Any backward-stable eigensolver gives parity here: the result only enters through Q f(L) Q^T e1.
+__device__ __forceinline__ bool tridiag_warp_reg(double &d, double &e, double *__restrict__ tz, const int ldz, const int m) {
+  const unsigned FULL = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
+  const bool row = lane < m;
+  double *zr = tz + (row ? lane : 0) * ldz;
+  bool ok = true;
+  for (int l = 0; l < m && ok; ++l) {
+    int iter = 0;
+    for (;;) {
+      // smallest mm >= l with a negligible e_mm (bit m-1 is always set: e_{m-1} = 0)
+      const double dn = __shfl_down_sync(FULL, d, 1);
+      const bool negl = lane >= m - 1 || fabs(e) <= 2.220446049250313e-16 * (fabs(d) + fabs(dn));
+      const unsigned mask = __ballot_sync(FULL, negl) & (FULL << l);
+      const int mm = __ffs(mask) - 1;
+      if (mm == l) break;
+      if (iter++ == 60) { ok = false; break; }
+      const double dl = __shfl_sync(FULL, d, l), dl1 = __shfl_sync(FULL, d, l + 1), el = __shfl_sync(FULL, e, l);
+      const double dmm = __shfl_sync(FULL, d, mm);
+      double g = (dl1 - dl) / (2.0 * el);
+      double r = sqrt(fma(g, g, 1.0));
+      g = dmm - dl + el / (g + copysign(r, g));
+      double s = 1.0, c = 1.0, p = 0.0;
+      int i = mm - 1;
+      bool early = false;
+      double e_i = __shfl_sync(FULL, e, i), d_i = __shfl_sync(FULL, d, i), d_hi = dmm;
+      double zh = row ? zr[mm] : 0.0;
+      for (; i >= l; --i) {
+        const int ip = i > l ? i - 1 : i;
+        const double e_n = __shfl_sync(FULL, e, ip), d_n = __shfl_sync(FULL, d, ip); // next rotation's pair
+        const double zl = row ? zr[i] : 0.0;
+        const double f = s * e_i;
+        const double b = c * e_i;
+        const double t2 = fma(f, f, g * g);
+        const double ir = rsqrt(t2);
+        r = t2 == 0.0 ? 0.0 : t2 * ir;
+        if (lane == i + 1) e = r;
+        if (r == 0.0) {
+          if (lane == i + 1) d = d_hi - p;
+          if (lane == mm) e = 0.0;
+          if (row) zr[i + 1] = zh;
+          early = true;
+          break;
+        }
+        s = f * ir;
+        c = g * ir;
+        g = d_hi - p;
+        r = (d_i - g) * s + 2.0 * c * b;
+        p = s * r;
+        if (lane == i + 1) d = g + p;
+        g = c * r - b;
+        if (row) zr[i + 1] = s * zl + c * zh;
+        zh = c * zl - s * zh;
+        d_hi = d_i;
+        d_i = d_n;
+        e_i = e_n;
+      }
+      if (early) continue;
+      if (row) zr[l] = zh;
+      if (lane == l) { d -= p; e = g; }
+      if (lane == mm) e = 0.0;
+    }
+  }
+  return ok;
+}
+
+// coefficient vectors from the decomposition held by tridiag_warp_reg's outputs (m <= 32):
+//   co_f[i] = scale_i * sum_k Z_ik f(t_f lambda_k) Z_0k,  scale_i = beta_0 / beta_i (columns are un-normalised)
+// zf: 2*32 doubles of shared scratch.  co: [nfn][costride] complex pairs.
+__device__ __forceinline__ void tridiag_coefs_reg(const double lam, const double *__restrict__ tz, const int ldz, const int m,
+                                                  const TridiagArgs &a, const double scale, double *__restrict__ zf,
+                                                  double *__restrict__ co, const int costride) {
+  const int lane = threadIdx.x & 31;
+  for (int f = 0; f < a.nfn; ++f) {
+    __syncwarp();
+    if (lane < m) {
+      const double2 fv = fn_eval(a.fn[f], a.tr[f], a.ti[f], lam);
+      const double z0 = tz[lane]; // Z_0k
+      zf[2 * lane] = fv.x * z0;
+      zf[2 * lane + 1] = fv.y * z0;
+    }
+    __syncwarp();
+    if (lane < m) {
+      const double *zr = tz + lane * ldz;
+      double sr = 0.0, si = 0.0;
+      for (int k = 0; k < m; ++k) {
+        const double z = zr[k];
+        sr = fma(z, zf[2 * k], sr);
+        si = fma(z, zf[2 * k + 1], si);
+      }
+      co[f * costride + 2 * lane] = sr * scale;
+      co[f * costride + 2 * lane + 1] = si * scale;
+    }
+  }
+  __syncwarp();
+}
+
+// One warp per trajectory.  m <= 32: register-resident QL above; larger m: the shared-memory form below.
 __global__ void __launch_bounds__(32)
 k_tridiag(const double *__restrict__ scal, double *__restrict__ coef, TridiagArgs a, int *status) {
   __shared__ double d[kMaxM], e[kMaxM], Z[kMaxM][kMaxM + 1];
   const int lane = threadIdx.x, m = a.m;
   const double *sb = scal + (size_t)blockIdx.x * kScalStride;
+  if (m <= 32) {
+    double *tz = &Z[0][0];
+    const int ldz = m + 1;
+    double dr = lane < m - 1 ? sb[kOffAlpha + lane * a.W] : 0.0;   // T(m-1,m-1) = 0
+    double er = lane < m - 1 ? sqrt(sb[kOffNrm2 + lane + 1]) : 0.0;
+    if (lane < m)
+      for (int k = 0; k < m; ++k) tz[lane * ldz + k] = lane == k ? 1.0 : 0.0;
+    __syncwarp();
+    if (!tridiag_warp_reg(dr, er, tz, ldz, m) && lane == 0) atomicExch(status, 1);
+    __syncwarp();
+    const double scale = lane < m ? sqrt(sb[kOffNrm2 + 0]) / sqrt(sb[kOffNrm2 + lane]) : 0.0;
+    tridiag_coefs_reg(dr, tz, ldz, m, a, scale, e, coef + (size_t)blockIdx.x * 2 * kCoefStride, kCoefStride);
+    return;
+  }
   for (int i = lane; i < m; i += 32) {
     d[i] = i < m - 1 ? sb[kOffAlpha + i * a.W] : 0.0;
     e[i] = i < m - 1 ? sqrt(sb[kOffNrm2 + i + 1]) : 0.0;

@@ -68,7 +68,7 @@ struct PkArgs {
   void *u0, *u1;       // NLSE: u ping-pong (u0 current at entry); real: u0 = u, u1 = u_past
   void *acc;           // Gautschi accumulator 2 cos(.)u - u_past
   const double *mf, *cf;
-  double *part;        // [2][kPkMaxK][kPkPartStride] per-CTA partial sums
+  double *part;        // [3][kPkMaxK][kPkPartStride] per-CTA partial sums (sentinel-armed, see GridSync)
   unsigned *bar;       // [0] arrival counter, [1] abort flag   (zeroed before every launch)
   int *status;
 };
@@ -106,14 +106,29 @@ __shared__ int pk_tr_n;
 #define PKT_DUMP(ncta) do { } while (0)
 #endif
 
-// ---------------------------------------------------------------- grid barrier
+// ---------------------------------------------------------------- grid-wide reduction = grid barrier
+// All CTAs are co-resident (cooperative launch).  A reduction round r is barrier AND all-reduce in one:
+//   publish: every CTA release-stores its K partial sums into part[r % 3][k][cta];
+//   gather:  every CTA polls (acquire loads) the 'ncta' entries of each k until none holds the SENTINEL bit
+//            pattern any more and sums them in the same fixed order -- all CTAs obtain bit-identical scalars.
+// Seeing every CTA's value of round r means every CTA has finished the phase before it (the release/acquire
+// pair also orders that phase's global writes before the reader's next phase), so no separate arrival counter
+// and no second L2 round trip are needed: one store -> one (polled) load per reduction instead of
+// store, atomic, polled counter, then the loads.
+// Slot recycling: while a CTA publishes round r every CTA has already published round r-1, hence finished
+// gathering round r-2; the publisher therefore re-arms its own entries of slot (r+1) % 3 = (r-2) % 3 with the
+// sentinel (before the __syncthreads that precedes its release stores, so the release covers them).
+// The host fills the whole array with the sentinel (0xFF bytes) before every launch.
 struct GridSync {
-  unsigned *ctr;
-  unsigned target; // arrivals expected at the next barrier
+  unsigned *ctr;   // [0] arrival counter of the plain barrier (Stoermer-Verlet kernel), [1] abort flag
+  unsigned target; // arrivals expected at the next plain barrier
   unsigned ncta;
-  int slot;        // parity of the barrier count: which partial-sum slot is live
+  int slot;        // r % 3 of the current round
   int *status;     // device status word of the handle: 4 = a grid barrier timed out / was aborted
+  int kreset;      // entries per slot this kernel ever uses (re-armed at every publish)
 };
+constexpr unsigned long long kPkSentinel = 0xffffffffffffffffull;
+constexpr int kPkSlots = 3;
 
 __device__ __forceinline__ unsigned ld_acquire_u32(const unsigned *p) {
   unsigned v;
@@ -123,9 +138,22 @@ __device__ __forceinline__ unsigned ld_acquire_u32(const unsigned *p) {
 __device__ __forceinline__ void red_release_add_u32(unsigned *p, unsigned v) {
   asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
+__device__ __forceinline__ unsigned long long ld_acquire_u64(const unsigned long long *p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_u64(unsigned long long *p, unsigned long long v) {
+  asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ void st_relaxed_u64(unsigned long long *p, unsigned long long v) {
+  asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
 
-// All CTAs are co-resident (cooperative launch).  Returns false if the barrier timed out or
-// another CTA raised the abort flag (the kernel then unwinds instead of hanging the GPU).
+__shared__ int pk_s_abort; // set by a poll that timed out; read after the next __syncthreads
+
+// plain barrier without a reduction (Stoermer-Verlet kernel).  Returns false if it timed out or another CTA
+// raised the abort flag (the kernel then unwinds instead of hanging the GPU; status 4 poisons the handle).
 __device__ __forceinline__ bool grid_barrier(GridSync &gs) {
   __shared__ int s_ok;
   __syncthreads();
@@ -146,15 +174,14 @@ __device__ __forceinline__ bool grid_barrier(GridSync &gs) {
   } else {
     gs.target += gs.ncta;
   }
-  gs.slot ^= 1;
   __syncthreads();
   return s_ok != 0;
 }
 
-// CTA-level partial sums: acc[K] per thread -> one value per CTA in part[slot][k][cta].
-// Must be followed by grid_barrier and then pk_gather.
+// CTA-level partial sums: acc[K] per thread -> one value per CTA in part[slot][koff + k][cta] (release stores).
+// Several publishes (different koff) may belong to one round; pk_round_done closes the round after the gather.
 template <int K>
-__device__ __forceinline__ void pk_publish(double (&acc)[K], double *part, int slot, double (*s_red)[kPkWarps], int koff = 0) {
+__device__ __forceinline__ void pk_publish(double (&acc)[K], double *part, const GridSync &gs, double (*s_red)[kPkWarps], int koff = 0) {
   PK_SHARED(s_red);
   PK_GLOBAL(part);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -165,42 +192,78 @@ __device__ __forceinline__ void pk_publish(double (&acc)[K], double *part, int s
     for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
     if (lane == 0) s_red[k][warp] = v;
   }
+  { // re-arm this CTA's entries of the slot after next (see above)
+    const int nslot = gs.slot == kPkSlots - 1 ? 0 : gs.slot + 1;
+    for (int k = threadIdx.x; k < gs.kreset; k += kPkThreads)
+      st_relaxed_u64((unsigned long long *)part + ((size_t)nslot * kPkMaxK + k) * kPkPartStride + blockIdx.x, kPkSentinel);
+  }
   __syncthreads();
   if (threadIdx.x < K) {
     double v = 0.0;
 #pragma unroll
     for (int w = 0; w < kPkWarps; ++w) v += s_red[threadIdx.x][w];
-    part[((size_t)slot * kPkMaxK + koff + threadIdx.x) * kPkPartStride + blockIdx.x] = v;
+    unsigned long long bits = (unsigned long long)__double_as_longlong(v);
+    if (bits == kPkSentinel) bits = 0x7ff8000000000000ull; // a NaN with the sentinel's payload: keep it a NaN
+    st_release_u64((unsigned long long *)part + ((size_t)gs.slot * kPkMaxK + koff + threadIdx.x) * kPkPartStride + blockIdx.x, bits);
   }
   __syncthreads(); // s_red may be reused by the next publish
 }
 
-// after the barrier: every CTA sums the partials of all CTAs in the same order -> s_out[k].
-// The (<= 5) loads of a lane are issued together: one L2 round trip per value, not one per load.
-__device__ __forceinline__ void pk_gather_nosync(int K, const double *part, int slot, int ncta, double *s_out) {
-  PK_SHARED(s_out);
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+// One warp: wait until every CTA's value k of the current round has arrived, return their sum (fixed order:
+// identical bits in every CTA).  All (<= 5) loads of a lane are in flight together.
+__device__ __forceinline__ double pk_poll_sum(const GridSync &gs, const double *part, int k) {
+  const int lane = threadIdx.x & 31;
   constexpr int kPer = (kPkPartStride + 31) / 32;
-  for (int k = warp; k < K; k += kPkWarps) {
-    const double *p = part + ((size_t)slot * kPkMaxK + k) * kPkPartStride;
-    double t[kPer];
+  const unsigned long long *p = (const unsigned long long *)part + ((size_t)gs.slot * kPkMaxK + k) * kPkPartStride;
+  unsigned long long t[kPer];
 #pragma unroll
-    for (int q = 0; q < kPer; ++q) {
-      const int c = lane + 32 * q;
-      t[q] = c < ncta ? __ldcg(p + c) : 0.0;
-    }
-    double v = 0.0;
+  for (int q = 0; q < kPer; ++q) t[q] = (unsigned)(lane + 32 * q) < gs.ncta ? kPkSentinel : 0ull;
+  const long long t0 = clock64();
+  int spins = 0;
+  for (;;) {
+    bool pending = false;
 #pragma unroll
     for (int q = 0; q < kPer; ++q)
-      if (lane + 32 * q < ncta) v += t[q];
+      if (t[q] == kPkSentinel) t[q] = ld_acquire_u64(p + lane + 32 * q);
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    for (int q = 0; q < kPer; ++q) pending |= t[q] == kPkSentinel;
+    if (!__any_sync(0xffffffffu, pending)) break;
+    if ((++spins & 31) == 0 && (clock64() - t0 > 4000000000LL || ld_acquire_u32(gs.ctr + 1) != 0u)) { // ~2 s
+      if (lane == 0) {
+        atomicExch(gs.ctr + 1, 1u);
+        atomicExch(gs.status, 4);
+        pk_s_abort = 1;
+      }
+      break;
+    }
+  }
+  double v = 0.0;
+#pragma unroll
+  for (int q = 0; q < kPer; ++q)
+    if ((unsigned)(lane + 32 * q) < gs.ncta) v += __longlong_as_double((long long)t[q]);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// after the publishes of a round: every CTA obtains the K totals in s_out (warp w takes k = w, w + 16, ...)
+__device__ __forceinline__ void pk_gather_nosync(int K, const double *part, const GridSync &gs, double *s_out) {
+  PK_SHARED(s_out);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int k = warp; k < K; k += kPkWarps) {
+    const double v = pk_poll_sum(gs, part, k);
     if (lane == 0) s_out[k] = v;
   }
 }
-__device__ __forceinline__ void pk_gather(int K, const double *part, int slot, int ncta, double *s_out) {
-  pk_gather_nosync(K, part, slot, ncta, s_out);
+// closes the round (call by all threads after the gather and a __syncthreads); false = aborted
+__device__ __forceinline__ bool pk_round_done(GridSync &gs) {
+  gs.slot = gs.slot == kPkSlots - 1 ? 0 : gs.slot + 1;
+  return pk_s_abort == 0;
+}
+__device__ __forceinline__ bool pk_gather(int K, const double *part, GridSync &gs, double *s_out) {
+  pk_gather_nosync(K, part, gs, s_out);
   __syncthreads();
+  return pk_round_done(gs);
 }
 
 // ---------------------------------------------------------------- in-kernel tridiagonal solve
@@ -562,13 +625,13 @@ __device__ __forceinline__ void pk_phase_a(const PkArgs &a, PkCtx<S> &c, GridSyn
       all[NC * W + k] = accM[k];
       all[(NC + 1) * W + k] = accA[k];
     }
-    pk_publish<(NC + 2) * W>(all, a.part, gs.slot, c.red(), 0);
+    pk_publish<(NC + 2) * W>(all, a.part, gs, c.red(), 0);
     return;
   }
-  if (NC > 0) pk_publish<NA * W>(acc, a.part, gs.slot, c.red(), i0 * W);
+  if (NC > 0) pk_publish<NA * W>(acc, a.part, gs, c.red(), i0 * W);
   if (FIRST) {
-    if (j > 0) pk_publish<W>(accM, a.part, gs.slot, c.red(), (j - 1) * W);
-    pk_publish<W>(accA, a.part, gs.slot, c.red(), j * W);
+    if (j > 0) pk_publish<W>(accM, a.part, gs, c.red(), (j - 1) * W);
+    pk_publish<W>(accA, a.part, gs, c.red(), j * W);
   }
 }
 
@@ -624,7 +687,7 @@ __device__ __forceinline__ void pk_phase_b(const PkArgs &a, PkCtx<S> &c, GridSyn
   nrm[0] = pk_loop_b<S, NC, LAST>(c.cnt, j, i0, c.X() + a.g.nx, c.Wt(), start + c.s0, (const S *)a.V + c.s0,
                                   a.colstride, (S *)a.V + (size_t)j * a.colstride + c.s0, c.gco());
   PKT(800 + j); // phase B site loop done
-  if (LAST) pk_publish<1>(nrm, a.part, gs.slot, c.red(), 0);
+  if (LAST) pk_publish<1>(nrm, a.part, gs, c.red(), 0);
 }
 
 #define PK_SWITCH_NC(nc, CALL)                                                                     \
@@ -665,9 +728,8 @@ __device__ bool pk_lanczos(const PkArgs &a, PkCtx<S> &c, GridSync &gs, S *start)
       }
     }
     PKT(200 + j); // phase A done (loop + publish)
-    if (!grid_barrier(gs)) return false;
-    PKT(300 + j); // barrier passed
-    pk_gather((j + 1) * W, a.part, gs.slot ^ 1, a.ncta, c.vals());
+    if (!pk_gather((j + 1) * W, a.part, gs, c.vals())) return false; // barrier + all-reduce in one
+    PKT(300 + j); // sums gathered
     // h_i = sums_i / beta_i ; w -= h_i v_i = (sums_i / beta_i^2) w_i ; alpha = Re h_j
     if (threadIdx.x <= j) {
       const int i = threadIdx.x;
@@ -683,15 +745,15 @@ __device__ bool pk_lanczos(const PkArgs &a, PkCtx<S> &c, GridSync &gs, S *start)
       PK_SWITCH_NC(nother - i0, (pk_phase_b<S, NC, true>(a, c, gs, start, j, i0)));
     }
     PKT(500 + j); // phase B done
-    if (!grid_barrier(gs)) return false;
-    PKT(600 + j); // barrier passed
-    // one latency window: warp 0 gathers ||w||^2 while warps 1.. fetch the next iteration's halo rows
-    if (j + 1 < a.m - 1 && threadIdx.x >= 32)
-      pk_load_halo_part<S>(a, c, pk_col<S>(a, start, j + 1), threadIdx.x - 32, kPkThreads - 32);
-    else
-      pk_gather_nosync(1, a.part, gs.slot ^ 1, a.ncta, c.vals());
-    if (threadIdx.x == 0) c.nrm2()[j + 1] = c.vals()[0];
+    // every warp polls ||w||^2 itself (its acquire then also covers the neighbours' rows of column j+1), so the
+    // next iteration's halo rows are fetched without another CTA-wide barrier in between
+    {
+      const double nv = pk_poll_sum(gs, a.part, 0);
+      if (threadIdx.x == 0) c.nrm2()[j + 1] = nv;
+      if (j + 1 < a.m - 1 && pk_s_abort == 0) pk_load_halo_nosync<S>(a, c, pk_col<S>(a, start, j + 1));
+    }
     __syncthreads();
+    if (!pk_round_done(gs)) return false;
     PKT(700 + j); // gathered
   }
   return true;
@@ -703,7 +765,27 @@ template <class S>
 __device__ __forceinline__ void pk_coefficients(const PkArgs &a, PkCtx<S> &c, int nfn, int f0, double t0r,
                                                 double t0i, int f1, double t1r, double t1i) {
   const int m = a.m;
-  if (threadIdx.x < 32) {
+  if (threadIdx.x < 32 && m <= 32) {
+    // register-resident QL (nls_kernels.cuh): lane i owns d_i, e_i; ~3x shorter than the shared-memory form
+    const int lane = threadIdx.x;
+    PkTri &T = c.tri;
+    double *const tz = T.Z;
+    const int ldz = T.ldz;
+    double dr = lane < m - 1 ? c.alpha()[lane] : 0.0; // T(m-1,m-1) = 0
+    double er = lane < m - 1 ? sqrt(c.nrm2()[lane + 1]) : 0.0;
+    if (lane < m)
+      for (int k = 0; k < m; ++k) tz[lane * ldz + k] = lane == k ? 1.0 : 0.0;
+    __syncwarp();
+    const bool ok = tridiag_warp_reg(dr, er, tz, ldz, m);
+    __syncwarp();
+    if (!ok && lane == 0) atomicExch(a.status, 1);
+    TridiagArgs ta;
+    ta.m = m; ta.W = 1; ta.nfn = nfn;
+    ta.fn[0] = f0; ta.tr[0] = t0r; ta.ti[0] = t0i;
+    ta.fn[1] = f1; ta.tr[1] = t1r; ta.ti[1] = t1i;
+    const double scale = lane < m ? sqrt(c.nrm2()[0]) / sqrt(c.nrm2()[lane]) : 0.0;
+    tridiag_coefs_reg(dr, tz, ldz, m, ta, scale, T.e, c.coef(), 2 * kMaxM);
+  } else if (threadIdx.x < 32) {
     const int lane = threadIdx.x;
     PkTri &T = c.tri;
     double *const td = T.d, *const te = T.e, *const tz = T.Z;
@@ -857,9 +939,8 @@ __device__ __forceinline__ void pk_carve(const PkArgs &a, PkCtx<S> &c, unsigned 
 // publish ||start||^2, barrier, gather -> nrm2[0]
 template <class S>
 __device__ __forceinline__ bool pk_start_norm(const PkArgs &a, PkCtx<S> &c, GridSync &gs, double (&nrm)[1]) {
-  pk_publish<1>(nrm, a.part, gs.slot, c.red(), 0);
-  if (!grid_barrier(gs)) return false;
-  pk_gather(1, a.part, gs.slot ^ 1, a.ncta, c.vals());
+  pk_publish<1>(nrm, a.part, gs, c.red(), 0);
+  if (!pk_gather(1, a.part, gs, c.vals())) return false;
   if (threadIdx.x == 0) c.nrm2()[0] = c.vals()[0];
   __syncthreads();
   return true;
@@ -889,7 +970,8 @@ __global__ void __launch_bounds__(kPkThreads, 1) k_pk_nlse(PkArgs a, double2 *sv
   extern __shared__ __align__(16) unsigned char pk_smem[];
   PkCtx<double2> c;
   pk_carve<double2>(a, c, pk_smem);
-  GridSync gs{a.bar, 0u, (unsigned)a.ncta, 0, a.status};
+  GridSync gs{a.bar, 0u, (unsigned)a.ncta, 0, a.status, min(kPkMaxK, 2 * a.m + 2)};
+  if (threadIdx.x == 0) pk_s_abort = 0;
   if (a.debug_fault && blockIdx.x == (unsigned)a.ncta - 1u) return; // test hook: one CTA never arrives
   const NlseParams p{0.5 * a.dt, a.s1, a.s2, a.kappa};
   double2 *ucur = (double2 *)a.u0, *unext = (double2 *)a.u1;
@@ -1032,7 +1114,8 @@ __global__ void __launch_bounds__(kPkThreads, 1) k_pk_gautschi(PkArgs a, double 
   extern __shared__ __align__(16) unsigned char pk_smem[];
   PkCtx<double> c;
   pk_carve<double>(a, c, pk_smem);
-  GridSync gs{a.bar, 0u, (unsigned)a.ncta, 0, a.status};
+  GridSync gs{a.bar, 0u, (unsigned)a.ncta, 0, a.status, min(kPkMaxK, 2 * a.m + 2)};
+  if (threadIdx.x == 0) pk_s_abort = 0;
   if (a.debug_fault && blockIdx.x == (unsigned)a.ncta - 1u) return; // test hook: one CTA never arrives
   double *u = (double *)a.u0, *up = (double *)a.u1 + c.s0, *accb = (double *)a.acc;
   PK_GLOBAL(u);
@@ -1150,7 +1233,8 @@ __global__ void __launch_bounds__(kPkThreads, 1) k_pk_sv(PkArgs a, double *b0, d
   extern __shared__ __align__(16) unsigned char pk_smem[];
   PkCtx<double> c;
   pk_carve<double>(a, c, pk_smem, 2 * a.g.nx); // both tiles carry halo rows: they swap roles every step
-  GridSync gs{a.bar, 0u, (unsigned)a.ncta, 0, a.status};
+  GridSync gs{a.bar, 0u, (unsigned)a.ncta, 0, a.status, min(kPkMaxK, 2 * a.m + 2)};
+  if (threadIdx.x == 0) pk_s_abort = 0;
   if (a.debug_fault && blockIdx.x == (unsigned)a.ncta - 1u) return; // test hook: one CTA never arrives
   double *buf[3] = {b0, b1, b2};
   double *xc = c.X() + a.g.nx, *pc = c.Wt() + a.g.nx; // u tile centre, u_past tile centre
@@ -1171,6 +1255,190 @@ __global__ void __launch_bounds__(kPkThreads, 1) k_pk_sv(PkArgs a, double *b0, d
     double *t = xc; xc = pc; pc = t; // u+ (written over u_past) becomes u, u becomes u_past
     if (!grid_barrier(gs)) return;   // starts with __syncthreads: all tile reads of this step are done
     p = (p + 1) % 3;
+  }
+}
+
+
+// ---------------------------------------------------------------- Stoermer-Verlet, 2D, temporally blocked ("sv2")
+// u+ = 2u - u_past + tau^2 (L u - m f(u)) followed by the no-flux copy (sg_single_sv_solver.hpp:9-19,
+// kg_sv_solver.hpp:13-21, boundaries.hpp:40-57) for 2D grids with the uniform Laplacian, nsteps steps per launch.
+// One CTA per SM owns a w x h TILE of the grid; u, u_past and m of the tile PLUS a halo ring of depth s stay in
+// shared memory for the whole launch.  The CTA advances s time steps between two exchanges: step t (1..s)
+// updates the tile grown by s - t rings (redundant rim compute, the valid region shrinks by one ring per step),
+// so per s steps there is ONE neighbour synchronisation and ONE halo exchange through L2 -- no HBM traffic at
+// all in steady state, no grid-wide barrier: a CTA only waits for the progress counters of its <= 8 neighbour
+// tiles (release/acquire).  Tiles are written to two global buffer sets in turn (set b % 2 after block b), so a
+// neighbour still reading block b's halo never races with block b+1's stores.
+// Only true interior sites are ever evaluated (boundary sites take the value of their clamped interior site, the
+// fused form of neumann_bc_no_velocity), so the stencil needs none of the boundary-row logic: all four neighbours
+// exist and the diagonal is -4 (laplacians.hpp:23-30 applies -3 to ring rows only).
+struct Sv2Plan {
+  int px, py, w, h, s; // tiles in x / y, tile extent, temporal block depth
+  size_t smem;
+};
+struct Sv2Args {
+  int nx, ny, nsteps;
+  Sv2Plan pl;
+  double sc, tau2;
+  const double *mf;
+  double *su[3], *sp[3];     // buffer sets (u, u_past): [0] = input, [1], [2] = ping-pong outputs
+  unsigned long long *prog;  // [ncta] blocks completed by each CTA (zeroed before the launch)
+  unsigned *abort_flag;
+  int *status;
+  int debug_fault;
+};
+
+inline size_t sv2_smem_bytes(int w, int h, int s) { return (size_t)3 * (w + 2 * s) * (h + 2 * s) * 8 + 64; }
+
+// host: choose the tiling and the block depth.  Cost model in site updates per step and SM: the grown regions
+// average (w+s)(h+s) sites, one exchange (neighbour wait + halo reload + tile store) costs about kSync updates.
+inline bool sv2_plan(int nx, int ny, int nsm, size_t smem_max, Sv2Plan &best) {
+  const double kSync = 6000.0;
+  double best_cost = 1e300;
+  bool found = false;
+  for (int py = 1; py <= nsm; ++py) {
+    int px = nsm / py;
+    if (px < 1) break;
+    int w = (nx + px - 1) / px, h = (ny + py - 1) / py;
+    if (w < 4) w = nx < 4 ? nx : 4;
+    if (h < 4) h = ny < 4 ? ny : 4;
+    px = (nx + w - 1) / w;
+    const int pyy = (ny + h - 1) / h;
+    if ((long long)px * pyy > nsm) continue;
+    // the last tile of a row / column may be narrower: it must still hold the clamped site of its boundary sites
+    if ((nx - (px - 1) * w) < 2 && px > 1) continue;
+    if ((ny - (pyy - 1) * h) < 2 && pyy > 1) continue;
+    const int lastw = nx - (px - 1) * w, lasth = ny - (pyy - 1) * h;
+    for (int s = 1; s <= 8; ++s) {
+      if (s > (lastw < w ? lastw : w) || s > (lasth < h ? lasth : h)) break; // halos reach adjacent tiles only
+      const size_t sm = sv2_smem_bytes(w, h, s);
+      if (sm > smem_max) break;
+      const double cost = (double)(w + s) * (h + s) + kSync / s;
+      if (cost < best_cost) {
+        best_cost = cost;
+        best = Sv2Plan{px, pyy, w, h, s, sm};
+        found = true;
+      }
+    }
+  }
+  return found;
+}
+
+template <int EQ>
+__global__ void __launch_bounds__(kPkThreads, 1) k_pk_sv2(Sv2Args a) {
+  extern __shared__ __align__(16) unsigned char pk_smem[];
+  __shared__ int s_ok;
+  const int w = a.pl.w, h = a.pl.h, S = a.pl.s, nx = a.nx, ny = a.ny;
+  const int P = w + 2 * S, H = h + 2 * S;
+  double *A = (double *)pk_smem, *B = A + (size_t)P * H, *M = B + (size_t)P * H;
+  const int tx = blockIdx.x % a.pl.px, ty = blockIdx.x / a.pl.px;
+  const int x0 = tx * w, x1 = min(nx, x0 + w), y0 = ty * h, y1 = min(ny, y0 + h);
+  const int lx = threadIdx.x & 31, ly = threadIdx.x >> 5;
+  const int org = S * P + S - y0 * P - x0; // smem index of grid site (x, y) = org + y*P + x
+  if (a.debug_fault && blockIdx.x == gridDim.x - 1) return; // test hook: this CTA never reports progress
+  // whole grown tile of u, u_past (input set) and m
+  {
+    const int gx0 = max(0, x0 - S), gx1 = min(nx, x1 + S), gy0 = max(0, y0 - S), gy1 = min(ny, y1 + S);
+    for (int y = gy0 + ly; y < gy1; y += kPkWarps)
+      for (int x = gx0 + lx; x < gx1; x += 32) {
+        const size_t gi = (size_t)y * nx + x;
+        const int si = org + y * P + x;
+        A[si] = __ldcg(a.su[0] + gi);
+        B[si] = __ldcg(a.sp[0] + gi);
+        M[si] = __ldcg(a.mf + gi);
+      }
+  }
+  __syncthreads();
+  const double sc = a.sc, tau2 = a.tau2, dg = -4.0 * a.sc;
+  int done = 0;
+  for (int b = 0; done < a.nsteps; ++b) {
+    const int sb = min(S, a.nsteps - done);
+    if (b > 0) {
+      // wait for the <= 8 neighbour tiles to have stored block b-1, then refresh the halo rings from their set
+      if (threadIdx.x < 9 && threadIdx.x != 4) {
+        const int nxt = tx + (int)(threadIdx.x % 3) - 1, nyt = ty + (int)(threadIdx.x / 3) - 1;
+        if (nxt >= 0 && nxt < a.pl.px && nyt >= 0 && nyt < a.pl.py) {
+          const unsigned long long *pp = a.prog + (nyt * a.pl.px + nxt);
+          const long long t0 = clock64();
+          while (ld_acquire_u64(pp) < (unsigned long long)b) {
+            if (clock64() - t0 > 4000000000LL || ld_acquire_u32(a.abort_flag) != 0u) { // ~2 s
+              atomicExch(a.abort_flag, 1u);
+              atomicExch(a.status, 4); // poisons the handle (nls.h)
+              break;
+            }
+          }
+        }
+      }
+      __syncthreads();
+      const double *ru = a.su[1 + ((b - 1) & 1)], *rp = a.sp[1 + ((b - 1) & 1)];
+      const int gx0 = max(0, x0 - sb), gx1 = min(nx, x1 + sb), gy0 = max(0, y0 - sb), gy1 = min(ny, y1 + sb);
+      for (int y = gy0 + ly; y < gy1; y += kPkWarps) {
+        const bool yin = y >= y0 && y < y1;
+        for (int x = gx0 + lx; x < gx1; x += 32) {
+          if (yin && x >= x0 && x < x1) continue; // own tile: already in shared memory
+          const size_t gi = (size_t)y * nx + x;
+          const int si = org + y * P + x;
+          A[si] = __ldcg(ru + gi);
+          B[si] = __ldcg(rp + gi);
+        }
+      }
+      if (threadIdx.x == 0) s_ok = ld_acquire_u32(a.abort_flag) == 0u;
+      __syncthreads();
+      if (!s_ok) return; // uniform: the whole CTA unwinds
+    }
+    for (int t = 1; t <= sb; ++t) {
+      const int g = sb - t;
+      const int rx0 = max(0, x0 - g), rx1 = min(nx, x1 + g), ry0 = max(0, y0 - g), ry1 = min(ny, y1 + g);
+      // pass 1: interior sites of the domain inside the region
+      const int ix0 = max(rx0, 1), ix1 = min(rx1, nx - 1), iy0 = max(ry0, 1), iy1 = min(ry1, ny - 1);
+      for (int y = iy0 + ly; y < iy1; y += kPkWarps) {
+        const int rowi = org + y * P;
+#pragma unroll 2
+        for (int x = ix0 + lx; x < ix1; x += 32) {
+          const int si = rowi + x;
+          const double uc = A[si];
+          double acc = sc * A[si - P];           // same accumulation order as stencil_site_f: y-, x-, centre, x+, y+
+          acc = fma(sc, A[si - 1], acc);
+          acc = fma(dg, uc, acc);
+          acc = fma(sc, A[si + 1], acc);
+          acc = fma(sc, A[si + P], acc);
+          const double buf = acc - M[si] * f_real<EQ>(uc);
+          B[si] = 2 * uc - B[si] + tau2 * buf;   // u+ over u_past, in place
+        }
+      }
+      __syncthreads();
+      // pass 2: boundary sites of the domain inside the region take their clamped site's new value
+      if (rx0 == 0 || rx1 == nx || ry0 == 0 || ry1 == ny) {
+        if (rx0 == 0 || rx1 == nx)
+          for (int y = ry0 + (int)threadIdx.x; y < ry1; y += kPkThreads) {
+            const int yc = min(max(y, 1), ny - 2);
+            if (rx0 == 0) B[org + y * P + 0] = B[org + yc * P + 1];
+            if (rx1 == nx) B[org + y * P + nx - 1] = B[org + yc * P + nx - 2];
+          }
+        if (ry0 == 0 || ry1 == ny)
+          for (int x = rx0 + (int)threadIdx.x; x < rx1; x += kPkThreads) {
+            const int xc = min(max(x, 1), nx - 2);
+            if (ry0 == 0) B[org + 0 * P + x] = B[org + 1 * P + xc];
+            if (ry1 == ny) B[org + (ny - 1) * P + x] = B[org + (ny - 2) * P + xc];
+          }
+        __syncthreads();
+      }
+      double *tmp = A; A = B; B = tmp; // u+ becomes u, u becomes u_past
+    }
+    // store the tile (u and u_past) to this block's set; neighbours read their halo rings from it
+    {
+      double *wu = a.su[1 + (b & 1)], *wp = a.sp[1 + (b & 1)];
+      for (int y = y0 + ly; y < y1; y += kPkWarps)
+        for (int x = x0 + lx; x < x1; x += 32) {
+          const size_t gi = (size_t)y * nx + x;
+          const int si = org + y * P + x;
+          wu[gi] = A[si];
+          wp[gi] = B[si];
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) st_release_u64(a.prog + blockIdx.x, (unsigned long long)(b + 1));
+    done += sb;
   }
 }
 

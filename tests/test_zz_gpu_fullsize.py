@@ -158,3 +158,50 @@ def test_persistent_kernel_long_run_is_split():
     for k in (30000, 40000):
         e2.step(1e-4, k)
     assert np.array_equal(e.get(), e2.get())
+
+
+# ---- temporally blocked Stoermer-Verlet kernel (k_pk_sv2: 2D tiles + halo rings in shared memory) ------------
+@pytest.mark.parametrize("nx,ny,steps,eq", [(131, 131, 61, EQ.SGE), (16, 16, 9, EQ.SGE), (20, 37, 23, EQ.KGE),
+                                            (300, 77, 40, EQ.PHI4), (512, 512, 50, EQ.SGE_DOUBLE),
+                                            (257, 640, 33, EQ.SGE_SINH), (1024, 1024, 37, EQ.SGE)])
+def test_sv2_tiles_match_oracle_and_graph_path(oracle_lib, nx, ny, steps, eq):
+    """default Stoermer-Verlet path for 2D uniform grids: every tile shape (ragged last tiles, tiles on the
+    domain boundary, non-square grids), step counts that are not multiples of the block depth, several
+    nls_step calls (buffer-role exchange), against the oracle and the one-kernel-per-step graph path."""
+    L, dt = 10.0, 1e-3
+    big = max(nx, ny)
+    u0 = ics.kink_2d(big, L)[:ny, :nx][None]
+    if eq in (EQ.KGE, EQ.PHI4, EQ.SGE_SINH):
+        u0 = 0.2 * u0
+    v0 = 0.05 * np.cos(u0)
+    mf = 1.0 + 0.2 * np.random.default_rng(1).standard_normal(nx * ny)
+    outs = []
+    for flags in (0, nls_b200.FLAG_NO_PERSISTENT):
+        d = Desc.make(nx, ny, dx=2 * L / (big - 1), equation=eq, integrator=INT.SV, dt=dt, flags=flags)
+        e = Engine(d)
+        e.set(FIELD.M, mf); e.set(FIELD.U, u0); e.set(FIELD.V, v0)
+        k1 = steps // 3
+        for k in (k1, 1, steps - k1 - 1):
+            e.step(dt, k)
+        outs.append((e.get(), e.get(FIELD.U_PAST), e.get(FIELD.V), e.launch_count()))
+    assert outs[0][3] == 3 + 2, "temporally blocked kernel: one launch per nls_step call (+ set V, get V)"
+    o = oracle_lib.Oracle(d)
+    o.set(FIELD.M, mf); o.set(FIELD.U, u0); o.set(FIELD.V, v0)
+    o.step(dt, steps)
+    eu, ep = rel_l2(outs[0][0], o.get()), rel_l2(outs[0][1], o.get(FIELD.U_PAST))
+    print(f"sv2 {nx}x{ny} x{steps}: vs oracle u {eu:.3e} u_past {ep:.3e}; vs graph path {rel_l2(outs[0][0], outs[1][0]):.3e}")
+    assert eu <= 1e-11 and ep <= 1e-11
+    assert rel_l2(outs[0][2], o.get(FIELD.V)) <= 1e-7
+    assert rel_l2(outs[0][0], outs[1][0]) <= 1e-13
+
+
+def test_sv2_barrier_timeout_is_reported():
+    n = 128
+    d = Desc.make(n, n, L=10.0, equation=EQ.SGE, integrator=INT.SV, dt=1e-3, flags=nls_b200.FLAG_DEBUG_PK_FAULT)
+    e = Engine(d)
+    u0 = ics.kink_2d(n, 10.0)[None]
+    e.set(FIELD.M, np.ones(d.n)); e.set(FIELD.U, u0); e.set(FIELD.V, np.zeros_like(u0))
+    with pytest.raises(nls_b200.NlsError, match="grid barrier"):
+        e.step(1e-3, 40)
+    with pytest.raises(nls_b200.NlsError, match="poisoned"):
+        e.get()
