@@ -205,14 +205,6 @@ def measured_traffic(workload):
         return None, None
 
 
-def pinned_like(a):
-    import torch
-    t = torch.empty(a.shape, dtype=torch.complex128 if np.iscomplexobj(a) else torch.float64, pin_memory=True)
-    out = t.numpy()
-    out[...] = a
-    return out, t  # keep the tensor alive
-
-
 def cpu_baseline(w, budget_s=20.0):
     """The oracle (CPU restatement of the reference's Eigen path, kind 'port') timed on ONE host
     thread -- how the reference's host path actually executes (no -fopenmp in its CMake) -- on a
@@ -338,42 +330,70 @@ def measure(cx, name, w, K, W, repeats, sample_clocks):
         ms_runs.append(cx.max_over_ranks([ms])[0])
     launches = (eng.launch_count() - l0) // repeats
     tma_launches = eng.tma_launch_count()
-    # ---- end to end through the C ABI with pinned HOST buffers: per segment of `seg` steps,
-    # H2D of the state (u, u_past / u) and D2H of the result (u, v / u)
+    # ---- end to end through the C ABI with pinned HOST buffers: per segment of `seg` steps the state (u [, u_past])
+    # is uploaded from page-locked host memory and the result (u [, v, u_past]) is read back to page-locked host
+    # memory.  "e2e": the asynchronous API (nls_set_field_async / nls_get_field_async: staging + snapshot rings, the
+    # copies overlap the neighbouring segments' steps); "e2e_blocking": nls_set_field / nls_get_field per segment.
     seg = min(w["seg"], K)
     nseg = max(1, K // seg)
-    hu, _k1 = pinned_like(eng.get(FIELD.U))
     real = not d.is_complex
+    st = eng.get(FIELD.U)
+    h_in = nls_b200.pinned_empty(st.shape, st.dtype)
+    h_in[...] = st
+    h_out = [nls_b200.pinned_empty(st.shape, st.dtype) for _ in range(2)]
+    pins = [h_in] + h_out
     if real:
-        hp, _k2 = pinned_like(eng.get(FIELD.U_PAST))
-        hv, _k3 = pinned_like(np.zeros_like(hu))
-    for _ in range(2):  # warm the copy path
-        eng.set(FIELD.U, hu)
-        eng.step(dt, 1)
-        eng.get_into(FIELD.U, hu)
-    e2e_runs = []
-    for _ in range(min(repeats, 3)):
-        cx.barrier()
-        t0 = time.perf_counter()
-        for _ in range(nseg):
-            eng.set(FIELD.U, hu)
+        hp_in = nls_b200.pinned_empty(st.shape, st.dtype)
+        hp_in[...] = eng.get(FIELD.U_PAST)
+        hv_out = [nls_b200.pinned_empty(st.shape, st.dtype) for _ in range(2)]
+        hp_out = [nls_b200.pinned_empty(st.shape, st.dtype) for _ in range(2)]
+        pins += [hp_in] + hv_out + hp_out
+    del st
+
+    def e2e_async():
+        for k in range(nseg):
+            eng.set_async(FIELD.U, h_in)
             if real:
-                eng.set(FIELD.U_PAST, hp)
+                eng.set_async(FIELD.U_PAST, hp_in)
+            eng.step(dt, seg, sync=False)
+            eng.get_async(FIELD.U, h_out[k & 1])
+            if real:
+                eng.get_async(FIELD.V, hv_out[k & 1])
+                eng.get_async(FIELD.U_PAST, hp_out[k & 1])
+        eng.wait()
+
+    def e2e_blocking():
+        for k in range(nseg):
+            eng.set(FIELD.U, h_in)
+            if real:
+                eng.set(FIELD.U_PAST, hp_in)
             eng.step(dt, seg)
-            eng.get_into(FIELD.U, hu)
+            eng.get_into(FIELD.U, h_out[k & 1])
             if real:
-                eng.get_into(FIELD.V, hv)
-                eng.get_into(FIELD.U_PAST, hp)
-        cx.barrier()
-        e2e_runs.append(cx.max_over_ranks([time.perf_counter() - t0])[0])
+                eng.get_into(FIELD.V, hv_out[k & 1])
+                eng.get_into(FIELD.U_PAST, hp_out[k & 1])
+
+    e2e_runs, e2e_blk_runs = [], []
+    for fn, runs in ((e2e_async, e2e_runs), (e2e_blocking, e2e_blk_runs)):
+        fn()  # warm the copy path (allocates the rings)
+        for _ in range(min(repeats, 3)):
+            cx.barrier()
+            t0 = time.perf_counter()
+            fn()
+            cx.barrier()
+            runs.append(cx.max_over_ranks([time.perf_counter() - t0])[0])
+    hbytes = h_in.nbytes
     clocks = sampler.stop() if sampler else None
     eng.close()
+    for a in pins:
+        nls_b200.pinned_free(a)
     if rank != 0:
         return None
-    h2d = hu.nbytes * (2 if real else 1)
-    d2h = hu.nbytes * (3 if real else 1)
+    h2d = hbytes * (2 if real else 1)
+    d2h = hbytes * (3 if real else 1)
     t_ms = float(np.median(ms_runs))
     t_e2e = float(np.median(e2e_runs))
+    t_e2e_blk = float(np.median(e2e_blk_runs))
     value = sites * world * K / (t_ms * 1e-3)
     e2e = sites * world * seg * nseg / t_e2e
     bpss, bpss_model = bytes_per_site_step(w), bytes_per_site_step(w, model=True)
@@ -397,8 +417,10 @@ def measure(cx, name, w, K, W, repeats, sample_clocks):
     return {"value": value, "ms_per_step": t_ms / K, "ms_per_step_runs": [x / K for x in ms_runs],
             "e2e": {"value": e2e, "unit": "site-steps/s", "h2d_bytes_per_step": h2d / seg,
                     "d2h_bytes_per_step": d2h / seg, "segment_steps": seg,
-                    "note": "per segment: pinned-host state -> device, seg steps, state(+velocity) -> pinned host; "
-                            "wall clock, max over ranks, median of 3"},
+                    "blocking_value": sites * world * seg * nseg / t_e2e_blk,
+                    "note": "per segment: pinned-host state -> device, seg steps, state(+velocity) -> pinned host through "
+                            "nls_set_field_async / nls_get_field_async (copies overlap the steps); blocking_value: the same "
+                            "with nls_set_field / nls_get_field; wall clock, max over ranks, median of 3"},
             "gpu_launches": int(launches), "tma_staged_launches_total": int(tma_launches),
             "clocks": clocks, "roofline": roof, "steps": K, "warmup": W, "sites_per_gpu": sites}
 

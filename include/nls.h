@@ -170,7 +170,8 @@ int nls_device_count(void);
 int nls_create(const nls_desc *desc, nls_handle *out);
 int nls_destroy(nls_handle h);
 
-/* host -> device. bytes must equal the field's size (batch*n*scalar for U/U_PAST/V, n*8 for M/C). */
+/* host -> device. bytes must equal the field's size (batch*n*scalar for U/U_PAST/V, n*8 for M/C).
+ * Pageable source: returns after the copy.  Page-locked source: asynchronous (see nls_set_field_async). */
 int nls_set_field(nls_handle h, int field, const void *host_src, size_t bytes);
 /* device -> host (synchronous on the handle's stream). */
 int nls_get_field(nls_handle h, int field, void *host_dst, size_t bytes);
@@ -193,6 +194,19 @@ int nls_matfunc(nls_handle h, int fn, double t_re, double t_im, const void *host
  * beta[j+1]=T(j+1,j)); trajectory 0 of the batch only. Any output may be NULL. */
 int nls_lanczos(nls_handle h, const void *host_in, void *host_V, void *host_alpha,
                 double *host_beta);
+/* the same two with DEVICE pointers on the handle's device (the reference's signatures: DeviceSpMV<T>::multiply
+ * device/spmv.hpp:65-72, MatrixFunctionApplicator*::apply device/matfunc_complex.hpp:155-156, matfunc_real.hpp:171);
+ * stream-ordered on the handle's stream (nls_stream), no host synchronisation */
+int nls_stencil_apply_dev(nls_handle h, const void *dev_x, void *dev_y);
+int nls_matfunc_dev(nls_handle h, int fn, double t_re, double t_im, const void *dev_in, void *dev_out);
+/* CSR compatibility check for the B2 class layer: rel_err = max|CSR x - L x| / max|L x| for a deterministic
+ * pseudo-random x, L = the handle's matrix-free stencil.  The reference ships an assembled CSR to its solver
+ * classes (sg_single_dev.hpp:28-31, device/spmv.hpp:30-52); this engine accepts one only if it IS its stencil.
+ * values: double (values_complex = 0) or interleaved complex128 (1); arrays on the host (on_device = 0) or device. */
+int nls_csr_residual(nls_handle h, const int *row_ptr, const int *col_ind, const void *values, uint32_t n, uint64_t nnz,
+                     int values_complex, int on_device, double *rel_err);
+int nls_pointer_is_device(const void *p);
+int nls_memcpy_to_host(void *dst, const void *dev_src, size_t bytes);
 /* out[batch] */
 int nls_reduce(nls_handle h, int what, double *out);
 
@@ -206,6 +220,28 @@ int nls_reduce(nls_handle h, int what, double *out);
  * handles. */
 int nls_get_field_resampled(nls_handle h, int field, uint32_t tnx, uint32_t tny, uint32_t tnz, void *host_dst,
                             size_t bytes);
+
+/* ---- asynchronous snapshot egress / state upload ----
+ * Replaces the blocking cudaMemcpy per snapshot of nlsolvers/device/include/nlse_dev.hpp:323-334
+ * (store_snapshot_online) and sg_single_dev.hpp:96-100: the snapshot is copied device-to-device into a 2-deep
+ * ring at this point of the handle's stream order (i.e. after all steps issued so far) and leaves for the host
+ * on a separate D2H stream while the following nls_step calls run.  dst should be page-locked
+ * (nls_host_alloc / nls_host_register); it holds the data after the next nls_wait / nls_sync.
+ * dst_traj_stride: bytes between consecutive trajectories of a batch in dst (0 = dense [batch][n]), so an
+ * ensemble's snapshot lands directly in a (B, num_snapshots, ...) trajectory file image.
+ * nls_set_field_async uploads through a 2-deep staging ring on an H2D stream (the copy overlaps the steps still
+ * running); the source must stay unchanged until nls_wait.  Fields: U, U_PAST, M, C. */
+int nls_get_field_async(nls_handle h, int field, void *host_dst, size_t bytes, size_t dst_traj_stride);
+int nls_get_field_resampled_async(nls_handle h, int field, uint32_t tnx, uint32_t tny, uint32_t tnz, void *host_dst,
+                                  size_t bytes, size_t dst_traj_stride);
+int nls_set_field_async(nls_handle h, int field, const void *host_src, size_t bytes);
+/* waits for the steps AND the asynchronous transfers issued so far; reports device-side failures (= nls_sync) */
+int nls_wait(nls_handle h);
+/* page-locked host memory for callers without a CUDA runtime of their own */
+int nls_host_alloc(void **out, size_t bytes);
+int nls_host_free(void *p);
+int nls_host_register(void *p, size_t bytes);
+int nls_host_unregister(void *p);
 
 /* number of kernel launches issued (directly or through graph replays) since creation */
 uint64_t nls_launch_count(nls_handle h);

@@ -126,6 +126,19 @@ _SIGS = {
     "nls_tma_launch_count": (C.c_uint64, [_vp]),
     "nls_stream": (_vp, [_vp]),
     "nls_step_timed": (C.c_int, [_vp, C.c_double, C.c_uint32, C.POINTER(C.c_float)]),
+    "nls_get_field_async": (C.c_int, [_vp, C.c_int, _vp, _sz, _sz]),
+    "nls_get_field_resampled_async": (C.c_int, [_vp, C.c_int, C.c_uint32, C.c_uint32, C.c_uint32, _vp, _sz, _sz]),
+    "nls_set_field_async": (C.c_int, [_vp, C.c_int, _vp, _sz]),
+    "nls_wait": (C.c_int, [_vp]),
+    "nls_host_alloc": (C.c_int, [C.POINTER(_vp), _sz]),
+    "nls_host_free": (C.c_int, [_vp]),
+    "nls_host_register": (C.c_int, [_vp, _sz]),
+    "nls_host_unregister": (C.c_int, [_vp]),
+    "nls_stencil_apply_dev": (C.c_int, [_vp, _vp, _vp]),
+    "nls_matfunc_dev": (C.c_int, [_vp, C.c_int, C.c_double, C.c_double, _vp, _vp]),
+    "nls_csr_residual": (C.c_int, [_vp, _vp, _vp, _vp, C.c_uint32, C.c_uint64, C.c_int, C.c_int, _dp]),
+    "nls_pointer_is_device": (C.c_int, [_vp]),
+    "nls_memcpy_to_host": (C.c_int, [_vp, _vp, _sz]),
     "nls_slab_export": (C.c_int, [_vp, _vp]),
     "nls_slab_connect": (C.c_int, [_vp, _vp, C.c_int, C.c_int]),
 }
@@ -152,6 +165,30 @@ def load_library(path=None):
 
 def _ptr(a):
     return a.ctypes.data_as(_vp)
+
+
+def pinned_empty(shape, dtype):
+    """page-locked numpy array (nls_host_alloc); keep the returned array alive, free with pinned_free()."""
+    lib = load_library()
+    n = int(np.prod(shape)) * np.dtype(dtype).itemsize
+    p = _vp()
+    rc = lib.nls_host_alloc(C.byref(p), max(n, 1))
+    if rc != 0:
+        raise NlsError(f"nls error {rc}: {lib.nls_last_error().decode()}")
+    buf = (C.c_char * max(n, 1)).from_address(p.value)
+    a = np.frombuffer(buf, dtype=dtype, count=int(np.prod(shape))).reshape(shape)
+    a.flags.writeable = True
+    _pinned[a.ctypes.data] = p
+    return a
+
+
+def pinned_free(a):
+    p = _pinned.pop(a.ctypes.data, None)
+    if p is not None:
+        load_library().nls_host_free(p)
+
+
+_pinned = {}
 
 
 class Engine:
@@ -206,6 +243,24 @@ class Engine:
         self._check(self.lib.nls_get_field(self.h, field, _ptr(out), out.nbytes))
         return out
 
+    def get_async(self, field, out, traj_stride=0):
+        """snapshot -> caller-provided (page-locked) array on the D2H stream; valid after wait()."""
+        assert out.flags.c_contiguous
+        nbytes = self.desc.batch * self.desc.n * np.dtype(self.desc.dtype).itemsize
+        self._check(self.lib.nls_get_field_async(self.h, field, _ptr(out), nbytes, traj_stride))
+
+    def get_resampled_async(self, field, tnx, tny, tnz, out, traj_stride=0):
+        nbytes = self.desc.batch * tnx * tny * tnz * np.dtype(self.desc.dtype).itemsize
+        self._check(self.lib.nls_get_field_resampled_async(self.h, field, tnx, tny, tnz, _ptr(out), nbytes, traj_stride))
+
+    def set_async(self, field, arr):
+        """upload through the H2D staging ring; `arr` must stay unchanged until wait()."""
+        assert arr.flags.c_contiguous
+        self._check(self.lib.nls_set_field_async(self.h, field, _ptr(arr), arr.nbytes))
+
+    def wait(self):
+        self._check(self.lib.nls_wait(self.h))
+
     def step(self, dt, nsteps=1, sync=True):
         self._check(self.lib.nls_step(self.h, dt, nsteps))
         if sync:
@@ -241,6 +296,17 @@ class Engine:
         self._check(self.lib.nls_lanczos(self.h, _ptr(x), _ptr(V), _ptr(alpha),
                                          beta.ctypes.data_as(_dp)))
         return V, alpha, beta
+
+    def csr_residual(self, csr):
+        """max |CSR x - L x| / max |L x| for a scipy.sparse CSR matrix (host arrays) -- nls_csr_residual"""
+        rp = np.ascontiguousarray(csr.indptr, dtype=np.int32)
+        ci = np.ascontiguousarray(csr.indices, dtype=np.int32)
+        cplx = np.iscomplexobj(csr.data)
+        val = np.ascontiguousarray(csr.data, dtype=np.complex128 if cplx else np.float64)
+        err = C.c_double()
+        self._check(self.lib.nls_csr_residual(self.h, _ptr(rp), _ptr(ci), _ptr(val), csr.shape[0], len(val), int(cplx), 0,
+                                              C.byref(err)))
+        return err.value
 
     def reduce(self, what):
         out = np.empty(self.desc.batch, dtype=np.float64)

@@ -82,6 +82,15 @@ struct nls_engine {
   double *pk_part = nullptr;
   unsigned *pk_bar = nullptr;
   uint64_t pk_launches = 0;
+  // asynchronous transfers (nls_get_field_async / nls_set_field_async): a 2-deep device-side snapshot ring drained
+  // by a D2H stream, a 2-deep staging ring filled by an H2D stream; the compute stream only does D2D copies
+  cudaStream_t d2h_stream = nullptr, h2d_stream = nullptr;
+  void *ring[2] = {nullptr, nullptr}, *stage[2] = {nullptr, nullptr};
+  size_t ring_bytes[2] = {0, 0}, stage_bytes[2] = {0, 0};
+  cudaEvent_t ring_ready[2] = {nullptr, nullptr}, ring_done[2] = {nullptr, nullptr};
+  cudaEvent_t stage_ready[2] = {nullptr, nullptr}, stage_free[2] = {nullptr, nullptr};
+  int ring_next = 0, stage_next = 0;
+  bool async_used = false;
   // temporally blocked 2D Stoermer-Verlet kernel (k_pk_sv2)
   bool sv2_ok = false;
   Sv2Plan sv2{};
@@ -769,6 +778,18 @@ int poisoned(nls_engine *e) {
   }
 }
 
+// device -> dense device buffer, no synchronisation
+int copy_out_async(nls_engine *e, void *dst, const void *dev, size_t esz, int nb) {
+  if (e->g.stride == e->g.n) {
+    CU(cudaMemcpyAsync(dst, dev, (size_t)nb * e->g.n * esz, cudaMemcpyDeviceToDevice, e->stream));
+  } else {
+    for (int b = 0; b < nb; ++b)
+      CU(cudaMemcpyAsync((char *)dst + (size_t)b * e->g.n * esz, (const char *)dev + ((size_t)b * e->g.stride + e->g.halo) * esz,
+                         e->g.n * esz, cudaMemcpyDeviceToDevice, e->stream));
+  }
+  return NLS_OK;
+}
+
 int check_status(nls_engine *e) {
   if (e->poison) return poisoned(e);
   int st = 0;
@@ -796,6 +817,8 @@ int nls_destroy(nls_handle e) {
   if (!e) return NLS_OK;
   cudaSetDevice(e->d.device);
   if (e->stream) cudaStreamSynchronize(e->stream);
+  if (e->d2h_stream) cudaStreamSynchronize(e->d2h_stream);
+  if (e->h2d_stream) cudaStreamSynchronize(e->h2d_stream);
   for (auto &ge : e->gexec)
     if (ge) cudaGraphExecDestroy(ge);
   if (e->arena) { // sub-allocations of the exchange arena
@@ -809,6 +832,14 @@ int nls_destroy(nls_handle e) {
                   e->pk_part, e->pk_bar, e->sv2_prog, e->arena, e->slab_dev, e->slab_scratch, e->rs};
   for (void *p : ptrs)
     if (p) cudaFree(p);
+  for (int k = 0; k < 2; ++k) {
+    if (e->ring[k]) cudaFree(e->ring[k]);
+    if (e->stage[k]) cudaFree(e->stage[k]);
+    for (cudaEvent_t ev : {e->ring_ready[k], e->ring_done[k], e->stage_ready[k], e->stage_free[k]})
+      if (ev) cudaEventDestroy(ev);
+  }
+  if (e->d2h_stream) cudaStreamDestroy(e->d2h_stream);
+  if (e->h2d_stream) cudaStreamDestroy(e->h2d_stream);
   if (e->stream) cudaStreamDestroy(e->stream);
   delete e;
   return NLS_OK;
@@ -922,7 +953,7 @@ int nls_create(const nls_desc *desc, nls_handle *out) {
   return NLS_OK;
 }
 
-static int set_field_impl(nls_handle e, int field, const void *src, size_t bytes, bool dev) {
+static int set_field_impl(nls_handle e, int field, const void *src, size_t bytes, bool dev, bool sync = true) {
   if (!e || !src) return fail(NLS_ERR_ARG, "null argument");
   if (e->poison) return poisoned(e);
   CU(cudaSetDevice(e->d.device));
@@ -939,7 +970,7 @@ static int set_field_impl(nls_handle e, int field, const void *src, size_t bytes
       if (e->d.integrator != NLS_INT_SEWI) return fail(NLS_ERR_STATE, "U_PAST: real equations or NLS_INT_SEWI only");
       rc = copy_in(e, e->u[(e->phase + 2) % 3], src, 16, e->batch, dev);
       if (rc) return rc;
-      CU(cudaStreamSynchronize(e->stream));
+      if (sync) CU(cudaStreamSynchronize(e->stream));
       e->sewi_started = true; // explicit u-: no SS2 start-up step
       return NLS_OK;
     }
@@ -972,7 +1003,7 @@ static int set_field_impl(nls_handle e, int field, const void *src, size_t bytes
     CU(cudaGetLastError());
   }
   e->start_valid = false;
-  CU(cudaStreamSynchronize(e->stream)); // host buffer may be reused by the caller
+  if (sync) CU(cudaStreamSynchronize(e->stream)); // host buffer may be reused by the caller
   return NLS_OK;
 }
 
@@ -1006,8 +1037,7 @@ static int get_field_impl(nls_handle e, int field, void *dst, size_t bytes, bool
   return check_status(e);
 }
 
-int nls_get_field_resampled(nls_handle e, int field, uint32_t tnx, uint32_t tny, uint32_t tnz, void *dst, size_t bytes) {
-  if (!e || !dst) return fail(NLS_ERR_ARG, "null argument");
+static int resample_check(nls_handle e, int field, uint32_t tnx, uint32_t tny, uint32_t tnz, size_t bytes) {
   if (e->slab) return fail(NLS_ERR_STATE, "nls_get_field_resampled is not available on z-slab handles");
   if (field != NLS_FIELD_U && field != NLS_FIELD_V) return fail(NLS_ERR_ARG, "resampled: NLS_FIELD_U or NLS_FIELD_V");
   if (field == NLS_FIELD_V && e->cplx) return fail(NLS_ERR_STATE, "V: real equations only");
@@ -1015,35 +1045,212 @@ int nls_get_field_resampled(nls_handle e, int field, uint32_t tnx, uint32_t tny,
   const uint32_t nz = e->g.dim3 ? (uint32_t)e->g.nz_loc : 1u;
   if (tnx < 2 || tny < 2 || (nz == 1 ? tnz != 1 : tnz < 2) || tnx > (1u << 20) || tny > (1u << 20) || tnz > (1u << 20))
     return fail(NLS_ERR_ARG, "resampled: target extents must be >= 2 (tnz == 1 for 2D handles)");
-  const size_t tot = (size_t)tnx * tny * tnz, need = tot * e->batch * e->esz;
+  const size_t need = (size_t)tnx * tny * tnz * e->batch * e->esz;
   if (bytes != need) return fail(NLS_ERR_ARG, "resampled: size mismatch");
-  CU(cudaSetDevice(e->d.device));
-  if (e->rs_bytes < need) {
-    if (e->rs) CU(cudaFree(e->rs));
-    e->rs = nullptr; e->rs_bytes = 0;
-    CU(cudaMalloc(&e->rs, need));
-    e->rs_bytes = need;
-  }
+  return NLS_OK;
+}
+static int resample_launch(nls_handle e, int field, uint32_t tnx, uint32_t tny, uint32_t tnz, void *out) {
+  const size_t tot = (size_t)tnx * tny * tnz;
   const unsigned gx = (unsigned)std::min<size_t>((tot + kThreads - 1) / kThreads, (size_t)e->nsm * 8);
   const dim3 gr(gx, (unsigned)e->batch);
   if (e->cplx)
     k_resample<double2, false><<<gr, kThreads, 0, e->stream>>>(e->g, (const double2 *)e->u[e->phase], nullptr, 0.0,
-                                                               (int)tnx, (int)tny, (int)tnz, (double2 *)e->rs);
+                                                               (int)tnx, (int)tny, (int)tnz, (double2 *)out);
   else if (field == NLS_FIELD_U)
     k_resample<double, false><<<gr, kThreads, 0, e->stream>>>(e->g, (const double *)cur_u(e), nullptr, 0.0, (int)tnx,
-                                                              (int)tny, (int)tnz, (double *)e->rs);
+                                                              (int)tny, (int)tnz, (double *)out);
   else
     k_resample<double, true><<<gr, kThreads, 0, e->stream>>>(e->g, (const double *)cur_u(e), (const double *)cur_upast(e),
-                                                             1.0 / e->d.dt, (int)tnx, (int)tny, (int)tnz, (double *)e->rs);
+                                                             1.0 / e->d.dt, (int)tnx, (int)tny, (int)tnz, (double *)out);
   e->count();
   CU(cudaGetLastError());
-  CU(cudaMemcpyAsync(dst, e->rs, need, cudaMemcpyDeviceToHost, e->stream));
+  return NLS_OK;
+}
+
+int nls_get_field_resampled(nls_handle e, int field, uint32_t tnx, uint32_t tny, uint32_t tnz, void *dst, size_t bytes) {
+  if (!e || !dst) return fail(NLS_ERR_ARG, "null argument");
+  int rc = resample_check(e, field, tnx, tny, tnz, bytes);
+  if (rc) return rc;
+  CU(cudaSetDevice(e->d.device));
+  if (e->rs_bytes < bytes) {
+    if (e->rs) CU(cudaFree(e->rs));
+    e->rs = nullptr; e->rs_bytes = 0;
+    CU(cudaMalloc(&e->rs, bytes));
+    e->rs_bytes = bytes;
+  }
+  rc = resample_launch(e, field, tnx, tny, tnz, e->rs);
+  if (rc) return rc;
+  CU(cudaMemcpyAsync(dst, e->rs, bytes, cudaMemcpyDeviceToHost, e->stream));
   CU(cudaStreamSynchronize(e->stream));
   return check_status(e);
 }
 
-int nls_set_field(nls_handle h, int f, const void *s, size_t b) { return set_field_impl(h, f, s, b, false); }
-int nls_set_field_dev(nls_handle h, int f, const void *s, size_t b) { return set_field_impl(h, f, s, b, true); }
+// ---- asynchronous transfers (replaces the blocking cudaMemcpy per snapshot of nlse_dev.hpp:323-334)
+static int async_init(nls_handle e) {
+  if (e->async_used) return NLS_OK;
+  CU(cudaStreamCreateWithFlags(&e->d2h_stream, cudaStreamNonBlocking));
+  CU(cudaStreamCreateWithFlags(&e->h2d_stream, cudaStreamNonBlocking));
+  for (int k = 0; k < 2; ++k) {
+    CU(cudaEventCreateWithFlags(&e->ring_ready[k], cudaEventDisableTiming));
+    CU(cudaEventCreateWithFlags(&e->ring_done[k], cudaEventDisableTiming));
+    CU(cudaEventCreateWithFlags(&e->stage_ready[k], cudaEventDisableTiming));
+    CU(cudaEventCreateWithFlags(&e->stage_free[k], cudaEventDisableTiming));
+  }
+  e->async_used = true;
+  return NLS_OK;
+}
+static int ring_slot(nls_handle e, size_t bytes, int *slot) {
+  const int k = e->ring_next;
+  e->ring_next ^= 1;
+  CU(cudaStreamWaitEvent(e->stream, e->ring_done[k], 0)); // the previous D2H out of this slot has finished
+  if (e->ring_bytes[k] < bytes) {
+    CU(cudaStreamSynchronize(e->d2h_stream));
+    if (e->ring[k]) CU(cudaFree(e->ring[k]));
+    e->ring[k] = nullptr; e->ring_bytes[k] = 0;
+    CU(cudaMalloc(&e->ring[k], bytes));
+    e->ring_bytes[k] = bytes;
+  }
+  *slot = k;
+  return NLS_OK;
+}
+// snapshot in ring[k] (dense [batch][per] bytes) -> host, on the D2H stream, overlapping whatever the compute stream does next
+static int ring_drain(nls_handle e, int k, void *dst, size_t per, size_t dst_stride) {
+  CU(cudaEventRecord(e->ring_ready[k], e->stream));
+  CU(cudaStreamWaitEvent(e->d2h_stream, e->ring_ready[k], 0));
+  if (dst_stride == 0 || dst_stride == per || e->batch == 1) {
+    CU(cudaMemcpyAsync(dst, e->ring[k], per * e->batch, cudaMemcpyDeviceToHost, e->d2h_stream));
+  } else {
+    for (int b = 0; b < e->batch; ++b)
+      CU(cudaMemcpyAsync((char *)dst + (size_t)b * dst_stride, (const char *)e->ring[k] + (size_t)b * per, per,
+                         cudaMemcpyDeviceToHost, e->d2h_stream));
+  }
+  CU(cudaEventRecord(e->ring_done[k], e->d2h_stream));
+  return NLS_OK;
+}
+
+int nls_get_field_async(nls_handle e, int field, void *dst, size_t bytes, size_t dst_traj_stride) {
+  if (!e || !dst) return fail(NLS_ERR_ARG, "null argument");
+  if (e->poison) return poisoned(e);
+  CU(cudaSetDevice(e->d.device));
+  const size_t per = (size_t)e->g.n * e->esz, sb = per * e->batch;
+  if (bytes != sb) return fail(NLS_ERR_ARG, "get_async: size mismatch");
+  if (dst_traj_stride != 0 && dst_traj_stride < per) return fail(NLS_ERR_ARG, "get_async: trajectory stride smaller than one state");
+  const void *src;
+  switch (field) {
+  case NLS_FIELD_U: src = e->cplx ? e->u[e->phase] : (void *)cur_u(e); break;
+  case NLS_FIELD_U_PAST:
+    if (e->cplx && e->d.integrator != NLS_INT_SEWI) return fail(NLS_ERR_STATE, "U_PAST: real equations or NLS_INT_SEWI only");
+    src = e->cplx ? e->u[(e->phase + 2) % 3] : (void *)cur_upast(e);
+    break;
+  case NLS_FIELD_V:
+    if (e->cplx) return fail(NLS_ERR_STATE, "V: real equations only");
+    src = nullptr;
+    break;
+  default: return fail(NLS_ERR_ARG, "bad field");
+  }
+  int rc = async_init(e);
+  if (rc) return rc;
+  int k;
+  rc = ring_slot(e, sb, &k);
+  if (rc) return rc;
+  if (field == NLS_FIELD_V) { // v = (u - u_past)/dt straight into the ring (dense layout: halo-free view)
+    Geom gd = e->g;
+    if (e->g.halo == 0) {
+      LAUNCH(e, k_velocity, e->grid(), gd, cur_u(e), cur_upast(e), (double *)e->ring[k], e->d.dt);
+      CU(cudaGetLastError());
+    } else {
+      LAUNCH(e, k_velocity, e->grid(), e->g, cur_u(e), cur_upast(e), (double *)e->wbuf[0], e->d.dt);
+      CU(cudaGetLastError());
+      rc = copy_out_async(e, e->ring[k], e->wbuf[0], 8, e->batch);
+      if (rc) return rc;
+    }
+  } else {
+    rc = copy_out_async(e, e->ring[k], src, e->esz, e->batch);
+    if (rc) return rc;
+  }
+  return ring_drain(e, k, dst, per, dst_traj_stride);
+}
+
+int nls_get_field_resampled_async(nls_handle e, int field, uint32_t tnx, uint32_t tny, uint32_t tnz, void *dst, size_t bytes,
+                                  size_t dst_traj_stride) {
+  if (!e || !dst) return fail(NLS_ERR_ARG, "null argument");
+  if (e->poison) return poisoned(e);
+  int rc = resample_check(e, field, tnx, tny, tnz, bytes);
+  if (rc) return rc;
+  CU(cudaSetDevice(e->d.device));
+  const size_t per = (size_t)tnx * tny * tnz * e->esz;
+  if (dst_traj_stride != 0 && dst_traj_stride < per) return fail(NLS_ERR_ARG, "resampled_async: trajectory stride too small");
+  rc = async_init(e);
+  if (rc) return rc;
+  int k;
+  rc = ring_slot(e, bytes, &k);
+  if (rc) return rc;
+  rc = resample_launch(e, field, tnx, tny, tnz, e->ring[k]);
+  if (rc) return rc;
+  return ring_drain(e, k, dst, per, dst_traj_stride);
+}
+
+// host (ideally page-locked) -> staging buffer on the H2D stream, then a device-to-device copy on the compute
+// stream: the upload overlaps the steps still running, the caller's buffer is free again after nls_wait
+int nls_set_field_async(nls_handle e, int field, const void *src, size_t bytes) {
+  if (!e || !src) return fail(NLS_ERR_ARG, "null argument");
+  if (e->poison) return poisoned(e);
+  if (field == NLS_FIELD_V) return fail(NLS_ERR_ARG, "set_async: U, U_PAST, M or C");
+  CU(cudaSetDevice(e->d.device));
+  int rc = async_init(e);
+  if (rc) return rc;
+  const int k = e->stage_next;
+  e->stage_next ^= 1;
+  CU(cudaStreamWaitEvent(e->h2d_stream, e->stage_free[k], 0)); // the compute stream has consumed this slot
+  if (e->stage_bytes[k] < bytes) {
+    CU(cudaStreamSynchronize(e->stream));
+    CU(cudaStreamSynchronize(e->h2d_stream));
+    if (e->stage[k]) CU(cudaFree(e->stage[k]));
+    e->stage[k] = nullptr; e->stage_bytes[k] = 0;
+    CU(cudaMalloc(&e->stage[k], bytes));
+    e->stage_bytes[k] = bytes;
+  }
+  CU(cudaMemcpyAsync(e->stage[k], src, bytes, cudaMemcpyHostToDevice, e->h2d_stream));
+  CU(cudaEventRecord(e->stage_ready[k], e->h2d_stream));
+  CU(cudaStreamWaitEvent(e->stream, e->stage_ready[k], 0));
+  rc = set_field_impl(e, field, e->stage[k], bytes, true, false);
+  if (rc) return rc;
+  CU(cudaEventRecord(e->stage_free[k], e->stream));
+  return NLS_OK;
+}
+
+// page-locked host memory for the asynchronous transfers (callers without a CUDA runtime of their own)
+int nls_host_alloc(void **out, size_t bytes) {
+  if (!out) return fail(NLS_ERR_ARG, "null argument");
+  CU(cudaMallocHost(out, bytes));
+  return NLS_OK;
+}
+int nls_host_free(void *p) {
+  if (p) CU(cudaFreeHost(p));
+  return NLS_OK;
+}
+int nls_host_register(void *p, size_t bytes) {
+  if (!p) return fail(NLS_ERR_ARG, "null argument");
+  CU(cudaHostRegister(p, bytes, cudaHostRegisterDefault));
+  return NLS_OK;
+}
+int nls_host_unregister(void *p) {
+  if (p) CU(cudaHostUnregister(p));
+  return NLS_OK;
+}
+
+// A page-locked source (cudaMallocHost / cudaHostRegister / nls_host_alloc) is copied asynchronously: the call
+// returns at once and the buffer must stay unchanged until the next nls_sync / nls_wait / blocking get on this handle.
+int nls_set_field(nls_handle h, int f, const void *s, size_t b) {
+  bool pinned = false;
+  if (s) {
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, s) == cudaSuccess) pinned = at.type == cudaMemoryTypeHost;
+    else cudaGetLastError();
+  }
+  return set_field_impl(h, f, s, b, false, !pinned);
+}
+int nls_set_field_dev(nls_handle h, int f, const void *s, size_t b) { return set_field_impl(h, f, s, b, true, false); }
 int nls_get_field(nls_handle h, int f, void *d, size_t b) { return get_field_impl(h, f, d, b, false); }
 int nls_get_field_dev(nls_handle h, int f, void *d, size_t b) { return get_field_impl(h, f, d, b, true); }
 
@@ -1064,8 +1271,14 @@ int nls_sync(nls_handle e) {
   if (!e) return fail(NLS_ERR_ARG, "null handle");
   CU(cudaSetDevice(e->d.device));
   CU(cudaStreamSynchronize(e->stream));
+  if (e->async_used) { // outstanding nls_get_field_async / nls_set_field_async transfers
+    CU(cudaStreamSynchronize(e->h2d_stream));
+    CU(cudaStreamSynchronize(e->d2h_stream));
+  }
   return check_status(e);
 }
+
+int nls_wait(nls_handle e) { return nls_sync(e); }
 
 int nls_step_timed(nls_handle e, double dt, uint32_t nsteps, float *ms) {
   if (!e || !ms) return fail(NLS_ERR_ARG, "null argument");
@@ -1090,11 +1303,12 @@ uint64_t nls_launch_count(nls_handle e) { return e ? e->launches : 0; }
 uint64_t nls_tma_launch_count(nls_handle e) { return e ? e->tma_launches : 0; }
 void *nls_stream(nls_handle e) { return e ? (void *)e->stream : nullptr; }
 
-int nls_stencil_apply(nls_handle e, const void *x, void *y) {
+static int stencil_apply_impl(nls_handle e, const void *x, void *y, bool dev) {
   if (!e || !x || !y) return fail(NLS_ERR_ARG, "null argument");
+  if (e->poison) return poisoned(e);
   CU(cudaSetDevice(e->d.device));
   if (slab_ready(e)) return NLS_ERR_STATE;
-  int rc = copy_in(e, e->w0, x, e->esz, e->batch, false);
+  int rc = copy_in(e, e->w0, x, e->esz, e->batch, dev);
   if (rc) return rc;
   if (e->cplx) halo_exchange<double2>(e, e->w0);
   else halo_exchange<double>(e, e->w0);
@@ -1111,13 +1325,16 @@ int nls_stencil_apply(nls_handle e, const void *x, void *y) {
   else halo_exchange<double>(e, e->wbuf[0]);
   CU(cudaGetLastError());
   e->start_valid = false; // w0 was overwritten
+  if (dev) return copy_out_async(e, y, e->wbuf[0], e->esz, e->batch); // stream-ordered, like the reference's multiply()
   return copy_out(e, y, e->wbuf[0], e->esz, e->batch, false);
 }
+int nls_stencil_apply(nls_handle e, const void *x, void *y) { return stencil_apply_impl(e, x, y, false); }
+int nls_stencil_apply_dev(nls_handle e, const void *x, void *y) { return stencil_apply_impl(e, x, y, true); }
 
 // upload `in` into w0, ||in||^2 -> scalA.nrm2[0], run the Lanczos process
-static int lanczos_from_host(nls_handle e, const void *in) {
+static int lanczos_from_host(nls_handle e, const void *in, bool dev = false) {
   if (slab_ready(e)) return NLS_ERR_STATE;
-  int rc = copy_in(e, e->w0, in, e->esz, e->batch, false);
+  int rc = copy_in(e, e->w0, in, e->esz, e->batch, dev);
   if (rc) return rc;
   e->start_valid = false;
   if (e->cplx) halo_exchange<double2>(e, e->w0);
@@ -1133,13 +1350,14 @@ static int lanczos_from_host(nls_handle e, const void *in) {
   return NLS_OK;
 }
 
-int nls_matfunc(nls_handle e, int fn, double t_re, double t_im, const void *in, void *out) {
+static int matfunc_impl(nls_handle e, int fn, double t_re, double t_im, const void *in, void *out, bool dev) {
   if (!e || !in || !out) return fail(NLS_ERR_ARG, "null argument");
+  if (e->poison) return poisoned(e);
   if (fn < NLS_FN_EXP || fn > NLS_FN_MOD_COSINE) return fail(NLS_ERR_ARG, "bad function id");
   if (!e->cplx && fn <= NLS_FN_SINC && fn == NLS_FN_EXP && t_im != 0.0)
     return fail(NLS_ERR_STATE, "complex exp needs a complex-state handle");
   CU(cudaSetDevice(e->d.device));
-  int rc = lanczos_from_host(e, in);
+  int rc = lanczos_from_host(e, in, dev);
   if (rc) return rc;
   tridiag(e, e->scalA, 1, fn, t_re, t_im, 0, 0, 0);
   void *dst = e->wbuf[1]; // scratch: neither state nor part of the basis
@@ -1148,8 +1366,84 @@ int nls_matfunc(nls_handle e, int fn, double t_re, double t_im, const void *in, 
   else
     LAUNCH(e, (k_combine<double>), e->grid(), e->g, (const double *)e->w0, (const double *)e->V, e->colstride, e->coef, 0, e->m, (double *)dst);
   CU(cudaGetLastError());
+  if (dev) return copy_out_async(e, out, dst, e->esz, e->batch); // stream-ordered; errors surface at the next nls_sync
   rc = copy_out(e, out, dst, e->esz, e->batch, false);
   return rc ? rc : check_status(e);
+}
+int nls_matfunc(nls_handle e, int fn, double t_re, double t_im, const void *in, void *out) {
+  return matfunc_impl(e, fn, t_re, t_im, in, out, false);
+}
+int nls_matfunc_dev(nls_handle e, int fn, double t_re, double t_im, const void *in, void *out) {
+  return matfunc_impl(e, fn, t_re, t_im, in, out, true);
+}
+
+// 1 = device (or managed) pointer, 0 = host pointer
+int nls_pointer_is_device(const void *p) {
+  cudaPointerAttributes at;
+  if (cudaPointerGetAttributes(&at, p) != cudaSuccess) { cudaGetLastError(); return 0; }
+  return at.type == cudaMemoryTypeDevice || at.type == cudaMemoryTypeManaged;
+}
+int nls_memcpy_to_host(void *dst, const void *dev_src, size_t bytes) {
+  if (!dst || !dev_src) return fail(NLS_ERR_ARG, "null argument");
+  CU(cudaMemcpy(dst, dev_src, bytes, cudaMemcpyDeviceToHost));
+  return NLS_OK;
+}
+
+// rel_err = max_i |(CSR x - L x)_i| / max_i |(L x)_i| for a deterministic pseudo-random x (see k_csr_residual)
+int nls_csr_residual(nls_handle e, const int *row_ptr, const int *col_ind, const void *values, uint32_t n, uint64_t nnz,
+                     int values_complex, int on_device, double *rel_err) {
+  if (!e || !row_ptr || !col_ind || !values || !rel_err) return fail(NLS_ERR_ARG, "null argument");
+  if (e->poison) return poisoned(e);
+  if (e->slab || e->batch != 1) return fail(NLS_ERR_STATE, "csr check: single-trajectory, single-GPU handles only");
+  if ((long long)n != e->g.n) return fail(NLS_ERR_ARG, "csr check: n does not match the handle's grid");
+  if (values_complex && !e->cplx) return fail(NLS_ERR_ARG, "csr check: complex values need a complex-state handle");
+  CU(cudaSetDevice(e->d.device));
+  const size_t vb = (size_t)nnz * (values_complex ? 16 : 8);
+  int *rp = nullptr, *ci = nullptr;
+  double *val = nullptr;
+  unsigned long long *out = nullptr;
+  const int *rpd = row_ptr, *cid = col_ind;
+  const double *vd = (const double *)values;
+  auto cleanup = [&]() { cudaFree(rp); cudaFree(ci); cudaFree(val); cudaFree(out); };
+  if (!on_device) {
+    if (cudaMalloc(&rp, (size_t)(n + 1) * 4) != cudaSuccess || cudaMalloc(&ci, (size_t)nnz * 4) != cudaSuccess ||
+        cudaMalloc(&val, vb) != cudaSuccess) { cleanup(); return fail(NLS_ERR_CUDA, "csr check: allocation failed"); }
+    cudaMemcpyAsync(rp, row_ptr, (size_t)(n + 1) * 4, cudaMemcpyHostToDevice, e->stream);
+    cudaMemcpyAsync(ci, col_ind, (size_t)nnz * 4, cudaMemcpyHostToDevice, e->stream);
+    cudaMemcpyAsync(val, values, vb, cudaMemcpyHostToDevice, e->stream);
+    rpd = rp; cid = ci; vd = val;
+  }
+  if (cudaMalloc(&out, 16) != cudaSuccess) { cleanup(); return fail(NLS_ERR_CUDA, "csr check: allocation failed"); }
+  cudaMemsetAsync(out, 0, 16, e->stream);
+  const bool an = e->d.laplacian == NLS_LAP_ANISO;
+  const dim3 gr = e->grid();
+  if (e->cplx) {
+    k_fill_hash<double2><<<gr, kThreads, 0, e->stream>>>(e->g, (double2 *)e->w0, 0x5eedull);
+    if (an) k_stencil<double2, true><<<gr, kThreads, 0, e->stream>>>(e->g, (const double2 *)e->w0, (double2 *)e->wbuf[0], e->cf);
+    else k_stencil<double2, false><<<gr, kThreads, 0, e->stream>>>(e->g, (const double2 *)e->w0, (double2 *)e->wbuf[0], e->cf);
+    if (values_complex)
+      k_csr_residual<double2, true><<<gr, kThreads, 0, e->stream>>>(e->g.n, rpd, cid, vd, (const double2 *)e->w0, (const double2 *)e->wbuf[0], out);
+    else
+      k_csr_residual<double2, false><<<gr, kThreads, 0, e->stream>>>(e->g.n, rpd, cid, vd, (const double2 *)e->w0, (const double2 *)e->wbuf[0], out);
+  } else {
+    k_fill_hash<double><<<gr, kThreads, 0, e->stream>>>(e->g, (double *)e->w0, 0x5eedull);
+    if (an) k_stencil<double, true><<<gr, kThreads, 0, e->stream>>>(e->g, (const double *)e->w0, (double *)e->wbuf[0], e->cf);
+    else k_stencil<double, false><<<gr, kThreads, 0, e->stream>>>(e->g, (const double *)e->w0, (double *)e->wbuf[0], e->cf);
+    k_csr_residual<double, false><<<gr, kThreads, 0, e->stream>>>(e->g.n, rpd, cid, vd, (const double *)e->w0, (const double *)e->wbuf[0], out);
+  }
+  e->launches += 3;
+  e->start_valid = false;
+  unsigned long long h[2] = {0, 0};
+  cudaError_t ce = cudaGetLastError();
+  if (ce == cudaSuccess) ce = cudaMemcpyAsync(h, out, 16, cudaMemcpyDeviceToHost, e->stream);
+  if (ce == cudaSuccess) ce = cudaStreamSynchronize(e->stream);
+  cleanup();
+  if (ce != cudaSuccess) return fail(NLS_ERR_CUDA, std::string("csr check: ") + cudaGetErrorString(ce));
+  double dmax, ymax;
+  std::memcpy(&dmax, &h[0], 8);
+  std::memcpy(&ymax, &h[1], 8);
+  *rel_err = ymax > 0 ? dmax / ymax : (dmax > 0 ? 1e300 : 0.0);
+  return NLS_OK;
 }
 
 int nls_lanczos(nls_handle e, const void *in, void *hV, void *halpha, double *hbeta) {

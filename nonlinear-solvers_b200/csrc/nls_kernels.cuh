@@ -975,6 +975,57 @@ k_reduce_energy(Geom g, const S *__restrict__ u, const double *__restrict__ upas
   grid_reduce<1>(acc, rc, dst + blockIdx.y);
 }
 
+// ---- CSR compatibility check of the B2 class layer (include/nls/solvers.hpp): the reference's solver classes are
+// handed an assembled CSR (device/spmv.hpp:30-52, sg_single_dev.hpp:28-31).  The engine is matrix-free; a CSR is
+// accepted only if it IS the handle's stencil: both operators are applied to a deterministic pseudo-random
+// vector and compared entry by entry (any differing matrix entry shows up with probability 1).
+__device__ __forceinline__ double hash_unit(unsigned long long i, unsigned long long seed) { // splitmix64 -> (-1, 1)
+  unsigned long long z = (i + 1) * 0x9e3779b97f4a7c15ull + seed;
+  z = (z ^ (z >> 30)) * 0xbf58476d1ce4e5b9ull;
+  z = (z ^ (z >> 27)) * 0x94d049bb133111ebull;
+  z ^= z >> 31;
+  return (double)(long long)(z >> 11) * (2.0 / 9007199254740992.0) - 1.0;
+}
+template <class S>
+__global__ void __launch_bounds__(kThreads) k_fill_hash(Geom g, S *__restrict__ x, unsigned long long seed) {
+  S *xb = traj(x, g);
+  for (long long idx = (long long)blockIdx.x * kThreads + threadIdx.x; idx < g.n; idx += (long long)gridDim.x * kThreads) {
+    const unsigned long long gi = (unsigned long long)(idx + g.goff);
+    if (Sc<S>::W == 2) ((double *)(xb + idx))[0] = hash_unit(2 * gi, seed), ((double *)(xb + idx))[1] = hash_unit(2 * gi + 1, seed);
+    else ((double *)(xb + idx))[0] = hash_unit(gi, seed);
+  }
+}
+// out[0] = max |(CSR x - y)_i|, out[1] = max |y_i|  (bit patterns of non-negative doubles order like integers)
+template <class S, bool VCPLX>
+__global__ void __launch_bounds__(kThreads)
+k_csr_residual(long long n, const int *__restrict__ rp, const int *__restrict__ ci, const double *__restrict__ val,
+               const S *__restrict__ x, const S *__restrict__ y, unsigned long long *out) {
+  using T = Sc<S>;
+  double dmax = 0.0, ymax = 0.0;
+  for (long long i = (long long)blockIdx.x * kThreads + threadIdx.x; i < n; i += (long long)gridDim.x * kThreads) {
+    S acc = T::zero();
+    for (int q = rp[i]; q < rp[i + 1]; ++q) {
+      const int c = ci[q];
+      if (c < 0 || c >= n) { dmax = 1e300; continue; }
+      const S xv = x[c];
+      if (VCPLX) acc = T::add(acc, T::mul(T::from(val + 2 * (size_t)q), xv));
+      else acc = T::fma_r(val[q], xv, acc);
+    }
+    const S d = T::sub(acc, y[i]);
+    dmax = fmax(dmax, sqrt(T::abs2(d)));
+    ymax = fmax(ymax, sqrt(T::abs2(y[i])));
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    dmax = fmax(dmax, __shfl_xor_sync(0xffffffffu, dmax, o));
+    ymax = fmax(ymax, __shfl_xor_sync(0xffffffffu, ymax, o));
+  }
+  if ((threadIdx.x & 31) == 0) {
+    atomicMax(out, (unsigned long long)__double_as_longlong(dmax));
+    atomicMax(out + 1, (unsigned long long)__double_as_longlong(ymax));
+  }
+}
+
 // Multilinear resampling of a state onto a coarser linspace grid (nls_get_field_resampled):
 // downsampling.py:68-104 / :215-258.  One thread per target point; out is dense [batch][tz][ty][tx].
 // VEL: sample v = (u - u_past)/dt instead of u (real states).

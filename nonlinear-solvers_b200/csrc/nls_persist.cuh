@@ -211,6 +211,15 @@ __device__ __forceinline__ void pk_publish(double (&acc)[K], double *part, const
 
 // One warp: wait until every CTA's value k of the current round has arrived, return their sum (fixed order:
 // identical bits in every CTA).  All (<= 5) loads of a lane are in flight together.
+#ifndef PK_POLL_ACQUIRE
+#define PK_POLL_ACQUIRE 0
+#endif
+__device__ __forceinline__ unsigned long long ld_relaxed_u64(const unsigned long long *p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void fence_acq_rel_gpu() { asm volatile("fence.acq_rel.gpu;" ::: "memory"); }
 __device__ __forceinline__ double pk_poll_sum(const GridSync &gs, const double *part, int k) {
   const int lane = threadIdx.x & 31;
   constexpr int kPer = (kPkPartStride + 31) / 32;
@@ -224,7 +233,7 @@ __device__ __forceinline__ double pk_poll_sum(const GridSync &gs, const double *
     bool pending = false;
 #pragma unroll
     for (int q = 0; q < kPer; ++q)
-      if (t[q] == kPkSentinel) t[q] = ld_acquire_u64(p + lane + 32 * q);
+      if (t[q] == kPkSentinel) t[q] = PK_POLL_ACQUIRE ? ld_acquire_u64(p + lane + 32 * q) : ld_relaxed_u64(p + lane + 32 * q);
 #pragma unroll
     for (int q = 0; q < kPer; ++q) pending |= t[q] == kPkSentinel;
     if (!__any_sync(0xffffffffu, pending)) break;
@@ -237,6 +246,7 @@ __device__ __forceinline__ double pk_poll_sum(const GridSync &gs, const double *
       break;
     }
   }
+  if (!PK_POLL_ACQUIRE) fence_acq_rel_gpu(); // relaxed polling + one fence = acquire, without an L1 invalidate per poll
   double v = 0.0;
 #pragma unroll
   for (int q = 0; q < kPer; ++q)
@@ -765,7 +775,10 @@ template <class S>
 __device__ __forceinline__ void pk_coefficients(const PkArgs &a, PkCtx<S> &c, int nfn, int f0, double t0r,
                                                 double t0i, int f1, double t1r, double t1i) {
   const int m = a.m;
-  if (threadIdx.x < 32 && m <= 32) {
+#ifndef PK_QL_REG
+#define PK_QL_REG 1
+#endif
+  if (PK_QL_REG && threadIdx.x < 32 && m <= 32) {
     // register-resident QL (nls_kernels.cuh): lane i owns d_i, e_i; ~3x shorter than the shared-memory form
     const int lane = threadIdx.x;
     PkTri &T = c.tri;
