@@ -26,8 +26,10 @@
 #include <cmath>
 #include <complex>
 #include <cstdint>
+#include <cstdlib>
 #include <cstring>
 #include <memory>
+#include <new>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -47,31 +49,39 @@ inline void check(int rc, const char *what) {
   if (rc != NLS_OK) throw std::runtime_error(std::string(what) + ": " + nls_last_error());
 }
 
-// page-locked host array (nls_host_alloc) for the asynchronous transfers
+// page-locked host array (nls_host_alloc) for the asynchronous transfers.  It is plain host memory: when page
+// locking is not possible (no CUDA device: nls_create will then report that loudly) it degrades to pageable memory,
+// with which the asynchronous copies simply become synchronous.
 template <class T> class Pinned {
 public:
   Pinned() = default;
   explicit Pinned(size_t count) { resize(count); }
-  ~Pinned() { nls_host_free(p_); }
+  ~Pinned() { release(); }
   Pinned(const Pinned &) = delete;
   Pinned &operator=(const Pinned &) = delete;
   void resize(size_t count) {
-    nls_host_free(p_);
-    p_ = nullptr;
+    release();
     n_ = count;
-    if (count) {
-      void *q = nullptr;
-      check(nls_host_alloc(&q, count * sizeof(T)), "nls_host_alloc");
-      p_ = (T *)q;
-    }
+    if (!count) return;
+    void *q = nullptr;
+    if (nls_host_alloc(&q, count * sizeof(T)) == NLS_OK) { p_ = (T *)q; locked_ = true; return; }
+    p_ = (T *)std::malloc(count * sizeof(T));
+    locked_ = false;
+    if (!p_) throw std::bad_alloc();
   }
   T *data() { return p_; }
   const T *data() const { return p_; }
   size_t size() const { return n_; }
+  bool page_locked() const { return locked_; }
 
 private:
+  void release() {
+    if (p_) { if (locked_) nls_host_free(p_); else std::free(p_); }
+    p_ = nullptr;
+  }
   T *p_ = nullptr;
   size_t n_ = 0;
+  bool locked_ = false;
 };
 
 // RAII owner of one nls_handle

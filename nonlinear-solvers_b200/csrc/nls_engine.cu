@@ -604,7 +604,8 @@ void pk_setup(nls_engine *e) {
     cudaGetLastError();
     return;
   }
-  if (cudaMalloc((void **)&e->pk_part, (size_t)kPkSlots * kPkMaxK * kPkPartStride * 8) != cudaSuccess) return;
+  if (cudaMalloc((void **)&e->pk_part, (size_t)2 * kPkMaxK * kPkPartStride * 8) != cudaSuccess) return;
+  cudaMemset(e->pk_part, 0, (size_t)2 * kPkMaxK * kPkPartStride * 8);
   if (cudaMalloc((void **)&e->pk_bar, 16) != cudaSuccess) return;
   e->pk_ncta = ncta;
   e->pk_csz = csz;
@@ -638,7 +639,6 @@ int run_steps_pk_once(nls_engine *e, double dt, uint32_t nsteps) {
   a.acc = e->acc; a.mf = e->mf; a.cf = e->cf;
   a.part = e->pk_part; a.bar = e->pk_bar; a.status = e->status;
   CU(cudaMemsetAsync(e->pk_bar, 0, 16, e->stream));
-  CU(cudaMemsetAsync(e->pk_part, 0xff, (size_t)kPkSlots * kPkMaxK * kPkPartStride * 8, e->stream)); // sentinel-arm every slot
   const bool an = a.aniso;
   if (e->cplx) {
     a.u0 = e->u[e->phase]; a.u1 = e->u[1 - e->phase];

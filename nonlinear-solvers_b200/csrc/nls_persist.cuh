@@ -68,7 +68,7 @@ struct PkArgs {
   void *u0, *u1;       // NLSE: u ping-pong (u0 current at entry); real: u0 = u, u1 = u_past
   void *acc;           // Gautschi accumulator 2 cos(.)u - u_past
   const double *mf, *cf;
-  double *part;        // [3][kPkMaxK][kPkPartStride] per-CTA partial sums (sentinel-armed, see GridSync)
+  double *part;        // [2][kPkMaxK][kPkPartStride] per-CTA partial sums
   unsigned *bar;       // [0] arrival counter, [1] abort flag   (zeroed before every launch)
   int *status;
 };
@@ -106,29 +106,31 @@ __shared__ int pk_tr_n;
 #define PKT_DUMP(ncta) do { } while (0)
 #endif
 
-// ---------------------------------------------------------------- grid-wide reduction = grid barrier
-// All CTAs are co-resident (cooperative launch).  A reduction round r is barrier AND all-reduce in one:
-//   publish: every CTA release-stores its K partial sums into part[r % 3][k][cta];
-//   gather:  every CTA polls (acquire loads) the 'ncta' entries of each k until none holds the SENTINEL bit
-//            pattern any more and sums them in the same fixed order -- all CTAs obtain bit-identical scalars.
-// Seeing every CTA's value of round r means every CTA has finished the phase before it (the release/acquire
-// pair also orders that phase's global writes before the reader's next phase), so no separate arrival counter
-// and no second L2 round trip are needed: one store -> one (polled) load per reduction instead of
-// store, atomic, polled counter, then the loads.
-// Slot recycling: while a CTA publishes round r every CTA has already published round r-1, hence finished
-// gathering round r-2; the publisher therefore re-arms its own entries of slot (r+1) % 3 = (r-2) % 3 with the
-// sentinel (before the __syncthreads that precedes its release stores, so the release covers them).
-// The host fills the whole array with the sentinel (0xFF bytes) before every launch.
+// ---------------------------------------------------------------- grid barrier
+// Grid-wide reduction = per-CTA partial sums in global memory, ONE counter barrier (red.release / ld.acquire spin by
+// thread 0), then every CTA sums all partials in the same fixed order.  Measured against the alternatives on B200
+// (tools/microbench/allreduce_bench.cu, profiles/r02d_allreduce_microbench.log; 148 CTAs x 512 threads, K = 1 / 10
+// doubles): this scheme 2.2 / 4.1 us per round, cooperative-groups grid.sync + gather 2.4 / 4.1, arrival counter
+// spread over 8 words 2.3 / 4.2, sentinel-polled partials (barrier folded into the gather: no counter, no second
+// round trip) 3.6 / 7.6 (3.0 / 5.8 with one 32-byte sector per entry; 9.6 / 25.8 when every warp polls), two-level
+// reduction through one CTA 4.2 / 6.4: polling the partial array itself hot-spots a few L2 sectors with ~150 x
+// more requests than one counter word, so the counter stays.
+__device__ __forceinline__ unsigned long long ld_acquire_u64(const unsigned long long *p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_u64(unsigned long long *p, unsigned long long v) {
+  asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
 struct GridSync {
-  unsigned *ctr;   // [0] arrival counter of the plain barrier (Stoermer-Verlet kernel), [1] abort flag
-  unsigned target; // arrivals expected at the next plain barrier
+  unsigned *ctr;
+  unsigned target; // arrivals expected at the next barrier
   unsigned ncta;
-  int slot;        // r % 3 of the current round
+  int slot;        // parity of the barrier count: which partial-sum slot is live
   int *status;     // device status word of the handle: 4 = a grid barrier timed out / was aborted
-  int kreset;      // entries per slot this kernel ever uses (re-armed at every publish)
 };
-constexpr unsigned long long kPkSentinel = 0xffffffffffffffffull;
-constexpr int kPkSlots = 3;
 
 __device__ __forceinline__ unsigned ld_acquire_u32(const unsigned *p) {
   unsigned v;
@@ -138,22 +140,9 @@ __device__ __forceinline__ unsigned ld_acquire_u32(const unsigned *p) {
 __device__ __forceinline__ void red_release_add_u32(unsigned *p, unsigned v) {
   asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
-__device__ __forceinline__ unsigned long long ld_acquire_u64(const unsigned long long *p) {
-  unsigned long long v;
-  asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-  return v;
-}
-__device__ __forceinline__ void st_release_u64(unsigned long long *p, unsigned long long v) {
-  asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
-}
-__device__ __forceinline__ void st_relaxed_u64(unsigned long long *p, unsigned long long v) {
-  asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
-}
 
-__shared__ int pk_s_abort; // set by a poll that timed out; read after the next __syncthreads
-
-// plain barrier without a reduction (Stoermer-Verlet kernel).  Returns false if it timed out or another CTA
-// raised the abort flag (the kernel then unwinds instead of hanging the GPU; status 4 poisons the handle).
+// All CTAs are co-resident (cooperative launch).  Returns false if the barrier timed out or
+// another CTA raised the abort flag (the kernel then unwinds instead of hanging the GPU).
 __device__ __forceinline__ bool grid_barrier(GridSync &gs) {
   __shared__ int s_ok;
   __syncthreads();
@@ -174,14 +163,15 @@ __device__ __forceinline__ bool grid_barrier(GridSync &gs) {
   } else {
     gs.target += gs.ncta;
   }
+  gs.slot ^= 1;
   __syncthreads();
   return s_ok != 0;
 }
 
-// CTA-level partial sums: acc[K] per thread -> one value per CTA in part[slot][koff + k][cta] (release stores).
-// Several publishes (different koff) may belong to one round; pk_round_done closes the round after the gather.
+// CTA-level partial sums: acc[K] per thread -> one value per CTA in part[slot][k][cta].
+// Must be followed by grid_barrier and then pk_gather.
 template <int K>
-__device__ __forceinline__ void pk_publish(double (&acc)[K], double *part, const GridSync &gs, double (*s_red)[kPkWarps], int koff = 0) {
+__device__ __forceinline__ void pk_publish(double (&acc)[K], double *part, int slot, double (*s_red)[kPkWarps], int koff = 0) {
   PK_SHARED(s_red);
   PK_GLOBAL(part);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -192,88 +182,42 @@ __device__ __forceinline__ void pk_publish(double (&acc)[K], double *part, const
     for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
     if (lane == 0) s_red[k][warp] = v;
   }
-  { // re-arm this CTA's entries of the slot after next (see above)
-    const int nslot = gs.slot == kPkSlots - 1 ? 0 : gs.slot + 1;
-    for (int k = threadIdx.x; k < gs.kreset; k += kPkThreads)
-      st_relaxed_u64((unsigned long long *)part + ((size_t)nslot * kPkMaxK + k) * kPkPartStride + blockIdx.x, kPkSentinel);
-  }
   __syncthreads();
   if (threadIdx.x < K) {
     double v = 0.0;
 #pragma unroll
     for (int w = 0; w < kPkWarps; ++w) v += s_red[threadIdx.x][w];
-    unsigned long long bits = (unsigned long long)__double_as_longlong(v);
-    if (bits == kPkSentinel) bits = 0x7ff8000000000000ull; // a NaN with the sentinel's payload: keep it a NaN
-    st_release_u64((unsigned long long *)part + ((size_t)gs.slot * kPkMaxK + koff + threadIdx.x) * kPkPartStride + blockIdx.x, bits);
+    part[((size_t)slot * kPkMaxK + koff + threadIdx.x) * kPkPartStride + blockIdx.x] = v;
   }
   __syncthreads(); // s_red may be reused by the next publish
 }
 
-// One warp: wait until every CTA's value k of the current round has arrived, return their sum (fixed order:
-// identical bits in every CTA).  All (<= 5) loads of a lane are in flight together.
-#ifndef PK_POLL_ACQUIRE
-#define PK_POLL_ACQUIRE 0
-#endif
-__device__ __forceinline__ unsigned long long ld_relaxed_u64(const unsigned long long *p) {
-  unsigned long long v;
-  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-  return v;
-}
-__device__ __forceinline__ void fence_acq_rel_gpu() { asm volatile("fence.acq_rel.gpu;" ::: "memory"); }
-__device__ __forceinline__ double pk_poll_sum(const GridSync &gs, const double *part, int k) {
-  const int lane = threadIdx.x & 31;
-  constexpr int kPer = (kPkPartStride + 31) / 32;
-  const unsigned long long *p = (const unsigned long long *)part + ((size_t)gs.slot * kPkMaxK + k) * kPkPartStride;
-  unsigned long long t[kPer];
-#pragma unroll
-  for (int q = 0; q < kPer; ++q) t[q] = (unsigned)(lane + 32 * q) < gs.ncta ? kPkSentinel : 0ull;
-  const long long t0 = clock64();
-  int spins = 0;
-  for (;;) {
-    bool pending = false;
-#pragma unroll
-    for (int q = 0; q < kPer; ++q)
-      if (t[q] == kPkSentinel) t[q] = PK_POLL_ACQUIRE ? ld_acquire_u64(p + lane + 32 * q) : ld_relaxed_u64(p + lane + 32 * q);
-#pragma unroll
-    for (int q = 0; q < kPer; ++q) pending |= t[q] == kPkSentinel;
-    if (!__any_sync(0xffffffffu, pending)) break;
-    if ((++spins & 31) == 0 && (clock64() - t0 > 4000000000LL || ld_acquire_u32(gs.ctr + 1) != 0u)) { // ~2 s
-      if (lane == 0) {
-        atomicExch(gs.ctr + 1, 1u);
-        atomicExch(gs.status, 4);
-        pk_s_abort = 1;
-      }
-      break;
-    }
-  }
-  if (!PK_POLL_ACQUIRE) fence_acq_rel_gpu(); // relaxed polling + one fence = acquire, without an L1 invalidate per poll
-  double v = 0.0;
-#pragma unroll
-  for (int q = 0; q < kPer; ++q)
-    if ((unsigned)(lane + 32 * q) < gs.ncta) v += __longlong_as_double((long long)t[q]);
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-  return v;
-}
-
-// after the publishes of a round: every CTA obtains the K totals in s_out (warp w takes k = w, w + 16, ...)
-__device__ __forceinline__ void pk_gather_nosync(int K, const double *part, const GridSync &gs, double *s_out) {
+// after the barrier: every CTA sums the partials of all CTAs in the same order -> s_out[k].
+// The (<= 5) loads of a lane are issued together: one L2 round trip per value, not one per load.
+__device__ __forceinline__ void pk_gather_nosync(int K, const double *part, int slot, int ncta, double *s_out) {
   PK_SHARED(s_out);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  constexpr int kPer = (kPkPartStride + 31) / 32;
   for (int k = warp; k < K; k += kPkWarps) {
-    const double v = pk_poll_sum(gs, part, k);
+    const double *p = part + ((size_t)slot * kPkMaxK + k) * kPkPartStride;
+    double t[kPer];
+#pragma unroll
+    for (int q = 0; q < kPer; ++q) {
+      const int c = lane + 32 * q;
+      t[q] = c < ncta ? __ldcg(p + c) : 0.0;
+    }
+    double v = 0.0;
+#pragma unroll
+    for (int q = 0; q < kPer; ++q)
+      if (lane + 32 * q < ncta) v += t[q];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
     if (lane == 0) s_out[k] = v;
   }
 }
-// closes the round (call by all threads after the gather and a __syncthreads); false = aborted
-__device__ __forceinline__ bool pk_round_done(GridSync &gs) {
-  gs.slot = gs.slot == kPkSlots - 1 ? 0 : gs.slot + 1;
-  return pk_s_abort == 0;
-}
-__device__ __forceinline__ bool pk_gather(int K, const double *part, GridSync &gs, double *s_out) {
-  pk_gather_nosync(K, part, gs, s_out);
+__device__ __forceinline__ void pk_gather(int K, const double *part, int slot, int ncta, double *s_out) {
+  pk_gather_nosync(K, part, slot, ncta, s_out);
   __syncthreads();
-  return pk_round_done(gs);
 }
 
 // ---------------------------------------------------------------- in-kernel tridiagonal solve
@@ -635,13 +579,13 @@ __device__ __forceinline__ void pk_phase_a(const PkArgs &a, PkCtx<S> &c, GridSyn
       all[NC * W + k] = accM[k];
       all[(NC + 1) * W + k] = accA[k];
     }
-    pk_publish<(NC + 2) * W>(all, a.part, gs, c.red(), 0);
+    pk_publish<(NC + 2) * W>(all, a.part, gs.slot, c.red(), 0);
     return;
   }
-  if (NC > 0) pk_publish<NA * W>(acc, a.part, gs, c.red(), i0 * W);
+  if (NC > 0) pk_publish<NA * W>(acc, a.part, gs.slot, c.red(), i0 * W);
   if (FIRST) {
-    if (j > 0) pk_publish<W>(accM, a.part, gs, c.red(), (j - 1) * W);
-    pk_publish<W>(accA, a.part, gs, c.red(), j * W);
+    if (j > 0) pk_publish<W>(accM, a.part, gs.slot, c.red(), (j - 1) * W);
+    pk_publish<W>(accA, a.part, gs.slot, c.red(), j * W);
   }
 }
 
@@ -697,7 +641,7 @@ __device__ __forceinline__ void pk_phase_b(const PkArgs &a, PkCtx<S> &c, GridSyn
   nrm[0] = pk_loop_b<S, NC, LAST>(c.cnt, j, i0, c.X() + a.g.nx, c.Wt(), start + c.s0, (const S *)a.V + c.s0,
                                   a.colstride, (S *)a.V + (size_t)j * a.colstride + c.s0, c.gco());
   PKT(800 + j); // phase B site loop done
-  if (LAST) pk_publish<1>(nrm, a.part, gs, c.red(), 0);
+  if (LAST) pk_publish<1>(nrm, a.part, gs.slot, c.red(), 0);
 }
 
 #define PK_SWITCH_NC(nc, CALL)                                                                     \
@@ -738,8 +682,9 @@ __device__ bool pk_lanczos(const PkArgs &a, PkCtx<S> &c, GridSync &gs, S *start)
       }
     }
     PKT(200 + j); // phase A done (loop + publish)
-    if (!pk_gather((j + 1) * W, a.part, gs, c.vals())) return false; // barrier + all-reduce in one
-    PKT(300 + j); // sums gathered
+    if (!grid_barrier(gs)) return false;
+    PKT(300 + j); // barrier passed
+    pk_gather((j + 1) * W, a.part, gs.slot ^ 1, a.ncta, c.vals());
     // h_i = sums_i / beta_i ; w -= h_i v_i = (sums_i / beta_i^2) w_i ; alpha = Re h_j
     if (threadIdx.x <= j) {
       const int i = threadIdx.x;
@@ -755,15 +700,15 @@ __device__ bool pk_lanczos(const PkArgs &a, PkCtx<S> &c, GridSync &gs, S *start)
       PK_SWITCH_NC(nother - i0, (pk_phase_b<S, NC, true>(a, c, gs, start, j, i0)));
     }
     PKT(500 + j); // phase B done
-    // every warp polls ||w||^2 itself (its acquire then also covers the neighbours' rows of column j+1), so the
-    // next iteration's halo rows are fetched without another CTA-wide barrier in between
-    {
-      const double nv = pk_poll_sum(gs, a.part, 0);
-      if (threadIdx.x == 0) c.nrm2()[j + 1] = nv;
-      if (j + 1 < a.m - 1 && pk_s_abort == 0) pk_load_halo_nosync<S>(a, c, pk_col<S>(a, start, j + 1));
-    }
+    if (!grid_barrier(gs)) return false;
+    PKT(600 + j); // barrier passed
+    // one latency window: warp 0 gathers ||w||^2 while warps 1.. fetch the next iteration's halo rows
+    if (j + 1 < a.m - 1 && threadIdx.x >= 32)
+      pk_load_halo_part<S>(a, c, pk_col<S>(a, start, j + 1), threadIdx.x - 32, kPkThreads - 32);
+    else
+      pk_gather_nosync(1, a.part, gs.slot ^ 1, a.ncta, c.vals());
+    if (threadIdx.x == 0) c.nrm2()[j + 1] = c.vals()[0];
     __syncthreads();
-    if (!pk_round_done(gs)) return false;
     PKT(700 + j); // gathered
   }
   return true;
@@ -952,8 +897,9 @@ __device__ __forceinline__ void pk_carve(const PkArgs &a, PkCtx<S> &c, unsigned 
 // publish ||start||^2, barrier, gather -> nrm2[0]
 template <class S>
 __device__ __forceinline__ bool pk_start_norm(const PkArgs &a, PkCtx<S> &c, GridSync &gs, double (&nrm)[1]) {
-  pk_publish<1>(nrm, a.part, gs, c.red(), 0);
-  if (!pk_gather(1, a.part, gs, c.vals())) return false;
+  pk_publish<1>(nrm, a.part, gs.slot, c.red(), 0);
+  if (!grid_barrier(gs)) return false;
+  pk_gather(1, a.part, gs.slot ^ 1, a.ncta, c.vals());
   if (threadIdx.x == 0) c.nrm2()[0] = c.vals()[0];
   __syncthreads();
   return true;
@@ -983,8 +929,7 @@ __global__ void __launch_bounds__(kPkThreads, 1) k_pk_nlse(PkArgs a, double2 *sv
   extern __shared__ __align__(16) unsigned char pk_smem[];
   PkCtx<double2> c;
   pk_carve<double2>(a, c, pk_smem);
-  GridSync gs{a.bar, 0u, (unsigned)a.ncta, 0, a.status, min(kPkMaxK, 2 * a.m + 2)};
-  if (threadIdx.x == 0) pk_s_abort = 0;
+  GridSync gs{a.bar, 0u, (unsigned)a.ncta, 0, a.status};
   if (a.debug_fault && blockIdx.x == (unsigned)a.ncta - 1u) return; // test hook: one CTA never arrives
   const NlseParams p{0.5 * a.dt, a.s1, a.s2, a.kappa};
   double2 *ucur = (double2 *)a.u0, *unext = (double2 *)a.u1;
@@ -1127,8 +1072,7 @@ __global__ void __launch_bounds__(kPkThreads, 1) k_pk_gautschi(PkArgs a, double 
   extern __shared__ __align__(16) unsigned char pk_smem[];
   PkCtx<double> c;
   pk_carve<double>(a, c, pk_smem);
-  GridSync gs{a.bar, 0u, (unsigned)a.ncta, 0, a.status, min(kPkMaxK, 2 * a.m + 2)};
-  if (threadIdx.x == 0) pk_s_abort = 0;
+  GridSync gs{a.bar, 0u, (unsigned)a.ncta, 0, a.status};
   if (a.debug_fault && blockIdx.x == (unsigned)a.ncta - 1u) return; // test hook: one CTA never arrives
   double *u = (double *)a.u0, *up = (double *)a.u1 + c.s0, *accb = (double *)a.acc;
   PK_GLOBAL(u);
@@ -1246,8 +1190,7 @@ __global__ void __launch_bounds__(kPkThreads, 1) k_pk_sv(PkArgs a, double *b0, d
   extern __shared__ __align__(16) unsigned char pk_smem[];
   PkCtx<double> c;
   pk_carve<double>(a, c, pk_smem, 2 * a.g.nx); // both tiles carry halo rows: they swap roles every step
-  GridSync gs{a.bar, 0u, (unsigned)a.ncta, 0, a.status, min(kPkMaxK, 2 * a.m + 2)};
-  if (threadIdx.x == 0) pk_s_abort = 0;
+  GridSync gs{a.bar, 0u, (unsigned)a.ncta, 0, a.status};
   if (a.debug_fault && blockIdx.x == (unsigned)a.ncta - 1u) return; // test hook: one CTA never arrives
   double *buf[3] = {b0, b1, b2};
   double *xc = c.X() + a.g.nx, *pc = c.Wt() + a.g.nx; // u tile centre, u_past tile centre

@@ -174,11 +174,14 @@ bool run_ensemble(const Spec &s, const nls::Grid &g, uint32_t krylov, double dt,
   if (ds) oshape.assign(want.size(), ds);
   oshape.insert(oshape.begin(), ns);
   if (Bu) oshape.insert(oshape.begin(), B);
-  std::vector<T> tu((size_t)B * ns * no), tv(real ? (size_t)B * ns * no : 0);
+  // the trajectory file images live in page-locked memory: every snapshot leaves the device through the
+  // asynchronous egress ring (nls_get_field[_resampled]_async) straight into its (b, snapshot) slot while the next
+  // segment's steps run (the reference blocks on a cudaMemcpy per snapshot, nlse_dev.hpp:323-334)
+  nls::Pinned<T> tu((size_t)B * ns * no), tv(real ? (size_t)B * ns * no : 0);
   if (!ds)
     for (uint64_t b = 0; b < B; ++b) {
-      std::copy(u0.begin() + b * n, u0.begin() + (b + 1) * n, tu.begin() + b * ns * n);
-      if (real) std::copy(v0.begin() + b * n, v0.begin() + (b + 1) * n, tv.begin() + b * ns * n);
+      std::copy(u0.begin() + b * n, u0.begin() + (b + 1) * n, tu.data() + b * ns * n);
+      if (real) std::copy(v0.begin() + b * n, v0.begin() + (b + 1) * n, tv.data() + b * ns * n);
     }
 
   // --diag: [mass, energy] of every stored snapshot, reduced on the device (nls_reduce)
@@ -193,7 +196,6 @@ bool run_ensemble(const Spec &s, const nls::Grid &g, uint32_t krylov, double dt,
       h.set(NLS_FIELD_M, m.data(), n * 8);
       h.set(NLS_FIELD_U, u0.data() + b0 * n, nb * n * sizeof(T));
       if (real) h.set(NLS_FIELD_V, v0.data() + b0 * n, nb * n * sizeof(T));
-      std::vector<T> su(nb > 1 || ds ? nb * no : 0), sv(real && (nb > 1 || ds) ? nb * no : 0);
       std::vector<double> red(nb);
       auto diagnose = [&](size_t snap) {
         if (!diag) return;
@@ -202,23 +204,17 @@ bool run_ensemble(const Spec &s, const nls::Grid &g, uint32_t krylov, double dt,
           for (uint64_t b = 0; b < nb; ++b) dg[((b0 + b) * ns + snap) * 2 + q] = red[b];
         }
       };
+      const size_t tstride = (size_t)ns * no * sizeof(T); // bytes between consecutive trajectories in the file image
       auto store = [&](size_t snap) {
         diagnose(snap);
-        if (!ds && nb == 1) { // straight into the trajectory
-          h.get(NLS_FIELD_U, tu.data() + (b0 * ns + snap) * n, n * sizeof(T));
-          if (real) h.get(NLS_FIELD_V, tv.data() + (b0 * ns + snap) * n, n * sizeof(T));
-          return;
-        }
+        T *du = tu.data() + (b0 * ns + snap) * no;
+        T *dv = real ? tv.data() + (b0 * ns + snap) * no : nullptr;
         if (ds) {
-          h.get_resampled(NLS_FIELD_U, ds, ds, dtz, su.data(), nb * no * sizeof(T));
-          if (real) h.get_resampled(NLS_FIELD_V, ds, ds, dtz, sv.data(), nb * no * sizeof(T));
+          h.get_resampled_async(NLS_FIELD_U, ds, ds, dtz, du, nb * no * sizeof(T), tstride);
+          if (real) h.get_resampled_async(NLS_FIELD_V, ds, ds, dtz, dv, nb * no * sizeof(T), tstride);
         } else {
-          h.get(NLS_FIELD_U, su.data(), nb * n * sizeof(T));
-          if (real) h.get(NLS_FIELD_V, sv.data(), nb * n * sizeof(T));
-        }
-        for (uint64_t b = 0; b < nb; ++b) {
-          std::copy(su.begin() + b * no, su.begin() + (b + 1) * no, tu.begin() + ((b0 + b) * ns + snap) * no);
-          if (real) std::copy(sv.begin() + b * no, sv.begin() + (b + 1) * no, tv.begin() + ((b0 + b) * ns + snap) * no);
+          h.get_async(NLS_FIELD_U, du, nb * n * sizeof(T), tstride);
+          if (real) h.get_async(NLS_FIELD_V, dv, nb * n * sizeof(T), tstride);
         }
       };
       if (ds) store(0);
@@ -231,7 +227,7 @@ bool run_ensemble(const Spec &s, const nls::Grid &g, uint32_t krylov, double dt,
         i = next + 1;
         if (next % freq == 0 && next / freq < ns) store(next / freq);
       }
-      h.sync();
+      h.wait(); // steps and snapshot transfers
     } catch (const std::exception &e) { errors[gi] = e.what(); }
   };
   if (G == 1) worker(0);
