@@ -306,12 +306,16 @@ def measure(cx, name, w, K, W, repeats, sample_clocks):
         eng, z0, nz = slabs.make_slab_engine(mk, nzg, cx.dist if world > 1 else None, rank, world,
                                              torch.device("cuda", lr))
         d = eng.desc
-        u0, v0 = slab_ic(n, z0, nz, nzg, w["L"])[None], None
+        # m(x) == 1 and the analytic initial condition are generated ON THE DEVICE from the global grid coordinates
+        # (nls_generate_field): no 2 GiB-per-rank host arrays
+        from nls_b200 import fieldgen, GEN
+        eng.generate(FIELD.M, [(GEN.CONST, 0, [1.0])], L=w["L"])
+        eng.generate(FIELD.U, *fieldgen.slab_ic(w["L"]), L=w["L"])
     else:
         d = make_desc(w, batch=batch, device=lr)
         u0, v0 = make_state(w, batch, seed0=rank * batch)
         eng = Engine(d)
-    load_state(eng, w, u0, v0)
+        load_state(eng, w, u0, v0)
     dt = w["dt"]
     sites = d.n * batch
 

@@ -221,6 +221,41 @@ int nls_reduce(nls_handle h, int what, double *out);
 int nls_get_field_resampled(nls_handle h, int field, uint32_t tnx, uint32_t tny, uint32_t tnz, void *host_dst,
                             size_t bytes);
 
+/* ---- on-device field / initial-condition generators ----
+ * The closed-form m(x) / c(x) fields of finalized_scripts/m_fields_2d.py:14-147 and c_fields_2d.py:12-169 and the
+ * analytic initial conditions, evaluated on the device at x_i = numpy.linspace(-L, L, n)[i] of the GLOBAL grid (a
+ * z-slab handle fills its own planes: no 16 GiB host array for the 1024^3 case).  field = sum of terms, then one
+ * post-operation.  The random PARAMETERS of the scripts' fields are drawn on the host by the caller (tools mirror
+ * the scripts' numpy RNG call order: nonlinear-solvers_b200/fieldgen.py); generators that need n x n random arrays
+ * or image filters (multiscale, turbulent, topological, waveguide) are not closed-form and stay host-side.
+ * Axes are the ENGINE's: x = fastest index.  (The scripts build X, Y with indexing='ij', i.e. their X runs along
+ * the slow array axis = the engine's y.)
+ *   NLS_GEN_CONST          p0
+ *   NLS_GEN_GAUSS          p0 amp, p1..p3 centre (x,y,z), p4 width:   amp exp(-r^2 / (2 w^2))
+ *   NLS_GEN_COSWAVE        p0 amp, p1..p3 k, p4 phase, p5 f; iparam 1 = sin:   amp cos(f (k.x) + phase)
+ *   NLS_GEN_TANH_BOUNDARY  p0 m1, p1 m2, p2 radius, p3 width; iparam 0 circle 1 square 2 x 3 y 4 diagonal
+ *   NLS_GEN_SINSIN         p0 base, p1 amp, p2 k:   base (1 + amp sin(k x) sin(k y))
+ *   NLS_GEN_LAYERS         p0 base, p1 contrast, p2 L, p3 axis (0 x, 1 y); iparam number of layers
+ *   NLS_GEN_CHECKER        p0 base, p1 cell, p2 sharpness (<= 0: sign)
+ *   NLS_GEN_HALFSPACE      p0 base, p1 sharpness, p2 L, p3 axis
+ *   NLS_GEN_GAUSS_WAVE     p0 amp, p1..p3 centre, p4 sigma, p5..p7 k:   amp exp(-r^2/(2 s^2)) exp(i k.x)  (complex)
+ *   NLS_GEN_KINK           p0 amp, p1 a, p2 b:   amp atan(exp(a - b sqrt((x-y)^2/3 + (x+y)^2/2)))
+ * post: NONE; CLAMP_MIN max(v, p0); MINMAX p0 (v - min)/(max - min); MAXABS v / max|v|; GRADIENT_MASS (no terms)
+ * p0 (1 + p1 g^2/(g^2 + p2^2)) with g = central differences / 2 of the handle's c field (m_fields_2d.py:38-49).
+ * field: NLS_FIELD_U (trajectory `traj`, or all with -1), NLS_FIELD_M, NLS_FIELD_C.  MINMAX / MAXABS need the
+ * whole field on one device: not on z-slab handles. */
+typedef struct nls_gen_term {
+  int32_t kind;   /* NLS_GEN_* */
+  int32_t iparam;
+  double p[10];
+} nls_gen_term;
+enum { NLS_GEN_CONST = 0, NLS_GEN_GAUSS = 1, NLS_GEN_COSWAVE = 2, NLS_GEN_TANH_BOUNDARY = 3, NLS_GEN_SINSIN = 4,
+       NLS_GEN_LAYERS = 5, NLS_GEN_CHECKER = 6, NLS_GEN_HALFSPACE = 7, NLS_GEN_GAUSS_WAVE = 8, NLS_GEN_KINK = 9 };
+enum { NLS_GENPOST_NONE = 0, NLS_GENPOST_CLAMP_MIN = 1, NLS_GENPOST_MINMAX = 2, NLS_GENPOST_MAXABS = 3,
+       NLS_GENPOST_GRADIENT_MASS = 4 };
+int nls_generate_field(nls_handle h, int field, int32_t traj, const nls_gen_term *terms, uint32_t nterms, int post,
+                       const double *post_params /* [3] */, double Lx, double Ly, double Lz);
+
 /* ---- asynchronous snapshot egress / state upload ----
  * Replaces the blocking cudaMemcpy per snapshot of nlsolvers/device/include/nlse_dev.hpp:323-334
  * (store_snapshot_online) and sg_single_dev.hpp:96-100: the snapshot is copied device-to-device into a 2-deep

@@ -37,6 +37,16 @@ class NlsError(RuntimeError):
     pass
 
 
+class GenTerm(C.Structure):
+    """struct nls_gen_term (include/nls.h): one term of an on-device field generator."""
+    _fields_ = [("kind", C.c_int32), ("iparam", C.c_int32), ("p", C.c_double * 10)]
+
+
+GEN = SimpleNamespace(CONST=0, GAUSS=1, COSWAVE=2, TANH_BOUNDARY=3, SINSIN=4, LAYERS=5, CHECKER=6, HALFSPACE=7,
+                      GAUSS_WAVE=8, KINK=9)
+GENPOST = SimpleNamespace(NONE=0, CLAMP_MIN=1, MINMAX=2, MAXABS=3, GRADIENT_MASS=4)
+
+
 class Desc(C.Structure):
     """struct nls_desc (include/nls.h)."""
     _fields_ = [
@@ -139,6 +149,7 @@ _SIGS = {
     "nls_csr_residual": (C.c_int, [_vp, _vp, _vp, _vp, C.c_uint32, C.c_uint64, C.c_int, C.c_int, _dp]),
     "nls_pointer_is_device": (C.c_int, [_vp]),
     "nls_memcpy_to_host": (C.c_int, [_vp, _vp, _sz]),
+    "nls_generate_field": (C.c_int, [_vp, C.c_int, C.c_int32, _vp, C.c_uint32, C.c_int, _dp, C.c_double, C.c_double, C.c_double]),
     "nls_slab_export": (C.c_int, [_vp, _vp]),
     "nls_slab_connect": (C.c_int, [_vp, _vp, C.c_int, C.c_int]),
 }
@@ -296,6 +307,19 @@ class Engine:
         self._check(self.lib.nls_lanczos(self.h, _ptr(x), _ptr(V), _ptr(alpha),
                                          beta.ctypes.data_as(_dp)))
         return V, alpha, beta
+
+    def generate(self, field, terms, post=0, post_params=(0.0, 0.0, 0.0), L=None, traj=-1):
+        """fill a field on the device from a term table (nls_generate_field).  terms: [(kind, iparam, [p...]), ...];
+        L: box half-length(s), scalar or (Lx, Ly, Lz)."""
+        arr = (GenTerm * max(len(terms), 1))()
+        for t, (kind, ip, ps) in zip(arr, terms):
+            t.kind, t.iparam = int(kind), int(ip)
+            for q, v in enumerate(ps):
+                t.p[q] = float(v)
+        Ls = (1.0, 1.0, 1.0) if L is None else (L, L, L) if np.isscalar(L) else tuple(L) + (L[-1],) * (3 - len(L))
+        pp = (C.c_double * 3)(*[float(x) for x in (list(post_params) + [0.0, 0.0, 0.0])[:3]])
+        self._check(self.lib.nls_generate_field(self.h, field, traj, arr if terms else None, len(terms), post, pp,
+                                                float(Ls[0]), float(Ls[1]), float(Ls[2])))
 
     def csr_residual(self, csr):
         """max |CSR x - L x| / max |L x| for a scipy.sparse CSR matrix (host arrays) -- nls_csr_residual"""

@@ -1085,6 +1085,68 @@ int nls_get_field_resampled(nls_handle e, int field, uint32_t tnx, uint32_t tny,
   return check_status(e);
 }
 
+// ---- on-device field / IC generators
+int nls_generate_field(nls_handle e, int field, int32_t traj, const nls_gen_term *terms, uint32_t nterms, int post,
+                       const double *pp, double Lx, double Ly, double Lz) {
+  if (!e) return fail(NLS_ERR_ARG, "null handle");
+  if (e->poison) return poisoned(e);
+  if (post < NLS_GENPOST_NONE || post > NLS_GENPOST_GRADIENT_MASS) return fail(NLS_ERR_ARG, "generate: bad post-operation");
+  if (post != NLS_GENPOST_GRADIENT_MASS && (!terms || nterms == 0 || nterms > 4096)) return fail(NLS_ERR_ARG, "generate: need 1..4096 terms");
+  if (post != NLS_GENPOST_NONE && !pp) return fail(NLS_ERR_ARG, "generate: post-operation parameters missing");
+  if (field != NLS_FIELD_U && field != NLS_FIELD_M && field != NLS_FIELD_C) return fail(NLS_ERR_ARG, "generate: NLS_FIELD_U, _M or _C");
+  if (field == NLS_FIELD_U && (traj < -1 || traj >= e->batch)) return fail(NLS_ERR_ARG, "generate: bad trajectory index");
+  if ((post == NLS_GENPOST_MINMAX || post == NLS_GENPOST_MAXABS) && e->slab)
+    return fail(NLS_ERR_STATE, "generate: normalising post-operations are not available on z-slab handles");
+  if (post == NLS_GENPOST_GRADIENT_MASS && (e->d.laplacian != NLS_LAP_ANISO || e->g.dim3 || field != NLS_FIELD_M))
+    return fail(NLS_ERR_STATE, "generate: GRADIENT_MASS fills m(x) from the c field of a 2D div(c grad) handle");
+  for (uint32_t q = 0; q < nterms; ++q)
+    if (terms[q].kind < NLS_GEN_CONST || terms[q].kind > NLS_GEN_KINK) return fail(NLS_ERR_ARG, "generate: bad term kind");
+  CU(cudaSetDevice(e->d.device));
+  nls_gen_term *dterms = nullptr;
+  unsigned long long *mm = nullptr;
+  auto cleanup = [&]() { cudaFree(dterms); cudaFree(mm); };
+  const int nb = (field == NLS_FIELD_U && traj < 0) ? e->batch : 1;
+  if (nterms) {
+    if (cudaMalloc(&dterms, nterms * sizeof(nls_gen_term)) != cudaSuccess) return fail(NLS_ERR_CUDA, "generate: allocation failed");
+    cudaMemcpyAsync(dterms, terms, nterms * sizeof(nls_gen_term), cudaMemcpyHostToDevice, e->stream);
+  }
+  std::vector<unsigned long long> init(3 * nb);
+  for (int b = 0; b < nb; ++b) { init[3 * b] = ~0ull; init[3 * b + 1] = 0ull; init[3 * b + 2] = 0ull; }
+  if (cudaMalloc(&mm, init.size() * 8) != cudaSuccess) { cleanup(); return fail(NLS_ERR_CUDA, "generate: allocation failed"); }
+  cudaMemcpyAsync(mm, init.data(), init.size() * 8, cudaMemcpyHostToDevice, e->stream);
+  const double p0 = pp ? pp[0] : 0.0, p1 = pp ? pp[1] : 0.0, p2 = pp ? pp[2] : 0.0;
+  const dim3 gr((unsigned)e->nblk, (unsigned)nb);
+  const bool cstate = field == NLS_FIELD_U && e->cplx;
+  void *dst;
+  if (field == NLS_FIELD_M) dst = e->mf;
+  else if (field == NLS_FIELD_C) dst = e->cf;
+  else dst = (char *)(e->cplx ? e->u[e->phase] : (void *)cur_u(e)) + (traj > 0 ? (size_t)traj * e->g.stride * e->esz : 0);
+  if (cstate) {
+    k_generate<double2><<<gr, kThreads, 0, e->stream>>>(e->g, dterms, (int)nterms, post, p0, p1, p2, e->cf, Lx, Ly, Lz, (double2 *)dst,
+                                                     e->g.stride, mm);
+    if (post == NLS_GENPOST_MINMAX || post == NLS_GENPOST_MAXABS)
+      k_generate_post<double2><<<gr, kThreads, 0, e->stream>>>(e->g, post, p0, (double2 *)dst, e->g.stride, mm);
+  } else {
+    k_generate<double><<<gr, kThreads, 0, e->stream>>>(e->g, dterms, (int)nterms, post, p0, p1, p2, e->cf, Lx, Ly, Lz, (double *)dst,
+                                                    e->g.stride, mm);
+    if (post == NLS_GENPOST_MINMAX || post == NLS_GENPOST_MAXABS)
+      k_generate_post<double><<<gr, kThreads, 0, e->stream>>>(e->g, post, p0, (double *)dst, e->g.stride, mm);
+  }
+  e->launches += (post == NLS_GENPOST_MINMAX || post == NLS_GENPOST_MAXABS) ? 2 : 1;
+  cudaError_t ce = cudaGetLastError();
+  if (ce == cudaSuccess && field == NLS_FIELD_U) e->sewi_started = false;
+  if (ce == cudaSuccess && e->slab && e->connected) { // collective on slab handles, like nls_set_field
+    if (field == NLS_FIELD_C) halo_exchange<double>(e, e->cf);
+    else if (field == NLS_FIELD_U && !e->cplx) halo_exchange<double>(e, cur_u(e));
+    ce = cudaGetLastError();
+  }
+  e->start_valid = false;
+  if (ce == cudaSuccess) ce = cudaStreamSynchronize(e->stream); // terms / mm are freed below
+  cleanup();
+  if (ce != cudaSuccess) return fail(NLS_ERR_CUDA, std::string("generate: ") + cudaGetErrorString(ce));
+  return NLS_OK;
+}
+
 // ---- asynchronous transfers (replaces the blocking cudaMemcpy per snapshot of nlse_dev.hpp:323-334)
 static int async_init(nls_handle e) {
   if (e->async_used) return NLS_OK;

@@ -1026,6 +1026,142 @@ k_csr_residual(long long n, const int *__restrict__ rp, const int *__restrict__ 
   }
 }
 
+// ---- on-device field / initial-condition generators (include/nls.h nls_generate_field) -------------
+// Closed-form fields of finalized_scripts/m_fields_2d.py:14-147 and c_fields_2d.py:12-169 (and the bench's analytic
+// initial conditions) evaluated at the grid points x_i = linspace(-L, L, n)[i] of the GLOBAL grid, so a z-slab
+// handle fills its own planes without any host array.  A field is a sum of terms followed by one post-operation.
+__device__ __forceinline__ double gen_coord(int i, int n, double L) { // numpy.linspace(-L, L, n)[i]
+  if (n <= 1) return -L;
+  const double step = (L - (-L)) / (double)(n - 1);
+  return i == n - 1 ? L : (double)i * step + (-L);
+}
+__device__ __forceinline__ double2 gen_term_eval(const nls_gen_term &t, double x, double y, double z, bool dim3) {
+  const double *p = t.p;
+  switch (t.kind) {
+  case NLS_GEN_CONST: return make_double2(p[0], 0.0);
+  case NLS_GEN_GAUSS: { // amp * exp(-r^2 / (2 w^2))      m_fields_2d.py:96-99
+    double r2 = (x - p[1]) * (x - p[1]) + (y - p[2]) * (y - p[2]);
+    if (dim3) r2 += (z - p[3]) * (z - p[3]);
+    return make_double2(p[0] * exp(-r2 / (2 * (p[4] * p[4]))), 0.0);
+  }
+  case NLS_GEN_COSWAVE: { // amp * cos|sin(f * (k . x) + phase)   m_fields_2d.py:121-125, c_fields_2d.py:60-66
+    double kd = p[1] * x + p[2] * y;
+    if (dim3) kd += p[3] * z;
+    const double a = p[5] * kd + p[4];
+    return make_double2(p[0] * (t.iparam ? sin(a) : cos(a)), 0.0);
+  }
+  case NLS_GEN_TANH_BOUNDARY: { // m1 + (m2 - m1) * 0.5 (1 + tanh(boundary / width))   m_fields_2d.py:17-36
+    double b;
+    switch (t.iparam) {
+    case 0: b = sqrt(x * x + y * y) - p[2]; break;
+    case 1: b = fmax(fabs(x), fabs(y)) - p[2]; break;
+    case 2: b = x; break; // boundary along the engine's x axis
+    case 3: b = y; break;
+    default: b = y + x; break;
+    }
+    return make_double2(p[0] + (p[1] - p[0]) * (0.5 * (1 + tanh(b / p[3]))), 0.0);
+  }
+  case NLS_GEN_SINSIN: // base * (1 + amp * sin(k x) sin(k y))   c_fields_2d.py:15-19
+    return make_double2(p[0] * (1 + p[1] * (sin(p[2] * y) * sin(p[2] * x))), 0.0);
+  case NLS_GEN_LAYERS: { // base, or base * contrast inside the odd layers along one axis   c_fields_2d.py:21-33
+    const double c = p[3] != 0.0 ? y : x, L = p[2];
+    const double lw = 2 * L / (double)t.iparam;
+    double v = p[0];
+    for (int i = 1; i < t.iparam; i += 2) {
+      const double lo = -L + i * lw, hi = -L + (i + 1) * lw;
+      if (c >= lo && c < hi) v = p[0] * p[1];
+    }
+    return make_double2(v, 0.0);
+  }
+  case NLS_GEN_CHECKER: { // base * tanh(sharp * sin(pi x / cell) sin(pi y / cell))   c_fields_2d.py:36-46
+    const double pi = 3.141592653589793;
+    const double pat = sin(pi * y / p[1]) * sin(pi * x / p[1]);
+    if (p[2] > 0) return make_double2(p[0] * tanh(p[2] * pat), 0.0);
+    return make_double2(p[0] * (pat > 0 ? 1.0 : pat < 0 ? -1.0 : 0.0), 0.0);
+  }
+  case NLS_GEN_HALFSPACE: // base * tanh(sharp * coordinate / L)   c_fields_2d.py:47-48
+    return make_double2(p[0] * tanh(p[1] * (p[3] != 0.0 ? y : x) / p[2]), 0.0);
+  case NLS_GEN_GAUSS_WAVE: { // amp * exp(-r^2 / (2 s^2)) * exp(i k . x): the Gaussian-bump initial conditions
+    double r2 = (x - p[1]) * (x - p[1]) + (y - p[2]) * (y - p[2]);
+    double ph = p[5] * x + p[6] * y;
+    if (dim3) { r2 += (z - p[3]) * (z - p[3]); ph += p[7] * z; }
+    const double a = p[0] * exp(-r2 / (2 * (p[4] * p[4])));
+    double sn, cs;
+    sincos(ph, &sn, &cs);
+    return make_double2(a * cs, a * sn);
+  }
+  default: { // NLS_GEN_KINK: amp * atan(exp(a - b sqrt((x-y)^2/3 + (x+y)^2/2)))   root sg_driver.cpp:62-64
+    const double r = sqrt((x - y) * (x - y) / 3.0 + (x + y) * (x + y) / 2.0);
+    return make_double2(p[0] * atan(exp(p[1] - p[2] * r)), 0.0);
+  }
+  }
+}
+// pass 1: out = sum of terms (POST_GRADIENT_MASS: from the c field); mm[0..2] = ordered-int min, max, max|.|
+template <class S>
+__global__ void __launch_bounds__(kThreads)
+k_generate(Geom g, const nls_gen_term *__restrict__ terms, int nterms, int post, double p0, double p1, double p2,
+           const double *__restrict__ cf, double Lx, double Ly, double Lz, S *__restrict__ out, long long ostride,
+           unsigned long long *mm) {
+  S *ob = out + (size_t)blockIdx.y * ostride + g.halo;
+  double vmin = 1e300, vmax = -1e300, amax = 0.0;
+  for (long long idx = (long long)blockIdx.x * kThreads + threadIdx.x; idx < g.n; idx += (long long)gridDim.x * kThreads) {
+    const unsigned ugi = (unsigned)(idx + g.goff);
+    const int i = (int)(ugi % (unsigned)g.nx), jj = (int)(ugi / (unsigned)g.nx);
+    const int j = g.dim3 ? jj % g.ny : jj, k = g.dim3 ? jj / g.ny : 0;
+    double2 v = make_double2(0.0, 0.0);
+    if (post == NLS_GENPOST_GRADIENT_MASS) { // m_fields_2d.py:38-49: central differences / 2 of c, zero on the edges
+      const double *c = cf + g.halo;
+      const double gy = (j >= 1 && j <= g.ny - 2) ? (c[idx + g.nx] - c[idx - g.nx]) / 2 : 0.0; // script axis 0 = engine y
+      const double gx = (i >= 1 && i <= g.nx - 2) ? (c[idx + 1] - c[idx - 1]) / 2 : 0.0;
+      const double gs = gy * gy + gx * gx;
+      v.x = p0 * (1 + p1 * gs / (gs + p2 * p2));
+    } else {
+      const double x = gen_coord(i, g.nx, Lx), y = gen_coord(j, g.ny, Ly), z = g.dim3 ? gen_coord(k, g.nz_glob, Lz) : 0.0;
+      for (int q = 0; q < nterms; ++q) {
+        const double2 t = gen_term_eval(terms[q], x, y, z, g.dim3 != 0);
+        v.x += t.x;
+        v.y += t.y;
+      }
+      if (post == NLS_GENPOST_CLAMP_MIN) v.x = fmax(v.x, p0);
+    }
+    if (Sc<S>::W == 2) ((double *)(ob + idx))[0] = v.x, ((double *)(ob + idx))[1] = v.y;
+    else ((double *)(ob + idx))[0] = v.x;
+    vmin = fmin(vmin, v.x);
+    vmax = fmax(vmax, v.x);
+    amax = fmax(amax, Sc<S>::W == 2 ? sqrt(v.x * v.x + v.y * v.y) : fabs(v.x));
+  }
+  if (post == NLS_GENPOST_MINMAX || post == NLS_GENPOST_MAXABS) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      vmin = fmin(vmin, __shfl_xor_sync(0xffffffffu, vmin, o));
+      vmax = fmax(vmax, __shfl_xor_sync(0xffffffffu, vmax, o));
+      amax = fmax(amax, __shfl_xor_sync(0xffffffffu, amax, o));
+    }
+    if ((threadIdx.x & 31) == 0) { // order-preserving map of doubles to unsigned integers
+      auto key = [](double d) { const long long b = __double_as_longlong(d); return (unsigned long long)(b < 0 ? ~b : (b | (long long)0x8000000000000000ull)); };
+      atomicMin(mm + 3 * blockIdx.y, key(vmin));
+      atomicMax(mm + 3 * blockIdx.y + 1, key(vmax));
+      atomicMax(mm + 3 * blockIdx.y + 2, key(amax));
+    }
+  }
+}
+// pass 2 of the normalising post-operations
+template <class S>
+__global__ void __launch_bounds__(kThreads)
+k_generate_post(Geom g, int post, double p0, S *__restrict__ out, long long ostride, const unsigned long long *mm) {
+  S *ob = out + (size_t)blockIdx.y * ostride + g.halo;
+  auto unkey = [](unsigned long long k) { const long long b = (k & 0x8000000000000000ull) ? (long long)(k & 0x7fffffffffffffffull) : ~(long long)k; return __longlong_as_double(b); };
+  const double vmin = unkey(mm[3 * blockIdx.y]), vmax = unkey(mm[3 * blockIdx.y + 1]), amax = unkey(mm[3 * blockIdx.y + 2]);
+  for (long long idx = (long long)blockIdx.x * kThreads + threadIdx.x; idx < g.n; idx += (long long)gridDim.x * kThreads) {
+    double *q = (double *)(ob + idx);
+    if (post == NLS_GENPOST_MINMAX) q[0] = p0 * ((q[0] - vmin) / (vmax - vmin)); // c_fields_2d.py:68-72
+    else {
+      q[0] = q[0] / amax; // u / abs(u).max()
+      if (Sc<S>::W == 2) q[1] = q[1] / amax;
+    }
+  }
+}
+
 // Multilinear resampling of a state onto a coarser linspace grid (nls_get_field_resampled):
 // downsampling.py:68-104 / :215-258.  One thread per target point; out is dense [batch][tz][ty][tx].
 // VEL: sample v = (u - u_past)/dt instead of u (real states).
