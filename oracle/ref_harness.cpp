@@ -28,6 +28,14 @@
 #include "sg_single_sv_solver.hpp"
 #include "kg_solver.hpp"
 #include "kg_sv_solver.hpp"
+#include "phi4_solver.hpp"
+#include "sg_double_solver.hpp"
+#include "sg_hyperbolic_solver.hpp"
+#include "sg_hyperbolic_sv_solver.hpp"
+#include "kg_solver_3d.hpp"
+#include "kg_sv_solver_3d.hpp"
+#undef NLSE_CUBIC_SOLVER_HPP // nlse_cubic_solver_3d.hpp re-uses the include guard of nlse_cubic_solver.hpp
+#include "nlse_cubic_solver_3d.hpp"
 
 using cplx = std::complex<double>;
 
@@ -147,6 +155,7 @@ static void bc_r(ref_ctx *h, Eigen::VectorX<double> &u) {
 
 // nsteps driver-loop bodies "step + boundary copy" of the NLSE solvers.
 // kind: 0 NLSESolver, 1 NLSEQuinticSolver, 2 NLSESaturatingSolver (SS2);
+//       3 NLSESolver3d (SS2, nlse_cubic_solver_3d.hpp);
 //       10 NLSECubicGautschiSolver (2D host convention), 11 NLSEGautschiSolver3d, 12 cq, 13 saturating (sEWI:
 //       u_prev in/out; the caller performs the SS2 start-up step with kind 0..2 like the drivers do)
 void ref_nlse_steps(ref_ctx *h, int kind, void *u_io, void *uprev_io, const double *mfield, double dt, double s1, double s2,
@@ -163,6 +172,7 @@ void ref_nlse_steps(ref_ctx *h, int kind, void *u_io, void *uprev_io, const doub
     case 0: NLSESolver::step<cplx>(buf, rho, u, h->Lc, m, tau); break;
     case 1: NLSEQuinticSolver::step<cplx>(buf, rho, u, h->Lc, m, tau, s1, s2); break;
     case 2: NLSESaturatingSolver::step<cplx>(buf, rho, u, h->Lc, m, tau, kappa); break;
+    case 3: NLSESolver3d::step<cplx>(buf, rho, u, h->Lc, mc, tau); break; // m declared complex there (nlse_cubic_solver_3d.hpp:12)
     case 10: NLSECubicGautschiSolver::step<cplx>(buf, rho, u, up, h->Lc, m, tau); break;
     case 11: NLSEGautschiSolver3d::step<cplx>(buf, rho, u, up, h->Lc, mc, tau); break;
     case 12: NLSECubicQuinticGautschiSolver::step<cplx>(buf, rho, u, up, h->Lc, m, tau, s1, s2); break;
@@ -174,7 +184,8 @@ void ref_nlse_steps(ref_ctx *h, int kind, void *u_io, void *uprev_io, const doub
   if (uprev_io) std::memcpy(uprev_io, up.data(), n * 16);
 }
 
-// kind: 0 SGESolver (Gautschi), 1 SGESolverSV, 2 KGESolver, 3 KGESVSolver
+// kind: 0 SGESolver (Gautschi), 1 SGESolverSV, 2 KGESolver, 3 KGESVSolver, 4 Phi4Solver, 5 SGEDoubleSolver,
+//       6 SGEHyperbolicSolver, 7 SGEHyperbolicSVSolver, 8 KGESolver3d, 9 KGESVSolver3d
 void ref_real_steps(ref_ctx *h, int kind, double *u_io, double *upast_io, const double *mfield, double dt, uint32_t nsteps) {
   const long n = h->Lr.rows();
   Eigen::VectorX<double> u(n), up(n), buf(n), m(n);
@@ -186,7 +197,13 @@ void ref_real_steps(ref_ctx *h, int kind, double *u_io, double *upast_io, const 
     case 0: SGESolver::step<double>(u, up, buf, h->Lr, m, dt); break;
     case 1: SGESolverSV::step<double>(u, up, buf, h->Lr, m, dt); break;
     case 2: KGESolver::step<double>(u, up, buf, h->Lr, m, dt); break;
-    default: KGESVSolver::step<double>(u, up, buf, h->Lr, m, dt);
+    case 3: KGESVSolver::step<double>(u, up, buf, h->Lr, m, dt); break;
+    case 4: Phi4Solver::step<double>(u, up, buf, h->Lr, m, dt); break;
+    case 5: SGEDoubleSolver::step<double>(u, up, buf, h->Lr, m, dt); break;
+    case 6: SGEHyperbolicSolver::step<double>(u, up, buf, h->Lr, m, dt); break;
+    case 7: SGEHyperbolicSVSolver::step<double>(u, up, buf, h->Lr, m, dt); break;
+    case 8: KGESolver3d::step<double>(u, up, buf, h->Lr, m, dt); break;
+    default: KGESVSolver3d::step<double>(u, up, buf, h->Lr, m, dt);
     }
     bc_r(h, u);
   }

@@ -133,3 +133,44 @@ def test_real_steps_match_reference_source(oracle_lib, R, eq, integ, kind, sign)
     u, up = R(n, n, 1, d.dx, sign=sign).real_steps(kind, u0.ravel(), (u0 - dt * v0).ravel(), mf, dt, steps)
     assert rel_l2(o.get(), u) < 1e-12
     assert rel_l2(o.get(FIELD.U_PAST), up) < 1e-12
+
+
+@pytest.mark.parametrize("eq,integ,kind,sign,dims", [
+    (EQ.PHI4, INT.GAUTSCHI, 4, -1.0, (32, 32, 1)),        # phi4_solver.hpp:13-23
+    (EQ.SGE_DOUBLE, INT.GAUTSCHI, 5, -1.0, (32, 32, 1)),  # sg_double_solver.hpp:13-23
+    (EQ.SGE_SINH, INT.GAUTSCHI, 6, -1.0, (32, 32, 1)),    # sg_hyperbolic_solver.hpp:13-23
+    (EQ.SGE_SINH, INT.SV, 7, 1.0, (32, 32, 1)),           # sg_hyperbolic_sv_solver.hpp:13-22
+    (EQ.KGE, INT.GAUTSCHI, 8, -1.0, (12, 12, 12)),        # kg_solver_3d.hpp:12-21
+    (EQ.KGE, INT.SV, 9, 1.0, (12, 12, 12))])              # kg_sv_solver_3d.hpp:13-21
+def test_remaining_real_step_headers_match_reference_source(oracle_lib, R, eq, integ, kind, sign, dims):
+    """the step headers VERDICT r01 listed as restated-only: now compiled from the reference tree as well"""
+    nx, ny, nz = dims
+    dt, steps = 1e-3, 8 if integ == INT.GAUTSCHI else 40
+    aniso = nz > 1
+    d = Desc.make(nx, ny, nz, L=10.0, equation=eq, integrator=integ, laplacian=LAP.ANISO if aniso else LAP.UNIFORM,
+                  krylov_m=10, dt=dt, op_sign=sign)
+    rng = np.random.default_rng(6)
+    u0 = 0.2 * (ics.kink_2d(nx, 10.0) if nz == 1 else np.abs(ics.gaussian_bumps_3d(nx, 10.0)))
+    v0 = 0.05 * np.cos(u0)
+    mf = 1.0 + 0.2 * rng.standard_normal(d.n)
+    c = 1.0 + 0.1 * rng.standard_normal(d.n) if aniso else None
+    o = oracle_lib.Oracle(d)
+    if aniso:
+        o.set(FIELD.C, c)
+    o.set(FIELD.U, u0); o.set(FIELD.V, v0); o.set(FIELD.M, mf); o.step(dt, steps)
+    u, up = R(nx, ny, nz, d.dx, aniso, c, sign=sign).real_steps(kind, u0.ravel(), (u0 - dt * v0).ravel(), mf, dt, steps)
+    assert rel_l2(o.get(), u) < 1e-12
+    assert rel_l2(o.get(FIELD.U_PAST), up) < 1e-12
+
+
+def test_nlse_cubic_3d_header_matches_reference_source(oracle_lib, R):
+    """nlse_cubic_solver_3d.hpp:10-27 (NLSESolver3d::step, m declared complex) on the anisotropic 3D operator"""
+    n, dt, steps = 12, 5e-4, 6
+    d = Desc.make(n, n, n, L=6.0, equation=EQ.NLSE_CUBIC, laplacian=LAP.ANISO, krylov_m=10)
+    c = 1.0 + 0.1 * np.random.default_rng(2).standard_normal(d.n)
+    mf = 1.0 + 0.2 * np.random.default_rng(1).standard_normal(d.n)
+    u0 = ics.gaussian_bumps_3d(n, 6.0)
+    o = oracle_lib.Oracle(d)
+    o.set(FIELD.C, c); o.set(FIELD.U, u0); o.set(FIELD.M, mf); o.step(dt, steps)
+    ref = R(n, n, n, d.dx, True, c).nlse_steps(3, u0.ravel(), mf, dt, steps)
+    assert rel_l2(o.get(), ref) < 1e-12
