@@ -88,7 +88,11 @@ enum {
 /* re-orthogonalisation mode of the Lanczos process */
 enum {
   NLS_REORTH_FULL = 0, /* alpha step + one block-dot + one block-update pass (reference: MGS sweep) */
-  NLS_REORTH_NONE = 1  /* plain 3-term recurrence (not the reference algorithm; opt-in) */
+  NLS_REORTH_NONE = 1, /* plain 3-term recurrence (not the reference algorithm; opt-in) */
+  NLS_REORTH_MGS = 2   /* the reference's sequential modified Gram-Schmidt sweep, operation for operation
+                        * (eigen_krylov_complex.hpp:28-38): one launch per dot product, multi-kernel path only.
+                        * Slow by construction; a bisecting tool that separates re-orthogonalisation rounding of
+                        * NLS_REORTH_FULL from a real defect when a parity run drifts */
 };
 
 /* matrix functions f(T) applied through the Krylov basis */
@@ -277,6 +281,14 @@ int nls_host_alloc(void **out, size_t bytes);
 int nls_host_free(void *p);
 int nls_host_register(void *p, size_t bytes);
 int nls_host_unregister(void *p);
+
+/* Spectral downsampling of a 2D field on the device = the launcher's `downsample_fft`
+ * (finalized_scripts/downsampling.py:10-34: ortho fft2 -> fftshift -> centred tny x tnx crop -> ifftshift -> ortho
+ * ifft2), evaluated as a direct cropped DFT (two small dense products, no FFT library).  host_dst:
+ * [batch][tny][tnx] scalars (real states: the real part, like the script).  2D single-GPU handles. */
+int nls_get_field_fft_resampled(nls_handle h, int field, uint32_t tnx, uint32_t tny, void *host_dst, size_t bytes);
+int nls_get_field_fft_resampled_async(nls_handle h, int field, uint32_t tnx, uint32_t tny, void *host_dst, size_t bytes,
+                                      size_t dst_traj_stride);
 
 /* number of kernel launches issued (directly or through graph replays) since creation */
 uint64_t nls_launch_count(nls_handle h);

@@ -130,6 +130,10 @@ public:
   void get_resampled_async(int field, uint32_t tnx, uint32_t tny, uint32_t tnz, void *dst, size_t bytes, size_t traj_stride = 0) {
     check(nls_get_field_resampled_async(h_, field, tnx, tny, tnz, dst, bytes, traj_stride), "nls_get_field_resampled_async");
   }
+  // spectral downsampling on the device (downsampling.py:10-34 downsample_fft), 2D handles
+  void get_fft_resampled_async(int field, uint32_t tnx, uint32_t tny, void *dst, size_t bytes, size_t traj_stride = 0) {
+    check(nls_get_field_fft_resampled_async(h_, field, tnx, tny, dst, bytes, traj_stride), "nls_get_field_fft_resampled_async");
+  }
   // NLS_RED_MASS / NLS_RED_ENERGY / NLS_RED_NONFINITE, one value per trajectory
   std::vector<double> reduce(int what) {
     std::vector<double> out(batch_);

@@ -20,7 +20,7 @@ _LIB = os.path.join(_PKG, "libnls_b200.so")
 EQ = SimpleNamespace(NLSE_CUBIC=0, NLSE_CQ=1, NLSE_SAT=2, SGE=3, KGE=4, PHI4=5, SGE_DOUBLE=6, SGE_SINH=7)
 INT = SimpleNamespace(SS2=0, GAUTSCHI=1, SV=2, SEWI=3)
 LAP = SimpleNamespace(UNIFORM=0, ANISO=1)
-REORTH = SimpleNamespace(FULL=0, NONE=1)
+REORTH = SimpleNamespace(FULL=0, NONE=1, MGS=2)
 FN = SimpleNamespace(EXP=0, SINC=1, COS_SQRT=2, SINC2_SQRT=3, ID_SQRT=4, SINC2_HALF=5, MOD_COSINE=6)
 FIELD = SimpleNamespace(U=0, U_PAST=1, V=2, M=3, C=4)
 RED = SimpleNamespace(MASS=0, NONFINITE=1, ENERGY=2)
@@ -150,6 +150,8 @@ _SIGS = {
     "nls_pointer_is_device": (C.c_int, [_vp]),
     "nls_memcpy_to_host": (C.c_int, [_vp, _vp, _sz]),
     "nls_generate_field": (C.c_int, [_vp, C.c_int, C.c_int32, _vp, C.c_uint32, C.c_int, _dp, C.c_double, C.c_double, C.c_double]),
+    "nls_get_field_fft_resampled": (C.c_int, [_vp, C.c_int, C.c_uint32, C.c_uint32, _vp, _sz]),
+    "nls_get_field_fft_resampled_async": (C.c_int, [_vp, C.c_int, C.c_uint32, C.c_uint32, _vp, _sz, _sz]),
     "nls_slab_export": (C.c_int, [_vp, _vp]),
     "nls_slab_connect": (C.c_int, [_vp, _vp, C.c_int, C.c_int]),
 }
@@ -246,6 +248,12 @@ class Engine:
         shape = (self.desc.batch, tnz, tny, tnx) if self.desc.nz > 1 else (self.desc.batch, tny, tnx)
         out = np.empty(shape, dtype=self.desc.dtype)
         self._check(self.lib.nls_get_field_resampled(self.h, field, tnx, tny, tnz, _ptr(out), out.nbytes))
+        return out
+
+    def get_fft_resampled(self, tnx, tny, field=FIELD.U):
+        """field downsampled spectrally on the device to (batch, tny, tnx) (downsampling.py:10-34 downsample_fft)."""
+        out = np.empty((self.desc.batch, tny, tnx), dtype=self.desc.dtype)
+        self._check(self.lib.nls_get_field_fft_resampled(self.h, field, tnx, tny, _ptr(out), out.nbytes))
         return out
 
     def get_into(self, field, out):

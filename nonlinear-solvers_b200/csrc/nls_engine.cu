@@ -53,6 +53,8 @@ struct nls_engine {
   void *V = nullptr;     // m-1 columns
   void *wbuf[2] = {nullptr, nullptr};
   void *rs = nullptr;   // dense output of nls_get_field_resampled (allocated on first use)
+  double2 *dft_wx = nullptr, *dft_wy = nullptr, *dft_t1 = nullptr; // cropped-DFT weights / intermediate (nls_get_field_fft_resampled)
+  uint32_t dft_tx = 0, dft_ty = 0;
   size_t rs_bytes = 0;
   void *w0 = nullptr;    // start vector (rho / g / matfunc input)
   void *u[3] = {nullptr, nullptr, nullptr};
@@ -293,7 +295,7 @@ void lanczos_t(nls_engine *e, const S *start, double *scal) {
   constexpr int kNC = 12; // columns per launch
   for (int j = 0; j < m - 1; ++j) {
     // columns taking part in the orthogonalisation: all of 0..j (reference), or only j (3-term)
-    const int c0 = e->d.reorth == NLS_REORTH_NONE ? j : 0;
+    const int c0 = e->d.reorth != NLS_REORTH_FULL ? j : 0;
     // pass A chunks: the stencil-carrying first chunk of a complex sweep takes at most kFirst columns;
     // beyond that the 128-register budget of 2 CTAs/SM costs more than re-reading w once in a second,
     // dots-only chunk.  Measured on B200 (profiles/r01f_firstcap.txt): div(c grad) stencil 6 (C3 12.0 ->
@@ -321,6 +323,14 @@ void lanczos_t(nls_engine *e, const S *start, double *scal) {
       else if (cnt <= 10) LA(10);
       else LA(12);
 #undef LA
+    }
+    if (e->d.reorth == NLS_REORTH_MGS) { // sequential sweep of the reference, one dot per launch (k_lanczos_mgs)
+      const Halo<S> none{nullptr, nullptr};
+      for (int i = 0; i <= j; ++i) // subtract the previous projection (first: the alpha term), dot with column i
+        LAUNCH(e, (k_lanczos_mgs<S, false>), gr, e->g, start, V, e->colstride, j, i == 0 ? j : i - 1, i, i == 0 ? 1 : 0, scal, e->rc, none);
+      LAUNCH(e, (k_lanczos_mgs<S, true>), gr, e->g, start, V, e->colstride, j, j, 0, 0, scal, e->rc,
+             halo_for<S>(e, V + (size_t)j * e->colstride));
+      continue;
     }
     // Gram entries of column j against the columns the LAST chunk of the previous pass B did not hold
     if (c0 == 0 && j >= 1)
@@ -829,7 +839,7 @@ int nls_destroy(nls_handle e) {
   }
   void *ptrs[] = {e->V, e->wbuf[0], e->wbuf[1], e->w0, e->u[0], e->u[1], e->u[2], e->acc, e->mf, e->cf,
                   e->scalA, e->scalB, e->coef, e->redout, e->rc.partials, e->rc.tickets, e->status,
-                  e->pk_part, e->pk_bar, e->sv2_prog, e->arena, e->slab_dev, e->slab_scratch, e->rs};
+                  e->pk_part, e->pk_bar, e->sv2_prog, e->dft_wx, e->dft_wy, e->dft_t1, e->arena, e->slab_dev, e->slab_scratch, e->rs};
   for (void *p : ptrs)
     if (p) cudaFree(p);
   for (int k = 0; k < 2; ++k) {
@@ -1085,6 +1095,69 @@ int nls_get_field_resampled(nls_handle e, int field, uint32_t tnx, uint32_t tny,
   return check_status(e);
 }
 
+// ---- spectral downsampling: downsample_fft (finalized_scripts/downsampling.py:10-34) as a direct cropped DFT
+static int dft_check(nls_handle e, int field, uint32_t tnx, uint32_t tny, size_t bytes) {
+  if (e->slab || e->g.dim3) return fail(NLS_ERR_STATE, "fft_resampled: 2D single-GPU handles only (the script's downsample_fft is 2D)");
+  if (field != NLS_FIELD_U && field != NLS_FIELD_V) return fail(NLS_ERR_ARG, "fft_resampled: NLS_FIELD_U or NLS_FIELD_V");
+  if (field == NLS_FIELD_V && e->cplx) return fail(NLS_ERR_STATE, "V: real equations only");
+  if (field == NLS_FIELD_V && !(e->d.dt > 0)) return fail(NLS_ERR_STATE, "V needs desc.dt > 0");
+  if (tnx < 1 || tny < 1 || tnx > (uint32_t)e->g.nx || tny > (uint32_t)e->g.ny)
+    return fail(NLS_ERR_ARG, "fft_resampled: need 1 <= tnx <= nx and 1 <= tny <= ny");
+  if (bytes != (size_t)tnx * tny * e->batch * e->esz) return fail(NLS_ERR_ARG, "fft_resampled: size mismatch");
+  return NLS_OK;
+}
+static int dft_launch(nls_handle e, int field, uint32_t tnx, uint32_t tny, void *out) {
+  if (e->dft_tx != tnx || e->dft_ty != tny) { // (re)build the two weight matrices for this target shape
+    CU(cudaStreamSynchronize(e->stream));
+    cudaFree(e->dft_wx); cudaFree(e->dft_wy); cudaFree(e->dft_t1);
+    e->dft_wx = e->dft_wy = e->dft_t1 = nullptr;
+    e->dft_tx = e->dft_ty = 0;
+    CU(cudaMalloc((void **)&e->dft_wx, (size_t)tnx * e->g.nx * 16));
+    CU(cudaMalloc((void **)&e->dft_wy, (size_t)tny * e->g.ny * 16));
+    CU(cudaMalloc((void **)&e->dft_t1, (size_t)e->batch * tny * e->g.nx * 16));
+    k_dft_weights<<<e->nsm * 4, kThreads, 0, e->stream>>>(e->dft_wx, e->g.nx, (int)tnx);
+    k_dft_weights<<<e->nsm * 4, kThreads, 0, e->stream>>>(e->dft_wy, e->g.ny, (int)tny);
+    e->launches += 2;
+    CU(cudaGetLastError());
+    e->dft_tx = tnx; e->dft_ty = tny;
+  }
+  const dim3 g1((e->g.nx + kThreads - 1) / kThreads, (unsigned)e->batch, (tny + 3) / 4);
+  const dim3 g2((unsigned)std::min<size_t>(((size_t)tnx * tny + kThreads - 1) / kThreads, (size_t)e->nsm * 8), (unsigned)e->batch);
+  if (e->cplx) {
+    k_dft_cols<double2, false><<<g1, kThreads, 0, e->stream>>>(e->g, (const double2 *)e->u[e->phase], nullptr, 0.0, e->dft_wy, (int)tny, e->dft_t1);
+    k_dft_rows<double2><<<g2, kThreads, 0, e->stream>>>(e->dft_t1, e->dft_wx, e->g.nx, (int)tnx, (int)tny, (double2 *)out);
+  } else {
+    if (field == NLS_FIELD_U)
+      k_dft_cols<double, false><<<g1, kThreads, 0, e->stream>>>(e->g, (const double *)cur_u(e), nullptr, 0.0, e->dft_wy, (int)tny, e->dft_t1);
+    else
+      k_dft_cols<double, true><<<g1, kThreads, 0, e->stream>>>(e->g, (const double *)cur_u(e), (const double *)cur_upast(e), 1.0 / e->d.dt,
+                                                               e->dft_wy, (int)tny, e->dft_t1);
+    k_dft_rows<double><<<g2, kThreads, 0, e->stream>>>(e->dft_t1, e->dft_wx, e->g.nx, (int)tnx, (int)tny, (double *)out);
+  }
+  e->launches += 2;
+  CU(cudaGetLastError());
+  return NLS_OK;
+}
+
+int nls_get_field_fft_resampled(nls_handle e, int field, uint32_t tnx, uint32_t tny, void *dst, size_t bytes) {
+  if (!e || !dst) return fail(NLS_ERR_ARG, "null argument");
+  if (e->poison) return poisoned(e);
+  int rc = dft_check(e, field, tnx, tny, bytes);
+  if (rc) return rc;
+  CU(cudaSetDevice(e->d.device));
+  if (e->rs_bytes < bytes) {
+    if (e->rs) CU(cudaFree(e->rs));
+    e->rs = nullptr; e->rs_bytes = 0;
+    CU(cudaMalloc(&e->rs, bytes));
+    e->rs_bytes = bytes;
+  }
+  rc = dft_launch(e, field, tnx, tny, e->rs);
+  if (rc) return rc;
+  CU(cudaMemcpyAsync(dst, e->rs, bytes, cudaMemcpyDeviceToHost, e->stream));
+  CU(cudaStreamSynchronize(e->stream));
+  return check_status(e);
+}
+
 // ---- on-device field / IC generators
 int nls_generate_field(nls_handle e, int field, int32_t traj, const nls_gen_term *terms, uint32_t nterms, int post,
                        const double *pp, double Lx, double Ly, double Lz) {
@@ -1248,6 +1321,25 @@ int nls_get_field_resampled_async(nls_handle e, int field, uint32_t tnx, uint32_
   rc = ring_slot(e, bytes, &k);
   if (rc) return rc;
   rc = resample_launch(e, field, tnx, tny, tnz, e->ring[k]);
+  if (rc) return rc;
+  return ring_drain(e, k, dst, per, dst_traj_stride);
+}
+
+int nls_get_field_fft_resampled_async(nls_handle e, int field, uint32_t tnx, uint32_t tny, void *dst, size_t bytes,
+                                      size_t dst_traj_stride) {
+  if (!e || !dst) return fail(NLS_ERR_ARG, "null argument");
+  if (e->poison) return poisoned(e);
+  int rc = dft_check(e, field, tnx, tny, bytes);
+  if (rc) return rc;
+  CU(cudaSetDevice(e->d.device));
+  const size_t per = (size_t)tnx * tny * e->esz;
+  if (dst_traj_stride != 0 && dst_traj_stride < per) return fail(NLS_ERR_ARG, "fft_resampled_async: trajectory stride too small");
+  rc = async_init(e);
+  if (rc) return rc;
+  int k;
+  rc = ring_slot(e, bytes, &k);
+  if (rc) return rc;
+  rc = dft_launch(e, field, tnx, tny, e->ring[k]);
   if (rc) return rc;
   return ring_drain(e, k, dst, per, dst_traj_stride);
 }

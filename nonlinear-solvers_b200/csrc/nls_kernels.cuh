@@ -280,6 +280,43 @@ k_lanczos_b(Geom g, const S *__restrict__ start, S *__restrict__ V, size_t colst
   }
 }
 
+// NLS_REORTH_MGS: the reference's sequential sweep, operation for operation (eigen_krylov_complex.hpp:28-38):
+//   w -= (v_j^H w) v_j;  for i = 0..j: w -= (v_i^H w) v_i;  ||w||.
+// One launch per dot: w -= (H[isub] / nrm2[isub]) column_isub, then H[idot] = column_idot^H w  (NORM: ||w||^2 instead).
+// j + 3 launches per iteration instead of 2: a bisecting tool that separates re-orthogonalisation rounding from bugs.
+template <class S, bool NORM>
+__global__ void __launch_bounds__(kThreads)
+k_lanczos_mgs(Geom g, const S *__restrict__ start, S *__restrict__ V, size_t colstride, int j, int isub, int idot,
+              int write_alpha, double *scal, RedCtx rc, Halo<S> hp) {
+  using T = Sc<S>;
+  double *sb = scal + (size_t)blockIdx.y * kScalStride;
+  S *wc = traj(V + (size_t)j * colstride, g);
+  const S *cs = traj(colptr<S>(start, V, colstride, isub), g);
+  const S *cd = NORM ? nullptr : traj(colptr<S>(start, V, colstride, idot), g);
+  const S coef = T::mulr(T::from(sb + kOffH + isub * T::W), 1.0 / sb[kOffNrm2 + isub]);
+  if (write_alpha && blockIdx.x == 0 && threadIdx.x == 0) // T(j,j) = Re(v_j^H w) = Re s_j / beta_j   (:28)
+    sb[kOffAlpha + j * T::W] = sb[kOffH + j * T::W] / sqrt(sb[kOffNrm2 + j]);
+  double acc[T::W];
+#pragma unroll
+  for (int k = 0; k < T::W; ++k) acc[k] = 0.0;
+  for (long long idx = (long long)blockIdx.x * kThreads + threadIdx.x; idx < g.n; idx += (long long)gridDim.x * kThreads) {
+    const S wv = T::sub(wc[idx], T::mul(coef, cs[idx]));
+    wc[idx] = wv;
+    if (NORM) {
+      acc[0] += T::abs2(wv);
+      halo_push<S>(hp, g.n, g.plane, idx, wv);
+    } else {
+      T::dot_acc(acc, cd[idx], wv);
+    }
+  }
+  if (NORM) {
+    double a1[1] = {acc[0]};
+    grid_reduce<1>(a1, rc, sb + kOffNrm2 + j + 1);
+  } else {
+    grid_reduce<T::W>(acc, rc, sb + kOffH + idot * T::W);
+  }
+}
+
 // Gram entries g_i = column_i^H column_j for the columns [i0, i0+cnt) that the LAST chunk of the
 // previous pass B did not hold (only when more than NC columns take part, i.e. m > NC + 1)
 template <class S, int NC>
@@ -1202,6 +1239,81 @@ k_resample(Geom g, const S *__restrict__ u, const double *__restrict__ upast, do
     S v = plane(p);
     if (nz > 1) v = T::add(T::mulr(v, 1.0 - fz), T::mulr(plane(p + dzs), fz));
     ob[o] = v;
+  }
+}
+
+// ---- spectral downsampling (nls_get_field_fft_resampled): the launcher's `downsample_fft`
+// (finalized_scripts/downsampling.py:10-34): ortho fft2 -> fftshift -> centred t x t crop -> ifftshift -> ortho ifft2.
+// Only t of the N frequencies per axis survive, so the whole pipeline is two small dense products
+//   out = Wy (ty x ny) . u (ny x nx) . Wx^T (nx x tx),   W[a][x] = 1/sqrt(N t) sum_kappa e^{2 pi i (kappa a / t - k(kappa) x / N)}
+// with k(kappa) the original index of kept frequency kappa: a direct cropped DFT, no FFT library.
+__global__ void __launch_bounds__(kThreads) k_dft_weights(double2 *__restrict__ W, int N, int t) {
+  const long long tot = (long long)t * N;
+  const int start = (N - t) / 2;
+  const double scale = 1.0 / sqrt((double)N * (double)t);
+  for (long long o = (long long)blockIdx.x * kThreads + threadIdx.x; o < tot; o += (long long)gridDim.x * kThreads) {
+    const long long a = o / N, x = o % N;
+    double sr = 0.0, si = 0.0;
+    for (int kap = 0; kap < t; ++kap) {
+      const long long k = (((long long)start + (kap + t / 2) % t - N / 2) % N + N) % N; // fftshift / crop / ifftshift
+      // phase in turns, reduced exactly in integers before the division
+      const double ph = (double)((kap * a) % t) / (double)t - (double)((k * x) % N) / (double)N;
+      double sn, cs;
+      sincospi(2.0 * ph, &sn, &cs);
+      sr += cs;
+      si += sn;
+    }
+    W[o] = make_double2(sr * scale, si * scale);
+  }
+}
+// T1[b][a][i] = sum_j Wy[a][j] * u[b][j][i]     (S = state scalar; VEL: u -> (u - u_past)/dt)
+template <class S, bool VEL>
+__global__ void __launch_bounds__(kThreads)
+k_dft_cols(Geom g, const S *__restrict__ u, const double *__restrict__ upast, double inv_dt, const double2 *__restrict__ Wy, int ty,
+           double2 *__restrict__ T1) {
+  constexpr int TA = 4;
+  const S *ub = traj(u, g);
+  const double *up = VEL ? traj(upast, g) : nullptr;
+  const int i = blockIdx.x * kThreads + threadIdx.x;
+  const int a0 = blockIdx.z * TA;
+  if (i >= g.nx) return;
+  double2 acc[TA];
+#pragma unroll
+  for (int q = 0; q < TA; ++q) acc[q] = make_double2(0.0, 0.0);
+  for (int j = 0; j < g.ny; ++j) {
+    const long long p = (long long)j * g.nx + i;
+    double2 v;
+    if (Sc<S>::W == 2) v = make_double2(((const double *)(ub + p))[0], ((const double *)(ub + p))[1]);
+    else v = make_double2(VEL ? (((const double *)(ub + p))[0] - up[p]) * inv_dt : ((const double *)(ub + p))[0], 0.0);
+#pragma unroll
+    for (int q = 0; q < TA; ++q)
+      if (a0 + q < ty) {
+        const double2 w = Wy[(size_t)(a0 + q) * g.ny + j];
+        acc[q].x = fma(w.x, v.x, fma(-w.y, v.y, acc[q].x));
+        acc[q].y = fma(w.x, v.y, fma(w.y, v.x, acc[q].y));
+      }
+  }
+#pragma unroll
+  for (int q = 0; q < TA; ++q)
+    if (a0 + q < ty) T1[((size_t)blockIdx.y * ty + a0 + q) * g.nx + i] = acc[q];
+}
+// out[b][a][c] = sum_i T1[b][a][i] * Wx[c][i]   (real states keep the real part, like the script)
+template <class S>
+__global__ void __launch_bounds__(kThreads)
+k_dft_rows(const double2 *__restrict__ T1, const double2 *__restrict__ Wx, int nx, int tx, int ty, S *__restrict__ out) {
+  const long long tot = (long long)tx * ty;
+  for (long long o = (long long)blockIdx.x * kThreads + threadIdx.x; o < tot; o += (long long)gridDim.x * kThreads) {
+    const int a = (int)(o / tx), c = (int)(o % tx);
+    const double2 *t1 = T1 + ((size_t)blockIdx.y * ty + a) * nx, *w = Wx + (size_t)c * nx;
+    double sr = 0.0, si = 0.0;
+    for (int i = 0; i < nx; ++i) {
+      const double2 tv = t1[i], wv = w[i];
+      sr = fma(tv.x, wv.x, fma(-tv.y, wv.y, sr));
+      si = fma(tv.x, wv.y, fma(tv.y, wv.x, si));
+    }
+    double *q = (double *)(out + (size_t)blockIdx.y * tot + o);
+    q[0] = sr;
+    if (Sc<S>::W == 2) q[1] = si;
   }
 }
 

@@ -16,6 +16,7 @@
 //   --downsample N  store every snapshot resampled on the device to N x N [x N] points with the launcher's
 //                 downsample_interpolation (finalized_scripts/downsampling.py:68-104, :215-258); the
 //                 trajectory files then have shape ([B,] num_snapshots, N, N[, N])
+//   --downsample-fft N  the same with the launcher's downsample_fft (downsampling.py:10-34; 2D drivers): spectral crop
 //   --devices G   spread an ensemble file over devices D..D+G-1 (one host thread each)
 // Ensemble input: when u0.npy [and v0.npy] carry one extra leading dimension
 // `(B, [nz,] ny, nx)`, all B trajectories advance in batched handles and the trajectory files
@@ -95,7 +96,7 @@ int usage(const Spec &s, const char *argv0) {
   if (is_nlse(s)) std::cerr << " input_u0.npy output_traj.npy";
   else std::cerr << " input_u0.npy input_v0.npy output_traj.npy output_vel.npy";
   std::cerr << " T nt num_snapshots" << (s.fields_req ? " input_m.npy input_c.npy" : " [input_m.npy]")
-            << " [--m K] [--device D] [--devices G] [--diag d.npy] [--downsample N]\n"
+            << " [--m K] [--device D] [--devices G] [--diag d.npy] [--downsample N | --downsample-fft N]\n"
             << "  (u0/v0 may be ensemble files of shape (B, ...): output is (B, num_snapshots, ...))\n";
   return 1;
 }
@@ -145,7 +146,7 @@ bool run_ensemble(const Spec &s, const nls::Grid &g, uint32_t krylov, double dt,
                   uint32_t ns, uint32_t freq, const std::vector<uint64_t> &want, const std::vector<double> &m,
                   const std::string &in_u, const std::string &in_v, const std::string &out_u,
                   const std::string &out_v, const std::vector<int> &devices, uint64_t &B_out,
-                  const std::string &diag_file, uint32_t ds) {
+                  const std::string &diag_file, uint32_t ds, bool ds_fft) {
   const bool real = !in_v.empty();
   const size_t n = g.n();
   std::vector<T> u0, v0;
@@ -209,7 +210,10 @@ bool run_ensemble(const Spec &s, const nls::Grid &g, uint32_t krylov, double dt,
         diagnose(snap);
         T *du = tu.data() + (b0 * ns + snap) * no;
         T *dv = real ? tv.data() + (b0 * ns + snap) * no : nullptr;
-        if (ds) {
+        if (ds && ds_fft) {
+          h.get_fft_resampled_async(NLS_FIELD_U, ds, ds, du, nb * no * sizeof(T), tstride);
+          if (real) h.get_fft_resampled_async(NLS_FIELD_V, ds, ds, dv, nb * no * sizeof(T), tstride);
+        } else if (ds) {
           h.get_resampled_async(NLS_FIELD_U, ds, ds, dtz, du, nb * no * sizeof(T), tstride);
           if (real) h.get_resampled_async(NLS_FIELD_V, ds, ds, dtz, dv, nb * no * sizeof(T), tstride);
         } else {
@@ -254,6 +258,7 @@ int run(const Spec &s, int argc, char **argv) {
   int device = 0, ndev = 1;
   std::string diag_file;
   uint32_t ds = 0;
+  bool ds_fft = false;
   if (const char *e = std::getenv("NLS_KRYLOV_M")) krylov = (uint32_t)std::stoul(e);
   std::vector<char *> av(argv, argv + argc);
   for (size_t i = 1; i + 1 < av.size();) {
@@ -261,6 +266,7 @@ int run(const Spec &s, int argc, char **argv) {
     if (a == "--m") { krylov = (uint32_t)std::stoul(av[i + 1]); av.erase(av.begin() + i, av.begin() + i + 2); }
     else if (a == "--device") { device = std::stoi(av[i + 1]); av.erase(av.begin() + i, av.begin() + i + 2); }
     else if (a == "--downsample") { ds = (uint32_t)std::stoul(av[i + 1]); av.erase(av.begin() + i, av.begin() + i + 2); }
+    else if (a == "--downsample-fft") { ds = (uint32_t)std::stoul(av[i + 1]); ds_fft = true; av.erase(av.begin() + i, av.begin() + i + 2); }
     else if (a == "--diag") { diag_file = av[i + 1]; av.erase(av.begin() + i, av.begin() + i + 2); }
     else if (a == "--devices") { ndev = std::stoi(av[i + 1]); av.erase(av.begin() + i, av.begin() + i + 2); }
     else ++i;
@@ -299,6 +305,10 @@ int run(const Spec &s, int argc, char **argv) {
   const uint32_t freq = nt / ns;
   const size_t n = g.n();
   std::vector<uint64_t> want = s.dim == 3 ? std::vector<uint64_t>{nz, ny, nx} : std::vector<uint64_t>{ny, nx};
+  if (ds_fft && s.dim == 3) {
+    std::cerr << "Error: --downsample-fft is 2D only (the launcher's downsample_fft is)\n";
+    return 1;
+  }
   if (ds == 1) {
     std::cerr << "Error: --downsample needs N >= 2\n";
     return 1;
@@ -331,9 +341,9 @@ int run(const Spec &s, int argc, char **argv) {
 
   const auto t0 = std::chrono::steady_clock::now();
   if (is_nlse(s)) {
-    if (!run_ensemble<cplx>(s, g, krylov, dt, sc, nt, ns, freq, want, m, in_u, "", out_u, "", devices, B, diag_file, ds)) return 1;
+    if (!run_ensemble<cplx>(s, g, krylov, dt, sc, nt, ns, freq, want, m, in_u, "", out_u, "", devices, B, diag_file, ds, ds_fft)) return 1;
   } else {
-    if (!run_ensemble<double>(s, g, krylov, dt, sc, nt, ns, freq, want, m, in_u, in_v, out_u, out_v, devices, B, diag_file, ds)) return 1;
+    if (!run_ensemble<double>(s, g, krylov, dt, sc, nt, ns, freq, want, m, in_u, in_v, out_u, out_v, devices, B, diag_file, ds, ds_fft)) return 1;
   }
   if (std::getenv("NLS_VERBOSE")) {
     const double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();

@@ -212,3 +212,16 @@ def sv_step(A, u, up, mfield, tau, kind="sge"):
     """SGESolverSV::step sg_single_sv_solver.hpp:9-19 / KGESVSolver::step kg_sv_solver.hpp:13-21."""
     b = A @ u - mfield * _F[kind](u)
     return 2 * u - up + tau * tau * b, u.copy()
+
+
+def downsample_fft(u, target_shape):
+    """finalized_scripts/downsampling.py:10-34 restated with numpy.fft: ortho fft2 over the last two axes, fftshift,
+    centred crop to target_shape, ifftshift, ortho ifft2; real input keeps the real part."""
+    u = np.asarray(u)
+    n0, n1 = u.shape[-2:]
+    t0, t1 = target_shape
+    ft = np.fft.fftshift(np.fft.fft2(u.astype(np.complex128), norm="ortho", axes=(-2, -1)), axes=(-2, -1))
+    s0, s1 = (n0 - t0) // 2, (n1 - t1) // 2
+    crop = np.fft.ifftshift(ft[..., s0:s0 + t0, s1:s1 + t1], axes=(-2, -1))
+    out = np.fft.ifft2(crop, norm="ortho", axes=(-2, -1))
+    return out if np.iscomplexobj(u) else out.real

@@ -124,3 +124,52 @@ def test_gpu_resample_bad_args():
             e.get_resampled(*args)
     with pytest.raises(Exception):
         e.get_resampled(8, 8, field=FIELD.V)
+
+
+# ---- spectral downsampling: downsample_fft (downsampling.py:10-34) as a direct cropped DFT on the device ------------
+def test_fft_restatement_matches_the_script():
+    """CPU, where /root/reference exists: the numpy restatement against the script's own torch.fft path"""
+    import os
+    import sys
+    import types
+    ref = "/root/reference/nlsolvers/finalized_scripts"
+    if not os.path.exists(ref):
+        pytest.skip("reference tree not present (GPU box)")
+    import oracle_np
+    mpl = types.ModuleType("matplotlib"); mpl.pyplot = types.ModuleType("matplotlib.pyplot")
+    sys.modules.setdefault("matplotlib", mpl); sys.modules.setdefault("matplotlib.pyplot", mpl.pyplot)
+    sys.path.insert(0, ref)
+    import downsampling
+    rng = np.random.default_rng(0)
+    for shape, tgt in (((3, 64, 64), (16, 16)), ((2, 50, 37), (17, 12)), ((1, 33, 40), (33, 8))):
+        for cplx in (True, False):
+            u = rng.standard_normal(shape) + (1j * rng.standard_normal(shape) if cplx else 0)
+            assert close(oracle_np.downsample_fft(u, tgt), downsampling.downsample_fft(u, tgt), 1e-13)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("ny,nx,ty,tx", [(64, 64, 16, 16), (50, 37, 17, 12), (33, 40, 33, 8), (256, 256, 128, 128)])
+@pytest.mark.parametrize("kind", ["nlse", "sge"])
+def test_gpu_fft_resample(ny, nx, ty, tx, kind):
+    import nls_b200
+    import oracle_np
+    B, dt = 2, 1e-3
+    rng = np.random.default_rng(5)
+    if kind == "nlse":
+        d = Desc.make(nx, ny, dx=0.1, equation=EQ.NLSE_CUBIC, batch=B)
+        u0 = rng.standard_normal((B, ny, nx)) + 1j * rng.standard_normal((B, ny, nx))
+    else:
+        d = Desc.make(nx, ny, dx=0.1, equation=EQ.SGE, integrator=INT.SV, dt=dt, batch=B)
+        u0 = rng.standard_normal((B, ny, nx))
+    e = nls_b200.Engine(d)
+    e.set(FIELD.U, u0)
+    if kind == "sge":
+        v0 = rng.standard_normal((B, ny, nx))
+        e.set(FIELD.V, v0)
+    got = e.get_fft_resampled(tx, ty)
+    assert got.shape == (B, ty, tx)
+    assert close(got, oracle_np.downsample_fft(u0, (ty, tx)), 1e-12)
+    if kind == "sge":
+        assert close(e.get_fft_resampled(tx, ty, field=FIELD.V), oracle_np.downsample_fft(e.get(FIELD.V), (ty, tx)), 1e-12)
+    # a second target shape on the same handle rebuilds the weights
+    assert close(e.get_fft_resampled(max(tx // 2, 1), ty), oracle_np.downsample_fft(u0, (ty, max(tx // 2, 1))), 1e-12)

@@ -320,3 +320,13 @@ def test_cli_downsampled_trajectory(drivers, tmp_path):
     for s in range(8):
         assert np.max(np.abs(su[s] - script_downsample_2d(fu[s], (N, N), L, L))) < 1e-12
         assert np.max(np.abs(sv[s] - script_downsample_2d(fv[s], (N, N), L, L))) < 1e-9
+    # --downsample-fft N: the launcher's downsample_fft (downsampling.py:10-34) of the full-resolution trajectory
+    import oracle_np
+    run(drivers, "nlse_ensemble_driver", *common, tmp_path / "fft.npy", T, nt, ns, "--downsample-fft", N, check=True)
+    sf = np.load(tmp_path / "fft.npy")
+    assert sf.shape == (B, ns, N, N)
+    for b in range(B):
+        ref = oracle_np.downsample_fft(full[b], (N, N))
+        assert np.max(np.abs(sf[b] - ref)) < 1e-12 * max(1.0, np.max(np.abs(ref)))
+    run(drivers, "sg_single", *rc, tmp_path / "gu.npy", tmp_path / "gv.npy", 0.2, 40, 8, "--downsample-fft", N, check=True)
+    assert np.max(np.abs(np.load(tmp_path / "gu.npy") - oracle_np.downsample_fft(fu, (N, N)))) < 1e-12

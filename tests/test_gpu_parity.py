@@ -485,3 +485,35 @@ def test_tma_passes_match_register_passes_and_oracle(orc, case):
         o.set(FIELD.V, np.zeros_like(u0))
     o.step(dt, steps)
     assert rel_l2(outs[0][3], o.get()) < 1e-11
+
+
+# ---- MGS-faithful re-orthogonalisation (NLS_REORTH_MGS): the reference's sequential sweep, a bisecting tool --------
+@pytest.mark.parametrize("eq,m", [(EQ.NLSE_CUBIC, 20), (EQ.NLSE_CUBIC, 30), (EQ.SGE, 20)])
+def test_mgs_faithful_mode_tracks_the_oracle_at_rounding_level(orc, eq, m):
+    """white-noise start vector, far from Krylov convergence: the block scheme (FULL) differs from the oracle's
+    sequential MGS by re-orthogonalisation rounding; the MGS mode performs the oracle's operations one by one."""
+    nx = 120
+    integ = INT.SS2 if eq == EQ.NLSE_CUBIC else INT.GAUTSCHI
+    errs = {}
+    for reorth in (REORTH.MGS, REORTH.FULL):
+        d = Desc.make(nx, nx, L=5.0, equation=eq, integrator=integ, krylov_m=m, reorth=reorth, op_sign=1.0,
+                      flags=nls_b200.FLAG_NO_PERSISTENT)
+        x = randn(d)
+        fn, t = (FN.EXP, 1e-2j) if d.is_complex else (FN.COS_SQRT, 1e-2)
+        e = Engine(d)
+        ref = orc.Oracle(d).matfunc(fn, t, x)
+        errs[reorth] = rel_l2(e.matfunc(fn, t, x), ref)
+        V, a, b = e.lanczos(x)
+        Vo, ao, bo = orc.Oracle(d).lanczos(x)
+        if reorth == REORTH.MGS:
+            assert np.allclose(b, bo, rtol=1e-13) and rel_l2(V, Vo) < 1e-9
+    print(f"eq={eq} m={m}: matfunc vs oracle: MGS-faithful {errs[REORTH.MGS]:.3e}, block (FULL) {errs[REORTH.FULL]:.3e}")
+    assert errs[REORTH.MGS] < 1e-12 and errs[REORTH.FULL] < 1e-11
+
+
+def test_mgs_faithful_steps(orc):
+    n, L, dt = 64, 10.0, 1e-3
+    d = Desc.make(n, n, L=L, equation=EQ.NLSE_CQ, krylov_m=12, s1=1.0, s2=-0.1, reorth=REORTH.MGS)
+    e, o = run_pair(orc, d, ics.gaussian_bumps_2d(n, L), 20, dt)
+    assert e.launch_count() > 20 * 11, "MGS mode runs on the multi-kernel path"
+    assert rel_l2(e.get(), o.get()) < 1e-12
