@@ -157,6 +157,8 @@ enum {
   NLS_FLAG_TMA = 32u,       /* TMA-staged Lanczos passes (nls_tma.cuh: cp.async.bulk + mbarrier ring, arithmetic from
                              * shared memory).  Correct and tested, but measured slower than the register-staged
                              * passes on B200 so far, hence opt-in */
+  NLS_FLAG_TMAP = 128u,     /* 3D single-trajectory grids: pass A of the Lanczos iteration with the stencil input staged through
+                             * shared memory by tensor-map TMA loads (nls_tmap.cuh: cp.async.bulk.tensor.3d boxes with halo) */
   NLS_FLAG_PK_SV = 64u,     /* Stoermer-Verlet through the persistent kernel (k_pk_sv); off by default: at
                              * 1024^2 one grid barrier per step (15.7 us) costs more than a k_sv launch (11-14 us) */
   NLS_FLAG_DEBUG_PK_FAULT = 0x80000000u, /* test hook: one CTA of the persistent kernel never reaches its first
@@ -294,6 +296,8 @@ int nls_get_field_fft_resampled_async(nls_handle h, int field, uint32_t tnx, uin
 uint64_t nls_launch_count(nls_handle h);
 /* how many of them were TMA-staged Lanczos passes (nls_tma.cuh) */
 uint64_t nls_tma_launch_count(nls_handle h);
+/* how many were tensor-map pass-A launches (nls_tmap.cuh; counted at issue, also inside graph capture) */
+uint64_t nls_tmap_launch_count(nls_handle h);
 /* the CUDA stream (cudaStream_t) the handle launches on */
 void *nls_stream(nls_handle h);
 /* time a run of nsteps steps with CUDA events on the handle's stream; ms returned */

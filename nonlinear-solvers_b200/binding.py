@@ -30,6 +30,7 @@ FLAG_SEWI_HOST2D = 4
 FLAG_MARCH = 8
 FLAG_TMA = 32
 FLAG_PK_SV = 64
+FLAG_TMAP = 128
 FLAG_DEBUG_PK_FAULT = 0x80000000
 
 
@@ -134,6 +135,7 @@ _SIGS = {
     "nls_reduce": (C.c_int, [_vp, C.c_int, _dp]),
     "nls_launch_count": (C.c_uint64, [_vp]),
     "nls_tma_launch_count": (C.c_uint64, [_vp]),
+    "nls_tmap_launch_count": (C.c_uint64, [_vp]),
     "nls_stream": (_vp, [_vp]),
     "nls_step_timed": (C.c_int, [_vp, C.c_double, C.c_uint32, C.POINTER(C.c_float)]),
     "nls_get_field_async": (C.c_int, [_vp, C.c_int, _vp, _sz, _sz]),
@@ -356,6 +358,9 @@ class Engine:
 
     def launch_count(self):
         return int(self.lib.nls_launch_count(self.h))
+
+    def tmap_launch_count(self):
+        return int(self.lib.nls_tmap_launch_count(self.h))
 
     def tma_launch_count(self):
         return int(self.lib.nls_tma_launch_count(self.h))

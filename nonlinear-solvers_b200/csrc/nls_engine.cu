@@ -3,6 +3,7 @@
 // No CPU fallback anywhere: without a CUDA device every entry point returns NLS_ERR_CUDA.
 #include "nls_persist.cuh"
 #include "nls_tma.cuh"
+#include "nls_tmap.cuh"
 
 #include <unistd.h>
 
@@ -48,6 +49,10 @@ struct nls_engine {
   int smem_optin = 0;  // max dynamic shared memory per CTA
   int first_cap = 0;   // complex pass A: columns in the stencil-carrying first chunk (0 = rule in lanczos_t)
   bool tma_ok = false; // TMA-staged Lanczos passes usable (alignment + size), see tma_setup
+  bool tm_ok = false;  // tensor-map pass A (nls_tmap.cuh) usable
+  TmGeom tmg{};
+  std::unordered_map<const void *, CUtensorMap> tmaps; // one 3-D tensor map per stencil-input vector (by base address)
+  uint64_t tm_launches = 0;
   cudaStream_t stream = nullptr;
   // device memory (all n-vectors: [batch][stride] scalars)
   void *V = nullptr;     // m-1 columns
@@ -287,6 +292,87 @@ bool launch_b_tma(nls_engine *e, const S *start, S *V, int j, int i0, int cnt, b
   return true;
 }
 
+// ---------------------------------------------------------------- tensor-map pass A (nls_tmap.cuh)
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                  const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn encode_tiled() {
+  static EncodeTiledFn fn = []() -> EncodeTiledFn {
+    void *p = nullptr;
+    cudaDriverEntryPointQueryResult qr;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qr) != cudaSuccess || qr != cudaDriverEntryPointSuccess) {
+      cudaGetLastError();
+      return nullptr;
+    }
+    return (EncodeTiledFn)p;
+  }();
+  return fn;
+}
+
+// 3-D map over a vector laid out like the state (`base` = first allocated element, ghost plane included for slabs):
+// dims (doubles per row, ny, planes), box (doubles per (BX+2) sites, BY+2, 1), zero fill outside
+bool tm_get(nls_engine *e, const void *base, int doubles_per_site, const CUtensorMap **out) {
+  auto it = e->tmaps.find(base);
+  if (it == e->tmaps.end()) {
+    EncodeTiledFn enc = encode_tiled();
+    if (!enc) return false;
+    CUtensorMap tm;
+    const Geom &g = e->g;
+    const cuuint64_t planes = (cuuint64_t)g.nz_loc + (g.halo ? 2 : 0);
+    const cuuint64_t dims[3] = {(cuuint64_t)g.nx * doubles_per_site, (cuuint64_t)g.ny, planes};
+    const cuuint64_t strides[2] = {(cuuint64_t)g.nx * doubles_per_site * 8, (cuuint64_t)g.plane * doubles_per_site * 8};
+    const cuuint32_t box[3] = {(cuuint32_t)(kTmPX * doubles_per_site), (cuuint32_t)kTmPY, 1};
+    const cuuint32_t estr[3] = {1, 1, 1};
+    if (enc(&tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, const_cast<void *>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+            CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+      return false;
+    it = e->tmaps.emplace(base, tm).first;
+  }
+  *out = &it->second;
+  return true;
+}
+
+void tm_setup(nls_engine *e) {
+  e->tm_ok = false;
+  const bool want = (e->d.flags & NLS_FLAG_TMAP) || getenv("NLS_PASS_A_TMAP");
+  if (!want || getenv("NLS_NO_TMAP")) return;
+  const Geom &g = e->g;
+  if (!g.dim3 || e->batch != 1 || g.nx < 4 || g.ny < 4) return;
+  if (!e->cplx && (g.nx % 2)) return; // row pitch must be a multiple of 16 bytes
+  if (!encode_tiled()) return;
+  e->tm_ok = true;
+}
+
+template <class S, bool ANISO, int NC>
+bool launch_a_tm(nls_engine *e, const S *start, S *V, int j, int i0, int cnt, double *scal) {
+  if (!e->tm_ok) return false;
+  const Geom &g = e->g;
+  const S *cj = j == 0 ? start : V + (size_t)(j - 1) * e->colstride; // base of column j (halo included)
+  const CUtensorMap *tmx = nullptr, *tmc = nullptr;
+  if (!tm_get(e, cj, (int)(sizeof(S) / 8), &tmx)) return false;
+  if (ANISO) { if (!tm_get(e, e->cf, 1, &tmc)) return false; }
+  else tmc = tmx;
+  const dim3 gr = grid_for(e, (const void *)k_lanczos_a_tm<S, ANISO, NC>);
+  TmGeom tg;
+  tg.ntx = (g.nx + kTmBX - 1) / kTmBX;
+  tg.nty = (g.ny + kTmBY - 1) / kTmBY;
+  const long long tiles = (long long)tg.ntx * tg.nty;
+  long long nzc = (3LL * gr.x + tiles - 1) / tiles;
+  if (nzc < 1) nzc = 1;
+  int zc = (int)((g.nz_loc + nzc - 1) / nzc);
+  if (zc < 8) zc = 8;
+  if (zc > g.nz_loc) zc = g.nz_loc;
+  tg.zc = zc;
+  tg.nzc = (g.nz_loc + zc - 1) / zc;
+  tg.units = tiles * tg.nzc;
+  tg.zoff = g.halo ? 1 : 0;
+  k_lanczos_a_tm<S, ANISO, NC><<<dim3(gr.x, 1), kThreads, 0, e->stream>>>(*tmx, *tmc, g, tg, start, V, e->colstride, j, i0, cnt, e->cf,
+                                                                      scal, e->rc, e->status);
+  e->count();
+  e->tm_launches += 1;
+  return true;
+}
+
 template <class S, bool ANISO>
 void lanczos_t(nls_engine *e, const S *start, double *scal) {
   const int m = e->m;
@@ -313,6 +399,7 @@ void lanczos_t(nls_engine *e, const S *start, double *scal) {
       const March mc = make_march(e->g, 8 * (int)g3.x);                                                  \
       k_lanczos_a3<S, ANISO, NC><<<g3, kThreads, 0, e->stream>>>(e->g, mc, start, V, e->colstride, j, cnt, e->cf, scal, e->rc); \
       e->count();                                                                                        \
+    } else if (first && launch_a_tm<S, ANISO, NC>(e, start, V, j, i0, cnt, scal)) {                                               \
     } else if (first) LAUNCH(e, (k_lanczos_a<S, ANISO, NC, true>), gr, e->g, start, V, e->colstride, j, i0, cnt, e->cf, scal, e->rc);  \
     else LAUNCH(e, (k_lanczos_a<S, ANISO, NC, false>), gr, e->g, start, V, e->colstride, j, i0, cnt, e->cf, scal, e->rc);       \
   } while (0)
@@ -954,6 +1041,7 @@ int nls_create(const nls_desc *desc, nls_handle *out) {
   if (ok) pk_setup(e);
   if (ok) sv2_setup(e);
   if (ok) tma_setup(e);
+  if (ok) tm_setup(e);
   if (!ok) {
     std::string msg = std::string("allocation failed: ") + cudaGetErrorString(cudaGetLastError());
     nls_destroy(e);
@@ -1455,6 +1543,7 @@ int nls_step_timed(nls_handle e, double dt, uint32_t nsteps, float *ms) {
 
 uint64_t nls_launch_count(nls_handle e) { return e ? e->launches : 0; }
 uint64_t nls_tma_launch_count(nls_handle e) { return e ? e->tma_launches : 0; }
+uint64_t nls_tmap_launch_count(nls_handle e) { return e ? e->tm_launches : 0; }
 void *nls_stream(nls_handle e) { return e ? (void *)e->stream : nullptr; }
 
 static int stencil_apply_impl(nls_handle e, const void *x, void *y, bool dev) {

@@ -20,9 +20,11 @@
 namespace nls {
 
 constexpr int kTmBX = 64, kTmBY = 4;  // tile: one site per thread and plane (kTmBX * kTmBY == kThreads)
-constexpr int kTmR = 5;               // plane slots: k-1, k, k+1 in use, k+2 and k+3 in flight
+constexpr int kTmR = 4;               // plane slots: k-1, k, k+1 in use + one in flight (plane k+3 re-uses k-1's slot)
 constexpr int kTmPX = kTmBX + 2, kTmPY = kTmBY + 2;
 constexpr int kTmSlotSites = kTmPX * kTmPY;
+constexpr int kTmSlotPad = 400;       // slot stride in elements: 400 * 8 and 400 * 16 bytes are multiples of 128 (TMA destination)
+static_assert(kTmSlotPad >= kTmSlotSites, "slot too small");
 
 struct TmGeom {
   int ntx, nty, nzc, zc; // tiles in x / y, z chunks, planes per chunk
@@ -45,8 +47,8 @@ k_lanczos_a_tm(const __grid_constant__ CUtensorMap tmx, const __grid_constant__ 
                const double *__restrict__ cf, double *scal, RedCtx rc, int *status) {
   using T = Sc<S>;
   constexpr int W = T::W;
-  __shared__ __align__(128) S xs[kTmR][kTmSlotSites];
-  __shared__ __align__(128) double cs[ANISO ? kTmR : 1][ANISO ? kTmSlotSites : 2];
+  __shared__ __align__(128) S xs[kTmR][kTmSlotPad];
+  __shared__ __align__(128) double cs[ANISO ? kTmR : 1][ANISO ? kTmSlotPad : 16];
   __shared__ __align__(8) unsigned long long bars[kTmR];
   __shared__ int s_abort;
   double *sb = scal;
@@ -104,8 +106,7 @@ k_lanczos_a_tm(const __grid_constant__ CUtensorMap tmx, const __grid_constant__ 
     long long idx = ((long long)k0 * g.ny + jj) * g.nx + i;
     for (int k = k0; k < k1; ++k, idx += g.plane) {
       const int sm = (k - k0) % kTmR, sc = (k - k0 + 1) % kTmR, sp = (k - k0 + 2) % kTmR;
-      // plane k+1 must have landed; plane k+3 may start once every thread has left step k-1 (it re-uses slot sm's
-      // predecessor, i.e. the slot that held plane k-2)
+      // plane k+1 must have landed
       mbar_wait(&bars[sp], (phase_bits >> sp) & 1u, &s_abort, status);
       phase_bits ^= 1u << sp;
       if (live) {
@@ -154,13 +155,12 @@ k_lanczos_a_tm(const __grid_constant__ CUtensorMap tmx, const __grid_constant__ 
             T::dot_acc(acc + q * W, vq, w);
           }
       }
-      __syncthreads(); // all reads of slot sm (plane k-1) are done: it may be overwritten by plane k+4's predecessor
+      __syncthreads(); // all reads of slot sm (plane k-1) are done: plane k+3 goes there, two steps ahead of its use
       if (threadIdx.x == 0 && k + 3 <= k1) {
         fence_proxy_async();
         issue(k + 3);
       }
     }
-    // drain: planes issued but not consumed by the loop (k1 was loaded as the z+1 neighbour and is already waited for)
   }
   grid_reduce<NC * W>(acc, rc, sb + kOffH + i0 * W);
 }

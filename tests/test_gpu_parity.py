@@ -517,3 +517,47 @@ def test_mgs_faithful_steps(orc):
     e, o = run_pair(orc, d, ics.gaussian_bumps_2d(n, L), 20, dt)
     assert e.launch_count() > 20 * 11, "MGS mode runs on the multi-kernel path"
     assert rel_l2(e.get(), o.get()) < 1e-12
+
+
+# ---- tensor-map TMA pass A (nls_tmap.cuh, NLS_FLAG_TMAP) vs the flat pass and the oracle ---------------------------
+@pytest.mark.parametrize("dims,eq,lap,m", [((64, 48, 40), EQ.NLSE_CQ, LAP.ANISO, 12), ((37, 29, 23), EQ.NLSE_CUBIC, LAP.UNIFORM, 10),
+                                           ((130, 9, 17), EQ.NLSE_CUBIC, LAP.ANISO, 8), ((48, 40, 36), EQ.KGE, LAP.ANISO, 10),
+                                           ((66, 5, 12), EQ.SGE, LAP.UNIFORM, 6), ((96, 96, 96), EQ.NLSE_CUBIC, LAP.UNIFORM, 12)])
+def test_tensor_map_pass_matches_flat_pass_and_oracle(orc, dims, eq, lap, m):
+    """3D boxes with halo staged by cp.async.bulk.tensor: ragged tiles, domain faces (zero fill + flags), the y-wrap
+    links (direct loads), div(c grad) with the c box, real and complex states, chunked z marching"""
+    nx, ny, nz = dims
+    real = eq >= EQ.SGE
+    kw = dict(equation=eq, integrator=INT.GAUTSCHI if real else INT.SS2, laplacian=lap, krylov_m=m, s1=1.0, s2=-0.1,
+              op_sign=-1.0 if eq == EQ.KGE else 1.0, dt=1e-3)
+    rng = np.random.default_rng(3)
+    cf = 1.0 + 0.1 * rng.standard_normal(nx * ny * nz)
+    mf = 1.0 + 0.2 * rng.standard_normal(nx * ny * nz)
+    u0 = ics.gaussian_bumps_3d(max(dims), 4.0)[:nz, :ny, :nx]
+    if real:
+        u0 = 0.3 * np.abs(u0)
+    outs = []
+    for flags in (nls_b200.FLAG_NO_PERSISTENT | nls_b200.FLAG_TMAP, nls_b200.FLAG_NO_PERSISTENT):
+        d = Desc.make(nx, ny, nz, dx=0.2, flags=flags, **kw)
+        e = Engine(d)
+        if lap == LAP.ANISO:
+            e.set(FIELD.C, cf)
+        e.set(FIELD.M, mf)
+        V, a, b = e.lanczos(randn(d, 5))
+        e.set(FIELD.U, u0)
+        if real:
+            e.set(FIELD.V, np.zeros_like(u0))
+        e.step(1e-3, 5)
+        outs.append((V, a, b, e.get(), e.tmap_launch_count()))
+    assert outs[0][4] > 0 and outs[1][4] == 0, "first handle must have run the tensor-map pass, second must not"
+    assert rel_l2(outs[0][0], outs[1][0]) < 1e-11 and np.allclose(outs[0][2], outs[1][2], rtol=1e-13)
+    assert rel_l2(outs[0][3], outs[1][3]) < 1e-13
+    o = orc.Oracle(d)
+    if lap == LAP.ANISO:
+        o.set(FIELD.C, cf)
+    o.set(FIELD.M, mf)
+    o.set(FIELD.U, u0)
+    if real:
+        o.set(FIELD.V, np.zeros_like(u0))
+    o.step(1e-3, 5)
+    assert rel_l2(outs[0][3], o.get()) < 1e-11
