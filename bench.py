@@ -70,6 +70,11 @@ WORKLOADS = {
                     "scalar exchange, m=10 (BASELINE configs[4] at G=8)",
                n=1024, dim=3, L=10.0, eq=EQ.NLSE_CUBIC, integ=INT.SS2, m=10, dt=2e-4, seg=5, slab_planes=128,
                short=(5, 3), cpu_n=128),
+    # STRONG scaling of the slab decomposition: the C3 grid (256^3, cubic-quintic, div(c grad), m=12) cut into
+    # G z-slabs of 256/G planes; total work fixed, so the cross-GPU reductions and halo planes show undiluted
+    "c3_strong": dict(desc="NLSE 3D cubic-quintic 256^3 (BASELINE configs[2]) cut into G z-slabs, strong scaling",
+                      n=256, dim=3, L=6.0, eq=EQ.NLSE_CQ, integ=INT.SS2, m=12, dt=5e-4, seg=10, lap=LAP.ANISO,
+                      s1=1.0, s2=-0.1, short=(10, 3), slab_total=256, cpu_n=64),
 }
 slab_ic = ics.slab_ic
 
@@ -88,6 +93,8 @@ def bytes_per_site_step(w, model=False):
 
 
 def grid_str(w, world):
+    if "slab_total" in w:
+        return f"{w['n']}x{w['n']}x{w['slab_total']}"
     if "slab_planes" in w:
         return f"{w['n']}x{w['n']}x{w['slab_planes'] * world}"
     return "x".join([str(w["n"])] * w["dim"])
@@ -95,7 +102,7 @@ def grid_str(w, world):
 
 def config_for(name, w, world):
     """identical in the native and the reference line (scalars and strings only)"""
-    slab = "slab_planes" in w
+    slab = "slab_planes" in w or "slab_total" in w
     cfg = {"workload": name, "description": w["desc"], "grid": grid_str(w, world),
            "trajectories_per_gpu": w.get("batch", 1), "krylov_m": w["m"], "dt": w["dt"], "reorth": "full",
            "l2": "no flush: the per-step working set (state + Krylov basis) is >= 20x the 126 MB L2 for the headline; "
@@ -119,7 +126,7 @@ def make_desc(w, batch=None, device=0, n=None):
 
 def make_state(w, batch, seed0=0, n=None):
     n = n or w["n"]
-    if "slab_planes" in w:
+    if "slab_planes" in w or "slab_total" in w:
         return slab_ic(n, 0, n, n, w["L"])[None].repeat(batch, axis=0), None
     if w["eq"] <= EQ.NLSE_SAT:
         if w["dim"] == 3:
@@ -293,14 +300,15 @@ def measure(cx, name, w, K, W, repeats, sample_clocks):
     torch = cx.torch
     rank, world, lr = cx.rank, cx.world, cx.local_rank
     batch = w.get("batch", 1)
-    slab = "slab_planes" in w
+    slab = "slab_planes" in w or "slab_total" in w
     if slab:  # z-slab decomposition: one slab handle per GPU, wired over peer memory
         from nls_b200 import slabs
-        n, nzg = w["n"], w["slab_planes"] * world
+        n, nzg = w["n"], (w["slab_total"] if "slab_total" in w else w["slab_planes"] * world)
         dx = 2.0 * w["L"] / (n - 1)
 
         def mk(nz, nz_global, z0):
             return Desc.make(n, n, nz, dx=dx, equation=w["eq"], integrator=w["integ"], krylov_m=w["m"],
+                             laplacian=w.get("lap", LAP.UNIFORM), s1=w.get("s1", 0.0), s2=w.get("s2", 0.0),
                              dt=w["dt"], device=lr, nz_global=nz_global, z0=z0,
                              flags=int(os.environ.get("NLS_BENCH_FLAGS", w.get("flags", 0))))
         eng, z0, nz = slabs.make_slab_engine(mk, nzg, cx.dist if world > 1 else None, rank, world,
@@ -310,6 +318,8 @@ def measure(cx, name, w, K, W, repeats, sample_clocks):
         # (nls_generate_field): no 2 GiB-per-rank host arrays
         from nls_b200 import fieldgen, GEN
         eng.generate(FIELD.M, [(GEN.CONST, 0, [1.0])], L=w["L"])
+        if d.laplacian == LAP.ANISO:
+            eng.generate(FIELD.C, [(GEN.CONST, 0, [1.0])], L=w["L"])
         eng.generate(FIELD.U, *fieldgen.slab_ic(w["L"]), L=w["L"])
     else:
         d = make_desc(w, batch=batch, device=lr)
@@ -456,7 +466,7 @@ def run_native(args, name, w, rank, world, local_rank):
     line = {
         "metric": METRIC, "value": head["value"], "unit": "site-steps/s", "n_gpus": world, "steps": K, "warmup": W,
         "ms_per_step": head["ms_per_step"], "ms_per_step_runs": head["ms_per_step_runs"],
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "higher_is_better": True, "scaling": "strong" if "slab_total" in w else "weak", "vs_baseline": None,
         "dtype": "f64", "data": "synthetic", "config": config_for(name, w, world),
         "e2e": head["e2e"], "gpu_launches": head["gpu_launches"] * REPEATS,
         "gpu_launches_per_repeat": head["gpu_launches"],
