@@ -339,6 +339,9 @@ void tm_setup(nls_engine *e) {
   const Geom &g = e->g;
   if (!g.dim3 || e->batch != 1 || g.nx < 4 || g.ny < 4) return;
   if (!e->cplx && (g.nx % 2)) return; // row pitch must be a multiple of 16 bytes
+  // div(c grad): the variant with the second (c) box load faulted with 'illegal instruction' on B200 (session r02-07,
+  // profiles/r02g_pytest_tmap_first_attempt.log); NLS_TMAP_ANISO=1 re-enables it for debugging only
+  if (e->d.laplacian == NLS_LAP_ANISO && !getenv("NLS_TMAP_ANISO")) return;
   if (!encode_tiled()) return;
   e->tm_ok = true;
 }
