@@ -19,6 +19,7 @@
 using namespace nls;
 
 namespace {
+constexpr size_t kDefaultColPad = 0; // see col_pad_bytes()
 thread_local std::string g_err;
 
 int fail(int code, const std::string &msg) {
@@ -160,6 +161,19 @@ S *col(nls_engine *e, int j) {
   return (S *)e->V + (size_t)j * e->colstride;
 }
 
+// Bytes added between consecutive basis columns (and arena slots).  Without it every column of a 256^3 or
+// 1024 x 1024 x 128 complex grid starts exactly 2^28 / 2^31 bytes after the previous one, so the up to 13 streams a
+// Lanczos pass reads concurrently alias onto the same DRAM banks (launch list profiles/r02g_launches_c3_flat.csv:
+// pass B 6.6 TB/s with 8 columns, 4.0 TB/s with 12).  NLS_COL_PAD (bytes, multiple of 256) overrides for tuning.
+size_t col_pad_bytes() {
+  static const size_t pad = []() -> size_t {
+    if (const char *s = getenv("NLS_COL_PAD")) return (size_t)strtoull(s, nullptr, 0) / 256 * 256;
+    return kDefaultColPad;
+  }();
+  return pad;
+}
+size_t slot_bytes_of(size_t stride_elems, size_t esz) { return (stride_elems * esz + 255) / 256 * 256 + col_pad_bytes(); }
+
 // ---------------------------------------------------------------- z-slab exchange arena
 constexpr int kArenaSlots = 7; // wbuf0, wbuf1, w0, u0, u1, u2, cf; then the m-1 basis columns
 constexpr size_t kMailboxBytes = (sizeof(SlabMailbox) + 4095) / 4096 * 4096;
@@ -186,12 +200,12 @@ Halo<S> halo_for(nls_engine *e, const void *local) {
   const size_t plane = (size_t)e->g.plane;
   if (e->rank > 0) {
     const nls_engine::Peer &p = e->peers[e->rank - 1];
-    const size_t pslot = (p.stride * e->esz + 255) / 256 * 256;
+    const size_t pslot = slot_bytes_of(p.stride, e->esz);
     h.lo = (S *)(p.base + kMailboxBytes + slot * pslot) + (p.stride - plane); // its upper ghost plane
   }
   if (e->rank + 1 < e->nranks) {
     const nls_engine::Peer &p = e->peers[e->rank + 1];
-    const size_t pslot = (p.stride * e->esz + 255) / 256 * 256;
+    const size_t pslot = slot_bytes_of(p.stride, e->esz);
     h.hi = (S *)(p.base + kMailboxBytes + slot * pslot); // its lower ghost plane
   }
   return h;
@@ -321,7 +335,7 @@ bool tm_get(nls_engine *e, const void *base, int doubles_per_site, const CUtenso
     const cuuint64_t planes = (cuuint64_t)g.nz_loc + (g.halo ? 2 : 0);
     const cuuint64_t dims[3] = {(cuuint64_t)g.nx * doubles_per_site, (cuuint64_t)g.ny, planes};
     const cuuint64_t strides[2] = {(cuuint64_t)g.nx * doubles_per_site * 8, (cuuint64_t)g.plane * doubles_per_site * 8};
-    const cuuint32_t box[3] = {(cuuint32_t)(kTmPX * doubles_per_site), (cuuint32_t)kTmPY, 1};
+    const cuuint32_t box[3] = {(cuuint32_t)(doubles_per_site == 2 ? TmRow<2>::PX * 2 : TmRow<1>::PX), (cuuint32_t)kTmPY, 1};
     const cuuint32_t estr[3] = {1, 1, 1};
     if (enc(&tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, const_cast<void *>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
             CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
@@ -339,9 +353,6 @@ void tm_setup(nls_engine *e) {
   const Geom &g = e->g;
   if (!g.dim3 || e->batch != 1 || g.nx < 4 || g.ny < 4) return;
   if (!e->cplx && (g.nx % 2)) return; // row pitch must be a multiple of 16 bytes
-  // div(c grad): the variant with the second (c) box load faulted with 'illegal instruction' on B200 (session r02-07,
-  // profiles/r02g_pytest_tmap_first_attempt.log); NLS_TMAP_ANISO=1 re-enables it for debugging only
-  if (e->d.laplacian == NLS_LAP_ANISO && !getenv("NLS_TMAP_ANISO")) return;
   if (!encode_tiled()) return;
   e->tm_ok = true;
 }
@@ -997,8 +1008,8 @@ int nls_create(const nls_desc *desc, nls_handle *out) {
   long long cap = 8LL * e->nsm; // at most 8 CTAs of 256 threads per SM
   e->nblk = (int)(want < cap ? want : cap);
   e->slab = g.halo != 0;
-  e->slot_bytes = (g.stride * e->esz + 255) / 256 * 256;
-  e->colstride = e->slab ? e->slot_bytes / e->esz : e->vec_elems();
+  e->slot_bytes = slot_bytes_of(g.stride, e->esz);
+  e->colstride = e->slab ? e->slot_bytes / e->esz : e->vec_elems() + col_pad_bytes() / e->esz;
   e->nphase = cplx ? (d.integrator == NLS_INT_SEWI ? 3 : 2) : (d.integrator == NLS_INT_SV ? 3 : 1);
 
   auto alloc = [&](void **p, size_t bytes) -> bool {
@@ -1009,7 +1020,7 @@ int nls_create(const nls_desc *desc, nls_handle *out) {
   const size_t vb = e->vec_bytes();
   const bool krylov = d.integrator != NLS_INT_SV;
   // the Krylov buffers are also used by nls_matfunc / nls_lanczos / nls_stencil_apply
-  if (!(g.halo != 0)) ok = ok && alloc(&e->V, vb * (e->m - 1));
+  if (!(g.halo != 0)) ok = ok && alloc(&e->V, e->colstride * e->esz * (e->m - 1));
   if (e->slab) { // stencil inputs (incl. the basis columns) + mailbox in one arena the other ranks can map
     ok = ok && alloc((void **)&e->arena, kMailboxBytes + (size_t)(kArenaSlots + e->m - 1) * e->slot_bytes);
     if (ok) {

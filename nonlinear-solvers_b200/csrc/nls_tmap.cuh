@@ -21,10 +21,17 @@ namespace nls {
 
 constexpr int kTmBX = 64, kTmBY = 4;  // tile: one site per thread and plane (kTmBX * kTmBY == kThreads)
 constexpr int kTmR = 4;               // plane slots: k-1, k, k+1 in use + one in flight (plane k+3 re-uses k-1's slot)
-constexpr int kTmPX = kTmBX + 2, kTmPY = kTmBY + 2;
-constexpr int kTmSlotSites = kTmPX * kTmPY;
-constexpr int kTmSlotPad = 400;       // slot stride in elements: 400 * 8 and 400 * 16 bytes are multiples of 128 (TMA destination)
-static_assert(kTmSlotPad >= kTmSlotSites, "slot too small");
+constexpr int kTmPY = kTmBY + 2;
+// Box rows.  A box row must span a multiple of 32 BYTES on sm_100a: a 66-double (528 B) row is accepted by
+// cuTensorMapEncodeTiled and then faults the TMA unit with "illegal instruction", a 132-double (1056 B) row works
+// (tools/microbench/tmap_probe.cu, profiles/r02i_tmap_probe.log).  Complex rows are 66 sites = 132 doubles; real rows
+// (real states, the c field) are widened to 68 doubles and start one site further left.
+template <int W> struct TmRow {
+  static constexpr int PX = W == 2 ? kTmBX + 2 : kTmBX + 4; // sites per box row
+  static constexpr int XO = W == 2 ? 1 : 2;                 // box offset of the tile's first site
+  static constexpr int kSites = PX * kTmPY;
+  static constexpr int kPad = (kSites * W * 8 + 127) / 128 * 128 / (W * 8); // slot stride in sites: 128-byte multiple
+};
 
 struct TmGeom {
   int ntx, nty, nzc, zc; // tiles in x / y, z chunks, planes per chunk
@@ -47,8 +54,10 @@ k_lanczos_a_tm(const __grid_constant__ CUtensorMap tmx, const __grid_constant__ 
                const double *__restrict__ cf, double *scal, RedCtx rc, int *status) {
   using T = Sc<S>;
   constexpr int W = T::W;
-  __shared__ __align__(128) S xs[kTmR][kTmSlotPad];
-  __shared__ __align__(128) double cs[ANISO ? kTmR : 1][ANISO ? kTmSlotPad : 16];
+  using RX = TmRow<W>;
+  using RC = TmRow<1>;
+  __shared__ __align__(128) S xs[kTmR][RX::kPad];
+  __shared__ __align__(128) double cs[ANISO ? kTmR : 1][ANISO ? RC::kPad : 16];
   __shared__ __align__(8) unsigned long long bars[kTmR];
   __shared__ int s_abort;
   double *sb = scal;
@@ -65,7 +74,7 @@ k_lanczos_a_tm(const __grid_constant__ CUtensorMap tmx, const __grid_constant__ 
 #pragma unroll
   for (int k = 0; k < NC * W; ++k) acc[k] = 0.0;
   const int tx = threadIdx.x % kTmBX, ty = threadIdx.x / kTmBX;
-  constexpr unsigned kBoxBytes = (unsigned)(kTmSlotSites * sizeof(S)) + (ANISO ? (unsigned)(kTmSlotSites * 8) : 0u);
+  constexpr unsigned kBoxBytes = (unsigned)(RX::kSites * sizeof(S)) + (ANISO ? (unsigned)(RC::kSites * 8) : 0u);
   if (threadIdx.x == 0) {
     for (int r = 0; r < kTmR; ++r) mbar_init(&bars[r], 1);
     s_abort = 0;
@@ -81,12 +90,12 @@ k_lanczos_a_tm(const __grid_constant__ CUtensorMap tmx, const __grid_constant__ 
     const int i = x0 + tx, jj = y0 + ty;
     const bool live = i < g.nx && jj < g.ny;
     // box origin in tensor-map coordinates: the inner dimension counts doubles (complex = 2 per site)
-    const int bx = (x0 - 1) * W, by = y0 - 1;
+    const int bx = (x0 - RX::XO) * W, by = y0 - 1;
     auto issue = [&](int k) { // plane k (local index, may be k0-1 .. k1) into slot (k - k0 + 1) % R
       const int slot = (k - k0 + 1) % kTmR;
       mbar_expect_tx(&bars[slot], kBoxBytes);
       tma_load_3d(&xs[slot][0], &tmx, bx, by, k + tg.zoff, &bars[slot]);
-      if (ANISO) tma_load_3d(&cs[slot][0], &tmc, x0 - 1, by, k + tg.zoff, &bars[slot]);
+      if (ANISO) tma_load_3d(&cs[slot][0], &tmc, x0 - RC::XO, by, k + tg.zoff, &bars[slot]);
     };
     __syncthreads(); // the previous unit's reads of the ring are done
     if (threadIdx.x == 0) {
@@ -102,7 +111,8 @@ k_lanczos_a_tm(const __grid_constant__ CUtensorMap tmx, const __grid_constant__ 
     if (i != 0) fxy |= NB_XM;
     if (i != g.nx - 1) fxy |= NB_XP;
     const bool ring_xy = i == 0 || i == g.nx - 1 || jj == 0 || jj == g.ny - 1;
-    const int sidx = (ty + 1) * kTmPX + tx + 1; // this thread's site inside a slot
+    const int sidx = (ty + 1) * RX::PX + tx + RX::XO; // this thread's site inside a slot
+    const int cidx = (ty + 1) * RC::PX + tx + RC::XO; // ... and inside a c slot
     long long idx = ((long long)k0 * g.ny + jj) * g.nx + i;
     for (int k = k0; k < k1; ++k, idx += g.plane) {
       const int sm = (k - k0) % kTmR, sc = (k - k0 + 1) % kTmR, sp = (k - k0 + 2) % kTmR;
@@ -118,14 +128,14 @@ k_lanczos_a_tm(const __grid_constant__ CUtensorMap tmx, const __grid_constant__ 
         if (kg < g.nz_glob - 1) f |= NB_ZP;
         if (ring_xy || kg == 0 || kg == g.nz_glob - 1) f |= NB_RING;
         const S xc = xs[sc][sidx];
-        S xym = xs[sc][sidx - kTmPX], xyp = xs[sc][sidx + kTmPX];
+        S xym = xs[sc][sidx - RX::PX], xyp = xs[sc][sidx + RX::PX];
         const S xxm = xs[sc][sidx - 1], xxp = xs[sc][sidx + 1];
         const S xzm = xs[sm][sidx], xzp = xs[sp][sidx];
         double cc = 0.0, czm = 0.0, czp = 0.0, cym = 0.0, cyp = 0.0, cxm = 0.0, cxp = 0.0;
         if (ANISO) {
-          cc = cs[sc][sidx]; cym = cs[sc][sidx - kTmPX]; cyp = cs[sc][sidx + kTmPX];
-          cxm = cs[sc][sidx - 1]; cxp = cs[sc][sidx + 1];
-          czm = cs[sm][sidx]; czp = cs[sp][sidx];
+          cc = cs[sc][cidx]; cym = cs[sc][cidx - RC::PX]; cyp = cs[sc][cidx + RC::PX];
+          cxm = cs[sc][cidx - 1]; cxp = cs[sc][cidx + 1];
+          czm = cs[sm][cidx]; czp = cs[sp][cidx];
         }
         // the reference's y links ignore plane boundaries: (i, 0, k) <-> (i, ny-1, k-1).  Those partners are not in
         // the box (its out-of-range rows are zero-filled): fetch them directly, two lines of sites per plane
