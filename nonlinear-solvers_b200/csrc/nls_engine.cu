@@ -346,6 +346,12 @@ bool tm_get(nls_engine *e, const void *base, int doubles_per_site, const CUtenso
   return true;
 }
 
+template <class S, bool ANISO> bool tm_attrs(int bytes) { // dynamic shared memory opt-in: not allowed later, inside a capture
+  return tma_attr((const void *)k_lanczos_a_tm<S, ANISO, 2>, bytes) && tma_attr((const void *)k_lanczos_a_tm<S, ANISO, 4>, bytes) &&
+         tma_attr((const void *)k_lanczos_a_tm<S, ANISO, 6>, bytes) && tma_attr((const void *)k_lanczos_a_tm<S, ANISO, 8>, bytes) &&
+         tma_attr((const void *)k_lanczos_a_tm<S, ANISO, 10>, bytes) && tma_attr((const void *)k_lanczos_a_tm<S, ANISO, 12>, bytes);
+}
+
 void tm_setup(nls_engine *e) {
   e->tm_ok = false;
   const bool want = (e->d.flags & NLS_FLAG_TMAP) || getenv("NLS_PASS_A_TMAP");
@@ -354,12 +360,16 @@ void tm_setup(nls_engine *e) {
   if (!g.dim3 || e->batch != 1 || g.nx < 4 || g.ny < 4) return;
   if (!e->cplx && (g.nx % 2)) return; // row pitch must be a multiple of 16 bytes
   if (!encode_tiled()) return;
-  e->tm_ok = true;
+  const bool an = e->d.laplacian == NLS_LAP_ANISO;
+  const int bytes = (int)tm_smem_bytes(e->W, an);
+  const bool ok = e->cplx ? (an ? tm_attrs<double2, true>(bytes) : tm_attrs<double2, false>(bytes))
+                          : (an ? tm_attrs<double, true>(bytes) : tm_attrs<double, false>(bytes));
+  e->tm_ok = ok;
 }
 
 template <class S, bool ANISO, int NC>
 bool launch_a_tm(nls_engine *e, const S *start, S *V, int j, int i0, int cnt, double *scal) {
-  if (!e->tm_ok) return false;
+  if (!e->tm_ok || (sizeof(S) == 16 && NC > 6)) return false; // two sites per thread: 2 * NC complex values in registers
   const Geom &g = e->g;
   const S *cj = j == 0 ? start : V + (size_t)(j - 1) * e->colstride; // base of column j (halo included)
   const CUtensorMap *tmx = nullptr, *tmc = nullptr;
@@ -380,7 +390,7 @@ bool launch_a_tm(nls_engine *e, const S *start, S *V, int j, int i0, int cnt, do
   tg.nzc = (g.nz_loc + zc - 1) / zc;
   tg.units = tiles * tg.nzc;
   tg.zoff = g.halo ? 1 : 0;
-  k_lanczos_a_tm<S, ANISO, NC><<<dim3(gr.x, 1), kThreads, 0, e->stream>>>(*tmx, *tmc, g, tg, start, V, e->colstride, j, i0, cnt, e->cf,
+  k_lanczos_a_tm<S, ANISO, NC><<<dim3(gr.x, 1), kThreads, tm_smem_bytes((int)(sizeof(S) / 8), ANISO), e->stream>>>(*tmx, *tmc, g, tg, start, V, e->colstride, j, i0, cnt, e->cf,
                                                                       scal, e->rc, e->status);
   e->count();
   e->tm_launches += 1;
@@ -400,7 +410,7 @@ void lanczos_t(nls_engine *e, const S *start, double *scal) {
     // beyond that the 128-register budget of 2 CTAs/SM costs more than re-reading w once in a second,
     // dots-only chunk.  Measured on B200 (profiles/r01f_firstcap.txt): div(c grad) stencil 6 (C3 12.0 ->
     // 10.8 ms/step), uniform stencil 10 (C4/C5 lose 3% with 6).  NLS_FIRST_CAP overrides for tuning.
-    const int kFirst = sizeof(S) == 16 ? (e->first_cap >= 2 && e->first_cap <= kNC ? e->first_cap : (ANISO ? 6 : 10)) : kNC;
+    const int kFirst = sizeof(S) == 16 ? (e->first_cap >= 2 && e->first_cap <= kNC ? e->first_cap : ((ANISO || e->tm_ok) ? 6 : 10)) : kNC;
     for (int i0 = c0, cnt = 0; i0 <= j; i0 += cnt) {
       const bool first = i0 == c0;
       const int cap = first ? kFirst : kNC;

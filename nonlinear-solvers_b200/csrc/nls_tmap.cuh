@@ -2,16 +2,20 @@
 // shared memory by TENSOR-MAP TMA loads (cp.async.bulk.tensor.3d, SASS UTMALDG), for 3D single-trajectory grids.
 //
 // The flat pass (k_lanczos_a) fetches the seven stencil inputs of a site through L1/L2: only the x neighbours hit
-// L1, the y / z neighbours (and, for div(c grad), six more c values) come from L2 for EVERY site -- 5 x 16 B (+ 5 x 8 B)
-// of L2 traffic per site on top of the streamed basis columns, which is what holds the stencil-carrying launches at
-// 2.4-4.3 TB/s (profiles/r01d_launches_c3_dram.csv).  Here a CTA owns a BX x BY in-plane tile and marches it through a
-// chunk of z planes.  One elected thread issues, two planes ahead, a 3-D box load of (BX+2) x (BY+2) x 1 sites of the
-// input column (and of c) into a ring of shared-memory plane slots; out-of-range halo elements are zero-filled by the
-// TMA unit, so faces need no address logic.  Every input site is fetched from L2/HBM once per tile (+ its halo ring),
-// the neighbour values are shared-memory reads, and the 64-bit index arithmetic leaves the inner loop.  The basis
-// columns for the dots and the store of w stream straight through registers as before.  The rows of the operator --
-// incl. the reference's quirks (ring diagonal, y-neighbour test on the flat index: laplacians.hpp:124-148, :181-210) --
-// are those of stencil_vals (nls_device.cuh), bit for bit the flat kernel's arithmetic.
+// L1, the y / z neighbours (and, for div(c grad), six more c values) come from L2 for EVERY site -- for a complex
+// div(c grad) pass with 6 basis columns that is ~264 B/site through L2 for ~120 B/site of DRAM traffic, i.e. the pass
+// sits at the L2 throughput cap (~12 TB/s) at its measured 5.0 TB/s of DRAM traffic, and the narrow early iterations
+// (2 / 4 columns) at 2.4 / 3.3 TB/s (profiles/r02g_launches_c3_flat.csv).  Here a CTA owns a 64 x 8 in-plane tile and
+// marches it through a chunk of z planes.  One elected thread issues, two planes ahead, a 3-D box load of
+// (64+2) x (8+2) x 1 sites of the input column (and of c) into a ring of shared-memory plane slots; out-of-range halo
+// elements are zero-filled by the TMA unit, so faces need no address logic.  Every input site is fetched from L2/HBM
+// once per tile (+ its halo ring, x1.29), the neighbour values are shared-memory reads, and the 64-bit index
+// arithmetic leaves the inner loop.  The basis columns for the dots and the store of w stream straight through
+// registers as before; every thread handles TWO sites of a plane (rows ty and ty+4) so that twice as many column
+// loads are in flight per barrier (version 1 -- one site per thread, 64 x 4 tiles -- was latency-bound: long-scoreboard
+// stall 12 per issue at 16 warps/SM, 2.5 TB/s; ncu capture profiles/r02i_ncu_full_c5_k_lanczos_a_tm_v1.txt).
+// The rows of the operator -- incl. the reference's quirks (ring diagonal, y-neighbour test on the flat index:
+// laplacians.hpp:124-148, :181-210) -- are those of stencil_vals (nls_device.cuh), the flat kernel's arithmetic.
 #pragma once
 #include <cuda.h>
 
@@ -19,9 +23,11 @@
 
 namespace nls {
 
-constexpr int kTmBX = 64, kTmBY = 4;  // tile: one site per thread and plane (kTmBX * kTmBY == kThreads)
+constexpr int kTmBX = 64, kTmBY = 8;  // tile; kThreads = 64 x 4 threads, two rows per thread
+constexpr int kTmRows = 2, kTmTY = kTmBY / kTmRows;
 constexpr int kTmR = 4;               // plane slots: k-1, k, k+1 in use + one in flight (plane k+3 re-uses k-1's slot)
 constexpr int kTmPY = kTmBY + 2;
+static_assert(kTmBX * kTmTY == kThreads, "tile / thread mapping");
 // Box rows.  A box row must span a multiple of 32 BYTES on sm_100a: a 66-double (528 B) row is accepted by
 // cuTensorMapEncodeTiled and then faults the TMA unit with "illegal instruction", a 132-double (1056 B) row works
 // (tools/microbench/tmap_probe.cu, profiles/r02i_tmap_probe.log).  Complex rows are 66 sites = 132 doubles; real rows
@@ -32,6 +38,13 @@ template <int W> struct TmRow {
   static constexpr int kSites = PX * kTmPY;
   static constexpr int kPad = (kSites * W * 8 + 127) / 128 * 128 / (W * 8); // slot stride in sites: 128-byte multiple
 };
+constexpr int kTmHdrBytes = 128; // mbarriers + abort word in front of the slots
+
+// dynamic shared memory of one CTA
+inline size_t tm_smem_bytes(int W, bool aniso) {
+  const size_t xs = (size_t)kTmR * (W == 2 ? TmRow<2>::kPad * 16 : TmRow<1>::kPad * 8);
+  return kTmHdrBytes + xs + (aniso ? (size_t)kTmR * TmRow<1>::kPad * 8 : 0);
+}
 
 struct TmGeom {
   int ntx, nty, nzc, zc; // tiles in x / y, z chunks, planes per chunk
@@ -46,6 +59,51 @@ __device__ __forceinline__ void tma_load_3d(void *dst_smem, const CUtensorMap *t
                : "memory");
 }
 
+// NB_* flags of site (i, jj, global plane kg): the reference's triplet-loop conditions (site_flags, nls_device.cuh)
+__device__ __forceinline__ unsigned tm_flags(const Geom &g, int i, int jj, int kg) {
+  unsigned f = 0;
+  if (i != 0) f |= NB_XM;
+  if (i != g.nx - 1) f |= NB_XP;
+  if (!(kg == 0 && jj == 0)) f |= NB_YM;                    // gi >= nx        (laplacians.hpp:140)
+  if (!(kg == g.nz_glob - 1 && jj == g.ny - 1)) f |= NB_YP; // gi + nx < nglob (no plane check: y-wrap quirk)
+  if (kg > 0) f |= NB_ZM;
+  if (kg < g.nz_glob - 1) f |= NB_ZP;
+  if (i == 0 || i == g.nx - 1 || jj == 0 || jj == g.ny - 1 || kg == 0 || kg == g.nz_glob - 1) f |= NB_RING;
+  return f;
+}
+
+// (L x)(site) * inv from the plane slots; wrap partners (two lines of sites per plane) come from global memory
+template <class S, bool ANISO>
+__device__ __forceinline__ S tm_stencil(const Geom &g, unsigned f, double inv, const S *__restrict__ xm, const S *__restrict__ xc,
+                                        const S *__restrict__ xp, const double *__restrict__ cm, const double *__restrict__ cc,
+                                        const double *__restrict__ cp, int sidx, int cidx, int jj, long long idx,
+                                        const S *__restrict__ cj, const double *__restrict__ cfb, S &centre) {
+  constexpr int W = Sc<S>::W;
+  using RX = TmRow<W>;
+  using RC = TmRow<1>;
+  centre = xc[sidx];
+  S xym = xc[sidx - RX::PX], xyp = xc[sidx + RX::PX];
+  const S xxm = xc[sidx - 1], xxp = xc[sidx + 1];
+  const S xzm = xm[sidx], xzp = xp[sidx];
+  double c0 = 0.0, czm = 0.0, czp = 0.0, cym = 0.0, cyp = 0.0, cxm = 0.0, cxp = 0.0;
+  if (ANISO) {
+    c0 = cc[cidx]; cym = cc[cidx - RC::PX]; cyp = cc[cidx + RC::PX];
+    cxm = cc[cidx - 1]; cxp = cc[cidx + 1];
+    czm = cm[cidx]; czp = cp[cidx];
+  }
+  // the reference's y links ignore plane boundaries: (i, 0, k) <-> (i, ny-1, k-1).  Those partners are not in the box
+  // (its out-of-range rows are zero-filled): fetch them directly
+  if (jj == 0 && (f & NB_YM)) {
+    xym = cj[idx - g.nx];
+    if (ANISO) cym = cfb[idx - g.nx];
+  }
+  if (jj == g.ny - 1 && (f & NB_YP)) {
+    xyp = cj[idx + g.nx];
+    if (ANISO) cyp = cfb[idx + g.nx];
+  }
+  return stencil_vals<S, ANISO>(g, f, inv, centre, xzm, xym, xxm, xxp, xyp, xzp, c0, czm, cym, cxm, cxp, cyp, czp);
+}
+
 // columns [i0, i0+cnt) of 0..j take part in the dots (first chunk of the iteration: also forms w)
 template <class S, bool ANISO, int NC>
 __global__ void __launch_bounds__(kThreads, 2)
@@ -56,10 +114,11 @@ k_lanczos_a_tm(const __grid_constant__ CUtensorMap tmx, const __grid_constant__ 
   constexpr int W = T::W;
   using RX = TmRow<W>;
   using RC = TmRow<1>;
-  __shared__ __align__(128) S xs[kTmR][RX::kPad];
-  __shared__ __align__(128) double cs[ANISO ? kTmR : 1][ANISO ? RC::kPad : 16];
-  __shared__ __align__(8) unsigned long long bars[kTmR];
-  __shared__ int s_abort;
+  extern __shared__ __align__(128) unsigned char tm_smem[];
+  unsigned long long *bars = (unsigned long long *)tm_smem;
+  volatile int *s_abort = (volatile int *)(tm_smem + 64);
+  S *xs = (S *)(tm_smem + kTmHdrBytes);                       // [kTmR][RX::kPad]
+  double *cs = (double *)(xs + (size_t)kTmR * RX::kPad);      // [kTmR][RC::kPad] (ANISO only)
   double *sb = scal;
   const S *cj = colptr<S>(start, V, colstride, j) + g.halo;
   const S *cm = j > 0 ? colptr<S>(start, V, colstride, j - 1) + g.halo : nullptr;
@@ -77,7 +136,7 @@ k_lanczos_a_tm(const __grid_constant__ CUtensorMap tmx, const __grid_constant__ 
   constexpr unsigned kBoxBytes = (unsigned)(RX::kSites * sizeof(S)) + (ANISO ? (unsigned)(RC::kSites * 8) : 0u);
   if (threadIdx.x == 0) {
     for (int r = 0; r < kTmR; ++r) mbar_init(&bars[r], 1);
-    s_abort = 0;
+    *s_abort = 0;
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
@@ -87,84 +146,67 @@ k_lanczos_a_tm(const __grid_constant__ CUtensorMap tmx, const __grid_constant__ 
     const int tile = (int)(unit % tiles), zc = (int)(unit / tiles);
     const int x0 = (tile % tg.ntx) * kTmBX, y0 = (tile / tg.ntx) * kTmBY;
     const int k0 = zc * tg.zc, k1 = min(k0 + tg.zc, g.nz_loc);
-    const int i = x0 + tx, jj = y0 + ty;
-    const bool live = i < g.nx && jj < g.ny;
+    const int i = x0 + tx;
+    const int jj[kTmRows] = {y0 + ty, y0 + ty + kTmTY};
+    const bool live[kTmRows] = {i < g.nx && jj[0] < g.ny, i < g.nx && jj[1] < g.ny};
     // box origin in tensor-map coordinates: the inner dimension counts doubles (complex = 2 per site)
     const int bx = (x0 - RX::XO) * W, by = y0 - 1;
     auto issue = [&](int k) { // plane k (local index, may be k0-1 .. k1) into slot (k - k0 + 1) % R
       const int slot = (k - k0 + 1) % kTmR;
       mbar_expect_tx(&bars[slot], kBoxBytes);
-      tma_load_3d(&xs[slot][0], &tmx, bx, by, k + tg.zoff, &bars[slot]);
-      if (ANISO) tma_load_3d(&cs[slot][0], &tmc, x0 - RC::XO, by, k + tg.zoff, &bars[slot]);
+      tma_load_3d(xs + (size_t)slot * RX::kPad, &tmx, bx, by, k + tg.zoff, &bars[slot]);
+      if (ANISO) tma_load_3d(cs + (size_t)slot * RC::kPad, &tmc, x0 - RC::XO, by, k + tg.zoff, &bars[slot]);
     };
     __syncthreads(); // the previous unit's reads of the ring are done
     if (threadIdx.x == 0) {
       fence_proxy_async();
       for (int k = k0 - 1; k <= min(k0 + 2, k1); ++k) issue(k);
     }
-    // wait for planes k0-1 and k0 (slots 0, 1)
-    for (int q = 0; q < 2; ++q) {
-      mbar_wait(&bars[q], (phase_bits >> q) & 1u, &s_abort, status);
+    for (int q = 0; q < 2; ++q) { // planes k0-1 and k0 (slots 0, 1)
+      mbar_wait(&bars[q], (phase_bits >> q) & 1u, s_abort, status);
       phase_bits ^= 1u << q;
     }
-    unsigned fxy = 0;
-    if (i != 0) fxy |= NB_XM;
-    if (i != g.nx - 1) fxy |= NB_XP;
-    const bool ring_xy = i == 0 || i == g.nx - 1 || jj == 0 || jj == g.ny - 1;
-    const int sidx = (ty + 1) * RX::PX + tx + RX::XO; // this thread's site inside a slot
-    const int cidx = (ty + 1) * RC::PX + tx + RC::XO; // ... and inside a c slot
-    long long idx = ((long long)k0 * g.ny + jj) * g.nx + i;
-    for (int k = k0; k < k1; ++k, idx += g.plane) {
+    const int sidx[kTmRows] = {(ty + 1) * RX::PX + tx + RX::XO, (ty + kTmTY + 1) * RX::PX + tx + RX::XO};
+    const int cidx[kTmRows] = {(ty + 1) * RC::PX + tx + RC::XO, (ty + kTmTY + 1) * RC::PX + tx + RC::XO};
+    long long idx0 = ((long long)k0 * g.ny + jj[0]) * g.nx + i;
+    for (int k = k0; k < k1; ++k, idx0 += g.plane) {
       const int sm = (k - k0) % kTmR, sc = (k - k0 + 1) % kTmR, sp = (k - k0 + 2) % kTmR;
-      // plane k+1 must have landed
-      mbar_wait(&bars[sp], (phase_bits >> sp) & 1u, &s_abort, status);
-      phase_bits ^= 1u << sp;
-      if (live) {
-        const int kg = g.z0 + k;
-        unsigned f = fxy;
-        if (!(kg == 0 && jj == 0)) f |= NB_YM;                    // gi >= nx        (laplacians.hpp:140)
-        if (!(kg == g.nz_glob - 1 && jj == g.ny - 1)) f |= NB_YP; // gi + nx < nglob (no plane check: y-wrap quirk)
-        if (kg > 0) f |= NB_ZM;
-        if (kg < g.nz_glob - 1) f |= NB_ZP;
-        if (ring_xy || kg == 0 || kg == g.nz_glob - 1) f |= NB_RING;
-        const S xc = xs[sc][sidx];
-        S xym = xs[sc][sidx - RX::PX], xyp = xs[sc][sidx + RX::PX];
-        const S xxm = xs[sc][sidx - 1], xxp = xs[sc][sidx + 1];
-        const S xzm = xs[sm][sidx], xzp = xs[sp][sidx];
-        double cc = 0.0, czm = 0.0, czp = 0.0, cym = 0.0, cyp = 0.0, cxm = 0.0, cxp = 0.0;
-        if (ANISO) {
-          cc = cs[sc][cidx]; cym = cs[sc][cidx - RC::PX]; cyp = cs[sc][cidx + RC::PX];
-          cxm = cs[sc][cidx - 1]; cxp = cs[sc][cidx + 1];
-          czm = cs[sm][cidx]; czp = cs[sp][cidx];
-        }
-        // the reference's y links ignore plane boundaries: (i, 0, k) <-> (i, ny-1, k-1).  Those partners are not in
-        // the box (its out-of-range rows are zero-filled): fetch them directly, two lines of sites per plane
-        if (jj == 0 && (f & NB_YM)) {
-          xym = cj[idx - g.nx];
-          if (ANISO) cym = cfb[idx - g.nx];
-        }
-        if (jj == g.ny - 1 && (f & NB_YP)) {
-          xyp = cj[idx + g.nx];
-          if (ANISO) cyp = cfb[idx + g.nx];
-        }
-        S w = stencil_vals<S, ANISO>(g, f, inv, xc, xzm, xym, xxm, xxp, xyp, xzp, cc, czm, cym, cxm, cxp, cyp, czp);
-        S cmv = T::zero();
-        if (j > 0) {
-          cmv = ld_stream(cm + idx);
-          w = T::fma_r(cmul, cmv, w);
-        }
-        __stcs(wc + idx, w);
+      const long long idx[kTmRows] = {idx0, idx0 + (long long)kTmTY * g.nx};
+      // the global loads of both sites first (independent of the ring), then the wait for plane k+1
+      S cmv[kTmRows], v[kTmRows][NC];
 #pragma unroll
-        for (int q = 0; q < NC; ++q)
-          if (q < cnt) {
-            const int col = i0 + q;
-            S vq;
-            if (col == j) vq = xc;
-            else if (col == j - 1) vq = cmv;
-            else vq = ld_stream((q == 0 ? cb : cb + cs0 + (size_t)(q - 1) * colstride) + idx);
-            T::dot_acc(acc + q * W, vq, w);
-          }
+      for (int r = 0; r < kTmRows; ++r) {
+        cmv[r] = T::zero();
+        if (live[r] && j > 0) cmv[r] = ld_stream(cm + idx[r]);
+#pragma unroll
+        for (int q = 0; q < NC; ++q) {
+          const int col = i0 + q;
+          v[r][q] = T::zero();
+          if (live[r] && q < cnt && col != j && col != j - 1)
+            v[r][q] = ld_stream((q == 0 ? cb : cb + cs0 + (size_t)(q - 1) * colstride) + idx[r]);
+        }
       }
+      mbar_wait(&bars[sp], (phase_bits >> sp) & 1u, s_abort, status);
+      phase_bits ^= 1u << sp;
+      const int kg = g.z0 + k;
+#pragma unroll
+      for (int r = 0; r < kTmRows; ++r)
+        if (live[r]) {
+          const unsigned f = tm_flags(g, i, jj[r], kg);
+          S xc;
+          S w = tm_stencil<S, ANISO>(g, f, inv, xs + (size_t)sm * RX::kPad, xs + (size_t)sc * RX::kPad, xs + (size_t)sp * RX::kPad,
+                                     cs + (size_t)sm * RC::kPad, cs + (size_t)sc * RC::kPad, cs + (size_t)sp * RC::kPad, sidx[r],
+                                     cidx[r], jj[r], idx[r], cj, cfb, xc);
+          if (j > 0) w = T::fma_r(cmul, cmv[r], w);
+          __stcs(wc + idx[r], w);
+#pragma unroll
+          for (int q = 0; q < NC; ++q)
+            if (q < cnt) {
+              const int col = i0 + q;
+              const S vq = col == j ? xc : col == j - 1 ? cmv[r] : v[r][q];
+              T::dot_acc(acc + q * W, vq, w);
+            }
+        }
       __syncthreads(); // all reads of slot sm (plane k-1) are done: plane k+3 goes there, two steps ahead of its use
       if (threadIdx.x == 0 && k + 3 <= k1) {
         fence_proxy_async();
