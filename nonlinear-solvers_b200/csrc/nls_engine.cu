@@ -19,6 +19,7 @@
 using namespace nls;
 
 namespace {
+constexpr int kDefaultPrefetch = 0; // L2 prefetch lead of the flat Lanczos passes, in grid sweeps (Geom::pf)
 constexpr size_t kDefaultColPad = 0; // see col_pad_bytes()
 thread_local std::string g_err;
 
@@ -48,6 +49,7 @@ struct nls_engine {
   int nblk = 1; // capacity of the partial-sum array (max CTAs per trajectory)
   int nsm = 148;
   int smem_optin = 0;  // max dynamic shared memory per CTA
+  int b_wide = 0;      // closing pass-B chunk with >= 10 complex columns: 1 = k_lanczos_b_wide (1 CTA/SM, no spills)
   int first_cap = 0;   // complex pass A: columns in the stencil-carrying first chunk (0 = rule in lanczos_t)
   bool tma_ok = false; // TMA-staged Lanczos passes usable (alignment + size), see tma_setup
   bool tm_ok = false;  // tensor-map pass A (nls_tmap.cuh) usable
@@ -346,15 +348,31 @@ bool tm_get(nls_engine *e, const void *base, int doubles_per_site, const CUtenso
   return true;
 }
 
+// kernel for (mode, columns in the chunk); nullptr when there is none
+constexpr int kTmMaxNC = 6; // two sites per thread: 2 * NC complex values in registers
+template <class S, bool ANISO> const void *tm_kernel(int mode, int nc) {
+#define TMK(M, N) if (mode == M && nc == N) return (const void *)k_lanczos_a_tm<S, ANISO, N, M>
+  TMK(TM_SELF, 1);
+  TMK(TM_TAIL, 2); TMK(TM_TAIL, 3); TMK(TM_TAIL, 4); TMK(TM_TAIL, 5); TMK(TM_TAIL, 6);
+  TMK(TM_BODY, 1); TMK(TM_BODY, 2); TMK(TM_BODY, 3); TMK(TM_BODY, 4); TMK(TM_BODY, 5); TMK(TM_BODY, 6);
+#undef TMK
+  return nullptr;
+}
 template <class S, bool ANISO> bool tm_attrs(int bytes) { // dynamic shared memory opt-in: not allowed later, inside a capture
-  return tma_attr((const void *)k_lanczos_a_tm<S, ANISO, 2>, bytes) && tma_attr((const void *)k_lanczos_a_tm<S, ANISO, 4>, bytes) &&
-         tma_attr((const void *)k_lanczos_a_tm<S, ANISO, 6>, bytes) && tma_attr((const void *)k_lanczos_a_tm<S, ANISO, 8>, bytes) &&
-         tma_attr((const void *)k_lanczos_a_tm<S, ANISO, 10>, bytes) && tma_attr((const void *)k_lanczos_a_tm<S, ANISO, 12>, bytes);
+  for (int mode = 0; mode < 3; ++mode)
+    for (int nc = 1; nc <= kTmMaxNC; ++nc)
+      if (const void *fn = tm_kernel<S, ANISO>(mode, nc))
+        if (!tma_attr(fn, bytes)) return false;
+  return true;
 }
 
 void tm_setup(nls_engine *e) {
   e->tm_ok = false;
-  const bool want = (e->d.flags & NLS_FLAG_TMAP) || getenv("NLS_PASS_A_TMAP");
+  // default for complex 3D single-trajectory handles (measured with version 2: C5 61.7 -> 53.7 ms/step, C3 10.76 ->
+  // 10.45, profiles/r02k_*); real-valued grids opt in with NLS_FLAG_TMAP / NLS_PASS_A_TMAP=1; NLS_PASS_A_TMAP=0 or
+  // NLS_NO_TMAP=1 force the flat pass
+  const char *env = getenv("NLS_PASS_A_TMAP");
+  const bool want = env ? atoi(env) != 0 : ((e->d.flags & NLS_FLAG_TMAP) || e->cplx);
   if (!want || getenv("NLS_NO_TMAP")) return;
   const Geom &g = e->g;
   if (!g.dim3 || e->batch != 1 || g.nx < 4 || g.ny < 4) return;
@@ -367,16 +385,35 @@ void tm_setup(nls_engine *e) {
   e->tm_ok = ok;
 }
 
-template <class S, bool ANISO, int NC>
-bool launch_a_tm(nls_engine *e, const S *start, S *V, int j, int i0, int cnt, double *scal) {
-  if (!e->tm_ok || (sizeof(S) == 16 && NC > 6)) return false; // two sites per thread: 2 * NC complex values in registers
-  const Geom &g = e->g;
+// First pass-A chunk of iteration j over the columns c0..j through the tensor-map kernel.  Chooses the chunk
+// (*cnt columns from c0) so that the role of every column is a compile-time fact (nls_tmap.cuh): all of c0..j when
+// they fit (TM_TAIL; TM_SELF for one column), else the leading columns below j-1 (TM_BODY).
+template <class S, bool ANISO>
+bool launch_a_tm(nls_engine *e, const S *start, S *V, int j, int c0, int cap, int *cnt, double *scal) {
+  if (!e->tm_ok) return false;
+  if (cap > kTmMaxNC) cap = kTmMaxNC;
+  const int total = j + 1 - c0;
+  int mode, nc;
+  if (total == 1) { mode = TM_SELF; nc = 1; }
+  else if (total <= cap) { mode = TM_TAIL; nc = total; }
+  else {
+    // The split between this chunk and the dots-only chunk that follows moves no bytes (the second chunk re-reads w
+    // either way), so the body chunk is kept at the width that still fits 128 registers without spills
+    // (6 columns: 184-208 bytes of stack per thread, 4: none); NLS_TM_BODY overrides for tuning.
+    static const int body = []() { const char *b = getenv("NLS_TM_BODY"); const int v = b ? atoi(b) : 4; return v >= 1 && v <= kTmMaxNC ? v : 4; }();
+    if (cap > body) cap = body;
+    mode = TM_BODY;
+    nc = j - 1 - c0 < cap ? j - 1 - c0 : cap;
+  }
+  const void *fn = nc >= 1 ? tm_kernel<S, ANISO>(mode, nc) : nullptr;
+  if (!fn) return false;
+  Geom g = e->g;
   const S *cj = j == 0 ? start : V + (size_t)(j - 1) * e->colstride; // base of column j (halo included)
   const CUtensorMap *tmx = nullptr, *tmc = nullptr;
   if (!tm_get(e, cj, (int)(sizeof(S) / 8), &tmx)) return false;
   if (ANISO) { if (!tm_get(e, e->cf, 1, &tmc)) return false; }
   else tmc = tmx;
-  const dim3 gr = grid_for(e, (const void *)k_lanczos_a_tm<S, ANISO, NC>);
+  const dim3 gr = grid_for(e, fn);
   TmGeom tg;
   tg.ntx = (g.nx + kTmBX - 1) / kTmBX;
   tg.nty = (g.ny + kTmBY - 1) / kTmBY;
@@ -390,10 +427,18 @@ bool launch_a_tm(nls_engine *e, const S *start, S *V, int j, int i0, int cnt, do
   tg.nzc = (g.nz_loc + zc - 1) / zc;
   tg.units = tiles * tg.nzc;
   tg.zoff = g.halo ? 1 : 0;
-  k_lanczos_a_tm<S, ANISO, NC><<<dim3(gr.x, 1), kThreads, tm_smem_bytes((int)(sizeof(S) / 8), ANISO), e->stream>>>(*tmx, *tmc, g, tg, start, V, e->colstride, j, i0, cnt, e->cf,
-                                                                      scal, e->rc, e->status);
+  CUtensorMap mx = *tmx, mc = *tmc;
+  size_t colstride = e->colstride;
+  int i0 = c0;
+  const double *cf = e->cf;
+  RedCtx rc = e->rc;
+  int *status = e->status;
+  void *args[] = {&mx, &mc, &g, &tg, &start, &V, &colstride, &j, &i0, &cf, &scal, &rc, &status};
+  if (cudaLaunchKernel(fn, dim3(gr.x, 1), dim3(kThreads), args, tm_smem_bytes((int)(sizeof(S) / 8), ANISO), e->stream) != cudaSuccess)
+    return false;
   e->count();
   e->tm_launches += 1;
+  *cnt = nc;
   return true;
 }
 
@@ -416,6 +461,7 @@ void lanczos_t(nls_engine *e, const S *start, double *scal) {
       const int cap = first ? kFirst : kNC;
       cnt = j + 1 - i0 < cap ? j + 1 - i0 : cap;
       if (first && i0 == 0 && cnt == j + 1 && launch_a_tma<S, ANISO>(e, start, V, j, scal)) continue;
+      if (first && !(e->g.dim3 && (e->d.flags & NLS_FLAG_MARCH)) && launch_a_tm<S, ANISO>(e, start, V, j, c0, cap, &cnt, scal)) continue;
 #define LA(NC)                                                                                           \
   do {                                                                                                   \
     if (first && i0 == 0 && e->g.dim3 && (e->d.flags & NLS_FLAG_MARCH)) {                            \
@@ -423,7 +469,6 @@ void lanczos_t(nls_engine *e, const S *start, double *scal) {
       const March mc = make_march(e->g, 8 * (int)g3.x);                                                  \
       k_lanczos_a3<S, ANISO, NC><<<g3, kThreads, 0, e->stream>>>(e->g, mc, start, V, e->colstride, j, cnt, e->cf, scal, e->rc); \
       e->count();                                                                                        \
-    } else if (first && launch_a_tm<S, ANISO, NC>(e, start, V, j, i0, cnt, scal)) {                                               \
     } else if (first) LAUNCH(e, (k_lanczos_a<S, ANISO, NC, true>), gr, e->g, start, V, e->colstride, j, i0, cnt, e->cf, scal, e->rc);  \
     else LAUNCH(e, (k_lanczos_a<S, ANISO, NC, false>), gr, e->g, start, V, e->colstride, j, i0, cnt, e->cf, scal, e->rc);       \
   } while (0)
@@ -454,7 +499,9 @@ void lanczos_t(nls_engine *e, const S *start, double *scal) {
       if (launch_b_tma<S>(e, start, V, j, i0, cnt, last, scal, hp)) continue;
 #define LB(NC)                                                                                           \
   do {                                                                                                   \
-    if (last) LAUNCH(e, (k_lanczos_b<S, NC, true>), gr, e->g, start, V, e->colstride, j, i0, cnt, scal, e->rc, hp);  \
+    if (last && NC >= 10 && sizeof(S) == 16 && e->b_wide) {                                               \
+      LAUNCH(e, (k_lanczos_b_wide<S, (NC >= 10 ? NC : 10)>), gr, e->g, start, V, e->colstride, j, i0, cnt, scal, e->rc, hp); \
+    } else if (last) LAUNCH(e, (k_lanczos_b<S, NC, true>), gr, e->g, start, V, e->colstride, j, i0, cnt, scal, e->rc, hp);  \
     else LAUNCH(e, (k_lanczos_b<S, NC, false>), gr, e->g, start, V, e->colstride, j, i0, cnt, scal, e->rc, hp);      \
   } while (0)
       if (cnt <= 2) LB(2);
@@ -1009,10 +1056,14 @@ int nls_create(const nls_desc *desc, nls_handle *out) {
   const double sgn = d.op_sign == 0.0 ? 1.0 : d.op_sign;
   // L *= 1/(dx*dy) (laplacians.hpp:49); 3D: 1/(dx*dx) (:153)
   g.sc = sgn * (1.0 / (g.dim3 ? d.dx * d.dx : d.dx * d.dy));
+  g.pf = kDefaultPrefetch;
+  if (const char *pf = getenv("NLS_PREFETCH")) g.pf = atoi(pf); // grid sweeps of L2 prefetch lead in the flat passes (tuning knob)
+  if (g.pf < 0 || g.pf > 8) g.pf = 0;
   cudaDeviceGetAttribute(&e->nsm, cudaDevAttrMultiProcessorCount, d.device);
   cudaDeviceGetAttribute(&e->smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, d.device);
   e->smem_optin -= 4096; // dynamic budget: leave room for the kernels' static shared memory
   if (e->nsm < 1) e->nsm = 148;
+  if (const char *bw = getenv("NLS_B_WIDE")) e->b_wide = atoi(bw);         // tuning knob, not API
   if (const char *fc = getenv("NLS_FIRST_CAP")) e->first_cap = atoi(fc); // tuning knob (2..12), not API
   long long want = (g.n + kThreads - 1) / kThreads;
   long long cap = 8LL * e->nsm; // at most 8 CTAs of 256 threads per SM

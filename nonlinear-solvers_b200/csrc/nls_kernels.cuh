@@ -107,8 +107,21 @@ k_lanczos_a(Geom g, const S *__restrict__ start, S *__restrict__ V, size_t colst
   double acc[NC * T::W];
 #pragma unroll
   for (int k = 0; k < NC * T::W; ++k) acc[k] = 0.0;
+  const long long pfd = (long long)g.pf * gridDim.x * kThreads;
   for (long long idx = (long long)blockIdx.x * kThreads + threadIdx.x; idx < g.n;
        idx += (long long)gridDim.x * kThreads) {
+    if (pfd && idx + pfd < g.n) {
+#pragma unroll
+      for (int i = 0; i < NC; ++i)
+        if (i < cnt) pf_l2((i == 0 ? cb : cb + cs0 + (size_t)(i - 1) * colstride) + idx + pfd);
+      if (FIRST) {
+        if (j >= i0 + cnt) pf_l2(cj + idx + pfd);
+        if (j > 0 && j - 1 >= i0 + cnt) pf_l2(cm + idx + pfd);
+        if (ANISO) pf_l2(cfb + idx + pfd);
+      } else {
+        pf_l2(wc + idx + pfd);
+      }
+    }
     S v[NC];
 #pragma unroll
     for (int i = 0; i < NC; ++i)
@@ -225,9 +238,8 @@ k_lanczos_a3(Geom g, March mc, const S *__restrict__ start, S *__restrict__ V, s
 
 // columns [i0, i0+cnt).  LAST: ||w||^2 -> nrm2[j+1], T(j,j) -> alpha[j], halo push of column j+1.
 template <class S, int NC, bool LAST>
-__global__ void __launch_bounds__(kThreads, 2)
-k_lanczos_b(Geom g, const S *__restrict__ start, S *__restrict__ V, size_t colstride, int j, int i0,
-            int cnt, double *scal, RedCtx rc, Halo<S> hp) {
+__device__ __forceinline__ void lanczos_b_body(const Geom &g, const S *__restrict__ start, S *__restrict__ V, size_t colstride, int j,
+                                               int i0, int cnt, double *scal, const RedCtx &rc, const Halo<S> &hp) {
   using T = Sc<S>;
   double *sb = scal + (size_t)blockIdx.y * kScalStride;
   S *wc = traj(V + (size_t)j * colstride, g);
@@ -254,8 +266,15 @@ k_lanczos_b(Geom g, const S *__restrict__ start, S *__restrict__ V, size_t colst
   double acc[KA];
 #pragma unroll
   for (int k = 0; k < KA; ++k) acc[k] = 0.0;
+  const long long pfd = (long long)g.pf * gridDim.x * kThreads;
   for (long long idx = (long long)blockIdx.x * kThreads + threadIdx.x; idx < g.n;
        idx += (long long)gridDim.x * kThreads) {
+    if (pfd && idx + pfd < g.n) {
+#pragma unroll
+      for (int i = 0; i < NC; ++i)
+        if (i < cnt) pf_l2((i == 0 ? cb : cb + cs0 + (size_t)(i - 1) * colstride) + idx + pfd);
+      pf_l2(wc + idx + pfd);
+    }
     S v[NC];
 #pragma unroll
     for (int i = 0; i < NC; ++i)
@@ -278,6 +297,24 @@ k_lanczos_b(Geom g, const S *__restrict__ start, S *__restrict__ V, size_t colst
       sb[kOffAlpha + j * T::W] = sb[kOffH + j * T::W] / sqrt(sb[kOffNrm2 + j]);
     grid_reduce2s<KA - 1>(acc, rc, sb + kOffG + i0 * T::W, sb + kOffNrm2 + j + 1);
   }
+}
+
+template <class S, int NC, bool LAST>
+__global__ void __launch_bounds__(kThreads, 2)
+k_lanczos_b(Geom g, const S *__restrict__ start, S *__restrict__ V, size_t colstride, int j, int i0,
+            int cnt, double *scal, RedCtx rc, Halo<S> hp) {
+  lanczos_b_body<S, NC, LAST>(g, start, V, colstride, j, i0, cnt, scal, rc, hp);
+}
+
+// The closing chunk of a complex sweep with 10 / 12 columns holds 2 NC + 1 accumulators next to NC complex column
+// values: at 128 registers (2 CTAs/SM) it spills 112 / 216 bytes per thread and drops from 6.7 TB/s (8 columns) to
+// 5.0 / 4.0 TB/s (profiles/r02g_launches_c3_flat.csv).  This variant trades occupancy for registers: one CTA per SM,
+// up to 255 registers, no spills, NC + 1 independent 16-byte loads in flight per thread.  Opt-in (NLS_B_WIDE=1).
+template <class S, int NC>
+__global__ void __launch_bounds__(kThreads, 1)
+k_lanczos_b_wide(Geom g, const S *__restrict__ start, S *__restrict__ V, size_t colstride, int j, int i0,
+                 int cnt, double *scal, RedCtx rc, Halo<S> hp) {
+  lanczos_b_body<S, NC, true>(g, start, V, colstride, j, i0, cnt, scal, rc, hp);
 }
 
 // NLS_REORTH_MGS: the reference's sequential sweep, operation for operation (eigen_krylov_complex.hpp:28-38):

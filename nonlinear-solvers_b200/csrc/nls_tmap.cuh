@@ -19,6 +19,8 @@
 #pragma once
 #include <cuda.h>
 
+#include <type_traits>
+
 #include "nls_tma.cuh"
 
 namespace nls {
@@ -72,8 +74,10 @@ __device__ __forceinline__ unsigned tm_flags(const Geom &g, int i, int jj, int k
   return f;
 }
 
-// (L x)(site) * inv from the plane slots; wrap partners (two lines of sites per plane) come from global memory
-template <class S, bool ANISO>
+// (L x)(site) * inv from the plane slots.  EDGE = false: every neighbour exists and none wraps (all flags set, no
+// ring diagonal) -- the compiler folds the flag selects away; EDGE = true: flags of the site, and the wrap partners
+// (two lines of sites per plane) fetched from global memory
+template <class S, bool ANISO, bool EDGE>
 __device__ __forceinline__ S tm_stencil(const Geom &g, unsigned f, double inv, const S *__restrict__ xm, const S *__restrict__ xc,
                                         const S *__restrict__ xp, const double *__restrict__ cm, const double *__restrict__ cc,
                                         const double *__restrict__ cp, int sidx, int cidx, int jj, long long idx,
@@ -91,6 +95,10 @@ __device__ __forceinline__ S tm_stencil(const Geom &g, unsigned f, double inv, c
     cxm = cc[cidx - 1]; cxp = cc[cidx + 1];
     czm = cm[cidx]; czp = cp[cidx];
   }
+  if (!EDGE) {
+    constexpr unsigned kAll = NB_XM | NB_XP | NB_YM | NB_YP | NB_ZM | NB_ZP;
+    return stencil_vals<S, ANISO>(g, kAll, inv, centre, xzm, xym, xxm, xxp, xyp, xzp, c0, czm, cym, cxm, cxp, cyp, czp);
+  }
   // the reference's y links ignore plane boundaries: (i, 0, k) <-> (i, ny-1, k-1).  Those partners are not in the box
   // (its out-of-range rows are zero-filled): fetch them directly
   if (jj == 0 && (f & NB_YM)) {
@@ -104,16 +112,25 @@ __device__ __forceinline__ S tm_stencil(const Geom &g, unsigned f, double inv, c
   return stencil_vals<S, ANISO>(g, f, inv, centre, xzm, xym, xxm, xxp, xyp, xzp, c0, czm, cym, cxm, cxp, cyp, czp);
 }
 
-// columns [i0, i0+cnt) of 0..j take part in the dots (first chunk of the iteration: also forms w)
-template <class S, bool ANISO, int NC>
+// Columns [i0, i0+NC) of 0..j take part in the dots; the kernel also forms w (first chunk of the iteration).
+// The role of every chunk column is a compile-time fact, so the site loop has no selects between value sources:
+//   TM_TAIL: the chunk ends with columns j-1 and j (i0 + NC - 1 == j, j >= 1): those two are at hand (the recurrence
+//            term, the stencil centre), only the first NC-2 columns are loaded;
+//   TM_BODY: the chunk holds neither (i0 + NC <= j - 1): all NC columns are loaded;
+//   TM_SELF: the chunk is column j alone (NC == 1: j == 0, or the three-term recurrence without re-orthogonalisation).
+enum { TM_TAIL = 0, TM_BODY = 1, TM_SELF = 2 };
+template <class S, bool ANISO, int NC, int MODE>
 __global__ void __launch_bounds__(kThreads, 2)
 k_lanczos_a_tm(const __grid_constant__ CUtensorMap tmx, const __grid_constant__ CUtensorMap tmc, Geom g, TmGeom tg,
-               const S *__restrict__ start, S *__restrict__ V, size_t colstride, int j, int i0, int cnt,
+               const S *__restrict__ start, S *__restrict__ V, size_t colstride, int j, int i0,
                const double *__restrict__ cf, double *scal, RedCtx rc, int *status) {
   using T = Sc<S>;
   constexpr int W = T::W;
   using RX = TmRow<W>;
   using RC = TmRow<1>;
+  constexpr int kLd = MODE == TM_TAIL ? NC - 2 : (MODE == TM_BODY ? NC : 0); // columns loaded for the dots
+  static_assert(MODE != TM_TAIL || NC >= 2, "tail chunk holds columns j-1 and j");
+  static_assert(MODE != TM_SELF || NC == 1, "self chunk is column j alone");
   extern __shared__ __align__(128) unsigned char tm_smem[];
   unsigned long long *bars = (unsigned long long *)tm_smem;
   volatile int *s_abort = (volatile int *)(tm_smem + 64);
@@ -149,6 +166,9 @@ k_lanczos_a_tm(const __grid_constant__ CUtensorMap tmx, const __grid_constant__ 
     const int i = x0 + tx;
     const int jj[kTmRows] = {y0 + ty, y0 + ty + kTmTY};
     const bool live[kTmRows] = {i < g.nx && jj[0] < g.ny, i < g.nx && jj[1] < g.ny};
+    // warp-uniform: some site of this warp lies on an x / y face of the grid (or outside it)
+    const bool edge_xy = __any_sync(0xffffffffu, !live[1] || i == 0 || i == g.nx - 1 || jj[0] == 0 || jj[1] == g.ny - 1 ||
+                                                     jj[0] == g.ny - 1 || jj[1] == 0);
     // box origin in tensor-map coordinates: the inner dimension counts doubles (complex = 2 per site)
     const int bx = (x0 - RX::XO) * W, by = y0 - 1;
     auto issue = [&](int k) { // plane k (local index, may be k0-1 .. k1) into slot (k - k0 + 1) % R
@@ -169,44 +189,46 @@ k_lanczos_a_tm(const __grid_constant__ CUtensorMap tmx, const __grid_constant__ 
     const int sidx[kTmRows] = {(ty + 1) * RX::PX + tx + RX::XO, (ty + kTmTY + 1) * RX::PX + tx + RX::XO};
     const int cidx[kTmRows] = {(ty + 1) * RC::PX + tx + RC::XO, (ty + kTmTY + 1) * RC::PX + tx + RC::XO};
     long long idx0 = ((long long)k0 * g.ny + jj[0]) * g.nx + i;
+    const long long rowskip = (long long)kTmTY * g.nx;
     for (int k = k0; k < k1; ++k, idx0 += g.plane) {
       const int sm = (k - k0) % kTmR, sc = (k - k0 + 1) % kTmR, sp = (k - k0 + 2) % kTmR;
-      const long long idx[kTmRows] = {idx0, idx0 + (long long)kTmTY * g.nx};
-      // the global loads of both sites first (independent of the ring), then the wait for plane k+1
-      S cmv[kTmRows], v[kTmRows][NC];
-#pragma unroll
-      for (int r = 0; r < kTmRows; ++r) {
-        cmv[r] = T::zero();
-        if (live[r] && j > 0) cmv[r] = ld_stream(cm + idx[r]);
-#pragma unroll
-        for (int q = 0; q < NC; ++q) {
-          const int col = i0 + q;
-          v[r][q] = T::zero();
-          if (live[r] && q < cnt && col != j && col != j - 1)
-            v[r][q] = ld_stream((q == 0 ? cb : cb + cs0 + (size_t)(q - 1) * colstride) + idx[r]);
-        }
-      }
-      mbar_wait(&bars[sp], (phase_bits >> sp) & 1u, s_abort, status);
-      phase_bits ^= 1u << sp;
       const int kg = g.z0 + k;
+      const bool edge = edge_xy || kg == 0 || kg == g.nz_glob - 1; // warp-uniform
+      const S *xsm = xs + (size_t)sm * RX::kPad, *xsc = xs + (size_t)sc * RX::kPad, *xsp = xs + (size_t)sp * RX::kPad;
+      const double *csm = cs + (size_t)sm * RC::kPad, *csc = cs + (size_t)sc * RC::kPad, *csp = cs + (size_t)sp * RC::kPad;
+      // one plane step of both sites: the global loads first (independent of the ring), then the wait for plane k+1
+      auto step = [&](auto edge_c) {
+        constexpr bool EDGE = decltype(edge_c)::value;
+        S cmv[kTmRows], v[kTmRows][kLd > 0 ? kLd : 1];
 #pragma unroll
-      for (int r = 0; r < kTmRows; ++r)
-        if (live[r]) {
-          const unsigned f = tm_flags(g, i, jj[r], kg);
-          S xc;
-          S w = tm_stencil<S, ANISO>(g, f, inv, xs + (size_t)sm * RX::kPad, xs + (size_t)sc * RX::kPad, xs + (size_t)sp * RX::kPad,
-                                     cs + (size_t)sm * RC::kPad, cs + (size_t)sc * RC::kPad, cs + (size_t)sp * RC::kPad, sidx[r],
-                                     cidx[r], jj[r], idx[r], cj, cfb, xc);
-          if (j > 0) w = T::fma_r(cmul, cmv[r], w);
-          __stcs(wc + idx[r], w);
+        for (int r = 0; r < kTmRows; ++r) {
+          const long long idx = idx0 + r * rowskip;
+          const bool on = !EDGE || live[r];
+          cmv[r] = T::zero();
+          if (on && j > 0) cmv[r] = ld_stream(cm + idx);
 #pragma unroll
-          for (int q = 0; q < NC; ++q)
-            if (q < cnt) {
-              const int col = i0 + q;
-              const S vq = col == j ? xc : col == j - 1 ? cmv[r] : v[r][q];
-              T::dot_acc(acc + q * W, vq, w);
-            }
+          for (int q = 0; q < kLd; ++q)
+            if (on) v[r][q] = ld_stream((q == 0 ? cb : cb + cs0 + (size_t)(q - 1) * colstride) + idx);
         }
+        mbar_wait(&bars[sp], (phase_bits >> sp) & 1u, s_abort, status);
+#pragma unroll
+        for (int r = 0; r < kTmRows; ++r) {
+          const long long idx = idx0 + r * rowskip;
+          if (EDGE && !live[r]) continue;
+          const unsigned f = EDGE ? tm_flags(g, i, jj[r], kg) : 0u;
+          S xc;
+          S w = tm_stencil<S, ANISO, EDGE>(g, f, inv, xsm, xsc, xsp, csm, csc, csp, sidx[r], cidx[r], jj[r], idx, cj, cfb, xc);
+          if (j > 0) w = T::fma_r(cmul, cmv[r], w);
+          __stcs(wc + idx, w);
+#pragma unroll
+          for (int q = 0; q < kLd; ++q) T::dot_acc(acc + q * W, v[r][q], w);
+          if constexpr (MODE == TM_TAIL) T::dot_acc(acc + (NC - 2) * W, cmv[r], w);
+          if constexpr (MODE != TM_BODY) T::dot_acc(acc + (NC - 1) * W, xc, w);
+        }
+      };
+      if (edge) step(std::true_type{});
+      else step(std::false_type{});
+      phase_bits ^= 1u << sp;
       __syncthreads(); // all reads of slot sm (plane k-1) are done: plane k+3 goes there, two steps ahead of its use
       if (threadIdx.x == 0 && k + 3 <= k1) {
         fence_proxy_async();
