@@ -158,7 +158,10 @@ enum {
                              * shared memory).  Correct and tested, but measured slower than the register-staged
                              * passes on B200 so far, hence opt-in */
   NLS_FLAG_TMAP = 128u,     /* 3D single-trajectory grids: pass A of the Lanczos iteration with the stencil input staged through
-                             * shared memory by tensor-map TMA loads (nls_tmap.cuh: cp.async.bulk.tensor.3d boxes with halo) */
+                             * shared memory by tensor-map TMA loads (nls_tmap.cuh: cp.async.bulk.tensor.3d boxes with halo).
+                             * DEFAULT for complex states (C3 10.6 -> 9.5, C5 61.7 -> 50.5 ms/step); the flag opts real
+                             * states in */
+  NLS_FLAG_NO_TMAP = 256u,  /* never use the tensor-map pass (flat register-streaming pass A instead) */
   NLS_FLAG_PK_SV = 64u,     /* Stoermer-Verlet through the persistent kernel (k_pk_sv); off by default: at
                              * 1024^2 one grid barrier per step (15.7 us) costs more than a k_sv launch (11-14 us) */
   NLS_FLAG_DEBUG_PK_FAULT = 0x80000000u, /* test hook: one CTA of the persistent kernel never reaches its first

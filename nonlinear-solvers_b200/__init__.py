@@ -5,7 +5,7 @@ C-ABI library ``libnls_b200.so`` (include/nls.h) and the C++ classes/drivers abo
 """
 from .binding import (  # noqa: F401
     Desc, Engine, NlsError, load_library, library_path, build_library, pinned_empty, pinned_free,
-    EQ, INT, LAP, FN, FIELD, RED, REORTH, FLAG_NO_GRAPH, FLAG_NO_PERSISTENT, FLAG_SEWI_HOST2D, FLAG_MARCH, FLAG_TMA, FLAG_PK_SV, FLAG_TMAP,
+    EQ, INT, LAP, FN, FIELD, RED, REORTH, FLAG_NO_GRAPH, FLAG_NO_PERSISTENT, FLAG_SEWI_HOST2D, FLAG_MARCH, FLAG_TMA, FLAG_PK_SV, FLAG_TMAP, FLAG_NO_TMAP,
     FLAG_DEBUG_PK_FAULT, GEN, GENPOST, GenTerm,
 )
 from . import slabs  # noqa: F401,E402

@@ -31,6 +31,7 @@ FLAG_MARCH = 8
 FLAG_TMA = 32
 FLAG_PK_SV = 64
 FLAG_TMAP = 128
+FLAG_NO_TMAP = 256
 FLAG_DEBUG_PK_FAULT = 0x80000000
 
 

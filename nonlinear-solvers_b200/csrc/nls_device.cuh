@@ -65,12 +65,13 @@ struct Geom {
   long long stride; // elements between consecutive trajectories (= n + 2*halo)
   double sc;     // op_sign / (dx*dy)   [2D]   or   op_sign / (dx*dx)   [3D]
   int pf;        // grid sweeps the flat Lanczos passes prefetch ahead into L2 (0 = off; pf_l2 below)
+  int pf_first;  // the same for the stencil-carrying flat pass A
 };
 
 // The flat passes are one batch of loads per thread and grid sweep: a sweep lasts one loaded DRAM round trip
 // (~2 us at 16 warps/SM, profiles/r02j_ncu_full_c3_pass_a_tm_v1_vs_flat.txt: long-scoreboard 11 per issue, issue
 // slots 27 % busy).  Prefetching the lines of the thread's NEXT sweep into L2 costs no registers and turns the
-// exposed latency into an L2 hit.  Tuning knob NLS_PREFETCH (sweeps of lead), default off until measured.
+// exposed latency into an L2 hit.  Lead of one sweep by default (nls_engine.cu: kDefaultPrefetch, measurements there).
 __device__ __forceinline__ void pf_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 
 // y = (L x)(idx) for one site.  x points at local site 0 (ghost planes, if any, sit at

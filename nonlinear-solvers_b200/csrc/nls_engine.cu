@@ -19,7 +19,7 @@
 using namespace nls;
 
 namespace {
-constexpr int kDefaultPrefetch = 0; // L2 prefetch lead of the flat Lanczos passes, in grid sweeps (Geom::pf)
+constexpr int kDefaultPrefetch = 1; // L2 prefetch lead of the flat Lanczos passes, in grid sweeps (Geom::pf)
 constexpr size_t kDefaultColPad = 0; // see col_pad_bytes()
 thread_local std::string g_err;
 
@@ -49,7 +49,6 @@ struct nls_engine {
   int nblk = 1; // capacity of the partial-sum array (max CTAs per trajectory)
   int nsm = 148;
   int smem_optin = 0;  // max dynamic shared memory per CTA
-  int b_wide = 0;      // closing pass-B chunk with >= 10 complex columns: 1 = k_lanczos_b_wide (1 CTA/SM, no spills)
   int first_cap = 0;   // complex pass A: columns in the stencil-carrying first chunk (0 = rule in lanczos_t)
   bool tma_ok = false; // TMA-staged Lanczos passes usable (alignment + size), see tma_setup
   bool tm_ok = false;  // tensor-map pass A (nls_tmap.cuh) usable
@@ -373,7 +372,7 @@ void tm_setup(nls_engine *e) {
   // NLS_NO_TMAP=1 force the flat pass
   const char *env = getenv("NLS_PASS_A_TMAP");
   const bool want = env ? atoi(env) != 0 : ((e->d.flags & NLS_FLAG_TMAP) || e->cplx);
-  if (!want || getenv("NLS_NO_TMAP")) return;
+  if (!want || (e->d.flags & NLS_FLAG_NO_TMAP) || getenv("NLS_NO_TMAP")) return;
   const Geom &g = e->g;
   if (!g.dim3 || e->batch != 1 || g.nx < 4 || g.ny < 4) return;
   if (!e->cplx && (g.nx % 2)) return; // row pitch must be a multiple of 16 bytes
@@ -499,9 +498,7 @@ void lanczos_t(nls_engine *e, const S *start, double *scal) {
       if (launch_b_tma<S>(e, start, V, j, i0, cnt, last, scal, hp)) continue;
 #define LB(NC)                                                                                           \
   do {                                                                                                   \
-    if (last && NC >= 10 && sizeof(S) == 16 && e->b_wide) {                                               \
-      LAUNCH(e, (k_lanczos_b_wide<S, (NC >= 10 ? NC : 10)>), gr, e->g, start, V, e->colstride, j, i0, cnt, scal, e->rc, hp); \
-    } else if (last) LAUNCH(e, (k_lanczos_b<S, NC, true>), gr, e->g, start, V, e->colstride, j, i0, cnt, scal, e->rc, hp);  \
+    if (last) LAUNCH(e, (k_lanczos_b<S, NC, true>), gr, e->g, start, V, e->colstride, j, i0, cnt, scal, e->rc, hp);  \
     else LAUNCH(e, (k_lanczos_b<S, NC, false>), gr, e->g, start, V, e->colstride, j, i0, cnt, scal, e->rc, hp);      \
   } while (0)
       if (cnt <= 2) LB(2);
@@ -1056,14 +1053,19 @@ int nls_create(const nls_desc *desc, nls_handle *out) {
   const double sgn = d.op_sign == 0.0 ? 1.0 : d.op_sign;
   // L *= 1/(dx*dy) (laplacians.hpp:49); 3D: 1/(dx*dx) (:153)
   g.sc = sgn * (1.0 / (g.dim3 ? d.dx * d.dx : d.dx * d.dy));
+  // L2 prefetch lead of the flat passes in grid sweeps; NLS_PREFETCH / NLS_PREFETCH_FIRST are tuning knobs.  Measured
+  // (profiles/r02l_bench_ab.jsonl): lead 1 takes C4 7.32 -> 6.35 ms/step, flat C3 10.62 -> 9.99, C5 (tensor-map pass A,
+  // flat pass B) 50.5 -> 49.1; lead 2 is no better.
   g.pf = kDefaultPrefetch;
-  if (const char *pf = getenv("NLS_PREFETCH")) g.pf = atoi(pf); // grid sweeps of L2 prefetch lead in the flat passes (tuning knob)
+  g.pf_first = kDefaultPrefetch;
+  if (const char *pf = getenv("NLS_PREFETCH")) g.pf = g.pf_first = atoi(pf);
+  if (const char *pf = getenv("NLS_PREFETCH_FIRST")) g.pf_first = atoi(pf);
   if (g.pf < 0 || g.pf > 8) g.pf = 0;
+  if (g.pf_first < 0 || g.pf_first > 8) g.pf_first = 0;
   cudaDeviceGetAttribute(&e->nsm, cudaDevAttrMultiProcessorCount, d.device);
   cudaDeviceGetAttribute(&e->smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, d.device);
   e->smem_optin -= 4096; // dynamic budget: leave room for the kernels' static shared memory
   if (e->nsm < 1) e->nsm = 148;
-  if (const char *bw = getenv("NLS_B_WIDE")) e->b_wide = atoi(bw);         // tuning knob, not API
   if (const char *fc = getenv("NLS_FIRST_CAP")) e->first_cap = atoi(fc); // tuning knob (2..12), not API
   long long want = (g.n + kThreads - 1) / kThreads;
   long long cap = 8LL * e->nsm; // at most 8 CTAs of 256 threads per SM

@@ -107,7 +107,7 @@ k_lanczos_a(Geom g, const S *__restrict__ start, S *__restrict__ V, size_t colst
   double acc[NC * T::W];
 #pragma unroll
   for (int k = 0; k < NC * T::W; ++k) acc[k] = 0.0;
-  const long long pfd = (long long)g.pf * gridDim.x * kThreads;
+  const long long pfd = (long long)(FIRST ? g.pf_first : g.pf) * gridDim.x * kThreads;
   for (long long idx = (long long)blockIdx.x * kThreads + threadIdx.x; idx < g.n;
        idx += (long long)gridDim.x * kThreads) {
     if (pfd && idx + pfd < g.n) {
@@ -304,17 +304,6 @@ __global__ void __launch_bounds__(kThreads, 2)
 k_lanczos_b(Geom g, const S *__restrict__ start, S *__restrict__ V, size_t colstride, int j, int i0,
             int cnt, double *scal, RedCtx rc, Halo<S> hp) {
   lanczos_b_body<S, NC, LAST>(g, start, V, colstride, j, i0, cnt, scal, rc, hp);
-}
-
-// The closing chunk of a complex sweep with 10 / 12 columns holds 2 NC + 1 accumulators next to NC complex column
-// values: at 128 registers (2 CTAs/SM) it spills 112 / 216 bytes per thread and drops from 6.7 TB/s (8 columns) to
-// 5.0 / 4.0 TB/s (profiles/r02g_launches_c3_flat.csv).  This variant trades occupancy for registers: one CTA per SM,
-// up to 255 registers, no spills, NC + 1 independent 16-byte loads in flight per thread.  Opt-in (NLS_B_WIDE=1).
-template <class S, int NC>
-__global__ void __launch_bounds__(kThreads, 1)
-k_lanczos_b_wide(Geom g, const S *__restrict__ start, S *__restrict__ V, size_t colstride, int j, int i0,
-                 int cnt, double *scal, RedCtx rc, Halo<S> hp) {
-  lanczos_b_body<S, NC, true>(g, start, V, colstride, j, i0, cnt, scal, rc, hp);
 }
 
 // NLS_REORTH_MGS: the reference's sequential sweep, operation for operation (eigen_krylov_complex.hpp:28-38):
@@ -745,8 +734,14 @@ k_nlse_finish(Geom g, const double2 *__restrict__ start, const double2 *__restri
   double2 *un = traj(uout, g), *rb = traj(rho, g);
   const double *mb = mf + g.halo;
   double acc[1] = {0.0};
+  const long long pfd = (long long)g.pf * gridDim.x * kThreads;
   for (long long idx = (long long)blockIdx.x * kThreads + threadIdx.x; idx < g.n;
        idx += (long long)gridDim.x * kThreads) {
+    if (pfd && idx + pfd < g.n) { // the m basis columns of this thread's next sweep -> L2 (pf_l2, nls_device.cuh)
+      pf_l2(st + idx + pfd);
+      for (int i = 1; i < m; ++i) pf_l2(vb + (size_t)(i - 1) * colstride + idx + pfd);
+      if (EQ != NLS_EQ_NLSE_CUBIC) pf_l2(uo + idx + pfd);
+    }
     const long long sc = clamp_site(g, idx);
     const double2 buf = combine_site<double2>(st, vb, colstride, co, m, sc);
     double2 unew;

@@ -537,7 +537,7 @@ def test_tensor_map_pass_matches_flat_pass_and_oracle(orc, dims, eq, lap, m):
     if real:
         u0 = 0.3 * np.abs(u0)
     outs = []
-    for flags in (nls_b200.FLAG_NO_PERSISTENT | nls_b200.FLAG_TMAP, nls_b200.FLAG_NO_PERSISTENT):
+    for flags in (nls_b200.FLAG_NO_PERSISTENT | nls_b200.FLAG_TMAP, nls_b200.FLAG_NO_PERSISTENT | nls_b200.FLAG_NO_TMAP):
         d = Desc.make(nx, ny, nz, dx=0.2, flags=flags, **kw)
         e = Engine(d)
         if lap == LAP.ANISO:
