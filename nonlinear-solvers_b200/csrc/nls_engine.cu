@@ -19,6 +19,7 @@
 using namespace nls;
 
 namespace {
+constexpr int kTmDefaultPipe = 0, kTmDefaultPrefetch = 0; // tensor-map pass A: per-warp ring hand-back, column prefetch lead (planes)
 constexpr int kDefaultPrefetch = 1; // L2 prefetch lead of the flat Lanczos passes, in grid sweeps (Geom::pf)
 constexpr size_t kDefaultColPad = 0; // see col_pad_bytes()
 thread_local std::string g_err;
@@ -349,8 +350,12 @@ bool tm_get(nls_engine *e, const void *base, int doubles_per_site, const CUtenso
 
 // kernel for (mode, columns in the chunk); nullptr when there is none
 constexpr int kTmMaxNC = 6; // two sites per thread: 2 * NC complex values in registers
-template <class S, bool ANISO> const void *tm_kernel(int mode, int nc) {
-#define TMK(M, N) if (mode == M && nc == N) return (const void *)k_lanczos_a_tm<S, ANISO, N, M>
+template <class S, bool ANISO> const void *tm_kernel(int mode, int nc, bool pipe) {
+  constexpr bool kHasPipe = sizeof(S) == 16; // the per-warp hand-back variant is built for complex states only
+  if (pipe && !kHasPipe) pipe = false;
+#define TMK(M, N)                                                                                       \
+  if (mode == M && nc == N)                                                                             \
+  return pipe ? (const void *)k_lanczos_a_tm<S, ANISO, N, M, kHasPipe> : (const void *)k_lanczos_a_tm<S, ANISO, N, M, false>
   TMK(TM_SELF, 1);
   TMK(TM_TAIL, 2); TMK(TM_TAIL, 3); TMK(TM_TAIL, 4); TMK(TM_TAIL, 5); TMK(TM_TAIL, 6);
   TMK(TM_BODY, 1); TMK(TM_BODY, 2); TMK(TM_BODY, 3); TMK(TM_BODY, 4); TMK(TM_BODY, 5); TMK(TM_BODY, 6);
@@ -360,8 +365,9 @@ template <class S, bool ANISO> const void *tm_kernel(int mode, int nc) {
 template <class S, bool ANISO> bool tm_attrs(int bytes) { // dynamic shared memory opt-in: not allowed later, inside a capture
   for (int mode = 0; mode < 3; ++mode)
     for (int nc = 1; nc <= kTmMaxNC; ++nc)
-      if (const void *fn = tm_kernel<S, ANISO>(mode, nc))
-        if (!tma_attr(fn, bytes)) return false;
+      for (int pipe = 0; pipe < 2; ++pipe)
+        if (const void *fn = tm_kernel<S, ANISO>(mode, nc, pipe != 0))
+          if (!tma_attr(fn, bytes)) return false;
   return true;
 }
 
@@ -378,7 +384,7 @@ void tm_setup(nls_engine *e) {
   if (!e->cplx && (g.nx % 2)) return; // row pitch must be a multiple of 16 bytes
   if (!encode_tiled()) return;
   const bool an = e->d.laplacian == NLS_LAP_ANISO;
-  const int bytes = (int)tm_smem_bytes(e->W, an);
+  const int bytes = (int)tm_smem_bytes(e->W, an, kTmRPipe); // opt-in for the larger of the two ring sizes
   const bool ok = e->cplx ? (an ? tm_attrs<double2, true>(bytes) : tm_attrs<double2, false>(bytes))
                           : (an ? tm_attrs<double, true>(bytes) : tm_attrs<double, false>(bytes));
   e->tm_ok = ok;
@@ -404,7 +410,11 @@ bool launch_a_tm(nls_engine *e, const S *start, S *V, int j, int c0, int cap, in
     mode = TM_BODY;
     nc = j - 1 - c0 < cap ? j - 1 - c0 : cap;
   }
-  const void *fn = nc >= 1 ? tm_kernel<S, ANISO>(mode, nc) : nullptr;
+  // ring hand-back style and L2 prefetch lead of the column values: tuning knobs (NLS_TM_PIPE, NLS_TM_PREFETCH)
+  static const int pipe_knob = []() { const char *v = getenv("NLS_TM_PIPE"); return v ? atoi(v) != 0 : kTmDefaultPipe; }();
+  static const int tpf = []() { const char *v = getenv("NLS_TM_PREFETCH"); const int n = v ? atoi(v) : kTmDefaultPrefetch; return n >= 0 && n <= 8 ? n : 0; }();
+  const bool pipe = pipe_knob && sizeof(S) == 16;
+  const void *fn = nc >= 1 ? tm_kernel<S, ANISO>(mode, nc, pipe) : nullptr;
   if (!fn) return false;
   Geom g = e->g;
   const S *cj = j == 0 ? start : V + (size_t)(j - 1) * e->colstride; // base of column j (halo included)
@@ -426,6 +436,7 @@ bool launch_a_tm(nls_engine *e, const S *start, S *V, int j, int c0, int cap, in
   tg.nzc = (g.nz_loc + zc - 1) / zc;
   tg.units = tiles * tg.nzc;
   tg.zoff = g.halo ? 1 : 0;
+  tg.pf = tpf;
   CUtensorMap mx = *tmx, mc = *tmc;
   size_t colstride = e->colstride;
   int i0 = c0;
@@ -433,7 +444,7 @@ bool launch_a_tm(nls_engine *e, const S *start, S *V, int j, int c0, int cap, in
   RedCtx rc = e->rc;
   int *status = e->status;
   void *args[] = {&mx, &mc, &g, &tg, &start, &V, &colstride, &j, &i0, &cf, &scal, &rc, &status};
-  if (cudaLaunchKernel(fn, dim3(gr.x, 1), dim3(kThreads), args, tm_smem_bytes((int)(sizeof(S) / 8), ANISO), e->stream) != cudaSuccess)
+  if (cudaLaunchKernel(fn, dim3(gr.x, 1), dim3(kThreads), args, tm_smem_bytes((int)(sizeof(S) / 8), ANISO, pipe ? kTmRPipe : kTmR), e->stream) != cudaSuccess)
     return false;
   e->count();
   e->tm_launches += 1;
@@ -1055,9 +1066,10 @@ int nls_create(const nls_desc *desc, nls_handle *out) {
   g.sc = sgn * (1.0 / (g.dim3 ? d.dx * d.dx : d.dx * d.dy));
   // L2 prefetch lead of the flat passes in grid sweeps; NLS_PREFETCH / NLS_PREFETCH_FIRST are tuning knobs.  Measured
   // (profiles/r02l_bench_ab.jsonl): lead 1 takes C4 7.32 -> 6.35 ms/step, flat C3 10.62 -> 9.99, C5 (tensor-map pass A,
-  // flat pass B) 50.5 -> 49.1; lead 2 is no better.
+  // flat pass B) 50.5 -> 48.4; lead 2 is no better.  The stencil-carrying flat pass of a 3D grid is the exception
+  // (flat C5 66.4 ms/step without, 72.1 with; 2D C4: 6.98 without, 6.33 with -- profiles/r02m_bench_ab.jsonl).
   g.pf = kDefaultPrefetch;
-  g.pf_first = kDefaultPrefetch;
+  g.pf_first = g.dim3 ? 0 : kDefaultPrefetch;
   if (const char *pf = getenv("NLS_PREFETCH")) g.pf = g.pf_first = atoi(pf);
   if (const char *pf = getenv("NLS_PREFETCH_FIRST")) g.pf_first = atoi(pf);
   if (g.pf < 0 || g.pf > 8) g.pf = 0;

@@ -275,21 +275,23 @@ __device__ __forceinline__ void lanczos_b_body(const Geom &g, const S *__restric
         if (i < cnt) pf_l2((i == 0 ? cb : cb + cs0 + (size_t)(i - 1) * colstride) + idx + pfd);
       pf_l2(wc + idx + pfd);
     }
-    S v[NC];
-#pragma unroll
-    for (int i = 0; i < NC; ++i)
-      if (i < cnt) v[i] = (i == 0 ? cb : cb + cs0 + (size_t)(i - 1) * colstride)[idx];
-    S wv = wc[idx];
-#pragma unroll
-    for (int i = 0; i < NC; ++i)
-      if (i < cnt) wv = T::sub(wv, T::mul(h[i], v[i]));
-    wc[idx] = wv;
-    if (LAST) {
+    {
+      S v[NC];
 #pragma unroll
       for (int i = 0; i < NC; ++i)
-        if (i < cnt) T::dot_acc(acc + i * T::W, v[i], wv);
-      acc[KA - 1] += T::abs2(wv);
-      halo_push<S>(hp, g.n, g.plane, idx, wv); // column j+1 is the next iteration's stencil input
+        if (i < cnt) v[i] = (i == 0 ? cb : cb + cs0 + (size_t)(i - 1) * colstride)[idx];
+      S wv = wc[idx];
+#pragma unroll
+      for (int i = 0; i < NC; ++i)
+        if (i < cnt) wv = T::sub(wv, T::mul(h[i], v[i]));
+      wc[idx] = wv;
+      if (LAST) {
+#pragma unroll
+        for (int i = 0; i < NC; ++i)
+          if (i < cnt) T::dot_acc(acc + i * T::W, v[i], wv);
+        acc[KA - 1] += T::abs2(wv);
+        halo_push<S>(hp, g.n, g.plane, idx, wv); // column j+1 is the next iteration's stencil input
+      }
     }
   }
   if (LAST) {

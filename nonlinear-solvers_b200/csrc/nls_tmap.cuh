@@ -27,7 +27,10 @@ namespace nls {
 
 constexpr int kTmBX = 64, kTmBY = 8;  // tile; kThreads = 64 x 4 threads, two rows per thread
 constexpr int kTmRows = 2, kTmTY = kTmBY / kTmRows;
-constexpr int kTmR = 4;               // plane slots: k-1, k, k+1 in use + one in flight (plane k+3 re-uses k-1's slot)
+// plane slots of the shared-memory ring.  4: planes k-1, k, k+1 in use + one in flight, the slot of plane k-1 is handed
+// back by a __syncthreads per plane step.  6 ("pipe"): three planes in flight, every warp hands a plane back by arriving
+// on the slot's EMPTY mbarrier and only the issuing thread waits for it, one step later -- no CTA-wide barrier per plane.
+constexpr int kTmR = 4, kTmRPipe = 6, kTmRMax = 8;
 constexpr int kTmPY = kTmBY + 2;
 static_assert(kTmBX * kTmTY == kThreads, "tile / thread mapping");
 // Box rows.  A box row must span a multiple of 32 BYTES on sm_100a: a 66-double (528 B) row is accepted by
@@ -40,19 +43,27 @@ template <int W> struct TmRow {
   static constexpr int kSites = PX * kTmPY;
   static constexpr int kPad = (kSites * W * 8 + 127) / 128 * 128 / (W * 8); // slot stride in sites: 128-byte multiple
 };
-constexpr int kTmHdrBytes = 128; // mbarriers + abort word in front of the slots
+constexpr int kTmHdrBytes = 256; // FULL mbarriers [8] + EMPTY mbarriers [8] + abort word in front of the slots
 
-// dynamic shared memory of one CTA
-inline size_t tm_smem_bytes(int W, bool aniso) {
-  const size_t xs = (size_t)kTmR * (W == 2 ? TmRow<2>::kPad * 16 : TmRow<1>::kPad * 8);
-  return kTmHdrBytes + xs + (aniso ? (size_t)kTmR * TmRow<1>::kPad * 8 : 0);
+// dynamic shared memory of one CTA with `nslot` plane slots
+inline size_t tm_smem_bytes(int W, bool aniso, int nslot) {
+  const size_t xs = (size_t)nslot * (W == 2 ? TmRow<2>::kPad * 16 : TmRow<1>::kPad * 8);
+  return kTmHdrBytes + xs + (aniso ? (size_t)nslot * TmRow<1>::kPad * 8 : 0);
 }
 
 struct TmGeom {
   int ntx, nty, nzc, zc; // tiles in x / y, z chunks, planes per chunk
   long long units;
   int zoff;              // tensor-map z coordinate of local plane 0 (1 when the arrays carry ghost planes)
+  int pf;                // planes the basis-column values are prefetched ahead into L2 (0 = off)
 };
+
+__device__ __forceinline__ void mbar_inval(unsigned long long *bar) {
+  asm volatile("mbarrier.inval.shared::cta.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(unsigned long long *bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
 
 __device__ __forceinline__ void tma_load_3d(void *dst_smem, const CUtensorMap *tm, int c0, int c1, int c2, unsigned long long *bar) {
   asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];" ::"r"(
@@ -119,7 +130,7 @@ __device__ __forceinline__ S tm_stencil(const Geom &g, unsigned f, double inv, c
 //   TM_BODY: the chunk holds neither (i0 + NC <= j - 1): all NC columns are loaded;
 //   TM_SELF: the chunk is column j alone (NC == 1: j == 0, or the three-term recurrence without re-orthogonalisation).
 enum { TM_TAIL = 0, TM_BODY = 1, TM_SELF = 2 };
-template <class S, bool ANISO, int NC, int MODE>
+template <class S, bool ANISO, int NC, int MODE, bool PIPE = false>
 __global__ void __launch_bounds__(kThreads, 2)
 k_lanczos_a_tm(const __grid_constant__ CUtensorMap tmx, const __grid_constant__ CUtensorMap tmc, Geom g, TmGeom tg,
                const S *__restrict__ start, S *__restrict__ V, size_t colstride, int j, int i0,
@@ -132,10 +143,11 @@ k_lanczos_a_tm(const __grid_constant__ CUtensorMap tmx, const __grid_constant__ 
   static_assert(MODE != TM_TAIL || NC >= 2, "tail chunk holds columns j-1 and j");
   static_assert(MODE != TM_SELF || NC == 1, "self chunk is column j alone");
   extern __shared__ __align__(128) unsigned char tm_smem[];
-  unsigned long long *bars = (unsigned long long *)tm_smem;
-  volatile int *s_abort = (volatile int *)(tm_smem + 64);
-  S *xs = (S *)(tm_smem + kTmHdrBytes);                       // [kTmR][RX::kPad]
-  double *cs = (double *)(xs + (size_t)kTmR * RX::kPad);      // [kTmR][RC::kPad] (ANISO only)
+  unsigned long long *full = (unsigned long long *)tm_smem, *empty = full + kTmRMax;
+  volatile int *s_abort = (volatile int *)(tm_smem + 128);
+  constexpr int R = PIPE ? kTmRPipe : kTmR;
+  S *xs = (S *)(tm_smem + kTmHdrBytes);                  // [R][RX::kPad]
+  double *cs = (double *)(xs + (size_t)R * RX::kPad);    // [R][RC::kPad] (ANISO only)
   double *sb = scal;
   const S *cj = colptr<S>(start, V, colstride, j) + g.halo;
   const S *cm = j > 0 ? colptr<S>(start, V, colstride, j - 1) + g.halo : nullptr;
@@ -151,18 +163,14 @@ k_lanczos_a_tm(const __grid_constant__ CUtensorMap tmx, const __grid_constant__ 
   for (int k = 0; k < NC * W; ++k) acc[k] = 0.0;
   const int tx = threadIdx.x % kTmBX, ty = threadIdx.x / kTmBX;
   constexpr unsigned kBoxBytes = (unsigned)(RX::kSites * sizeof(S)) + (ANISO ? (unsigned)(RC::kSites * 8) : 0u);
-  if (threadIdx.x == 0) {
-    for (int r = 0; r < kTmR; ++r) mbar_init(&bars[r], 1);
-    *s_abort = 0;
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-  }
-  __syncthreads();
-  unsigned phase_bits = 0; // parity of every slot's next completion
+  if (threadIdx.x == 0) *s_abort = 0;
   const long long tiles = (long long)tg.ntx * tg.nty;
+  bool first_unit = true;
   for (long long unit = blockIdx.x; unit < tg.units; unit += gridDim.x) {
     const int tile = (int)(unit % tiles), zc = (int)(unit / tiles);
     const int x0 = (tile % tg.ntx) * kTmBX, y0 = (tile / tg.ntx) * kTmBY;
     const int k0 = zc * tg.zc, k1 = min(k0 + tg.zc, g.nz_loc);
+    const int np = k1 - k0 + 2; // planes of this unit: ring plane p <-> local plane k0 - 1 + p, slot p % R, use p / R
     const int i = x0 + tx;
     const int jj[kTmRows] = {y0 + ty, y0 + ty + kTmTY};
     const bool live[kTmRows] = {i < g.nx && jj[0] < g.ny, i < g.nx && jj[1] < g.ny};
@@ -171,27 +179,37 @@ k_lanczos_a_tm(const __grid_constant__ CUtensorMap tmx, const __grid_constant__ 
                                                      jj[0] == g.ny - 1 || jj[1] == 0);
     // box origin in tensor-map coordinates: the inner dimension counts doubles (complex = 2 per site)
     const int bx = (x0 - RX::XO) * W, by = y0 - 1;
-    auto issue = [&](int k) { // plane k (local index, may be k0-1 .. k1) into slot (k - k0 + 1) % R
-      const int slot = (k - k0 + 1) % kTmR;
-      mbar_expect_tx(&bars[slot], kBoxBytes);
-      tma_load_3d(xs + (size_t)slot * RX::kPad, &tmx, bx, by, k + tg.zoff, &bars[slot]);
-      if (ANISO) tma_load_3d(cs + (size_t)slot * RC::kPad, &tmc, x0 - RC::XO, by, k + tg.zoff, &bars[slot]);
+    auto issue = [&](int p, int slot) {
+      mbar_expect_tx(&full[slot], kBoxBytes);
+      tma_load_3d(xs + (size_t)slot * RX::kPad, &tmx, bx, by, k0 - 1 + p + tg.zoff, &full[slot]);
+      if (ANISO) tma_load_3d(cs + (size_t)slot * RC::kPad, &tmc, x0 - RC::XO, by, k0 - 1 + p + tg.zoff, &full[slot]);
     };
-    __syncthreads(); // the previous unit's reads of the ring are done
+    __syncthreads(); // the previous unit's reads of the ring and its arrivals are done
+    if (threadIdx.x == 0) { // fresh barriers per unit: the parity of plane p's completion is (p / R) & 1, no bookkeeping
+      for (int r = 0; r < R; ++r) {
+        if (!first_unit) { mbar_inval(&full[r]); mbar_inval(&empty[r]); }
+        mbar_init(&full[r], 1);
+        mbar_init(&empty[r], kThreads / 32);
+      }
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    first_unit = false;
+    __syncthreads();
+    constexpr int lead = PIPE ? R - 1 : 4; // planes issued up front
     if (threadIdx.x == 0) {
       fence_proxy_async();
-      for (int k = k0 - 1; k <= min(k0 + 2, k1); ++k) issue(k);
+      for (int p = 0; p < min(lead, np); ++p) issue(p, p);
     }
-    for (int q = 0; q < 2; ++q) { // planes k0-1 and k0 (slots 0, 1)
-      mbar_wait(&bars[q], (phase_bits >> q) & 1u, s_abort, status);
-      phase_bits ^= 1u << q;
-    }
+    mbar_wait(&full[0], 0u, s_abort, status); // planes k0-1 and k0
+    mbar_wait(&full[1], 0u, s_abort, status);
     const int sidx[kTmRows] = {(ty + 1) * RX::PX + tx + RX::XO, (ty + kTmTY + 1) * RX::PX + tx + RX::XO};
     const int cidx[kTmRows] = {(ty + 1) * RC::PX + tx + RC::XO, (ty + kTmTY + 1) * RC::PX + tx + RC::XO};
     long long idx0 = ((long long)k0 * g.ny + jj[0]) * g.nx + i;
     const long long rowskip = (long long)kTmTY * g.nx;
     for (int k = k0; k < k1; ++k, idx0 += g.plane) {
-      const int sm = (k - k0) % kTmR, sc = (k - k0 + 1) % kTmR, sp = (k - k0 + 2) % kTmR;
+      const int pc = k - k0 + 1; // ring plane of the centre; slots of planes pc-1, pc, pc+1:
+      const int sm = (pc - 1) % R, sc = pc % R, sp = (pc + 1) % R;
+      const unsigned par_p = (unsigned)((pc + 1) / R) & 1u; // parity of plane pc+1's completion
       const int kg = g.z0 + k;
       const bool edge = edge_xy || kg == 0 || kg == g.nz_glob - 1; // warp-uniform
       const S *xsm = xs + (size_t)sm * RX::kPad, *xsc = xs + (size_t)sc * RX::kPad, *xsp = xs + (size_t)sp * RX::kPad;
@@ -209,8 +227,14 @@ k_lanczos_a_tm(const __grid_constant__ CUtensorMap tmx, const __grid_constant__ 
 #pragma unroll
           for (int q = 0; q < kLd; ++q)
             if (on) v[r][q] = ld_stream((q == 0 ? cb : cb + cs0 + (size_t)(q - 1) * colstride) + idx);
+          if (tg.pf && on && k + tg.pf < k1) { // the same values of a later plane -> L2
+            const long long ipf = idx + (long long)tg.pf * g.plane;
+            if (j > 0) pf_l2(cm + ipf);
+#pragma unroll
+            for (int q = 0; q < kLd; ++q) pf_l2((q == 0 ? cb : cb + cs0 + (size_t)(q - 1) * colstride) + ipf);
+          }
         }
-        mbar_wait(&bars[sp], (phase_bits >> sp) & 1u, s_abort, status);
+        mbar_wait(&full[sp], par_p, s_abort, status);
 #pragma unroll
         for (int r = 0; r < kTmRows; ++r) {
           const long long idx = idx0 + r * rowskip;
@@ -228,11 +252,20 @@ k_lanczos_a_tm(const __grid_constant__ CUtensorMap tmx, const __grid_constant__ 
       };
       if (edge) step(std::true_type{});
       else step(std::false_type{});
-      phase_bits ^= 1u << sp;
-      __syncthreads(); // all reads of slot sm (plane k-1) are done: plane k+3 goes there, two steps ahead of its use
-      if (threadIdx.x == 0 && k + 3 <= k1) {
-        fence_proxy_async();
-        issue(k + 3);
+      if constexpr (PIPE) {
+        __syncwarp();
+        if ((threadIdx.x & 31) == 0) mbar_arrive(&empty[sm]); // this warp is done with plane pc-1
+        if (threadIdx.x == 0 && pc + R - 2 < np) {            // plane pc+R-2 goes where plane pc-2 was
+          if (pc >= 2) mbar_wait(&empty[(pc - 2) % R], (unsigned)((pc - 2) / R) & 1u, s_abort, status); // handed back one step ago
+          fence_proxy_async();
+          issue(pc + R - 2, (pc + R - 2) % R);
+        }
+      } else {
+        __syncthreads(); // all reads of plane pc-1 are done: plane pc+3 goes there, two steps ahead of its use
+        if (threadIdx.x == 0 && pc + 3 < np) {
+          fence_proxy_async();
+          issue(pc + 3, (pc + 3) % R);
+        }
       }
     }
   }
