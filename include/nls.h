@@ -219,6 +219,28 @@ int nls_memcpy_to_host(void *dst, const void *dev_src, size_t bytes);
 /* out[batch] */
 int nls_reduce(nls_handle h, int what, double *out);
 
+/* Allocation-free mass reduction.  NO COUNTERPART IN THE REFERENCE: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ *   dev_out[t] = cell * sum_i |dev_u[t * traj_stride + i]|^2,  i < n_sites, t < batch
+ * -- the NLS_RED_MASS value of nls_reduce (finalized_scripts/compare_utils_complex_2d.py:142-143) for a state the
+ * CALLER holds in device memory: no handle, no cudaMalloc / cudaFree / allocating library routine inside.  The per-CTA
+ * partial sums and the completion tickets of the grid reduction live in ONE file-scope static __device__ array
+ * (NLS_NOALLOC_SCRATCH_BYTES, held by every GPU that loads the library until exit), hence the limits:
+ * batch <= NLS_NOALLOC_MAX_BATCH, n_sites * batch <= NLS_NOALLOC_MAX_SITES; anything larger returns NLS_ERR_ARG
+ * with a message.  dev_u: complex128 (is_complex = 1) or double (0); traj_stride in elements (0 = n_sites);
+ * dev_out: `batch` doubles in device memory; stream: a cudaStream_t (NULL = the default stream); the call is
+ * stream-ordered (one memset node + one kernel node, capturable) and does not synchronise.
+ * All calls SHARE the scratch array, which keeps the last call's contents: the tickets are cleared at the start of
+ * every call; calls that overlap on the GPU (different streams, or several host threads on one device) RACE and must
+ * be serialised by the caller.  The first call on each device resolves the array's device address
+ * (cudaGetSymbolAddress): make it outside a capture. */
+#define NLS_NOALLOC_MAX_BATCH 256u
+#define NLS_NOALLOC_MAX_CTAS 4096u
+#define NLS_NOALLOC_MAX_SITES (1ull << 31)
+#define NLS_NOALLOC_SCRATCH_BYTES (NLS_NOALLOC_MAX_CTAS * 8u + NLS_NOALLOC_MAX_BATCH * 4u)
+int nls_reduce_mass_noalloc(int device, const void *dev_u, uint64_t n_sites, uint32_t batch, uint64_t traj_stride,
+                            int is_complex, double cell, double *dev_out, void *stream);
+
 /* Snapshot egress with on-device downsampling: the field (NLS_FIELD_U, or NLS_FIELD_V
  * for real equations) is resampled on the device to tnx x tny [x tnz] points per trajectory with the
  * launcher's `downsample_interpolation` (finalized_scripts/downsampling.py:68-104, 3D :215-258:

@@ -152,6 +152,7 @@ _SIGS = {
     "nls_csr_residual": (C.c_int, [_vp, _vp, _vp, _vp, C.c_uint32, C.c_uint64, C.c_int, C.c_int, _dp]),
     "nls_pointer_is_device": (C.c_int, [_vp]),
     "nls_memcpy_to_host": (C.c_int, [_vp, _vp, _sz]),
+    "nls_reduce_mass_noalloc": (C.c_int, [C.c_int, _vp, C.c_uint64, C.c_uint32, C.c_uint64, C.c_int, C.c_double, _vp, _vp]),
     "nls_generate_field": (C.c_int, [_vp, C.c_int, C.c_int32, _vp, C.c_uint32, C.c_int, _dp, C.c_double, C.c_double, C.c_double]),
     "nls_get_field_fft_resampled": (C.c_int, [_vp, C.c_int, C.c_uint32, C.c_uint32, _vp, _sz]),
     "nls_get_field_fft_resampled_async": (C.c_int, [_vp, C.c_int, C.c_uint32, C.c_uint32, _vp, _sz, _sz]),

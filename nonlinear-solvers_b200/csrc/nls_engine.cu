@@ -11,6 +11,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <unordered_map>
 #include <utility>
@@ -1843,6 +1844,86 @@ int nls_reduce(nls_handle e, int what, double *out) {
     if (what == NLS_RED_ENERGY && !e->cplx) cell *= 0.5; // energy_sge.py:14
     for (int b = 0; b < e->batch; ++b) out[b] *= cell;
   }
+  return NLS_OK;
+}
+
+// ---------------------------------------------------------------- allocation-free mass reduction (nls.h)
+// Scratch of the grid reduction in a file-scope device array instead of the handle's cudaMalloc'ed RedCtx buffers:
+// [0, kNaCtas) doubles = per-CTA partial sums, then kNaBatch unsigned completion tickets.  In HOST code the name
+// g_noalloc_scratch is only a stand-in for the symbol: its device address comes from cudaGetSymbolAddress, once per
+// device with that device current (noalloc_scratch_ptr), and is what the kernel is given.
+} // extern "C"
+namespace {
+constexpr unsigned kNaCtas = NLS_NOALLOC_MAX_CTAS, kNaBatch = NLS_NOALLOC_MAX_BATCH;
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NLS_NOALLOC_SCRATCH_BYTES];
+constexpr int kNaMaxDev = 64;
+unsigned char *g_noalloc_ptr[kNaMaxDev] = {};
+int g_noalloc_nsm[kNaMaxDev] = {};
+std::mutex g_noalloc_mu;
+
+// variant of k_reduce_state<S, NLS_RED_MASS> (nls_kernels.cuh) without Geom / handle: trajectory t at u + t * stride
+template <class S>
+__global__ void __launch_bounds__(kThreads)
+k_reduce_mass_noalloc(const S *__restrict__ u, long long n, long long stride, double cell, double *dst, RedCtx rc) {
+  const S *ub = u + (size_t)blockIdx.y * stride;
+  double acc[1] = {0.0};
+  for (long long idx = (long long)blockIdx.x * kThreads + threadIdx.x; idx < n; idx += (long long)gridDim.x * kThreads)
+    acc[0] += Sc<S>::abs2(ub[idx]);
+  acc[0] *= cell; // nls_reduce scales the total on the host; here every thread's partial sum is scaled (differs in the last bits only)
+  grid_reduce<1>(acc, rc, dst + blockIdx.y);
+}
+} // namespace
+extern "C" {
+
+int nls_reduce_mass_noalloc(int device, const void *dev_u, uint64_t n_sites, uint32_t batch, uint64_t traj_stride,
+                            int is_complex, double cell, double *dev_out, void *stream) {
+  if (!dev_u || !dev_out) return fail(NLS_ERR_ARG, "nls_reduce_mass_noalloc: null argument");
+  if (device < 0 || device >= kNaMaxDev) return fail(NLS_ERR_ARG, "nls_reduce_mass_noalloc: bad device ordinal");
+  if (n_sites == 0 || batch == 0) return fail(NLS_ERR_ARG, "nls_reduce_mass_noalloc: empty input");
+  if (batch > kNaBatch)
+    return fail(NLS_ERR_ARG, "nls_reduce_mass_noalloc: batch " + std::to_string(batch) + " exceeds NLS_NOALLOC_MAX_BATCH = " +
+                                 std::to_string(kNaBatch) + " (static scratch, no allocation)");
+  if (n_sites > NLS_NOALLOC_MAX_SITES / batch)
+    return fail(NLS_ERR_ARG, "nls_reduce_mass_noalloc: n_sites * batch = " + std::to_string(n_sites) + " * " + std::to_string(batch) +
+                                 " exceeds NLS_NOALLOC_MAX_SITES = " + std::to_string(NLS_NOALLOC_MAX_SITES));
+  if (traj_stride == 0) traj_stride = n_sites;
+  if (traj_stride < n_sites) return fail(NLS_ERR_ARG, "nls_reduce_mass_noalloc: traj_stride < n_sites");
+  CU(cudaSetDevice(device));
+  unsigned char *scratch;
+  int nsm;
+  {
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    if (!g_noalloc_ptr[device]) { // set-up, once per device, with that device current
+      unsigned char *p = nullptr;
+      CU(cudaGetSymbolAddress((void **)&p, g_noalloc_scratch));
+      if (!p) return fail(NLS_ERR_CUDA, "nls_reduce_mass_noalloc: cudaGetSymbolAddress returned a null address");
+      int n = 0;
+      CU(cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, device));
+      g_noalloc_nsm[device] = n > 0 ? n : 148;
+      g_noalloc_ptr[device] = p;
+    }
+    scratch = g_noalloc_ptr[device];
+    nsm = g_noalloc_nsm[device];
+  }
+  RedCtx rc;
+  rc.partials = (double *)scratch;
+  rc.tickets = (unsigned *)(scratch + (size_t)kNaCtas * 8);
+  rc.slab = nullptr;
+  // CTAs per trajectory: one wave of 8 CTAs/SM over the batch, within the scratch's kNaCtas partial slots
+  long long per = (8LL * nsm) / batch;
+  const long long want = (long long)((n_sites + kThreads - 1) / kThreads);
+  if (per > want) per = want;
+  if (per > (long long)(kNaCtas / batch)) per = kNaCtas / batch;
+  if (per < 1) per = 1;
+  cudaStream_t st = (cudaStream_t)stream;
+  // the tickets must start at zero (the array keeps whatever the last -- possibly aborted -- call left there)
+  CU(cudaMemsetAsync(rc.tickets, 0, (size_t)batch * sizeof(unsigned), st));
+  const dim3 grid((unsigned)per, batch);
+  if (is_complex)
+    k_reduce_mass_noalloc<double2><<<grid, kThreads, 0, st>>>((const double2 *)dev_u, (long long)n_sites, (long long)traj_stride, cell, dev_out, rc);
+  else
+    k_reduce_mass_noalloc<double><<<grid, kThreads, 0, st>>>((const double *)dev_u, (long long)n_sites, (long long)traj_stride, cell, dev_out, rc);
+  CU(cudaGetLastError());
   return NLS_OK;
 }
 
