@@ -20,7 +20,9 @@
 using namespace nls;
 
 namespace {
-constexpr int kTmDefaultPipe = 0, kTmDefaultPrefetch = 0; // tensor-map pass A: per-warp ring hand-back, column prefetch lead (planes)
+// tensor-map pass A: per-warp ring hand-back (measured slower: C3 9.37 -> 10.03 ms/step, profiles/r02n_*; opt-in) and the
+// L2 prefetch lead of the column values in planes (2: C3 9.37 -> 9.26, C5 47.46 -> 46.84)
+constexpr int kTmDefaultPipe = 0, kTmDefaultPrefetch = 2;
 constexpr int kDefaultPrefetch = 1; // L2 prefetch lead of the flat Lanczos passes, in grid sweeps (Geom::pf)
 constexpr size_t kDefaultColPad = 0; // see col_pad_bytes()
 thread_local std::string g_err;

@@ -1,7 +1,7 @@
 #!/bin/bash
 # GPU session r02-14 (1 GPU): tensor-map pass A version 4 knobs -- per-warp ring hand-back through EMPTY mbarriers
 # (NLS_TM_PIPE=1, 6 plane slots, no CTA barrier per plane) and L2 prefetch of the column values (NLS_TM_PREFETCH=planes):
-# parity under each, then A/B on C3 / C5; split closing pass B once more on the final register allocation.
+# parity under each, then A/B on C3 / C5.
 set -x
 mkdir -p gpurun_out
 for pipe in 0 1; do
@@ -27,7 +27,6 @@ for wl in c3 c5; do
   run pipe_pf2 $wl NLS_TM_PIPE=1 NLS_TM_PREFETCH=2
   run pf2 $wl NLS_TM_PREFETCH=2
   run pipe_body6 $wl NLS_TM_PIPE=1 NLS_TM_BODY=6
-  run bsplit $wl NLS_B_SPLIT=1
 done
 NLS_TM_PIPE=1 timeout 300 python bench.py --workload c3 --no-others --no-cpu --steps 1 --warmup 3 > gpurun_out/r02n_plain_c3.log 2>&1 && \
 NLS_TM_PIPE=1 timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_lanczos_a_tm -s 24 -c 4 -o gpurun_out/r02n_c3_lanczos_a_tm_v4pipe python bench.py --workload c3 --no-others --no-cpu --steps 1 --warmup 3 > gpurun_out/r02n_ncu_tm.log 2>&1
