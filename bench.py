@@ -68,7 +68,7 @@ WORKLOADS = {
     # (G = 8 is the full 1024^3 of BASELINE configs[4]; the full cube does not fit fewer than 2 GPUs)
     "c5": dict(desc="NLSE 3D cubic 1024x1024x(128*G) complex128, z-slabs over G GPUs, in-kernel NVLink halo + "
                     "scalar exchange, m=10 (BASELINE configs[4] at G=8)",
-               n=1024, dim=3, L=10.0, eq=EQ.NLSE_CUBIC, integ=INT.SS2, m=10, dt=2e-4, seg=5, slab_planes=128,
+               n=1024, dim=3, L=10.0, eq=EQ.NLSE_CUBIC, integ=INT.SS2, m=10, dt=2e-4, seg=10, slab_planes=128,
                short=(5, 3), cpu_n=128),
     # STRONG scaling of the slab decomposition: the C3 grid (256^3, cubic-quintic, div(c grad), m=12) cut into
     # G z-slabs of 256/G planes; total work fixed, so the cross-GPU reductions and halo planes show undiluted

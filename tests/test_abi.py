@@ -51,3 +51,18 @@ def test_sass_is_sm100(lib):
     import subprocess
     out = subprocess.run(["cuobjdump", "-lelf", nls_b200.library_path()], capture_output=True, text=True).stdout
     assert "sm_100a" in out
+
+
+def test_noalloc_entry_point_validates_before_touching_cuda(lib):
+    """nls_reduce_mass_noalloc rejects sizes beyond its static scratch with NLS_ERR_ARG and a message -- checked before
+    any CUDA call, so this runs without a GPU (the compute path: tests/test_zz_no_alloc.py, -m gpu)"""
+    buf = (C.c_double * 8)()
+    p = C.cast(buf, C.c_void_p)
+    assert lib.nls_reduce_mass_noalloc(0, p, 4, 257, 0, 0, 1.0, p, None) == -1
+    assert b"NLS_NOALLOC_MAX_BATCH" in lib.nls_last_error()
+    assert lib.nls_reduce_mass_noalloc(0, p, (1 << 31) + 1, 1, 0, 1, 1.0, p, None) == -1
+    assert b"NLS_NOALLOC_MAX_SITES" in lib.nls_last_error()
+    assert lib.nls_reduce_mass_noalloc(0, p, 16, 2, 8, 0, 1.0, p, None) == -1  # traj_stride < n_sites
+    assert lib.nls_reduce_mass_noalloc(0, None, 4, 1, 0, 0, 1.0, p, None) == -1
+    hdr = open(os.path.join(ROOT, "include", "nls.h")).read()
+    assert "NLS_NOALLOC_MAX_BATCH 256u" in hdr and "no counterpart in the reference" in hdr.lower()
