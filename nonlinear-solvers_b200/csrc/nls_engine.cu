@@ -20,6 +20,7 @@
 using namespace nls;
 
 namespace {
+constexpr long long kPkMinSites = 64; // persistent kernel: minimum sites per CTA (pk_setup)
 // tensor-map pass A: per-warp ring hand-back (measured slower: C3 9.37 -> 10.03 ms/step, profiles/r02n_*; opt-in) and the
 // L2 prefetch lead of the column values in planes (2: C3 9.37 -> 9.26, C5 47.46 -> 46.84)
 constexpr int kTmDefaultPipe = 0, kTmDefaultPrefetch = 2;
@@ -766,7 +767,12 @@ void pk_setup(nls_engine *e) {
   cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
   if (!coop || nsm <= 0 || nsm > kPkPartStride) return;
   long long csz = (e->g.n + nsm - 1) / nsm;
-  if (csz < 64) csz = 64;
+  // Fewer, larger CTAs on small grids were tried and lose: a grid-wide round costs 2.2 us + 0.23 us per reduced value at
+  // 148 CTAs (profiles/r02d_allreduce_microbench.log) and gets cheaper with fewer CTAs, but the site loops between the
+  // rounds are L2-latency chains that grow faster: C1 0.100 ms/step at 148 CTAs, 0.108 at 74, 0.125 at 37, 0.165 at 16
+  // (profiles/r02o_pk_min_csz_sweep.txt).  NLS_PK_MIN_CSZ (minimum sites per CTA) stays as the tuning knob.
+  static const long long min_csz = []() { const char *v = getenv("NLS_PK_MIN_CSZ"); const long long n = v ? atoll(v) : kPkMinSites; return n >= 64 ? n : 64; }();
+  if (csz < min_csz) csz = min_csz;
   const int ncta = (int)((e->g.n + csz - 1) / csz);
   const size_t smem = pk_smem_bytes(e->esz, csz, e->g.nx, e->m, sv ? 2 * e->g.nx : 0);
   if (smem > (size_t)smem_max) return;

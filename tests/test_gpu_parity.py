@@ -561,3 +561,27 @@ def test_tensor_map_pass_matches_flat_pass_and_oracle(orc, dims, eq, lap, m):
         o.set(FIELD.V, np.zeros_like(u0))
     o.step(1e-3, 5)
     assert rel_l2(outs[0][3], o.get()) < 1e-11
+
+
+def test_tensor_map_pass_is_the_default_for_complex_3d_only():
+    """complex 3D single-trajectory handles take the tensor-map pass A without a flag; real ones need NLS_FLAG_TMAP;
+    NLS_FLAG_NO_TMAP forces the flat pass; 2D grids and batches never use it"""
+    def launches(dims, eq, flags=0, batch=1):
+        real = eq >= EQ.SGE
+        d = Desc.make(*dims, dx=0.2, equation=eq, integrator=INT.GAUTSCHI if real else INT.SS2, krylov_m=6, dt=1e-3, batch=batch,
+                      flags=flags | nls_b200.FLAG_NO_PERSISTENT)
+        e = Engine(d)
+        e.set(FIELD.M, np.ones(d.n))
+        u0 = 0.1 * randn(d, 7, batch)
+        e.set(FIELD.U, u0)
+        if real:
+            e.set(FIELD.V, np.zeros_like(u0))
+        e.step(1e-3, 1)
+        e.get()
+        return e.tmap_launch_count()
+    assert launches((32, 24, 16), EQ.NLSE_CUBIC) > 0
+    assert launches((32, 24, 16), EQ.NLSE_CUBIC, nls_b200.FLAG_NO_TMAP) == 0
+    assert launches((32, 24, 16), EQ.KGE) == 0
+    assert launches((32, 24, 16), EQ.KGE, nls_b200.FLAG_TMAP) > 0
+    assert launches((32, 24), EQ.NLSE_CUBIC) == 0
+    assert launches((32, 24, 16), EQ.NLSE_CUBIC, batch=2) == 0
