@@ -66,6 +66,7 @@ struct Geom {
   double sc;     // op_sign / (dx*dy)   [2D]   or   op_sign / (dx*dx)   [3D]
   int pf;        // grid sweeps the flat Lanczos passes prefetch ahead into L2 (0 = off; pf_l2 below)
   int pf_first;  // the same for the stencil-carrying flat pass A
+  int pf_fin;    // the same for the recombination kernel (k_nlse_finish)
 };
 
 // The flat passes are one batch of loads per thread and grid sweep: a sweep lasts one loaded DRAM round trip

@@ -1079,8 +1079,14 @@ int nls_create(const nls_desc *desc, nls_handle *out) {
   // (flat C5 66.4 ms/step without, 72.1 with; 2D C4: 6.98 without, 6.33 with -- profiles/r02m_bench_ab.jsonl).
   g.pf = kDefaultPrefetch;
   g.pf_first = g.dim3 ? 0 : kDefaultPrefetch;
+  // the recombination kernel is the exception too: its prefetch re-fetches a quarter of the columns from DRAM (C3: 4.60
+  // GB read per launch with, 3.57 = algorithmic without; 855 -> 662 us; C3 9.60 -> 9.35, C5 48.4 -> 47.7 ms/step,
+  // profiles/r02q_*): off by default, NLS_PREFETCH_FINISH=1 turns it on
+  g.pf_fin = 0;
   if (const char *pf = getenv("NLS_PREFETCH")) g.pf = g.pf_first = atoi(pf);
   if (const char *pf = getenv("NLS_PREFETCH_FIRST")) g.pf_first = atoi(pf);
+  if (const char *pf = getenv("NLS_PREFETCH_FINISH")) g.pf_fin = atoi(pf);
+  if (g.pf_fin < 0 || g.pf_fin > 8) g.pf_fin = 0;
   if (g.pf < 0 || g.pf > 8) g.pf = 0;
   if (g.pf_first < 0 || g.pf_first > 8) g.pf_first = 0;
   cudaDeviceGetAttribute(&e->nsm, cudaDevAttrMultiProcessorCount, d.device);

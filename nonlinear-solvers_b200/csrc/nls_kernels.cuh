@@ -736,7 +736,7 @@ k_nlse_finish(Geom g, const double2 *__restrict__ start, const double2 *__restri
   double2 *un = traj(uout, g), *rb = traj(rho, g);
   const double *mb = mf + g.halo;
   double acc[1] = {0.0};
-  const long long pfd = (long long)g.pf * gridDim.x * kThreads;
+  const long long pfd = (long long)g.pf_fin * gridDim.x * kThreads;
   for (long long idx = (long long)blockIdx.x * kThreads + threadIdx.x; idx < g.n;
        idx += (long long)gridDim.x * kThreads) {
     if (pfd && idx + pfd < g.n) { // the m basis columns of this thread's next sweep -> L2 (pf_l2, nls_device.cuh)
