@@ -12,8 +12,15 @@
 // once per tile (+ its halo ring, x1.29), the neighbour values are shared-memory reads, and the 64-bit index
 // arithmetic leaves the inner loop.  The basis columns for the dots and the store of w stream straight through
 // registers as before; every thread handles TWO sites of a plane (rows ty and ty+4) so that twice as many column
-// loads are in flight per barrier (version 1 -- one site per thread, 64 x 4 tiles -- was latency-bound: long-scoreboard
-// stall 12 per issue at 16 warps/SM, 2.5 TB/s; ncu capture profiles/r02i_ncu_full_c5_k_lanczos_a_tm_v1.txt).
+// loads are in flight per barrier.  Measured history (C3 / C5, DESIGN.md section 3 has the table):
+//   v1  one site per thread, 64 x 4 tiles: latency-bound (long-scoreboard 12 per issue), 2.2-2.4 TB/s -- slower than flat
+//       (profiles/r02j_ncu_full_c3_pass_a_tm_v1_vs_flat.txt);
+//   v2  two sites per thread, column loads before the mbarrier wait: 3.7-4.3 TB/s, issue-bound (215 M warp instructions);
+//   v3  warp-uniform interior / boundary paths (interior warps carry no flag logic) + compile-time column roles (MODE):
+//       119 M instructions, 4.5-5.5 TB/s with div(c grad), 5.8-6.6 TB/s uniform; C3 10.6 -> 9.4, C5 61.7 -> 47.7 ms/step
+//       (profiles/r02l_ncu_full_c3_pass_a_tm_v3.txt, r02m_launches_c3.csv, r02p_launches_c5.csv): the default;
+//   v4  knobs: L2 prefetch of the column values two planes ahead (default, -1.2 %), per-warp ring hand-back through
+//       EMPTY mbarriers (PIPE; removes the CTA barrier stall but loses to its own shared-memory footprint: opt-in).
 // The rows of the operator -- incl. the reference's quirks (ring diagonal, y-neighbour test on the flat index:
 // laplacians.hpp:124-148, :181-210) -- are those of stencil_vals (nls_device.cuh), the flat kernel's arithmetic.
 #pragma once
