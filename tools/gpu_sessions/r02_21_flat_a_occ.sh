@@ -1,5 +1,6 @@
 #!/bin/bash
 # GPU session r02-21 (1 GPU): stencil-carrying flat pass A with the grid dimension compiled in (NLS_A_SPEC=1) and with the
+# NOTE: the two variants measured here lost (profiles/r02u_flat_pass_a_occupancy_ab.txt) and their knobs (NLS_A_SPEC, NLS_A_OCC) were removed again.
 # 3-CTAs/SM register allocation for its narrow chunks (NLS_A_OCC=3): parity subset under the knob, then C4 A/B.
 set -x
 mkdir -p gpurun_out
