@@ -48,7 +48,11 @@ def lz_model(m):
 
 def lz_impl(m):
     """vector passes of one Lanczos run as IMPLEMENTED: two fused passes per iteration over an un-normalised
-    basis, pass A (stencil + all dots) j+2, pass B (block update + norm) j+3 -> sum_j (2j+5) = (m-1)(m+3)."""
+    basis, pass A (stencil + all dots) j+2, pass B (block update + norm) j+3 -> sum_j (2j+5) = (m-1)(m+3).
+    With NLS_REORTH=3 in the environment (Gram-delayed re-orthogonalisation, multi-kernel path, m <= 13) the handles of
+    this process run a 3-pass stencil sweep + a (j+3)-pass update per iteration: sum_j (j+6) = (m-1)(m+10)/2."""
+    if os.environ.get("NLS_REORTH") == "3" and m <= 13:
+        return (m - 1) * (m + 10) // 2
     return (m - 1) * (m + 3)
 
 
@@ -419,7 +423,7 @@ def measure(cx, name, w, K, W, repeats, sample_clocks):
             "traffic_source": traffic_src, "peak_source": peak_src,
             "bytes_per_site_step": bpss, "bytes_per_site_step_survey_model": bpss_model,
             "frac_survey_model": bpss_model / bpss * achieved / peak,
-            "model": f"{bpss:.0f} algorithmic B/site-step of the algorithm executed ((m-1)(m+3) vector passes per Lanczos run "
+            "model": f"{bpss:.0f} algorithmic B/site-step of the algorithm executed ({lz_impl(w['m'])} vector passes per Lanczos run "
                      f"+ recombination/pointwise tail; SURVEY 8d's table counts {bpss_model:.0f}) x site-steps/s of one GPU; "
                      f"{launches // max(K, 1)} kernels/step"}
     if traffic is not None:

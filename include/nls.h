@@ -89,6 +89,13 @@ enum {
 enum {
   NLS_REORTH_FULL = 0, /* alpha step + one block-dot + one block-update pass (reference: MGS sweep) */
   NLS_REORTH_NONE = 1, /* plain 3-term recurrence (not the reference algorithm; opt-in) */
+  NLS_REORTH_GRAM = 3, /* Gram-delayed full re-orthogonalisation (opt-in, multi-kernel path, m <= 13; larger m fall back to
+                        * NLS_REORTH_FULL): per iteration ONE narrow stencil pass that writes the raw vector L v_j and
+                        * measures only its products with v_j and v_{j-1}, and ONE update pass over all columns whose
+                        * projections on the older columns are derived from the Gram entries of the two newest columns
+                        * through the three-term recurrence -- j + 6 vector passes per iteration instead of 2j + 5.
+                        * Tracks the reference's MGS sweep at rounding level (tests/test_single_sweep_prototype.py,
+                        * tests/test_gpu_parity.py::test_gram_delayed_*) */
   NLS_REORTH_MGS = 2   /* the reference's sequential modified Gram-Schmidt sweep, operation for operation
                         * (eigen_krylov_complex.hpp:28-38): one launch per dot product, multi-kernel path only.
                         * Slow by construction; a bisecting tool that separates re-orthogonalisation rounding of

@@ -31,6 +31,9 @@ template <> struct Sc<double> {
   // acc[0..W) += conj(a) * b
   __device__ static void dot_acc(double *acc, double a, double b) { acc[0] = fma(a, b, acc[0]); }
   __device__ static double from(const double *p) { return p[0]; }
+  __device__ static double conj(double a) { return a; }
+  __device__ static double real(double r) { return r; }
+  __device__ static double re(double a) { return a; }
 };
 template <> struct Sc<double2> {
   static constexpr int W = 2;
@@ -50,6 +53,9 @@ template <> struct Sc<double2> {
     acc[1] = fma(a.x, b.y, fma(-a.y, b.x, acc[1]));
   }
   __device__ static double2 from(const double *p) { return make_double2(p[0], p[1]); }
+  __device__ static double2 conj(double2 a) { return make_double2(a.x, -a.y); }
+  __device__ static double2 real(double r) { return make_double2(r, 0.0); }
+  __device__ static double re(double2 a) { return a.x; }
 };
 
 // ---------------------------------------------------------------- geometry
@@ -67,6 +73,7 @@ struct Geom {
   int pf;        // grid sweeps the flat Lanczos passes prefetch ahead into L2 (0 = off; pf_l2 below)
   int pf_first;  // the same for the stencil-carrying flat pass A
   int pf_fin;    // the same for the recombination kernel (k_nlse_finish)
+  int raw;       // pass A writes the RAW vector L column_j (no 1/beta, no recurrence term): NLS_REORTH_GRAM
 };
 
 // The flat passes are one batch of loads per thread and grid sweep: a sweep lasts one loaded DRAM round trip

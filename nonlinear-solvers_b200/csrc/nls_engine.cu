@@ -398,7 +398,7 @@ void tm_setup(nls_engine *e) {
 // (*cnt columns from c0) so that the role of every column is a compile-time fact (nls_tmap.cuh): all of c0..j when
 // they fit (TM_TAIL; TM_SELF for one column), else the leading columns below j-1 (TM_BODY).
 template <class S, bool ANISO>
-bool launch_a_tm(nls_engine *e, const S *start, S *V, int j, int c0, int cap, int *cnt, double *scal) {
+bool launch_a_tm(nls_engine *e, const S *start, S *V, int j, int c0, int cap, int *cnt, double *scal, bool raw = false) {
   if (!e->tm_ok) return false;
   if (cap > kTmMaxNC) cap = kTmMaxNC;
   const int total = j + 1 - c0;
@@ -421,6 +421,7 @@ bool launch_a_tm(nls_engine *e, const S *start, S *V, int j, int c0, int cap, in
   const void *fn = nc >= 1 ? tm_kernel<S, ANISO>(mode, nc, pipe) : nullptr;
   if (!fn) return false;
   Geom g = e->g;
+  g.raw = raw ? 1 : 0;
   const S *cj = j == 0 ? start : V + (size_t)(j - 1) * e->colstride; // base of column j (halo included)
   const CUtensorMap *tmx = nullptr, *tmc = nullptr;
   if (!tm_get(e, cj, (int)(sizeof(S) / 8), &tmx)) return false;
@@ -462,9 +463,33 @@ void lanczos_t(nls_engine *e, const S *start, double *scal) {
   const dim3 gr = e->grid();
   S *V = (S *)e->V;
   constexpr int kNC = 12; // columns per launch
+  // NLS_REORTH_GRAM: one narrow stencil pass S(j) (raw r_j = L column_j, true dots with columns j-1 and j only) and one
+  // update pass U(j+1) over all columns whose older projections come from Gram entries (lanczos_b_body<GDR>): j + 6
+  // vector passes per iteration instead of 2j + 5.  All columns must fit one closing chunk (m <= kNC + 1).
+  const bool gdr = e->d.reorth == NLS_REORTH_GRAM && m - 1 <= kNC;
+  for (int j = 0; gdr && j < m - 1; ++j) {
+    const int c0 = j > 0 ? j - 1 : 0, total = j + 1 - c0;
+    int cnt = 0;
+    if (!launch_a_tm<S, ANISO>(e, start, V, j, c0, 2, &cnt, scal, true)) {
+      Geom graw = e->g;
+      graw.raw = 1;
+      LAUNCH(e, (k_lanczos_a<S, ANISO, 2, true>), gr, graw, start, V, e->colstride, j, c0, total, e->cf, scal, e->rc);
+    }
+    const Halo<S> hp = halo_for<S>(e, V + (size_t)j * e->colstride);
+#define LG(NC) LAUNCH(e, (k_lanczos_b_gdr<S, NC>), gr, e->g, start, V, e->colstride, j, 0, j + 1, scal, e->rc, hp)
+    if (j + 1 <= 2) LG(2);
+    else if (j + 1 <= 4) LG(4);
+    else if (j + 1 <= 6) LG(6);
+    else if (j + 1 <= 8) LG(8);
+    else if (j + 1 <= 10) LG(10);
+    else LG(12);
+#undef LG
+  }
+  if (gdr) return;
+  const int reorth = e->d.reorth == NLS_REORTH_GRAM ? NLS_REORTH_FULL : e->d.reorth; // m too large for one chunk: two-pass form
   for (int j = 0; j < m - 1; ++j) {
     // columns taking part in the orthogonalisation: all of 0..j (reference), or only j (3-term)
-    const int c0 = e->d.reorth != NLS_REORTH_FULL ? j : 0;
+    const int c0 = reorth != NLS_REORTH_FULL ? j : 0;
     // pass A chunks: the stencil-carrying first chunk of a complex sweep takes at most kFirst columns;
     // beyond that the 128-register budget of 2 CTAs/SM costs more than re-reading w once in a second,
     // dots-only chunk.  Measured on B200 (profiles/r01f_firstcap.txt): div(c grad) stencil 6 (C3 12.0 ->
@@ -494,7 +519,7 @@ void lanczos_t(nls_engine *e, const S *start, double *scal) {
       else LA(12);
 #undef LA
     }
-    if (e->d.reorth == NLS_REORTH_MGS) { // sequential sweep of the reference, one dot per launch (k_lanczos_mgs)
+    if (reorth == NLS_REORTH_MGS) { // sequential sweep of the reference, one dot per launch (k_lanczos_mgs)
       const Halo<S> none{nullptr, nullptr};
       for (int i = 0; i <= j; ++i) // subtract the previous projection (first: the alpha term), dot with column i
         LAUNCH(e, (k_lanczos_mgs<S, false>), gr, e->g, start, V, e->colstride, j, i == 0 ? j : i - 1, i, i == 0 ? 1 : 0, scal, e->rc, none);
@@ -1054,8 +1079,11 @@ int nls_create(const nls_desc *desc, nls_handle *out) {
   if (d.device < 0 || d.device >= ndev) return fail(NLS_ERR_CUDA, "no such CUDA device (there is no CPU fallback)");
   CU(cudaSetDevice(d.device));
 
+  if (d.reorth < NLS_REORTH_FULL || d.reorth > NLS_REORTH_GRAM) return fail(NLS_ERR_ARG, "bad reorth mode");
   nls_engine *e = new nls_engine;
   e->d = d;
+  if (const char *ro = getenv("NLS_REORTH")) // tuning knob (bench A/B): handles asking for the default take this mode
+    if (d.reorth == NLS_REORTH_FULL && atoi(ro) >= NLS_REORTH_FULL && atoi(ro) <= NLS_REORTH_GRAM) e->d.reorth = atoi(ro);
   e->cplx = cplx;
   e->W = cplx ? 2 : 1;
   e->esz = cplx ? 16 : 8;

@@ -27,7 +27,9 @@ constexpr int kOffNrm2 = 0;
 constexpr int kOffAlpha = 65;
 constexpr int kOffH = 193;
 constexpr int kOffG = 328;  // g[i] = column_i^H column_j of the current iteration (W doubles each)
-constexpr int kScalStride = 456;
+constexpr int kOffG2 = 456; // NLS_REORTH_GRAM: the Gram entries of the two newest columns alternate between g and g2
+constexpr int kScalStride = 584;
+__device__ __host__ __forceinline__ int gram_off(int j) { return (j & 1) ? kOffG2 : kOffG; } // Gram entries of column j
 constexpr int kCoefStride = 2 * kMaxM; // doubles per coefficient vector
 
 // arrays hold [batch][stride] scalars with `halo` ghost elements in front of site 0
@@ -103,6 +105,7 @@ k_lanczos_a(Geom g, const S *__restrict__ start, S *__restrict__ V, size_t colst
     const double bj = sqrt(sb[kOffNrm2 + j]);
     inv = 1.0 / bj;
     cmul = j > 0 ? -bj / sqrt(sb[kOffNrm2 + j - 1]) : 0.0; // -beta_j * (1/beta_{j-1})
+    if (g.raw) { inv = 1.0; cmul = 0.0; }                   // w = L column_j as it is (NLS_REORTH_GRAM)
   }
   double acc[NC * T::W];
 #pragma unroll
@@ -237,7 +240,14 @@ k_lanczos_a3(Geom g, March mc, const S *__restrict__ start, S *__restrict__ V, s
 }
 
 // columns [i0, i0+cnt).  LAST: ||w||^2 -> nrm2[j+1], T(j,j) -> alpha[j], halo push of column j+1.
-template <class S, int NC, bool LAST>
+// GDR (NLS_REORTH_GRAM, closing chunk holding ALL columns 0..j): the column slot holds the RAW vector r = L column_j and
+// only s_j = column_j^H r and s_{j-1} = column_{j-1}^H r were measured (k_lanczos_a* with Geom::raw).  The update is
+//   column_{j+1} = r / beta_j - (beta_j / beta_{j-1}) column_{j-1} - sum_i h_i column_i
+// with the projections on the older columns derived from the Gram entries g1 of column_j and g0 of column_{j-1} through
+// the recurrence L column_i = beta_i (column_{i+1} - cmul_i column_{i-1} + (alpha_i / beta_i) column_i):
+//   column_i^H w = (beta_i / beta_j)(g1_{i+1} + (alpha_i / beta_i) g1_i - cmul_i g1_{i-1}) + cmul_j g0_i      (i <= j-2)
+// (tools/prototypes/single_sweep_lanczos.py: gram_delayed; tests/test_single_sweep_prototype.py).
+template <class S, int NC, bool LAST, bool GDR = false>
 __device__ __forceinline__ void lanczos_b_body(const Geom &g, const S *__restrict__ start, S *__restrict__ V, size_t colstride, int j,
                                                int i0, int cnt, double *scal, const RedCtx &rc, const Halo<S> &hp) {
   using T = Sc<S>;
@@ -246,7 +256,37 @@ __device__ __forceinline__ void lanczos_b_body(const Geom &g, const S *__restric
   const S *cb = traj(colptr<S>(start, V, colstride, i0), g);
   const size_t cs0 = i0 == 0 ? (size_t)((V + 0) - start) : colstride;
   __shared__ S h[NC];
-  if ((int)threadIdx.x < NC) { // coefficient of column i: (alpha v_j + h_i v_i) in un-normalised form
+  __shared__ double s_gdr[2]; // GDR: 1 / beta_j, Re s_j
+  if (GDR && (int)threadIdx.x < NC) {
+    constexpr int W = T::W;
+    const int ci = threadIdx.x; // i0 == 0
+    const double *g1 = sb + gram_off(j), *g0 = sb + gram_off(j - 1);
+    const double nj = sb[kOffNrm2 + j], bj = sqrt(nj), inv = 1.0 / bj;
+    const double nm = j > 0 ? sb[kOffNrm2 + j - 1] : 1.0;
+    const double cmul = j > 0 ? -bj / sqrt(nm) : 0.0;
+    // column_k^H column_j for k <= j
+    auto gj = [&](int k) -> S { return k < j ? T::from(g1 + k * W) : T::real(nj); };
+    S sj = T::mulr(T::from(sb + kOffH + j * W), inv);
+    if (j > 0) sj = T::add(sj, T::mulr(T::conj(T::from(g1 + (j - 1) * W)), cmul));
+    S hv = T::zero();
+    if (ci < cnt) {
+      S si;
+      if (ci == j) si = sj;
+      else if (ci == j - 1) si = T::add(T::mulr(T::from(sb + kOffH + ci * W), inv), T::real(cmul * nm));
+      else {
+        const double ni = sb[kOffNrm2 + ci], bi = sqrt(ni);
+        S est = T::add(gj(ci + 1), T::mulr(gj(ci), sb[kOffAlpha + ci * W] / bi));
+        if (ci > 0) est = T::sub(est, T::mulr(gj(ci - 1), -bi / sqrt(sb[kOffNrm2 + ci - 1])));
+        si = T::add(T::mulr(est, bi * inv), T::mulr(T::from(g0 + ci * W), cmul));
+      }
+      if (ci < j) si = T::sub(si, T::mulr(T::from(g1 + ci * W), T::re(sj) / nj));
+      hv = T::mulr(si, 1.0 / sb[kOffNrm2 + ci]);
+      if (ci == j - 1) hv = T::sub(hv, T::real(cmul)); // the recurrence term rides on column j-1's coefficient
+    }
+    h[ci] = hv;
+    if (ci == 0) { s_gdr[0] = inv; s_gdr[1] = T::re(sj); }
+  }
+  if (!GDR && (int)threadIdx.x < NC) { // coefficient of column i: (alpha v_j + h_i v_i) in un-normalised form
     const int i = threadIdx.x;
     S hv = T::zero();
     if (i < cnt) {
@@ -281,6 +321,7 @@ __device__ __forceinline__ void lanczos_b_body(const Geom &g, const S *__restric
       for (int i = 0; i < NC; ++i)
         if (i < cnt) v[i] = (i == 0 ? cb : cb + cs0 + (size_t)(i - 1) * colstride)[idx];
       S wv = wc[idx];
+      if (GDR) wv = T::mulr(wv, s_gdr[0]);
 #pragma unroll
       for (int i = 0; i < NC; ++i)
         if (i < cnt) wv = T::sub(wv, T::mul(h[i], v[i]));
@@ -296,9 +337,16 @@ __device__ __forceinline__ void lanczos_b_body(const Geom &g, const S *__restric
   }
   if (LAST) {
     if (blockIdx.x == 0 && threadIdx.x == 0) // T(j,j) = Re(v_j^H w) = Re s_j / beta_j
-      sb[kOffAlpha + j * T::W] = sb[kOffH + j * T::W] / sqrt(sb[kOffNrm2 + j]);
-    grid_reduce2s<KA - 1>(acc, rc, sb + kOffG + i0 * T::W, sb + kOffNrm2 + j + 1);
+      sb[kOffAlpha + j * T::W] = (GDR ? s_gdr[1] : sb[kOffH + j * T::W]) / sqrt(sb[kOffNrm2 + j]);
+    grid_reduce2s<KA - 1>(acc, rc, sb + (GDR ? gram_off(j + 1) : kOffG) + i0 * T::W, sb + kOffNrm2 + j + 1);
   }
+}
+
+template <class S, int NC>
+__global__ void __launch_bounds__(kThreads, 2)
+k_lanczos_b_gdr(Geom g, const S *__restrict__ start, S *__restrict__ V, size_t colstride, int j, int i0,
+                int cnt, double *scal, RedCtx rc, Halo<S> hp) {
+  lanczos_b_body<S, NC, true, true>(g, start, V, colstride, j, i0, cnt, scal, rc, hp);
 }
 
 template <class S, int NC, bool LAST>

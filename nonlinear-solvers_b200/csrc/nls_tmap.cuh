@@ -163,8 +163,8 @@ k_lanczos_a_tm(const __grid_constant__ CUtensorMap tmx, const __grid_constant__ 
   const size_t cs0 = i0 == 0 ? (size_t)((V + 0) - start) : colstride;
   const double *cfb = ANISO ? cf + g.halo : nullptr;
   const double bj = sqrt(sb[kOffNrm2 + j]);
-  const double inv = 1.0 / bj;
-  const double cmul = j > 0 ? -bj / sqrt(sb[kOffNrm2 + j - 1]) : 0.0;
+  const double inv = g.raw ? 1.0 : 1.0 / bj; // raw: w = L column_j as it is (NLS_REORTH_GRAM)
+  const double cmul = (j > 0 && !g.raw) ? -bj / sqrt(sb[kOffNrm2 + j - 1]) : 0.0;
   double acc[NC * W];
 #pragma unroll
   for (int k = 0; k < NC * W; ++k) acc[k] = 0.0;

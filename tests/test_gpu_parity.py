@@ -585,3 +585,74 @@ def test_tensor_map_pass_is_the_default_for_complex_3d_only():
     assert launches((32, 24, 16), EQ.KGE, nls_b200.FLAG_TMAP) > 0
     assert launches((32, 24), EQ.NLSE_CUBIC) == 0
     assert launches((32, 24, 16), EQ.NLSE_CUBIC, batch=2) == 0
+
+
+# ---- NLS_REORTH_GRAM: Gram-delayed re-orthogonalisation (j + 6 passes per iteration) vs the reference's MGS sweep ---------
+def _gram_pair(orc, dims, **kw):
+    flags = kw.pop("flags", 0) | nls_b200.FLAG_NO_PERSISTENT
+    dg = Desc.make(*dims, reorth=REORTH.GRAM, flags=flags, **kw)
+    do = Desc.make(*dims, flags=flags, **kw)
+    return dg, do
+
+
+@pytest.mark.parametrize("dims,eq,m", [((64, 64), EQ.NLSE_CUBIC, 10), ((50, 44), EQ.SGE, 13), ((24, 20, 18), EQ.NLSE_CUBIC, 12),
+                                        ((24, 20, 18), EQ.KGE, 10), ((130, 9, 17), EQ.NLSE_CUBIC, 8)])
+def test_gram_delayed_lanczos_tracks_the_reference_on_white_noise(orc, dims, eq, m):
+    real = eq >= EQ.SGE
+    dg, do = _gram_pair(orc, dims, dx=0.25, equation=eq, integrator=INT.GAUTSCHI if real else INT.SS2, krylov_m=m, dt=1e-3)
+    x = randn(dg, 11)
+    eg, ef = Engine(dg), Engine(do)
+    V, a, b = eg.lanczos(x)
+    Vf, af, bf = ef.lanczos(x)
+    Vo, ao, bo = orc.Oracle(do).lanczos(x)
+    assert not np.array_equal(V[-1], Vf[-1]), "the Gram mode must be a different computation from the two-pass form"
+    assert np.allclose(b, bo, rtol=1e-12)
+    assert np.allclose(a, ao, rtol=1e-11, atol=1e-11 * np.abs(ao).max())
+    assert rel_l2(V, Vo) < 1e-9 and rel_l2(V[:5], Vo[:5]) < 1e-12
+    G = V.conj() @ V.T
+    assert np.abs(G - np.eye(m)).max() < 1e-12
+    print("gram-delayed: beta %.1e alpha %.1e V %.1e (two-pass V %.1e) orth %.1e" % (
+        np.abs(b / bo - 1).max(), np.abs(a - ao).max() / np.abs(ao).max(), rel_l2(V, Vo), rel_l2(Vf, Vo), np.abs(G - np.eye(m)).max()))
+
+
+@pytest.mark.parametrize("case", ["nlse2d", "nlse2d_batch", "nlse3d_cq_aniso", "sge2d", "kge3d", "sewi2d"])
+def test_gram_delayed_steps_match_the_oracle(orc, case):
+    rng = np.random.default_rng(2)
+    kw, steps, dt, v0, cf = dict(krylov_m=10), 20, 1e-3, None, None
+    if case == "nlse2d":
+        dims, u0 = (96, 96), ics.gaussian_bumps_2d(96, 10.0)
+        kw.update(L=10.0, equation=EQ.NLSE_CUBIC)
+    elif case == "nlse2d_batch":
+        dims, u0 = (64, 64), np.stack([ics.gaussian_bumps_2d(64, 10.0, seed=5 + b) for b in range(3)])
+        kw.update(L=10.0, equation=EQ.NLSE_CUBIC, batch=3)
+    elif case == "nlse3d_cq_aniso":
+        dims = (40, 36, 32)
+        u0 = ics.gaussian_bumps_3d(40, 4.0)[:32, :36, :40]
+        kw.update(dx=0.2, equation=EQ.NLSE_CQ, laplacian=LAP.ANISO, krylov_m=12, s1=1.0, s2=-0.1)
+        cf = 1.0 + 0.1 * rng.standard_normal(40 * 36 * 32)
+        dt = 5e-4
+    elif case == "sge2d":
+        dims, u0 = (96, 96), ics.kink_2d(96, 10.0)
+        kw.update(L=10.0, equation=EQ.SGE, integrator=INT.GAUTSCHI, dt=dt)
+        v0 = 0.05 * np.cos(u0)
+    elif case == "kge3d":
+        dims = (24, 20, 18)
+        u0 = 0.3 * np.abs(ics.gaussian_bumps_3d(24, 4.0)[:18, :20, :24])
+        kw.update(dx=0.2, equation=EQ.KGE, integrator=INT.GAUTSCHI, op_sign=-1.0, dt=dt)
+        v0 = np.zeros_like(u0)
+    else:
+        dims, u0 = (64, 64), ics.gaussian_bumps_2d(64, 10.0)
+        kw.update(L=10.0, equation=EQ.NLSE_CUBIC, integrator=INT.SEWI, krylov_m=8)
+    dg, do = _gram_pair(orc, dims, **kw)
+    e, o = Engine(dg), orc.Oracle(do)
+    for s in (e, o):
+        if cf is not None:
+            s.set(FIELD.C, cf)
+        s.set(FIELD.M, 1.0 + 0.2 * np.random.default_rng(1).standard_normal(dg.n))
+        s.set(FIELD.U, u0)
+        if v0 is not None:
+            s.set(FIELD.V, v0)
+        s.step(dt, steps)
+    err = rel_l2(e.get(), o.get())
+    print("gram-delayed steps %s: rel-L2 vs oracle %.2e" % (case, err))
+    assert err < 1e-11
