@@ -46,14 +46,19 @@ def lz_model(m):
     return (m - 1) * (m + 8) + (m - 2)
 
 
-def lz_impl(m):
+def lz_impl(m, gdr=False):
     """vector passes of one Lanczos run as IMPLEMENTED: two fused passes per iteration over an un-normalised
     basis, pass A (stencil + all dots) j+2, pass B (block update + norm) j+3 -> sum_j (2j+5) = (m-1)(m+3).
-    With NLS_REORTH=3 in the environment (Gram-delayed re-orthogonalisation, multi-kernel path, m <= 13) the handles of
-    this process run a 3-pass stencil sweep + a (j+3)-pass update per iteration: sum_j (j+6) = (m-1)(m+10)/2."""
-    if os.environ.get("NLS_REORTH") == "3" and m <= 13:
-        return (m - 1) * (m + 10) // 2
-    return (m - 1) * (m + 3)
+    gdr: the Gram-delayed form (the multi-kernel path's default for m <= 13; NLS_REORTH=0 in the environment switches it
+    off): a 3-pass raw stencil sweep + a (j+3)-pass update per iteration, sum_j (j+6) = (m-1)(m+10)/2."""
+    return (m - 1) * (m + 10) // 2 if gdr else (m - 1) * (m + 3)
+
+
+def runs_gram_delayed(w):
+    """does this workload's handle run the Gram-delayed Lanczos form?  (multi-kernel path = 3D grids, batches and slabs
+    of the bench; the 2D single-trajectory workloads run the persistent kernel's one-pass block form)"""
+    multi_kernel = w["dim"] == 3 or w.get("batch", 1) > 1
+    return multi_kernel and w["m"] <= 13 and os.environ.get("NLS_REORTH", "3") != "0"
 
 
 WORKLOADS = {
@@ -87,7 +92,7 @@ def bytes_per_site_step(w, model=False):
     """algorithmic bytes per site-step of the algorithm actually EXECUTED (model=False)
     or as SURVEY.md 8d's table counts them (model=True).  S = 16 complex / 8 real."""
     m = w["m"]
-    lz = lz_model(m) if model else lz_impl(m)
+    lz = lz_model(m) if model else lz_impl(m, runs_gram_delayed(w))
     if w["integ"] == INT.SS2:  # Lanczos + finish [read m columns, write u, write next start vector, read m(x) (1/2)]
         extra = 1.0 if (w["eq"] != EQ.NLSE_CUBIC and not model) else 0.0  # cq/sat: old-u density read (Q7)
         return 16 * (lz + m + 2.5 + extra)
@@ -423,7 +428,7 @@ def measure(cx, name, w, K, W, repeats, sample_clocks):
             "traffic_source": traffic_src, "peak_source": peak_src,
             "bytes_per_site_step": bpss, "bytes_per_site_step_survey_model": bpss_model,
             "frac_survey_model": bpss_model / bpss * achieved / peak,
-            "model": f"{bpss:.0f} algorithmic B/site-step of the algorithm executed ({lz_impl(w['m'])} vector passes per Lanczos run "
+            "model": f"{bpss:.0f} algorithmic B/site-step of the algorithm executed ({lz_impl(w['m'], runs_gram_delayed(w))} vector passes per Lanczos run "
                      f"+ recombination/pointwise tail; SURVEY 8d's table counts {bpss_model:.0f}) x site-steps/s of one GPU; "
                      f"{launches // max(K, 1)} kernels/step"}
     if traffic is not None:

@@ -87,15 +87,20 @@ enum {
 
 /* re-orthogonalisation mode of the Lanczos process */
 enum {
-  NLS_REORTH_FULL = 0, /* alpha step + one block-dot + one block-update pass (reference: MGS sweep) */
+  NLS_REORTH_FULL = 0, /* full re-orthogonalisation against all previous columns (reference: MGS sweep), in the form the
+                        * engine prefers: NLS_REORTH_GRAM where it applies (multi-kernel path, m <= 13, no NLS_FLAG_TMA /
+                        * NLS_FLAG_MARCH), else NLS_REORTH_BLOCK; the persistent kernel has its own one-pass block form */
   NLS_REORTH_NONE = 1, /* plain 3-term recurrence (not the reference algorithm; opt-in) */
-  NLS_REORTH_GRAM = 3, /* Gram-delayed full re-orthogonalisation (opt-in, multi-kernel path, m <= 13; larger m fall back to
-                        * NLS_REORTH_FULL): per iteration ONE narrow stencil pass that writes the raw vector L v_j and
+  NLS_REORTH_BLOCK = 4, /* force the two-pass block form: pass A = stencil + recurrence term + ALL dots, pass B =
+                         * Gram-corrected block update (2j + 5 vector passes per iteration); multi-kernel path */
+  NLS_REORTH_GRAM = 3, /* force the Gram-delayed form (multi-kernel path, m <= 13; larger m fall back to
+                        * NLS_REORTH_BLOCK): per iteration ONE narrow stencil pass that writes the raw vector L v_j and
                         * measures only its products with v_j and v_{j-1}, and ONE update pass over all columns whose
                         * projections on the older columns are derived from the Gram entries of the two newest columns
                         * through the three-term recurrence -- j + 6 vector passes per iteration instead of 2j + 5.
                         * Tracks the reference's MGS sweep at rounding level (tests/test_single_sweep_prototype.py,
-                        * tests/test_gpu_parity.py::test_gram_delayed_*) */
+                        * tests/test_gpu_parity.py::test_gram_delayed_*); C5 47.6 -> 36.4, C3 9.3 -> 7.1, C4 6.2 -> 5.2
+                        * ms/step (profiles/r02v_bench_gram_delayed_ab.txt) */
   NLS_REORTH_MGS = 2   /* the reference's sequential modified Gram-Schmidt sweep, operation for operation
                         * (eigen_krylov_complex.hpp:28-38): one launch per dot product, multi-kernel path only.
                         * Slow by construction; a bisecting tool that separates re-orthogonalisation rounding of

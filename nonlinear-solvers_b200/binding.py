@@ -20,7 +20,7 @@ _LIB = os.path.join(_PKG, "libnls_b200.so")
 EQ = SimpleNamespace(NLSE_CUBIC=0, NLSE_CQ=1, NLSE_SAT=2, SGE=3, KGE=4, PHI4=5, SGE_DOUBLE=6, SGE_SINH=7)
 INT = SimpleNamespace(SS2=0, GAUTSCHI=1, SV=2, SEWI=3)
 LAP = SimpleNamespace(UNIFORM=0, ANISO=1)
-REORTH = SimpleNamespace(FULL=0, NONE=1, MGS=2, GRAM=3)
+REORTH = SimpleNamespace(FULL=0, NONE=1, MGS=2, GRAM=3, BLOCK=4)
 FN = SimpleNamespace(EXP=0, SINC=1, COS_SQRT=2, SINC2_SQRT=3, ID_SQRT=4, SINC2_HALF=5, MOD_COSINE=6)
 FIELD = SimpleNamespace(U=0, U_PAST=1, V=2, M=3, C=4)
 RED = SimpleNamespace(MASS=0, NONFINITE=1, ENERGY=2)

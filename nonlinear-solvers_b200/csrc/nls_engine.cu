@@ -54,6 +54,7 @@ struct nls_engine {
   int nblk = 1; // capacity of the partial-sum array (max CTAs per trajectory)
   int nsm = 148;
   int smem_optin = 0;  // max dynamic shared memory per CTA
+  bool gdr_auto = true; // NLS_REORTH_FULL runs the Gram-delayed form on the multi-kernel path (nls_create)
   int first_cap = 0;   // complex pass A: columns in the stencil-carrying first chunk (0 = rule in lanczos_t)
   bool tma_ok = false; // TMA-staged Lanczos passes usable (alignment + size), see tma_setup
   bool tm_ok = false;  // tensor-map pass A (nls_tmap.cuh) usable
@@ -284,7 +285,7 @@ TmaPlan tma_plan(nls_engine *e, int nseg, size_t extra) {
 
 template <class S, bool ANISO>
 bool launch_a_tma(nls_engine *e, const S *start, S *V, int j, double *scal) {
-  if (!e->tma_ok || j + 1 > kTmaMaxCols || e->d.reorth != NLS_REORTH_FULL) return false;
+  if (!e->tma_ok || j + 1 > kTmaMaxCols || (e->d.reorth != NLS_REORTH_FULL && e->d.reorth != NLS_REORTH_BLOCK)) return false;
   const TmaPlan pl = tma_plan(e, j + 1 + (ANISO ? 10 : 5), 64);
   const void *fn = (const void *)k_lanczos_a_tma<S, ANISO>;
   if (pl.nstages < 2 || !tma_attr(fn, e->smem_optin)) return false;
@@ -466,7 +467,7 @@ void lanczos_t(nls_engine *e, const S *start, double *scal) {
   // NLS_REORTH_GRAM: one narrow stencil pass S(j) (raw r_j = L column_j, true dots with columns j-1 and j only) and one
   // update pass U(j+1) over all columns whose older projections come from Gram entries (lanczos_b_body<GDR>): j + 6
   // vector passes per iteration instead of 2j + 5.  All columns must fit one closing chunk (m <= kNC + 1).
-  const bool gdr = e->d.reorth == NLS_REORTH_GRAM && m - 1 <= kNC;
+  const bool gdr = m - 1 <= kNC && (e->d.reorth == NLS_REORTH_GRAM || (e->d.reorth == NLS_REORTH_FULL && e->gdr_auto));
   for (int j = 0; gdr && j < m - 1; ++j) {
     const int c0 = j > 0 ? j - 1 : 0, total = j + 1 - c0;
     int cnt = 0;
@@ -486,7 +487,7 @@ void lanczos_t(nls_engine *e, const S *start, double *scal) {
 #undef LG
   }
   if (gdr) return;
-  const int reorth = e->d.reorth == NLS_REORTH_GRAM ? NLS_REORTH_FULL : e->d.reorth; // m too large for one chunk: two-pass form
+  const int reorth = (e->d.reorth == NLS_REORTH_GRAM || e->d.reorth == NLS_REORTH_BLOCK) ? NLS_REORTH_FULL : e->d.reorth;
   for (int j = 0; j < m - 1; ++j) {
     // columns taking part in the orthogonalisation: all of 0..j (reference), or only j (3-term)
     const int c0 = reorth != NLS_REORTH_FULL ? j : 0;
@@ -1079,11 +1080,13 @@ int nls_create(const nls_desc *desc, nls_handle *out) {
   if (d.device < 0 || d.device >= ndev) return fail(NLS_ERR_CUDA, "no such CUDA device (there is no CPU fallback)");
   CU(cudaSetDevice(d.device));
 
-  if (d.reorth < NLS_REORTH_FULL || d.reorth > NLS_REORTH_GRAM) return fail(NLS_ERR_ARG, "bad reorth mode");
+  if (d.reorth < NLS_REORTH_FULL || d.reorth > NLS_REORTH_BLOCK) return fail(NLS_ERR_ARG, "bad reorth mode");
   nls_engine *e = new nls_engine;
   e->d = d;
-  if (const char *ro = getenv("NLS_REORTH")) // tuning knob (bench A/B): handles asking for the default take this mode
-    if (d.reorth == NLS_REORTH_FULL && atoi(ro) >= NLS_REORTH_FULL && atoi(ro) <= NLS_REORTH_GRAM) e->d.reorth = atoi(ro);
+  // NLS_REORTH_FULL on the multi-kernel path = the Gram-delayed form unless the handle asks for a pass variant that only
+  // exists in the two-pass form; NLS_REORTH=0 in the environment keeps the two-pass form (A/B knob)
+  e->gdr_auto = !(d.flags & (NLS_FLAG_TMA | NLS_FLAG_MARCH));
+  if (const char *ro = getenv("NLS_REORTH")) e->gdr_auto = e->gdr_auto && atoi(ro) != 0;
   e->cplx = cplx;
   e->W = cplx ? 2 : 1;
   e->esz = cplx ? 16 : 8;

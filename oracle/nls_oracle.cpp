@@ -220,7 +220,7 @@ double lanczos(const Csr &A, double sgn, const S *u, int m, int reorth, std::vec
     const S a = adj_dot(vj, w.data(), n);
     alpha[j] = a;
     for (int64_t i = 0; i < n; ++i) w[i] -= a * vj[i]; // :29
-    if (reorth == NLS_REORTH_FULL)
+    if (reorth != NLS_REORTH_NONE) // every other mode of nls.h is the reference's full sweep in a different kernel form
       for (int i2 = 0; i2 <= j; ++i2) { // :32-35 MGS sweep
         const S *vi = &V[(size_t)i2 * n];
         const S c = adj_dot(vi, w.data(), n);

@@ -403,7 +403,7 @@ def test_march_pass_matches_flat_pass_and_oracle(orc, dims, eq, lap):
         u0 = 0.3 * np.abs(u0)
     outs = []
     for flags in (nls_b200.FLAG_NO_PERSISTENT | nls_b200.FLAG_MARCH, nls_b200.FLAG_NO_PERSISTENT):
-        d = Desc.make(nx, ny, nz, dx=0.2, flags=flags, **kw)
+        d = Desc.make(nx, ny, nz, dx=0.2, flags=flags, reorth=REORTH.BLOCK, **kw)  # the march pass exists in the two-pass form only
         e = Engine(d)
         if lap == LAP.ANISO:
             e.set(FIELD.C, cf)
@@ -460,7 +460,7 @@ def test_tma_passes_match_register_passes_and_oracle(orc, case):
     base = nls_b200.FLAG_NO_PERSISTENT
     outs = []
     for flags in (base | nls_b200.FLAG_TMA, base):
-        d = Desc.make(nx, ny, nz, dx=0.2, flags=flags, krylov_m=m, reorth=reorth, dt=dt, **kw)
+        d = Desc.make(nx, ny, nz, dx=0.2, flags=flags, krylov_m=m, reorth=reorth or REORTH.BLOCK, dt=dt, **kw)  # TMA passes: two-pass form
         e = Engine(d)
         if d.laplacian == LAP.ANISO:
             e.set(FIELD.C, cf)
@@ -591,7 +591,7 @@ def test_tensor_map_pass_is_the_default_for_complex_3d_only():
 def _gram_pair(orc, dims, **kw):
     flags = kw.pop("flags", 0) | nls_b200.FLAG_NO_PERSISTENT
     dg = Desc.make(*dims, reorth=REORTH.GRAM, flags=flags, **kw)
-    do = Desc.make(*dims, flags=flags, **kw)
+    do = Desc.make(*dims, reorth=REORTH.BLOCK, flags=flags, **kw)  # the two-pass form; the oracle runs the reference's MGS sweep
     return dg, do
 
 
