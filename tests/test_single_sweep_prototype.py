@@ -42,3 +42,61 @@ def test_single_sweep_tracks_reference_like_two_pass(m, cplx):
     assert max(one[:2]) < 1e-12 and one[3] < 1e-11            # the proposal
     assert one[2] < 1e-9 and two[2] < 1e-9
     assert one[2] < 10 * two[2] + 1e-13                       # no worse than the implemented scheme by more than rounding
+
+
+@pytest.mark.parametrize("m", [10, 13, 20, 30])
+@pytest.mark.parametrize("cplx", [True, False])
+def test_gram_delayed_tracks_reference_like_two_pass(m, cplx):
+    """the form the CUDA engine runs by default on its multi-kernel path (lanczos_b_body<GDR>, m <= 13 there)"""
+    nx = ny = 40
+    A = oracle_np.lap2d_uniform(nx, ny, 0.25, 0.25)
+    rng = np.random.default_rng(70 + m)
+    u = rng.standard_normal(nx * ny)
+    if cplx:
+        u = u + 1j * rng.standard_normal(nx * ny)
+        A = A.astype(np.complex128)
+    two = _errors(proto.two_pass, A, u, m)
+    gdr = _errors(proto.gram_delayed, A, u, m)
+    print("m=%d %s  gram-delayed alpha %.1e beta %.1e V %.1e orth %.1e" % ((m, "c" if cplx else "r") + gdr))
+    assert max(gdr[:2]) < 1e-12 and gdr[3] < 1e-11 and gdr[2] < 1e-9
+    assert gdr[2] < 10 * two[2] + 1e-13
+
+
+def _three_term(A, u, m):
+    C, nrm2, alpha = [u.copy()], [np.vdot(u, u).real], []
+    for j in range(m - 1):
+        bj = np.sqrt(nrm2[j])
+        w = A @ (C[j] / bj)
+        if j > 0:
+            w = w - (bj / np.sqrt(nrm2[j - 1])) * C[j - 1]
+        s = np.vdot(C[j], w)
+        alpha.append(s.real / bj)
+        w = w - (s / nrm2[j]) * C[j]
+        C.append(w)
+        nrm2.append(np.vdot(w, w).real)
+    return proto._finish(C, nrm2, alpha, m)
+
+
+def test_gram_delayed_keeps_orthogonality_where_the_three_term_recurrence_loses_it():
+    """near-invariant Krylov space (n = 64, m = 40): the sensitivity check of the two tests above -- without
+    re-orthogonalisation the basis is lost, with the Gram-derived projections it stays orthonormal to rounding"""
+    import scipy.linalg as sl
+    A = oracle_np.lap2d_uniform(8, 8, 1.0, 1.0).astype(np.complex128)
+    rng = np.random.default_rng(1)
+    u = rng.standard_normal(64) + 1j * rng.standard_normal(64)
+    m = 40
+    orth = {}
+    for name, scheme in (("three_term", _three_term), ("two_pass", proto.two_pass), ("gram_delayed", proto.gram_delayed),
+                         ("single_sweep", proto.single_sweep)):
+        V, alpha, beta = scheme(A, u, m)
+        orth[name] = np.max(np.abs(V.conj().T @ V - np.eye(m)))
+    print(orth)
+    assert orth["three_term"] > 1e-3
+    assert orth["two_pass"] < 1e-13 and orth["gram_delayed"] < 1e-13 and orth["single_sweep"] < 1e-13
+    # and the matrix function the integrators take from it agrees with the reference scheme
+    Vr, Tr, b0 = oracle_np.lanczos(A, u, 30)
+    ref = b0 * (Vr @ sl.expm(0.3j * Tr)[:, 0])
+    V, alpha, beta = proto.gram_delayed(A, u, 30)
+    T = np.diag(np.append(alpha, 0.0)).astype(complex) + np.diag(beta[1:], 1) + np.diag(beta[1:], -1)
+    got = beta[0] * (V @ sl.expm(0.3j * T)[:, 0])
+    assert np.linalg.norm(got - ref) / np.linalg.norm(ref) < 1e-12
