@@ -17,6 +17,7 @@
 //   [65 .. 65+128)      alpha[j] : T(j,j) (W doubles each)
 //   [193 .. 193+128)    s[i]     : column_i^H w of the current iteration
 //   [328 .. 328+128)    g[i]     : column_i^H column_j (Gram entries of the newest column)
+//   [456 .. 456+128)    g2[i]    : NLS_REORTH_GRAM: the Gram entries of the newest two columns alternate between g and g2
 #pragma once
 #include "nls_device.cuh"
 #include "../../include/nls.h"
@@ -82,6 +83,8 @@ k_norm2(Geom g, const S *__restrict__ x, double *dst, int dst_stride, RedCtx rc)
 //   pass B (k_lanczos_b): w -= alpha v_j + sum_i h_i v_i  (:29,:34), ||w||^2 (:38).
 // 2j+5 vector passes per iteration instead of the 2j+10 of "alpha step, then block dots, then
 // block update, then normalise" (SURVEY 8d counts the latter).
+// NLS_REORTH_GRAM (what NLS_REORTH_FULL runs for m <= 13): pass A with Geom::raw writes r = L column_j and measures only
+// s_j, s_{j-1}; the closing pass B (lanczos_b_body<GDR>) derives the older projections from Gram entries: j+6 passes.
 template <class S>
 __device__ __forceinline__ const S *colptr(const S *start, const S *V, size_t colstride, int i) {
   return i == 0 ? start : V + (size_t)(i - 1) * colstride;
